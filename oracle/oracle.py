@@ -1,0 +1,266 @@
+"""ctypes front-end of the CPU oracle (oracle/ypp_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py.  The product package
+(pytorch-object-detection_b200/ypp) never imports this module.
+
+Function names mirror the reference symbols they restate:
+  decode_predictions_v3  utils/yolov3_utils.py:12-59
+  decode_predictions_v2  utils/yolov2_utils.py:12-58
+  decode_multi_scale     utils/yolov3_utils.py:76-84 / :112-120 (scale loop + cat)
+  nms_v3                 utils/yolo_utils.py:321-348 (+ torchvision batched_nms)
+  get_target_rows        utils/yolo_utils.py:682-710 + utils/yolov3_utils.py:134-137
+  mean_average_precision utils/yolo_utils.py:351-456, metrics_per_class :458-574
+  box_iou                utils/metrics.py:233-255
+  bbox_iou_cxcywh        utils/yolo_utils.py:75-123,143-144 (IoU branch)
+Parity status: pinned against the reference's own outputs (tests/golden/).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SRC = os.path.join(_HERE, "ypp_oracle.c")
+_LIB = os.path.join(_HERE, "libypp_oracle.so")
+
+OFFSET_NONE, OFFSET_TRICK, OFFSET_AUTO_CPU, OFFSET_AUTO_CUDA = 0, 1, 2, 3
+UNION_SEPARATE, UNION_FMA = 0, 1
+
+
+def build(force=False):
+    """gcc the C restatement into oracle/libypp_oracle.so (idempotent)."""
+    if (not force and os.path.exists(_LIB)
+            and os.path.getmtime(_LIB) >= os.path.getmtime(_SRC)):
+        return _LIB
+    cmd = ["gcc", "-O2", "-ffp-contract=off", "-fno-fast-math", "-fopenmp", "-shared",
+           "-fPIC", "-o", _LIB, _SRC, "-lm"]
+    subprocess.run(cmd, check=True)
+    return _LIB
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = ctypes.CDLL(_LIB)
+        fp = ctypes.POINTER(ctypes.c_float)
+        ip = ctypes.POINTER(ctypes.c_int)
+        up = ctypes.POINTER(ctypes.c_ubyte)
+        L.ypo_decode_scale.argtypes = [fp, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                       ctypes.c_int, fp, fp, ctypes.c_float, ctypes.c_float, fp,
+                                       ctypes.c_int64, ctypes.c_int64]
+        L.ypo_decode_scale.restype = None
+        L.ypo_effective_thr.argtypes = [ctypes.c_double, ctypes.c_int]
+        L.ypo_effective_thr.restype = ctypes.c_float
+        L.ypo_nms_xyxy.argtypes = [fp, fp, ctypes.c_int, ctypes.c_float, ctypes.c_int, ip]
+        L.ypo_nms_xyxy.restype = ctypes.c_int
+        L.ypo_batched_nms.argtypes = [fp, fp, fp, ctypes.c_int, ctypes.c_float, ctypes.c_int,
+                                      ctypes.c_int, ip]
+        L.ypo_batched_nms.restype = ctypes.c_int
+        L.ypo_nms_v3.argtypes = [fp, ctypes.c_int, ctypes.c_float, ctypes.c_float, ctypes.c_int,
+                                 ctypes.c_int, ip, ip]
+        L.ypo_nms_v3.restype = ctypes.c_int
+        L.ypo_nms_v3_batch.argtypes = [fp, ctypes.c_int, ctypes.c_int, ctypes.c_float,
+                                       ctypes.c_float, ctypes.c_int, ctypes.c_int, ip, ip, ip]
+        L.ypo_nms_v3_batch.restype = None
+        L.ypo_bbox_iou_cxcywh_pairs.argtypes = [fp, fp, ctypes.c_int, fp]
+        L.ypo_bbox_iou_cxcywh_pairs.restype = None
+        L.ypo_box_iou.argtypes = [fp, ctypes.c_int, fp, ctypes.c_int, fp]
+        L.ypo_box_iou.restype = None
+        L.ypo_target_rows.argtypes = [fp, ctypes.c_int, ctypes.c_int, ctypes.c_float,
+                                      ctypes.c_float, fp]
+        L.ypo_target_rows.restype = ctypes.c_int
+        L.ypo_mean_average_precision.argtypes = [fp, ctypes.c_int, fp, ctypes.c_int, ctypes.c_int,
+                                                 ctypes.c_float, up, fp]
+        L.ypo_mean_average_precision.restype = ctypes.c_float
+        L.ypo_num_threads.restype = ctypes.c_int
+        L.ypo_set_num_threads.argtypes = [ctypes.c_int]
+        _lib = L
+    return _lib
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _fp(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _ip(a):
+    return a.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+
+
+def num_threads():
+    return lib().ypo_num_threads()
+
+
+def set_num_threads(n):
+    lib().ypo_set_num_threads(int(n))
+
+
+def effective_thr(thr, compare_in_double):
+    return float(lib().ypo_effective_thr(float(thr), int(bool(compare_in_double))))
+
+
+def scale_params_v3(anchors, input_size, layer_h, layer_w):
+    """anchors in pixels -> (anchor_w, anchor_h) fp32 grid units, stride_w, stride_h.
+    Mirrors utils/yolov3_utils.py:29-31,38,40: python-float division, one fp32 rounding."""
+    stride_h = input_size / layer_h
+    stride_w = input_size / layer_w
+    aw = np.array([a[0] / stride_w for a in anchors], dtype=np.float32)
+    ah = np.array([a[1] / stride_h for a in anchors], dtype=np.float32)
+    return aw, ah, np.float32(stride_w), np.float32(stride_h)
+
+
+def scale_params_v2(scaled_anchors, input_size, layer_h, layer_w):
+    """utils/yolov2_utils.py:27-30,37,39: anchors already in grid units."""
+    stride_h = input_size / layer_h
+    stride_w = input_size / layer_w
+    aw = np.array([a[0] for a in scaled_anchors], dtype=np.float32)
+    ah = np.array([a[1] for a in scaled_anchors], dtype=np.float32)
+    return aw, ah, np.float32(stride_w), np.float32(stride_h)
+
+
+def _decode_into(head, nc, aw, ah, sw, sh, out, box_offset):
+    head = _f32(head)
+    B, CH, H, W = head.shape
+    A = len(aw)
+    assert CH == A * (5 + nc), (CH, A, nc)
+    lib().ypo_decode_scale(_fp(head), B, A, nc, H, W, _fp(aw), _fp(ah), float(sw), float(sh),
+                           _fp(out), out.shape[1] * 6, box_offset)
+
+
+def decode_predictions_v3(head, num_classes, anchors, input_size):
+    head = _f32(head)
+    B, _, H, W = head.shape
+    aw, ah, sw, sh = scale_params_v3(anchors, input_size, H, W)
+    out = np.empty((B, len(anchors) * H * W, 6), dtype=np.float32)
+    _decode_into(head, num_classes, aw, ah, sw, sh, out, 0)
+    return out
+
+
+def decode_predictions_v2(head, num_classes, scaled_anchors, input_size):
+    head = _f32(head)
+    B, _, H, W = head.shape
+    aw, ah, sw, sh = scale_params_v2(scaled_anchors, input_size, H, W)
+    out = np.empty((B, len(scaled_anchors) * H * W, 6), dtype=np.float32)
+    _decode_into(head, num_classes, aw, ah, sw, sh, out, 0)
+    return out
+
+
+def decode_multi_scale(heads, num_classes, anchors, input_size, anchors_per_scale=3):
+    """Scale loop + torch.cat(dim=1) of DecodeYoloV3.forward / update_state."""
+    heads = [_f32(h) for h in heads]
+    B = heads[0].shape[0]
+    n_tot = sum(anchors_per_scale * h.shape[2] * h.shape[3] for h in heads)
+    out = np.empty((B, n_tot, 6), dtype=np.float32)
+    off = 0
+    for i, h in enumerate(heads):
+        an = anchors[anchors_per_scale * i: anchors_per_scale * (i + 1)]
+        aw, ah, sw, sh = scale_params_v3(an, input_size, h.shape[2], h.shape[3])
+        _decode_into(h, num_classes, aw, ah, sw, sh, out, off)
+        off += anchors_per_scale * h.shape[2] * h.shape[3]
+    return out
+
+
+def nms_v3_indices(rows, conf_threshold=0.25, iou_threshold=0.45,
+                   offset_mode=OFFSET_AUTO_CPU, union_mode=UNION_SEPARATE,
+                   compare_in_double=None):
+    """Kept box indices (into rows [N,6]) in NMS order, plus candidate count."""
+    rows = _f32(rows)
+    N = rows.shape[0]
+    if compare_in_double is None:
+        compare_in_double = (union_mode == UNION_SEPARATE)
+    thr = effective_thr(iou_threshold, compare_in_double)
+    keep = np.empty(max(N, 1), dtype=np.int32)
+    ncand = ctypes.c_int(0)
+    k = lib().ypo_nms_v3(_fp(rows), N, float(np.float32(conf_threshold)), thr, offset_mode,
+                         union_mode, _ip(keep), ctypes.byref(ncand))
+    return keep[:k].copy(), int(ncand.value)
+
+
+def nms_v3(rows, conf_threshold=0.25, iou_threshold=0.45, **kw):
+    rows = _f32(rows)
+    keep, _ = nms_v3_indices(rows, conf_threshold, iou_threshold, **kw)
+    return rows[keep]
+
+
+def nms_v3_batch(rows, conf_threshold=0.25, iou_threshold=0.45,
+                 offset_mode=OFFSET_AUTO_CPU, union_mode=UNION_SEPARATE, compare_in_double=None):
+    """rows [B,N,6] -> keep_src [B,N] int32, keep_count [B], cand_count [B] (OpenMP over images)."""
+    rows = _f32(rows)
+    B, N, _ = rows.shape
+    if compare_in_double is None:
+        compare_in_double = (union_mode == UNION_SEPARATE)
+    thr = effective_thr(iou_threshold, compare_in_double)
+    keep = np.full((B, max(N, 1)), -1, dtype=np.int32)
+    kc = np.zeros(B, dtype=np.int32)
+    cc = np.zeros(B, dtype=np.int32)
+    lib().ypo_nms_v3_batch(_fp(rows), B, N, float(np.float32(conf_threshold)), thr, offset_mode,
+                           union_mode, _ip(keep), _ip(kc), _ip(cc))
+    return keep, kc, cc
+
+
+def batched_nms(boxes, scores, idxs, iou_threshold, offset_mode=OFFSET_TRICK,
+                union_mode=UNION_SEPARATE, compare_in_double=None):
+    boxes, scores, idxs = _f32(boxes), _f32(scores), _f32(idxs)
+    n = boxes.shape[0]
+    if compare_in_double is None:
+        compare_in_double = (union_mode == UNION_SEPARATE)
+    thr = effective_thr(iou_threshold, compare_in_double)
+    keep = np.empty(max(n, 1), dtype=np.int32)
+    mode = offset_mode
+    if mode == OFFSET_AUTO_CPU:
+        mode = OFFSET_NONE if boxes.size > 4000 else OFFSET_TRICK
+    if mode == OFFSET_AUTO_CUDA:
+        mode = OFFSET_NONE if boxes.size > 100000 else OFFSET_TRICK
+    k = lib().ypo_batched_nms(_fp(boxes), _fp(scores), _fp(idxs), n, thr, mode, union_mode, _ip(keep))
+    return keep[:k].copy()
+
+
+def get_target_rows(annot, input_size, img_base=0):
+    """[B,T,5] padded annots -> [G,7] rows img,cx,cy,w,h,1,cls (image-major order)."""
+    annot = _f32(annot)
+    B, T, _ = annot.shape
+    out = np.empty((max(B * T, 1), 7), dtype=np.float32)
+    g = lib().ypo_target_rows(_fp(annot), B, T, float(input_size), float(img_base), _fp(out))
+    return out[:g].copy()
+
+
+def mean_average_precision(true_boxes, pred_boxes, num_classes, iou_threshold=0.5,
+                           return_details=False):
+    gt = _f32(true_boxes).reshape(-1, 7)
+    det = _f32(pred_boxes).reshape(-1, 7)
+    tp = np.empty(max(det.shape[0], 1), dtype=np.uint8)
+    pc = np.zeros((num_classes, 4), dtype=np.float32)
+    m = lib().ypo_mean_average_precision(_fp(gt), gt.shape[0], _fp(det), det.shape[0],
+                                         int(num_classes), float(np.float32(iou_threshold)),
+                                         tp.ctypes.data_as(ctypes.POINTER(ctypes.c_ubyte)), _fp(pc))
+    if return_details:
+        return np.float32(m), tp[:det.shape[0]].copy(), pc
+    return np.float32(m)
+
+
+def metrics_per_class(true_boxes, pred_boxes, num_classes, iou_threshold=0.5):
+    _, _, pc = mean_average_precision(true_boxes, pred_boxes, num_classes, iou_threshold, True)
+    return pc
+
+
+def box_iou(box1, box2):
+    a, b = _f32(box1), _f32(box2)
+    out = np.empty((a.shape[0], b.shape[0]), dtype=np.float32)
+    lib().ypo_box_iou(_fp(a), a.shape[0], _fp(b), b.shape[0], _fp(out))
+    return out
+
+
+def bbox_iou_cxcywh(a, b):
+    a, b = _f32(a).reshape(-1, 4), _f32(b).reshape(-1, 4)
+    out = np.empty(a.shape[0], dtype=np.float32)
+    lib().ypo_bbox_iou_cxcywh_pairs(_fp(a), _fp(b), a.shape[0], _fp(out))
+    return out

@@ -1,0 +1,175 @@
+/*
+ * ypp.h -- C ABI of libypp.so: B200 (sm_100a) YOLO post-processing hot path.
+ *
+ * Drop-in boundary for the reference's Python helpers (the reference has no FFI of
+ * its own; these are the entry points a binding for this path would need -- see
+ * INTEGRATION.md for the ctypes stub).  Paths below are relative to the reference
+ * checkout (myungsanglee/PyTorch-Object-Detection).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller unless named host_*;
+ *   - every call is asynchronous on the given stream (a cudaStream_t passed as void*),
+ *     never synchronises, never allocates: scratch memory comes from the caller and its
+ *     size is queried first (ypp_workspace_bytes / ypp_map_workspace_bytes);
+ *   - returns 0 on success, a negative YPP_E_* otherwise; ypp_last_error() gives the
+ *     text for the calling thread;  re-entrant per (workspace, stream); no global state.
+ *   - fp32 throughout; heads are contiguous NCHW exactly as the detectors emit them
+ *     (models/detector/yolov3.py:71-91, models/detector/yolov2.py).
+ */
+#ifndef YPP_H_
+#define YPP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YPP_MAX_SCALES 4
+#define YPP_MAX_ANCHORS 8
+#define YPP_MAX_CLASSES 1024      /* class id field of the sort key is 12 bits; S1 smem table */
+#define YPP_MAX_BOXES (1 << 20)   /* box index field of the sort key is 20 bits */
+
+enum {
+    YPP_OK = 0,
+    YPP_E_BADARG = -1,        /* null pointer, non-positive size, bad enum */
+    YPP_E_UNSUPPORTED = -2,   /* shape outside the limits above */
+    YPP_E_WORKSPACE = -3,     /* workspace too small / misaligned */
+    YPP_E_CUDA = -4           /* a CUDA call failed; text in ypp_last_error() */
+};
+
+/* score written to the rows / used for thresholding and ordering */
+enum {
+    YPP_SCORE_OBJ = 0,            /* sigmoid(objectness): what the reference computes
+                                     (utils/yolov3_utils.py:50,59) */
+    YPP_SCORE_OBJ_TIMES_CLS = 1   /* objectness x best class probability (the vendored,
+                                     uncalled utils/general.py:684 flavour) */
+};
+
+/* how torchvision.ops.batched_nms separates classes (site-packages boxes.py, v0.26.0) */
+enum {
+    YPP_OFFSET_NONE = 0,       /* _batched_nms_vanilla: per class, unshifted boxes */
+    YPP_OFFSET_TRICK = 1,      /* _batched_nms_coordinate_trick: + cls*(max+1), class-agnostic */
+    YPP_OFFSET_AUTO_CPU = 2,   /* per image: 4*n_cand > 4000   ? vanilla : trick */
+    YPP_OFFSET_AUTO_CUDA = 3   /* per image: 4*n_cand > 100000 ? vanilla : trick */
+};
+
+/* rounding of the union term inside torchvision::nms */
+enum {
+    YPP_UNION_SEPARATE = 0,    /* (Sa + Sb) - inter, both areas rounded (CPU kernel) */
+    YPP_UNION_FMA = 1          /* fma(w_b, h_b, Sa) - inter (nvcc contraction of the CUDA kernel) */
+};
+
+/* One detection head (one scale).  Replaces the per-scale arguments of
+ * decode_predictions: utils/yolov3_utils.py:12 / utils/yolov2_utils.py:12. */
+typedef struct {
+    const float* head;                  /* [B, A*(5+nc), H, W] */
+    int A, H, W;
+    float anchor_w[YPP_MAX_ANCHORS];    /* GRID units, rounded to fp32 once by the caller  */
+    float anchor_h[YPP_MAX_ANCHORS];    /* (yolov3_utils.py:31,40; yolov2 passes them as is) */
+    float stride_w, stride_h;           /* input_size / layer_w, input_size / layer_h      */
+} ypp_scale;
+
+typedef struct {
+    int nc;               /* classes */
+    int B;                /* images in the batch */
+    int n_scales;         /* 1..YPP_MAX_SCALES, concatenated in this order (yolov3_utils.py:84) */
+    float conf_thr;       /* keep score > conf_thr (strict, utils/yolo_utils.py:334) */
+    float iou_thr;        /* suppress iou > iou_thr (strict fp32 compare; see ypp_effective_iou_thr) */
+    int score_mode;       /* YPP_SCORE_* */
+    int offset_mode;      /* YPP_OFFSET_* */
+    int union_mode;       /* YPP_UNION_* */
+} ypp_cfg;
+
+/* ---- whole chain: decode -> threshold/compact -> sort -> per-class NMS -> rows -------- */
+
+/* Bytes of scratch for a batch of cfg->B images of n_boxes boxes each (n_boxes is the sum
+ * over scales of A*H*W, or N for ypp_nms_rows). */
+size_t ypp_workspace_bytes(int B, int n_boxes, int nc);
+
+/* torchvision's CPU kernel compares the fp32 IoU against a DOUBLE threshold, the CUDA
+ * kernel against (float)thr.  Returns the fp32 value to put in cfg->iou_thr so that the
+ * strict fp32 compare reproduces either (compare_in_double = 1 for the CPU behaviour). */
+float ypp_effective_iou_thr(double iou_thr, int compare_in_double);
+
+/* = decode_predictions on every scale + torch.cat(dim=1): out [B, n_boxes, 6] rows
+ * cx,cy,w,h,score,cls(float).  utils/yolov3_utils.py:12-59,76-84; utils/yolov2_utils.py:12-58. */
+int ypp_decode_dense(const ypp_cfg* cfg, const ypp_scale* scales, float* out_BN6, void* stream);
+
+/* D1: fused decode + confidence threshold + stream compaction into the workspace
+ * (replaces decode_predictions + the torch.where of nms_v3, utils/yolo_utils.py:334). */
+int ypp_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,
+                       void* stream);
+
+/* Same compaction, but from already decoded rows [B, n_boxes, 6] (the nms_v3 entry point:
+ * utils/yolo_utils.py:321-337). */
+int ypp_rows_compact(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* ws,
+                     size_t ws_bytes, void* stream);
+
+/* S1: per image stable order by score (desc, ties -> lower box index) and per class
+ * segmentation (scores.sort(stable=True, descending=True) inside torchvision::nms). */
+int ypp_sort_segments(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, void* stream);
+
+/* N1+N2: bitmask IoU suppression + greedy keep scan per (image, class) segment
+ * (torchvision batched_nms as called from utils/yolo_utils.py:346), then the row gather
+ * (boxes[keep], utils/yolo_utils.py:348, and the img_idx column of
+ * utils/yolov3_utils.py:126-129).
+ *   cand_count [B] out (optional): boxes passing the threshold
+ *   keep_count [B] out: boxes kept per image
+ *   keep_idx   [B, n_boxes] out (optional): kept box indices n in NMS order, per image
+ *   det_rows   out (optional): packed rows, image after image, row_width floats each:
+ *              7 -> img,cx,cy,w,h,score,cls ; 6 -> cx,cy,w,h,score,cls
+ *   det_total  [1] out (optional): total rows written
+ *   det_capacity: rows that fit in det_rows (extra rows are dropped; det_total still counts them) */
+int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes,
+            int* cand_count, int* keep_count, int* keep_idx,
+            float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+            float img_idx_base, void* stream);
+
+/* The three stages above, back to back, from the heads (DecodeYoloV3/V2.forward and the body
+ * of MeanAveragePrecision.update_state: utils/yolov3_utils.py:73-90,108-146). */
+int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,
+                    int* cand_count, int* keep_count, int* keep_idx,
+                    float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+                    float img_idx_base, void* stream);
+
+/* nms_v3 on decoded rows [B, n_boxes, 6] (utils/yolo_utils.py:321-348), batched. */
+int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* ws, size_t ws_bytes,
+                 int* cand_count, int* keep_count, int* keep_idx,
+                 float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+                 float img_idx_base, void* stream);
+
+/* ---- mAP side ------------------------------------------------------------------------ */
+
+/* get_target_boxes_for_map + the img_idx column (utils/yolo_utils.py:682-710,
+ * utils/yolov3_utils.py:134-137): annot [B,T,5] -> packed rows [G,7] img,cx,cy,w,h,1,cls in
+ * (image, slot) order; rows with sum <= 0 are dropped.  gt_count [1] out.  out needs B*T rows. */
+int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, float img_idx_base,
+                    float* out_G7, int* gt_count, void* stream);
+
+/* box_iou, utils/metrics.py:233-255: xyxy [N,4] x [M,4] -> [N,M]. */
+int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream);
+
+size_t ypp_map_workspace_bytes(int64_t G, int64_t K, int nc);
+
+/* mean_average_precision / metrics_per_class, utils/yolo_utils.py:351-456,458-574.
+ *   gt [G,7], det [K,7] rows img,cx,cy,w,h,score,cls (any order)
+ *   tp [K] out (optional): 1 TP, 0 FP, 255 class without ground truth
+ *   per_class [nc,4] out (optional): AP, TP, FP, FN
+ *   map [1] out: mean AP over all nc classes */
+int ypp_map_match(const float* gt_G7, int64_t G, const float* det_K7, int64_t K, int nc,
+                  float iou_thr, void* ws, size_t ws_bytes,
+                  unsigned char* tp, float* per_class, float* map, void* stream);
+
+/* ---- misc ---------------------------------------------------------------------------- */
+
+const char* ypp_last_error(void);
+int ypp_version(void);
+/* kernels launched by this library in the calling thread since the last reset (bench bookkeeping) */
+int64_t ypp_launch_count(int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YPP_H_ */

@@ -1,0 +1,265 @@
+// extern "C" surface of libypp.so (declared in include/ypp.h): argument checking, parameter
+// blocks, stream-ordered launches.  No allocation, no synchronisation, no global state.
+#include "ypp_kernels.cuh"
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+static thread_local char g_err[512] = "";
+static thread_local long long g_launches = 0;
+
+void ypp_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int ypp_check_launch(const char* what)
+{
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        ypp_set_error("%s: %s", what, cudaGetErrorString(e));
+        return YPP_E_CUDA;
+    }
+    return YPP_OK;
+}
+
+void ypp_count_launch(int n) { g_launches += n; }
+
+namespace {
+
+
+int check_cfg(const ypp_cfg* cfg)
+{
+    if (!cfg) { ypp_set_error("cfg is null"); return YPP_E_BADARG; }
+    if (cfg->B <= 0 || cfg->nc <= 0) { ypp_set_error("B=%d nc=%d must be positive", cfg->B, cfg->nc); return YPP_E_BADARG; }
+    if (cfg->nc > YPP_MAX_CLASSES) { ypp_set_error("nc=%d > %d", cfg->nc, YPP_MAX_CLASSES); return YPP_E_UNSUPPORTED; }
+    if (cfg->offset_mode < 0 || cfg->offset_mode > 3 || cfg->union_mode < 0 || cfg->union_mode > 1 ||
+        cfg->score_mode < 0 || cfg->score_mode > 1) { ypp_set_error("bad mode enum"); return YPP_E_BADARG; }
+    if (cfg->B > 65535) { ypp_set_error("B=%d > 65535", cfg->B); return YPP_E_UNSUPPORTED; }
+    return YPP_OK;
+}
+
+int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, YppDecodeParams* p)
+{
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    if (!sc || cfg->n_scales < 1 || cfg->n_scales > YPP_MAX_SCALES) { ypp_set_error("n_scales=%d out of range", cfg->n_scales); return YPP_E_BADARG; }
+    memset(p, 0, sizeof(*p));
+    p->n_scales = cfg->n_scales;
+    p->nc = cfg->nc;
+    p->C = 5 + cfg->nc;
+    p->conf = cfg->conf_thr;
+    p->score_mode = cfg->score_mode;
+    int box_base = 0, tile = 0;
+    for (int i = 0; i < cfg->n_scales; ++i) {
+        const ypp_scale& s = sc[i];
+        if (!s.head || s.A < 1 || s.A > YPP_MAX_ANCHORS || s.H < 1 || s.W < 1) { ypp_set_error("scale %d: bad head/A/H/W", i); return YPP_E_BADARG; }
+        YppScaleParams& d = p->sc[i];
+        d.head = s.head; d.A = s.A; d.H = s.H; d.W = s.W; d.HW = s.H * s.W;
+        d.box_base = box_base;
+        const bool vec_ok = !dense && (d.HW % 4 == 0) && (((uintptr_t)s.head & 15u) == 0);
+        d.vec = vec_ok ? 4 : 1;
+        d.units = s.A * d.HW / d.vec;
+        for (int a = 0; a < s.A; ++a) { d.aw[a] = s.anchor_w[a]; d.ah[a] = s.anchor_h[a]; }
+        d.sw = s.stride_w; d.sh = s.stride_h;
+        p->tile_base[i] = tile;
+        tile += (d.units + YPP_DECODE_THREADS - 1) / YPP_DECODE_THREADS;
+        box_base += s.A * d.HW;
+        if (box_base > YPP_MAX_BOXES) { ypp_set_error("more than %d boxes per image", YPP_MAX_BOXES); return YPP_E_UNSUPPORTED; }
+    }
+    for (int i = cfg->n_scales; i <= YPP_MAX_SCALES; ++i) p->tile_base[i] = tile;
+    p->N = box_base;
+    return YPP_OK;
+}
+
+int bind_ws(int B, int N, int nc, void* ws, size_t ws_bytes, YppWs* out)
+{
+    if (!ws) { ypp_set_error("workspace is null"); return YPP_E_WORKSPACE; }
+    if (((uintptr_t)ws & 255u) != 0) { ypp_set_error("workspace must be 256-byte aligned"); return YPP_E_WORKSPACE; }
+    *out = ypp_make_ws(ws, B, N, nc);
+    if (out->total_bytes > ws_bytes) { ypp_set_error("workspace %zu bytes < required %zu", ws_bytes, out->total_bytes); return YPP_E_WORKSPACE; }
+    return YPP_OK;
+}
+
+int reset_counters(const YppWs& w, cudaStream_t st)
+{
+    const cudaError_t e = cudaMemsetAsync(w.cand_count, 0, w.counter_bytes, st);
+    if (e != cudaSuccess) { ypp_set_error("memset: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    return YPP_OK;
+}
+
+int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int* keep_count, int* keep_idx,
+                 float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
+                 const float* src_rows, bool do_sort, bool do_nms, cudaStream_t st)
+{
+    int rc = YPP_OK;
+    if (do_sort) {
+        YppOrgParams o;
+        memset(&o, 0, sizeof(o));
+        o.ws = w; o.B = cfg->B; o.N = N; o.nc = cfg->nc;
+        o.offset_mode = cfg->offset_mode; o.union_mode = cfg->union_mode; o.iou_thr = cfg->iou_thr;
+        rc = ypp_launch_organise(o, st);
+        if (rc) return rc;
+    }
+    if (do_nms) {
+        if (det_rows && row_width != 6 && row_width != 7) { ypp_set_error("row_width must be 6 or 7"); return YPP_E_BADARG; }
+        YppNmsParams n;
+        memset(&n, 0, sizeof(n));
+        n.ws = w; n.B = cfg->B; n.N = N; n.nc = cfg->nc; n.iou_thr = cfg->iou_thr; n.union_mode = cfg->union_mode;
+        rc = ypp_launch_nms(n, st);
+        if (rc) return rc;
+        YppGatherParams g;
+        memset(&g, 0, sizeof(g));
+        g.ws = w; g.B = cfg->B; g.N = N;
+        g.cand_count_out = cand_count; g.keep_count_out = keep_count; g.keep_idx = keep_idx;
+        g.det_rows = det_rows; g.row_width = row_width; g.det_capacity = det_capacity; g.det_total = det_total;
+        g.img_idx_base = img_idx_base; g.src_rows = src_rows;
+        rc = ypp_launch_gather(g, st);
+    }
+    return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t ypp_workspace_bytes(int B, int n_boxes, int nc)
+{
+    if (B <= 0 || n_boxes <= 0 || nc <= 0) return 0;
+    return ypp_make_ws(nullptr, B, n_boxes, nc).total_bytes;
+}
+
+float ypp_effective_iou_thr(double iou_thr, int compare_in_double)
+{
+    float tf = (float)iou_thr;
+    if (compare_in_double && (double)tf > iou_thr) tf = nextafterf(tf, -INFINITY);
+    return tf;
+}
+
+int ypp_decode_dense(const ypp_cfg* cfg, const ypp_scale* scales, float* out_BN6, void* stream)
+{
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, true, &p);
+    if (rc) return rc;
+    if (!out_BN6) { ypp_set_error("out is null"); return YPP_E_BADARG; }
+    return ypp_launch_decode_dense(p, cfg->B, out_BN6, (cudaStream_t)stream);
+}
+
+int ypp_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, void* stream)
+{
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, false, &p);
+    if (rc) return rc;
+    rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
+    if (rc) return rc;
+    rc = reset_counters(p.ws, (cudaStream_t)stream);
+    if (rc) return rc;
+    return ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
+}
+
+int ypp_rows_compact(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* ws, size_t ws_bytes, void* stream)
+{
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    if (!rows_BN6 || n_boxes <= 0 || n_boxes > YPP_MAX_BOXES) { ypp_set_error("rows null or n_boxes=%d out of range", n_boxes); return YPP_E_BADARG; }
+    YppWs w;
+    rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
+    if (rc) return rc;
+    rc = reset_counters(w, (cudaStream_t)stream);
+    if (rc) return rc;
+    return ypp_launch_rows_compact(rows_BN6, cfg->B, n_boxes, cfg->conf_thr, w, (cudaStream_t)stream);
+}
+
+int ypp_sort_segments(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, void* stream)
+{
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    YppWs w;
+    rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
+    if (rc) return rc;
+    return run_sort_nms(cfg, n_boxes, w, nullptr, nullptr, nullptr, nullptr, 7, 0, nullptr, 0.f, nullptr, true, false,
+                        (cudaStream_t)stream);
+}
+
+int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count, int* keep_idx,
+            float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base, void* stream)
+{
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    YppWs w;
+    rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
+    if (rc) return rc;
+    return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, nullptr, false, true, (cudaStream_t)stream);
+}
+
+int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
+                    int* keep_count, int* keep_idx, float* det_rows, int row_width, int64_t det_capacity,
+                    int* det_total, float img_idx_base, void* stream)
+{
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, false, &p);
+    if (rc) return rc;
+    rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
+    if (rc) return rc;
+    rc = reset_counters(p.ws, (cudaStream_t)stream);
+    if (rc) return rc;
+    rc = ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
+    if (rc) return rc;
+    return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, nullptr, true, true, (cudaStream_t)stream);
+}
+
+int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* ws, size_t ws_bytes, int* cand_count,
+                 int* keep_count, int* keep_idx, float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+                 float img_idx_base, void* stream)
+{
+    int rc = ypp_rows_compact(cfg, rows_BN6, n_boxes, ws, ws_bytes, stream);
+    if (rc) return rc;
+    YppWs w = ypp_make_ws(ws, cfg->B, n_boxes, cfg->nc);
+    return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, rows_BN6, true, true, (cudaStream_t)stream);
+}
+
+int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, float img_idx_base, float* out_G7,
+                    int* gt_count, void* stream)
+{
+    if (!annot_BT5 || !out_G7 || !gt_count || B <= 0 || T <= 0) { ypp_set_error("target_rows: bad argument"); return YPP_E_BADARG; }
+    return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, gt_count, (cudaStream_t)stream);
+}
+
+int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream)
+{
+    if (N < 0 || M < 0) { ypp_set_error("box_iou: negative size"); return YPP_E_BADARG; }
+    if (N == 0 || M == 0) return YPP_OK;
+    if (!a_N4 || !b_M4 || !out_NM) { ypp_set_error("box_iou: null pointer"); return YPP_E_BADARG; }
+    if ((((uintptr_t)a_N4) | ((uintptr_t)b_M4)) & 15u) { ypp_set_error("box_iou: inputs must be 16-byte aligned"); return YPP_E_BADARG; }
+    if ((N + 7) / 8 > 65535) { ypp_set_error("box_iou: N too large"); return YPP_E_UNSUPPORTED; }
+    return ypp_launch_box_iou(a_N4, N, b_M4, M, out_NM, (cudaStream_t)stream);
+}
+
+size_t ypp_map_workspace_bytes(int64_t G, int64_t K, int nc) { return ypp_map_ws_bytes(G, K, nc); }
+
+int ypp_map_match(const float* gt_G7, int64_t G, const float* det_K7, int64_t K, int nc, float iou_thr, void* ws,
+                  size_t ws_bytes, unsigned char* tp, float* per_class, float* map, void* stream)
+{
+    if (G < 0 || K < 0 || nc <= 0 || !map || !ws) { ypp_set_error("map_match: bad argument"); return YPP_E_BADARG; }
+    if ((G > 0 && !gt_G7) || (K > 0 && !det_K7)) { ypp_set_error("map_match: null rows"); return YPP_E_BADARG; }
+    if (nc > 65535 || K >= (1LL << 31) || G >= (1LL << 31)) { ypp_set_error("map_match: size out of range"); return YPP_E_UNSUPPORTED; }
+    return ypp_launch_map(gt_G7, G, det_K7, K, nc, iou_thr, ws, ws_bytes, tp, per_class, map, (cudaStream_t)stream);
+}
+
+const char* ypp_last_error(void) { return g_err; }
+int ypp_version(void) { return 100; }
+int64_t ypp_launch_count(int reset)
+{
+    const long long v = g_launches;
+    if (reset) g_launches = 0;
+    return v;
+}
+
+}  // extern "C"

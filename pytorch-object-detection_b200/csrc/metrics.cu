@@ -1,0 +1,438 @@
+// mAP@.5 side of the path: ground-truth ingest, N x M box_iou, and the TP/FP matching + AP.
+//
+// Reference semantics:
+//   get_target_boxes_for_map      utils/yolo_utils.py:682-710
+//   box_iou                       utils/metrics.py:233-255
+//   mean_average_precision        utils/yolo_utils.py:351-456  (metrics_per_class :458-574)
+//   bbox_iou (IoU branch)         utils/yolo_utils.py:75-123,143-144
+//
+// The reference matches detections one by one in Python.  The greedy rule is order-free once
+// restated: the best ground truth g*(d) of a detection depends only on d and the ground truths
+// (strict >, first maximum wins, utils/yolo_utils.py:412-417), and d is a true positive iff
+// IoU(d, g*) > thr and d is the FIRST detection in descending-score order that selects g*
+// (:419-430).  So: one stable radix sort of the detections by (class, score desc), one parallel
+// pass computing g*(d) and an atomicMin of the sort rank per ground truth, one pass comparing.
+#include "ypp_kernels.cuh"
+#include <limits.h>
+
+namespace {
+
+// ------------------------------------------------------------------ GT ingest
+__global__ void __launch_bounds__(1024)
+ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float input_size, float img_base,
+                       float* __restrict__ out, int* __restrict__ gt_count)
+{
+    __shared__ int warp_tot[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int total = B * T;
+    int running = 0;
+    for (int i0 = 0; i0 < total; i0 += 1024) {
+        const int i = i0 + tid;
+        bool ok = false;
+        float r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+        if (i < total) {
+            const float* r = annot + (size_t)i * 5;
+            r0 = r[0]; r1 = r[1]; r2 = r[2]; r3 = r[3]; r4 = r[4];
+            float s = __fadd_rn(r0, r1); s = __fadd_rn(s, r2); s = __fadd_rn(s, r3); s = __fadd_rn(s, r4);
+            ok = !(s <= 0.0f);                       // `if target[b, t].sum() <= 0: continue` (:697)
+        }
+        const u32 m = __ballot_sync(YPP_FULL_MASK, ok);
+        if (lane == 0) warp_tot[warp] = __popc(m);
+        __syncthreads();
+        int before = 0, tot = 0;
+        for (int w = 0; w < 32; ++w) { const int t = warp_tot[w]; if (w < warp) before += t; tot += t; }
+        if (ok) {
+            float* o = out + (size_t)(running + before + __popc(m & ((1u << lane) - 1u))) * 7;
+            o[0] = img_base + (float)(i / T);
+            o[1] = __fmul_rn(r0, input_size); o[2] = __fmul_rn(r1, input_size);
+            o[3] = __fmul_rn(r2, input_size); o[4] = __fmul_rn(r3, input_size);
+            o[5] = 1.0f; o[6] = r4;
+        }
+        running += tot;
+        __syncthreads();
+    }
+    if (tid == 0) *gt_count = running;
+}
+
+// ------------------------------------------------------------------ box_iou (N x M)
+__global__ void __launch_bounds__(256)
+ypp_box_iou_kernel(const float4* __restrict__ a, int N, const float4* __restrict__ b, int M, float* __restrict__ out)
+{
+    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (i >= N || j >= M) return;
+    const float4 p = __ldg(a + i), q = __ldg(b + j);
+    const float s1 = __fmul_rn(__fsub_rn(p.z, p.x), __fsub_rn(p.w, p.y));
+    const float s2 = __fmul_rn(__fsub_rn(q.z, q.x), __fsub_rn(q.w, q.y));
+    const float w = fmaxf(__fsub_rn(fminf(p.z, q.z), fmaxf(p.x, q.x)), 0.0f);
+    const float h = fmaxf(__fsub_rn(fminf(p.w, q.w), fmaxf(p.y, q.y)), 0.0f);
+    const float inter = __fmul_rn(w, h);
+    out[(size_t)i * M + j] = __fdiv_rn(inter, __fsub_rn(__fadd_rn(s1, s2), inter));
+}
+
+// ------------------------------------------------------------------ stable LSD radix sort
+#define RS_THREADS 256
+#define RS_ITEMS 8
+#define RS_TILE (RS_THREADS * RS_ITEMS)
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_hist_kernel(const u64* __restrict__ keys, long long n, int shift, int* __restrict__ counts, int nblocks)
+{
+    __shared__ int h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * RS_TILE;
+    for (int it = 0; it < RS_ITEMS; ++it) {
+        const long long i = base + it * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&h[(int)((keys[i] >> shift) & 255ull)], 1);
+    }
+    __syncthreads();
+    counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan over the digit-major [256][nblocks] table, one CTA
+__global__ void __launch_bounds__(1024)
+rs_scan_kernel(int* __restrict__ counts, long long total)
+{
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (long long i0 = 0; i0 < total; i0 += 1024) {
+        const long long i = i0 + tid;
+        const int v = i < total ? counts[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        int before = 0, tot = 0;
+        for (int w = 0; w < 32; ++w) { const int t = warp_tot[w]; if (w < warp) before += t; tot += t; }
+        const int c = carry;
+        if (i < total) counts[i] = c + before + inc - v;
+        __syncthreads();
+        if (tid == 0) carry = c + tot;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_scatter_kernel(const u64* __restrict__ kin, const u32* __restrict__ vin, u64* __restrict__ kout, u32* __restrict__ vout,
+                  long long n, int shift, const int* __restrict__ offsets, int nblocks)
+{
+    __shared__ int wc[RS_THREADS / 32][256];
+    __shared__ int dbase[256];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    dbase[tid] = offsets[(size_t)tid * nblocks + blockIdx.x];
+    const long long base = (long long)blockIdx.x * RS_TILE;
+    for (int it = 0; it < RS_ITEMS; ++it) {
+        for (int w = 0; w < RS_THREADS / 32; ++w) wc[w][tid] = 0;
+        __syncthreads();
+        const long long i = base + it * RS_THREADS + tid;
+        const bool ok = i < n;
+        u64 k = 0;
+        int d = -1 - lane;
+        if (ok) { k = kin[i]; d = (int)((k >> shift) & 255ull); }
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        if (ok && rank == 0) wc[warp][d] = __popc(peers);
+        __syncthreads();
+        {   // thread tid owns digit tid: turn per-warp counts into destinations
+            int run = dbase[tid];
+            for (int w = 0; w < RS_THREADS / 32; ++w) { const int t = wc[w][tid]; wc[w][tid] = run; run += t; }
+            dbase[tid] = run;
+        }
+        __syncthreads();
+        if (ok) {
+            const int dst = wc[warp][d] + rank;
+            kout[dst] = k;
+            vout[dst] = vin[i];
+        }
+        __syncthreads();
+    }
+}
+
+struct RsBuffers { u64* k[2]; u32* v[2]; int* counts; };
+
+// sorts (k[0], v[0]) over bits [0, nbits); returns which buffer holds the result
+int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st)
+{
+    int cur = 0;
+    if (n <= 0) return cur;
+    const int nblocks = (int)((n + RS_TILE - 1) / RS_TILE);
+    for (int shift = 0; shift < nbits; shift += 8) {
+        rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], n, shift, rb.counts, nblocks);
+        rs_scan_kernel<<<1, 1024, 0, st>>>(rb.counts, 256LL * nblocks);
+        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], rb.v[cur], rb.k[cur ^ 1], rb.v[cur ^ 1], n, shift,
+                                                          rb.counts, nblocks);
+        ypp_count_launch(3);
+        cur ^= 1;
+    }
+    return cur;
+}
+
+// ------------------------------------------------------------------ matching
+#define MAP_IMG_BITS 24
+
+// class ids that are not integers in [0, nc) can never equal a loop class c (:370-375): marker nc
+__device__ __forceinline__ u32 map_cls(float cf, int nc)
+{
+    return (cf >= 0.0f && cf < (float)nc && (float)(int)cf == cf) ? (u32)cf : (u32)nc;
+}
+
+__global__ void map_gt_keys_kernel(const float* __restrict__ gt, long long G, int nc, u64* __restrict__ keys, u32* __restrict__ vals,
+                                   int* __restrict__ first_rank)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    const u32 img = (u32)gt[g * 7 + 0] & ((1u << MAP_IMG_BITS) - 1u);
+    const u32 cls = map_cls(gt[g * 7 + 6], nc);
+    keys[g] = ((u64)cls << MAP_IMG_BITS) | img;
+    vals[g] = (u32)g;
+    first_rank[g] = INT_MAX;
+}
+
+__global__ void map_det_keys_kernel(const float* __restrict__ det, long long K, int nc, u64* __restrict__ keys, u32* __restrict__ vals,
+                                    unsigned char* __restrict__ tp_out)
+{
+    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= K) return;
+    const u32 cls = map_cls(det[d * 7 + 6], nc);
+    keys[d] = ((u64)cls << 32) | (u64)(~ypp_enc(det[d * 7 + 5]));
+    vals[d] = (u32)d;
+    if (tp_out) tp_out[d] = 255;
+}
+
+__device__ __forceinline__ long long lower_bound_u64(const u64* a, long long n, u64 key)
+{
+    long long lo = 0, hi = n;
+    while (lo < hi) { const long long mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
+// bbox_iou IoU branch on cxcywh (abs areas, eps on the union): utils/yolo_utils.py:103-123
+__device__ __forceinline__ float map_iou(const float* a, const float* b)
+{
+    const float ahw = __fmul_rn(a[2], 0.5f), ahh = __fmul_rn(a[3], 0.5f);
+    const float bhw = __fmul_rn(b[2], 0.5f), bhh = __fmul_rn(b[3], 0.5f);
+    const float ax1 = __fsub_rn(a[0], ahw), ay1 = __fsub_rn(a[1], ahh), ax2 = __fadd_rn(a[0], ahw), ay2 = __fadd_rn(a[1], ahh);
+    const float bx1 = __fsub_rn(b[0], bhw), by1 = __fsub_rn(b[1], bhh), bx2 = __fadd_rn(b[0], bhw), by2 = __fadd_rn(b[1], bhh);
+    const float iw = fmaxf(__fsub_rn(fminf(ax2, bx2), fmaxf(ax1, bx1)), 0.0f);
+    const float ih = fmaxf(__fsub_rn(fminf(ay2, by2), fmaxf(ay1, by1)), 0.0f);
+    const float inter = __fmul_rn(iw, ih);
+    const float sa = fabsf(__fmul_rn(__fsub_rn(ax2, ax1), __fsub_rn(ay2, ay1)));
+    const float sb = fabsf(__fmul_rn(__fsub_rn(bx2, bx1), __fsub_rn(by2, by1)));
+    const float uni = __fadd_rn(__fsub_rn(__fadd_rn(sa, sb), inter), 1e-6f);
+    return __fdiv_rn(inter, uni);
+}
+
+__global__ void map_best_kernel(const float* __restrict__ det, long long K, const float* __restrict__ gt, long long G,
+                                const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
+                                const u64* __restrict__ gkeys, const u32* __restrict__ gvals,
+                                float iou_thr, int* __restrict__ best_g, int* __restrict__ first_rank)
+{
+    const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= K) return;
+    const u32 d = dvals[p];
+    const float* dr = det + (size_t)d * 7;
+    const u32 cls = (u32)(dkeys[p] >> 32);
+    const u32 img = (u32)dr[0] & ((1u << MAP_IMG_BITS) - 1u);
+    const u64 gk = ((u64)cls << MAP_IMG_BITS) | img;
+    long long s = lower_bound_u64(gkeys, G, gk);
+    float best = 0.0f;
+    int bg = -1;
+    for (; s < G && gkeys[s] == gk; ++s) {
+        const float iou = map_iou(dr + 1, gt + (size_t)gvals[s] * 7 + 1);
+        if (iou > best) { best = iou; bg = (int)s; }          // strict >, first max wins (:415-417)
+    }
+    if (!(best > iou_thr)) bg = -1;                            // :419
+    best_g[p] = bg;
+    if (bg >= 0) atomicMin(first_rank + bg, (int)p);
+}
+
+// one CTA per class: TP flags, cumulative precision/recall, envelope, AP
+#define AP_THREADS 1024
+__global__ void __launch_bounds__(AP_THREADS)
+map_ap_kernel(long long K, long long G, int nc, const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
+              const u64* __restrict__ gkeys, const int* __restrict__ best_g, const int* __restrict__ first_rank,
+              float* __restrict__ prec, float* __restrict__ contrib, unsigned char* __restrict__ tp_out,
+              float* __restrict__ per_class)
+{
+    __shared__ int warp_i[32];
+    __shared__ float warp_f[32];
+    __shared__ long long s_lo, s_hi, g_lo, g_hi;
+    __shared__ int carry_i;
+    __shared__ float carry_f;
+    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        s_lo = lower_bound_u64(dkeys, K, (u64)c << 32);
+        s_hi = lower_bound_u64(dkeys, K, (u64)(c + 1) << 32);
+        g_lo = lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
+        g_hi = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS);
+        carry_i = 0;
+    }
+    __syncthreads();
+    const long long lo = s_lo, hi = s_hi;
+    const long long ng = g_hi - g_lo;
+    float* pc = per_class ? per_class + 4 * (size_t)c : nullptr;
+    if (ng == 0) {                                           // class skipped, AP 0 (:379-381)
+        if (tp_out) for (long long p = lo + tid; p < hi; p += AP_THREADS) tp_out[dvals[p]] = 255;
+        if (pc && tid < 4) pc[tid] = 0.0f;
+        return;
+    }
+    const float rec_den = (float)((double)ng + 1e-6);         // python float64 (G + eps) -> fp32
+    // forward: cumulative TP -> precision at every rank
+    for (long long p0 = lo; p0 < hi; p0 += AP_THREADS) {
+        const long long p = p0 + tid;
+        int t = 0;
+        if (p < hi) { const int bg = best_g[p]; t = (bg >= 0 && first_rank[bg] == (int)p) ? 1 : 0; }
+        int inc = t;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
+        if (lane == 31) warp_i[warp] = inc;
+        __syncthreads();
+        int before = 0, tot = 0;
+        for (int w = 0; w < 32; ++w) { const int v = warp_i[w]; if (w < warp) before += v; tot += v; }
+        const int cbase = carry_i;
+        if (p < hi) {
+            const int tpc = cbase + before + inc;
+            const float ftp = (float)tpc, ffp = (float)((int)(p - lo + 1) - tpc);
+            const float pr = __fdiv_rn(ftp, __fadd_rn(__fadd_rn(ftp, ffp), 1e-6f));      // :435
+            // positive tpc marks a TP rank (recall change point); sign carries the flag
+            prec[p] = pr;
+            if (tp_out) tp_out[dvals[p]] = (unsigned char)t;
+            if (t) contrib[g_lo + tpc - 1] = __uint_as_float((u32)(p - lo));             // rank of the tpc-th TP (int bits)
+        }
+        __syncthreads();
+        if (tid == 0) carry_i = cbase + tot;
+        __syncthreads();
+    }
+    const int n_tp = carry_i;
+    // backward: precision envelope = running max from the right (:442-443)
+    if (tid == 0) carry_f = -INFINITY;
+    __syncthreads();
+    const long long len = hi - lo;
+    const long long nchunks = (len + AP_THREADS - 1) / AP_THREADS;
+    for (long long ch = nchunks - 1; ch >= 0; --ch) {
+        const long long p = lo + ch * AP_THREADS + (AP_THREADS - 1 - tid);   // thread 0 = right-most
+        float v = p < hi ? prec[p] : -INFINITY;
+        float inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const float o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc = fmaxf(inc, o); }
+        if (lane == 31) warp_f[warp] = inc;
+        __syncthreads();
+        float before = carry_f, tot = carry_f;
+        for (int w = 0; w < 32; ++w) { const float x = warp_f[w]; if (w < warp) before = fmaxf(before, x); tot = fmaxf(tot, x); }
+        if (p < hi) prec[p] = fmaxf(before, inc);
+        __syncthreads();
+        if (tid == 0) carry_f = tot;
+        __syncthreads();
+    }
+    // AP = sum over recall change points, accumulated sequentially in fp32 like the reference (:445-452)
+    if (tid == 0) {
+        float ap = 0.0f;
+        for (int t = 1; t <= n_tp; ++t) {
+            const long long p = lo + (long long)__float_as_uint(contrib[g_lo + t - 1]);
+            const float r1 = __fdiv_rn((float)t, rec_den), r0 = __fdiv_rn((float)(t - 1), rec_den);
+            ap = __fadd_rn(ap, __fmul_rn(__fsub_rn(r1, r0), prec[p]));
+        }
+        if (pc) { pc[0] = ap; pc[1] = (float)n_tp; pc[2] = (float)((int)len - n_tp); pc[3] = (float)((int)ng - n_tp); }
+        contrib[g_lo] = ap;       // per-class AP parked for the mean kernel (slot is free again)
+    }
+}
+
+__global__ void map_mean_kernel(int nc, long long G, const u64* __restrict__ gkeys, const float* __restrict__ contrib,
+                                float* __restrict__ map_out)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float s = 0.0f;
+    for (int c = 0; c < nc; ++c) {
+        const long long g_lo = lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
+        const long long g_hi = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS);
+        if (g_hi > g_lo) s = __fadd_rn(s, contrib[g_lo]);
+    }
+    *map_out = __fdiv_rn(s, (float)nc);                       // torch.mean over all nc classes (:456)
+}
+
+struct MapWs {
+    RsBuffers det, gt;
+    int* best_g; float* prec; int* first_rank; float* contrib;
+    size_t total;
+};
+
+MapWs make_map_ws(void* base, long long G, long long K)
+{
+    MapWs w;
+    char* p = (char*)base;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char* r = p + off; off += ypp_align_up(bytes ? bytes : 8, 256); return r; };
+    const long long Kp = K > 0 ? K : 1, Gp = G > 0 ? G : 1;
+    const size_t nbk = (size_t)((Kp + RS_TILE - 1) / RS_TILE), nbg = (size_t)((Gp + RS_TILE - 1) / RS_TILE);
+    w.det.k[0] = (u64*)take(8 * Kp); w.det.k[1] = (u64*)take(8 * Kp);
+    w.det.v[0] = (u32*)take(4 * Kp); w.det.v[1] = (u32*)take(4 * Kp);
+    w.det.counts = (int*)take(4 * 256 * nbk);
+    w.gt.k[0] = (u64*)take(8 * Gp); w.gt.k[1] = (u64*)take(8 * Gp);
+    w.gt.v[0] = (u32*)take(4 * Gp); w.gt.v[1] = (u32*)take(4 * Gp);
+    w.gt.counts = (int*)take(4 * 256 * nbg);
+    w.best_g = (int*)take(4 * Kp);
+    w.prec = (float*)take(4 * Kp);
+    w.first_rank = (int*)take(4 * Gp);
+    w.contrib = (float*)take(4 * Gp);
+    w.total = off;
+    return w;
+}
+
+int bits_for(int n) { int b = 1; while ((1 << b) < n) ++b; return b; }
+
+}  // namespace
+
+int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
+                           float* out, int* gt_count, cudaStream_t st)
+{
+    ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count);
+    ypp_count_launch(1);
+    return ypp_check_launch("target_rows");
+}
+
+int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st)
+{
+    dim3 grid((M + 31) / 32, (N + 7) / 8);
+    ypp_box_iou_kernel<<<grid, 256, 0, st>>>((const float4*)a, N, (const float4*)b, M, out);
+    ypp_count_launch(1);
+    return ypp_check_launch("box_iou");
+}
+
+size_t ypp_map_ws_bytes(long long G, long long K, int nc)
+{
+    (void)nc;
+    return make_map_ws(nullptr, G, K).total;
+}
+
+int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
+                   void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
+                   cudaStream_t st)
+{
+    MapWs w = make_map_ws(ws, G, K);
+    if (ws_bytes < w.total) { ypp_set_error("map_match: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
+    const int cbits = bits_for(nc + 1);
+    int gcur = 0, dcur = 0;
+    if (G > 0) {
+        map_gt_keys_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, w.gt.k[0], w.gt.v[0], w.first_rank);
+        ypp_count_launch(1);
+        gcur = rs_sort(w.gt, G, MAP_IMG_BITS + cbits, st);
+    }
+    if (K > 0) {
+        map_det_keys_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, nc, w.det.k[0], w.det.v[0], tp);
+        ypp_count_launch(1);
+        dcur = rs_sort(w.det, K, 32 + cbits, st);
+        map_best_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, gt, G, w.det.k[dcur], w.det.v[dcur],
+                                                                     w.gt.k[gcur], w.gt.v[gcur], iou_thr, w.best_g, w.first_rank);
+        ypp_count_launch(1);
+    }
+    map_ap_kernel<<<nc, AP_THREADS, 0, st>>>(K, G, nc, w.det.k[dcur], w.det.v[dcur], w.gt.k[gcur], w.best_g, w.first_rank,
+                                             w.prec, w.contrib, tp, per_class);
+    map_mean_kernel<<<1, 32, 0, st>>>(nc, G, w.gt.k[gcur], w.contrib, map);
+    ypp_count_launch(2);
+    return ypp_check_launch("map_match");
+}

@@ -1,0 +1,265 @@
+// S1: per image ordering.  One CTA per image:
+//   1. sort the compacted 64-bit keys (~score | box index | class) ascending in shared memory:
+//      the result is the stable descending-score order of torchvision::nms
+//      (scores.sort(stable=True, descending=True); ties -> lower box index) for the whole image;
+//   2. stable counting partition by class -> per (image, class) segments in the same order;
+//   3. emit xyxy boxes (utils/yolo_utils.py:339-343) in segment order, shifted by
+//      cls * (max_coordinate + 1) when torchvision would take the coordinate-trick path
+//      (_batched_nms_coordinate_trick), and the segment -> global-rank map;
+//   4. coordinate trick only: detect cross-class suppression edges (possible when a box with
+//      negative x1,y1 is shifted onto the previous class band); such an image is re-emitted as
+//      ONE class-agnostic segment so the greedy scan sees exactly what torchvision's does.
+#include "ypp_kernels.cuh"
+
+namespace {
+
+#define YPP_DET_LIST 64
+
+struct DetEntry { float4 box; int cls; int rank; };
+
+struct OrgSmemHeader {
+    DetEntry lowl[YPP_DET_LIST];
+    DetEntry highl[YPP_DET_LIST];
+    int n_low, n_high, flagged, pad;
+};
+
+__device__ __forceinline__ void ce(u64* a, int i, int l)
+{
+    const u64 x = a[i], y = a[l];
+    if (x > y) { a[i] = y; a[l] = x; }
+}
+
+// Bitonic network with every compare-exchange ascending (mirror first step), so a virtual
+// +inf padding beyond n never moves: pairs whose upper index is >= n are simply skipped.
+__device__ void bitonic_sort(u64* a, int n)
+{
+    int n_pad = 1;
+    while (n_pad < n) n_pad <<= 1;
+    const int half = n_pad >> 1;
+    for (int k = 2; k <= n_pad; k <<= 1) {
+        const int hk = k >> 1;
+        for (int t = threadIdx.x; t < half; t += YPP_ORG_THREADS) {
+            const int blk = t / hk, r = t - blk * hk;
+            const int i = blk * k + r, l = blk * k + (k - 1 - r);
+            if (l < n) ce(a, i, l);
+        }
+        __syncthreads();
+        for (int j = hk >> 1; j > 0; j >>= 1) {
+            for (int t = threadIdx.x; t < half; t += YPP_ORG_THREADS) {
+                const int blk = t / j, r = t - blk * j;
+                const int i = blk * 2 * j + r, l = i + j;
+                if (l < n) ce(a, i, l);
+            }
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(YPP_ORG_THREADS, 1)
+ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    OrgSmemHeader* hd = reinterpret_cast<OrgSmemHeader*>(smem_raw);
+    int* table = reinterpret_cast<int*>(smem_raw + sizeof(OrgSmemHeader));   // [32][nc]
+    int* seg = table + 32 * p.nc;                                            // [nc+1]
+    size_t koff = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)(33 * p.nc + 1);
+    koff = (koff + 15) / 16 * 16;
+
+    const int b = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nc = p.nc, N = p.N;
+    const int n = min(p.ws.cand_count[b], N);
+    u64* gkeys = p.ws.keys + (size_t)b * N;
+    u64* keys = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : gkeys;
+    int* gseg = p.ws.seg_start + (size_t)b * (nc + 1);
+
+    if (n == 0) {
+        for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = 0;
+        return;
+    }
+    if (p.keys_in_smem) {
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) keys[i] = gkeys[i];
+    }
+    if (tid == 0) { hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; }
+    for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
+    unsigned char* kf = p.ws.keepflag + (size_t)b * N;
+    for (int i = tid; i < n; i += YPP_ORG_THREADS) kf[i] = 0;
+    __syncthreads();
+
+    bitonic_sort(keys, n);       // ends with __syncthreads()
+
+    if (p.keys_in_smem) {
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) gkeys[i] = keys[i];
+    }
+
+    // ---- stable partition by class: warp w owns ranks [w*L, (w+1)*L)
+    const int L = ((n + 31) / 32 + 31) / 32 * 32;
+    const int r_begin = warp * L, r_end = min(n, r_begin + L);
+    int* my = table + warp * nc;
+    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
+        const int r = r0 + lane;
+        const bool ok = r < r_end;
+        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
+        if (ok && (peers & ((1u << lane) - 1u)) == 0) my[c] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
+        int t = 0;
+        for (int w = 0; w < 32; ++w) t += table[w * nc + c];
+        seg[c] = t;
+    }
+    __syncthreads();
+    if (warp == 0) {   // exclusive scan of seg[0..nc) -> seg[0..nc]
+        int run = 0;
+        for (int c0 = 0; c0 < nc; c0 += 32) {
+            const int c = c0 + lane;
+            const int v = c < nc ? seg[c] : 0;
+            int inc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (c < nc) seg[c] = run + inc - v;
+            run += __shfl_sync(YPP_FULL_MASK, inc, 31);
+        }
+        if (lane == 0) seg[nc] = run;
+    }
+    __syncthreads();
+    for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
+        int run = seg[c];
+        for (int w = 0; w < 32; ++w) { const int t = table[w * nc + c]; table[w * nc + c] = run; run += t; }
+    }
+    __syncthreads();
+
+    // ---- which torchvision path would run for this image
+    bool trick = p.offset_mode == YPP_OFFSET_TRICK;
+    if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
+    if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
+    const float M = ypp_dec(p.ws.maxc[b]);
+    const float step = __fadd_rn(M, 1.0f);                 // max_coordinate + 1
+    const float x1min = -ypp_dec(p.ws.nminx1[b]), y1min = -ypp_dec(p.ws.nminy1[b]);
+    const float slack = fmaf(step * (float)nc, 1e-6f, 1e-3f);
+    const bool detect = trick && nc > 1;
+    const float low_lim = -1.0f + slack;
+    const float hx_lim = step + x1min - slack, hy_lim = step + y1min - slack;
+    if (detect && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
+
+    const float4* gbox = p.ws.box + (size_t)b * N;
+    float4* sbox = p.ws.sbox + (size_t)b * N;
+    int* grank = p.ws.grank + (size_t)b * N;
+
+    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
+        const int r = r0 + lane;
+        const bool ok = r < r_end;
+        u64 k = 0;
+        int c = -1 - lane;
+        if (ok) { k = keys[r]; c = ypp_key_cls(k); }
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        int q = 0;
+        if (ok) q = my[c] + rank;
+        __syncwarp();
+        if (ok && rank == 0) my[c] += __popc(peers);
+        __syncwarp();
+        if (ok) {
+            const float4 cb = gbox[ypp_key_idx(k)];
+            float4 xy = ypp_xyxy(cb);
+            if (detect) {
+                const bool is_low = xy.x < low_lim && xy.y < low_lim;
+                const bool is_high = xy.z > hx_lim && xy.w > hy_lim;
+                if (is_low || is_high) {
+                    const float off = __fmul_rn((float)c, step);
+                    DetEntry e;
+                    e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                    e.cls = c; e.rank = r;
+                    if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
+                    if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
+                }
+            }
+            if (trick) {
+                const float off = __fmul_rn((float)c, step);    // idxs.to(boxes) * (max_coordinate + 1)
+                xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+            }
+            sbox[q] = xy;
+            grank[q] = r;
+        }
+    }
+    __syncthreads();
+
+    if (detect) {
+        const int nl = hd->n_low, nh = hd->n_high;
+        if (nl > 0 && nh > 0) {
+            if (nl > YPP_DET_LIST || nh > YPP_DET_LIST) {
+                if (tid == 0) hd->flagged = 1;
+            } else {
+                const bool neg_thr = !(p.iou_thr >= 0.0f);
+                for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) {
+                    const DetEntry lo = hd->lowl[t / nh], hi = hd->highl[t % nh];
+                    if (lo.cls == hi.cls) continue;
+                    const DetEntry& row = lo.rank < hi.rank ? lo : hi;
+                    const DetEntry& col = lo.rank < hi.rank ? hi : lo;
+                    const float sa = ypp_area(row.box);
+                    const bool s = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
+                                           : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
+                    if (s) hd->flagged = 1;
+                }
+            }
+        }
+        __syncthreads();
+        if (hd->flagged) {
+            // class-agnostic single segment in global score order, shifted coordinates
+            for (int r = tid; r < n; r += YPP_ORG_THREADS) {
+                const u64 k = keys[r];
+                const float off = __fmul_rn((float)ypp_key_cls(k), step);
+                const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+                sbox[r] = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                grank[r] = r;
+            }
+            for (int c = tid; c <= nc; c += YPP_ORG_THREADS) seg[c] = c == 0 ? 0 : n;
+            if (tid == 0) p.ws.imgflag[b] = 1;
+            __syncthreads();
+        }
+    }
+
+    for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = seg[c];
+    for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
+        if (seg[c + 1] - seg[c] > YPP_SMALL_SEG) {
+            const int s = atomicAdd(p.ws.q, 1);
+            p.ws.bigq[s] = b * nc + c;
+        }
+    }
+}
+
+}  // namespace
+
+int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem)
+{
+    size_t fixed = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)(33 * nc + 1);
+    fixed = (fixed + 15) / 16 * 16;
+    const size_t cap = 227 * 1024;
+    if (fixed > cap) return -1;
+    if (fixed + (size_t)N * 8 <= cap) { *keys_in_smem = 1; return (int)(fixed + (size_t)N * 8); }
+    *keys_in_smem = 0;
+    return (int)fixed;
+}
+
+int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
+{
+    int kin = 0;
+    const int smem = ypp_org_smem_bytes(p.N, p.nc, &kin);
+    if (smem < 0) { ypp_set_error("organise: nc=%d needs more shared memory than one CTA has", p.nc); return YPP_E_UNSUPPORTED; }
+    YppOrgParams q = p;
+    q.keys_in_smem = kin;
+    static int configured_smem = 0;
+    if (smem > configured_smem) {
+        cudaError_t e = cudaFuncSetAttribute(ypp_organise_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) { ypp_set_error("organise: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+        configured_smem = 227 * 1024;
+    }
+    ypp_organise_kernel<<<p.B, YPP_ORG_THREADS, smem, st>>>(q);
+    ypp_count_launch(1);
+    return ypp_check_launch("organise");
+}

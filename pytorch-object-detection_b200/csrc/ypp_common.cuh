@@ -1,0 +1,144 @@
+// Shared device/host helpers of libypp (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/ypp.h"
+
+typedef unsigned long long u64;
+typedef unsigned int u32;
+
+#define YPP_FULL_MASK 0xffffffffu
+#define YPP_KEY_CLS_BITS 12
+#define YPP_KEY_IDX_BITS 20
+#define YPP_KEY_CLS_MASK ((1u << YPP_KEY_CLS_BITS) - 1u)
+#define YPP_KEY_IDX_MASK ((1u << YPP_KEY_IDX_BITS) - 1u)
+
+// segments longer than this go to the persistent "big" NMS kernel
+#define YPP_SMALL_SEG 2048
+// boxes the big kernel keeps staged in shared memory (x 16 B)
+#define YPP_BIG_CACHE 11264
+#define YPP_NMS_SMALL_THREADS 256
+#define YPP_NMS_BIG_THREADS 1024
+#define YPP_ORG_THREADS 1024
+#define YPP_DECODE_THREADS 256
+
+// ---------------------------------------------------------------- workspace layout
+// All per-image arrays are [B][N]; the counter block is zeroed by one memset per call.
+struct YppWs {
+    // counter block (zero-initialised each call)
+    int* cand_count;      // [B]
+    int* keep_count;      // [B]
+    u32* maxc;            // [B] order-encoded max over candidate x1,y1,x2,y2
+    u32* nminx1;          // [B] order-encoded max of -x1  (=> min x1)
+    u32* nminy1;          // [B] order-encoded max of -y1
+    int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge)
+    int* q;               // [4] q[0] big-segment queue length, q[1] queue head, q[2] error bits
+    size_t counter_bytes;
+    // arrays
+    int* bigq;            // [B * bigq_per_image] entries b*nc + c
+    int* seg_start;       // [B][nc+1] segment starts in class order
+    u64* keys;            // [B][N] (~enc(score))<<32 | idx<<12 | cls ; sorted in place by S1
+    float4* box;          // [B][N] cx,cy,w,h indexed by box index n
+    float4* sbox;         // [B][N] x1,y1,x2,y2 (+ class offset) in class-segment order
+    int* grank;           // [B][N] class-order position -> global score rank
+    unsigned char* keepflag;  // [B][N] by global score rank
+    int bigq_per_image;
+    size_t total_bytes;
+};
+
+static inline size_t ypp_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
+{
+    YppWs w;
+    char* p = (char*)base;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char* r = p + off; off += ypp_align_up(bytes, 256); return r; };
+    size_t c0 = off;
+    w.cand_count = (int*)take(sizeof(int) * B);
+    w.keep_count = (int*)take(sizeof(int) * B);
+    w.maxc = (u32*)take(sizeof(u32) * B);
+    w.nminx1 = (u32*)take(sizeof(u32) * B);
+    w.nminy1 = (u32*)take(sizeof(u32) * B);
+    w.imgflag = (int*)take(sizeof(int) * B);
+    w.q = (int*)take(sizeof(int) * 4);
+    w.counter_bytes = off - c0;
+    int per = N / YPP_SMALL_SEG + 1;
+    if (per > nc) per = nc;
+    w.bigq_per_image = per;
+    w.bigq = (int*)take(sizeof(int) * (size_t)B * per);
+    w.seg_start = (int*)take(sizeof(int) * (size_t)B * (nc + 1));
+    w.keys = (u64*)take(sizeof(u64) * (size_t)B * N);
+    w.box = (float4*)take(sizeof(float4) * (size_t)B * N);
+    w.sbox = (float4*)take(sizeof(float4) * (size_t)B * N);
+    w.grank = (int*)take(sizeof(int) * (size_t)B * N);
+    w.keepflag = (unsigned char*)take((size_t)B * N);
+    w.total_bytes = off;
+    return w;
+}
+
+// ---------------------------------------------------------------- error plumbing (api.cu)
+void ypp_set_error(const char* fmt, ...);
+int ypp_check_launch(const char* what);
+void ypp_count_launch(int n);
+
+#ifdef __CUDACC__
+// ---------------------------------------------------------------- device helpers
+
+// monotone float -> uint map (works for negatives): a < b  <=>  enc(a) < enc(b)
+__device__ __forceinline__ u32 ypp_enc(float f)
+{
+    u32 b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ypp_dec(u32 e)
+{
+    u32 b = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+    return __uint_as_float(b);
+}
+
+// 1/(1+exp(-x)) with IEEE add/div and the accurate expf: the formula ATen's CUDA sigmoid uses
+__device__ __forceinline__ float ypp_sigmoid(float x)
+{
+    return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x)));
+}
+
+__device__ __forceinline__ u64 ypp_make_key(float score, int idx, int cls)
+{
+    return ((u64)(~ypp_enc(score)) << 32) | ((u64)(u32)idx << YPP_KEY_CLS_BITS) | (u64)(u32)cls;
+}
+__device__ __forceinline__ float ypp_key_score(u64 k) { return ypp_dec(~(u32)(k >> 32)); }
+__device__ __forceinline__ int ypp_key_idx(u64 k) { return (int)(((u32)k >> YPP_KEY_CLS_BITS) & YPP_KEY_IDX_MASK); }
+__device__ __forceinline__ int ypp_key_cls(u64 k) { return (int)((u32)k & YPP_KEY_CLS_MASK); }
+
+// cxcywh -> xyxy exactly as nms_v3 does (utils/yolo_utils.py:339-343): c -/+ (wh / 2)
+__device__ __forceinline__ float4 ypp_xyxy(float4 c)
+{
+    const float hw = __fmul_rn(c.z, 0.5f), hh = __fmul_rn(c.w, 0.5f);   // x/2 == x*0.5 exactly
+    return make_float4(__fsub_rn(c.x, hw), __fsub_rn(c.y, hh), __fadd_rn(c.x, hw), __fadd_rn(c.y, hh));
+}
+
+__device__ __forceinline__ float ypp_area(float4 b)
+{
+    return __fmul_rn(__fsub_rn(b.z, b.x), __fsub_rn(b.w, b.y));
+}
+
+// torchvision::nms pair test. a = row (earlier in score order), b = column.
+// union_fma: union = fma(w_b, h_b, S_a) - inter ; else (S_a + S_b) - inter.
+template <bool kEarlyOut>
+__device__ __forceinline__ bool ypp_suppresses(const float4 a, const float sa, const float4 b,
+                                               const float thr, const int union_fma)
+{
+    const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
+    const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
+    const float w = fmaxf(__fsub_rn(r, l), 0.0f), h = fmaxf(__fsub_rn(bt, t), 0.0f);
+    const float inter = __fmul_rn(w, h);
+    if (kEarlyOut && !(inter > 0.0f)) return false;   // iou is 0 or NaN: never > thr when thr >= 0
+    const float wb = __fsub_rn(b.z, b.x), hb = __fsub_rn(b.w, b.y);
+    float uni;
+    if (union_fma) uni = __fsub_rn(__fmaf_rn(wb, hb, sa), inter);
+    else           uni = __fsub_rn(__fadd_rn(sa, __fmul_rn(wb, hb)), inter);
+    return __fdiv_rn(inter, uni) > thr;
+}
+#endif  // __CUDACC__

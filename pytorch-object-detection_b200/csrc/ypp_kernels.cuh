@@ -1,0 +1,68 @@
+// Kernel parameter blocks and host launcher prototypes (internal to libypp).
+#pragma once
+#include "ypp_common.cuh"
+
+struct YppScaleParams {
+    const float* head;
+    int A, H, W, HW;
+    int box_base;        // first box index of this scale inside the image (cat order)
+    int vec;             // cells per thread: 4 when H*W % 4 == 0 and the head is 16 B aligned, else 1
+    int units;           // A*HW/vec work items per image
+    float aw[YPP_MAX_ANCHORS], ah[YPP_MAX_ANCHORS];
+    float sw, sh;
+};
+
+struct YppDecodeParams {
+    YppScaleParams sc[YPP_MAX_SCALES];
+    int tile_base[YPP_MAX_SCALES + 1];   // blockIdx.x ranges per scale
+    int n_scales, nc, C, N;
+    float conf;
+    int score_mode;
+    YppWs ws;
+};
+
+struct YppOrgParams {
+    YppWs ws;
+    int B, N, nc;
+    int offset_mode, union_mode;
+    float iou_thr;
+    int keys_in_smem;      // 1: sort in shared memory, 0: in place in global memory
+    int table_ints;        // 32 * nc
+};
+
+struct YppNmsParams {
+    YppWs ws;
+    int B, N, nc;
+    float iou_thr;
+    int union_mode;
+};
+
+struct YppGatherParams {
+    YppWs ws;
+    int B, N;
+    int* cand_count_out;
+    int* keep_count_out;
+    int* keep_idx;
+    float* det_rows;
+    int row_width;
+    long long det_capacity;
+    int* det_total;
+    float img_idx_base;
+    const float* src_rows;   // optional [B,N,6]: copy the class column verbatim (nms_rows entry)
+};
+
+int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st);
+int ypp_launch_decode_dense(const YppDecodeParams& p, int B, float* out, cudaStream_t st);
+int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const YppWs& ws, cudaStream_t st);
+int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st);
+int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st);
+int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st);
+int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem);
+
+int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
+                           float* out, int* gt_count, cudaStream_t st);
+int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);
+size_t ypp_map_ws_bytes(long long G, long long K, int nc);
+int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
+                   void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
+                   cudaStream_t st);

@@ -1,0 +1,276 @@
+"""Host side of the hot path: torch tensors in, stream-ordered C-ABI calls, torch tensors out.
+
+PyTorch is used for device memory (caching allocator), the current CUDA stream and, in
+ypp.dist, torch.distributed.  All arithmetic happens in libypp.so (csrc/*.cu).
+"""
+import ctypes
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import YppCfg, YppScale, check, lib
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
+    """One scratch buffer per (device, tag), grown on demand; safe because every consumer is
+    ordered on the current stream."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), tag)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def _check_head(t: torch.Tensor, name="head") -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or t.dim() != 4:
+        raise ValueError("%s must be a 4-d tensor [B, A*(5+nc), H, W]" % name)
+    if not t.is_cuda:
+        raise ValueError("%s must live on a CUDA device (ypp has no CPU path)" % name)
+    if t.dtype != torch.float32:
+        raise ValueError("%s must be float32, got %s" % (name, t.dtype))
+    return t if t.is_contiguous() else t.contiguous()
+
+
+@dataclass
+class PostResult:
+    """Device-side result of one batch; nothing here has synchronised with the host."""
+    det_rows: torch.Tensor            # [capacity, row_width], first det_total rows valid
+    det_total: torch.Tensor           # int32 [1]
+    keep_count: torch.Tensor          # int32 [B]
+    cand_count: torch.Tensor          # int32 [B]
+    keep_idx: Optional[torch.Tensor]  # int32 [B, N] (first keep_count[b] entries valid) or None
+    n_boxes: int
+
+    def rows(self) -> torch.Tensor:
+        """Valid rows (one host sync for the count)."""
+        return self.det_rows[: int(self.det_total.item())]
+
+    def per_image(self) -> List[torch.Tensor]:
+        counts = self.keep_count.tolist()
+        out, off = [], 0
+        for c in counts:
+            out.append(self.det_rows[off: off + c])
+            off += c
+        return out
+
+
+class PostProcessor:
+    """decode -> threshold/compact -> sort -> per-class NMS -> rows for a batch of heads.
+
+    anchors: pixels for kind="v3" (divided by the stride in float64, rounded to fp32 once, as
+    utils/yolov3_utils.py:31,40 does) or grid units for kind="v2" (utils/yolov2_utils.py:39).
+    Heads are consumed in list order with anchors[A*i : A*i+A] (utils/yolov3_utils.py:76-78).
+    Defaults reproduce what the reference computes when it runs on a CUDA device:
+    torchvision's CUDA heuristic for the coordinate trick and its fma-contracted union.
+    """
+
+    def __init__(self, num_classes, anchors, input_size, conf_threshold=0.25, iou_threshold=0.45,
+                 kind="v3", anchors_per_scale=None, offset_mode="auto_cuda", union_mode="fma",
+                 score_mode="obj", compare_in_double=None):
+        self.num_classes = int(num_classes)
+        self.anchors = [list(map(float, a)) for a in anchors]
+        self.input_size = input_size
+        self.conf_threshold = float(conf_threshold)
+        self.iou_threshold = float(iou_threshold)
+        self.kind = kind
+        if anchors_per_scale is None:
+            anchors_per_scale = len(self.anchors) if kind == "v2" else 3
+        self.A = int(anchors_per_scale)
+        self.offset_mode = _lib.OFFSET_MODES[offset_mode] if isinstance(offset_mode, str) else int(offset_mode)
+        self.union_mode = _lib.UNION_MODES[union_mode] if isinstance(union_mode, str) else int(union_mode)
+        self.score_mode = _lib.SCORE_MODES[score_mode] if isinstance(score_mode, str) else int(score_mode)
+        if compare_in_double is None:
+            compare_in_double = self.union_mode == _lib.UNION_SEPARATE   # CPU kernel semantics
+        self.iou_thr_eff = float(lib().ypp_effective_iou_thr(self.iou_threshold, int(bool(compare_in_double))))
+
+    # -- parameter blocks ------------------------------------------------------------------
+    def _cfg(self, B, n_scales):
+        return YppCfg(self.num_classes, int(B), int(n_scales), self.conf_threshold, self.iou_thr_eff,
+                      self.score_mode, self.offset_mode, self.union_mode)
+
+    def _scales(self, heads: Sequence[torch.Tensor]):
+        n = len(heads)
+        if n < 1 or n > _lib.YPP_MAX_SCALES:
+            raise ValueError("1..%d heads supported, got %d" % (_lib.YPP_MAX_SCALES, n))
+        arr = (YppScale * n)()
+        heads = [_check_head(h, "head %d" % i) for i, h in enumerate(heads)]
+        B = heads[0].shape[0]
+        n_boxes = 0
+        for i, h in enumerate(heads):
+            if h.shape[0] != B or h.device != heads[0].device:
+                raise ValueError("all heads must share batch size and device")
+            _, C, H, W = h.shape
+            an = self.anchors[self.A * i: self.A * i + self.A]
+            if len(an) != self.A:
+                raise ValueError("not enough anchors for head %d" % i)
+            if C != self.A * (5 + self.num_classes):
+                raise ValueError("head %d has %d channels, expected %d*(5+%d)" % (i, C, self.A, self.num_classes))
+            stride_h = self.input_size / H
+            stride_w = self.input_size / W
+            s = arr[i]
+            s.head = h.data_ptr()
+            s.A, s.H, s.W = self.A, H, W
+            for a, (w_, h_) in enumerate(an):
+                if self.kind == "v2":
+                    s.anchor_w[a], s.anchor_h[a] = w_, h_
+                else:
+                    s.anchor_w[a], s.anchor_h[a] = w_ / stride_w, h_ / stride_h
+            s.stride_w, s.stride_h = stride_w, stride_h
+            n_boxes += self.A * H * W
+        return arr, heads, B, n_boxes
+
+    # -- entry points ------------------------------------------------------------------------
+    def decode(self, heads: Sequence[torch.Tensor]) -> torch.Tensor:
+        """= decode_predictions per scale + torch.cat(dim=1): [B, n_boxes, 6]."""
+        arr, heads, B, n_boxes = self._scales(heads)
+        out = torch.empty((B, n_boxes, 6), dtype=torch.float32, device=heads[0].device)
+        cfg = self._cfg(B, len(heads))
+        with torch.cuda.device(heads[0].device):
+            check(lib().ypp_decode_dense(ctypes.byref(cfg), arr, _ptr(out), _stream()))
+        return out
+
+    def _outputs(self, B, n_boxes, device, row_width, want_keep_idx, out):
+        if out is not None:
+            return out
+        cap = B * n_boxes
+        return PostResult(
+            det_rows=torch.empty((cap, row_width), dtype=torch.float32, device=device),
+            det_total=torch.empty(1, dtype=torch.int32, device=device),
+            keep_count=torch.empty(B, dtype=torch.int32, device=device),
+            cand_count=torch.empty(B, dtype=torch.int32, device=device),
+            keep_idx=torch.empty((B, n_boxes), dtype=torch.int32, device=device) if want_keep_idx else None,
+            n_boxes=n_boxes)
+
+    def __call__(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
+                 out: Optional[PostResult] = None) -> PostResult:
+        arr, heads, B, n_boxes = self._scales(heads)
+        dev = heads[0].device
+        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
+        cfg = self._cfg(B, len(heads))
+        L = lib()
+        nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
+        ws = _workspace(nbytes, dev, "post")
+        with torch.cuda.device(dev):
+            check(L.ypp_postprocess(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                    res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                    float(img_idx_base), _stream()))
+        return res
+
+    def staged(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
+               stages=("decode", "sort", "nms")) -> PostResult:
+        """Same chain through the three separate C-ABI stages (used to time / profile D1 alone)."""
+        arr, heads, B, n_boxes = self._scales(heads)
+        dev = heads[0].device
+        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, None)
+        cfg = self._cfg(B, len(heads))
+        L = lib()
+        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, "post")
+        with torch.cuda.device(dev):
+            if "decode" in stages:
+                check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
+            if "sort" in stages:
+                check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
+            if "nms" in stages:
+                check(L.ypp_nms(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                float(img_idx_base), _stream()))
+        return res
+
+    def nms_rows(self, rows: torch.Tensor, img_idx_base=0, row_width=6, want_keep_idx=False) -> PostResult:
+        """nms_v3 on decoded rows [B, N, 6] (or [N, 6]); class ids must be integers in [0, nc)."""
+        if rows.dim() == 2:
+            rows = rows.unsqueeze(0)
+        if rows.dim() != 3 or rows.shape[-1] != 6:
+            raise ValueError("rows must be [B, N, 6] or [N, 6]")
+        if not rows.is_cuda or rows.dtype != torch.float32:
+            raise ValueError("rows must be a float32 CUDA tensor")
+        rows = rows.contiguous()
+        B, N, _ = rows.shape
+        dev = rows.device
+        if N == 0:
+            z = torch.zeros
+            return PostResult(z((0, row_width), device=dev), z(1, dtype=torch.int32, device=dev),
+                              z(B, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                              z((B, 0), dtype=torch.int32, device=dev) if want_keep_idx else None, 0)
+        res = self._outputs(B, N, dev, row_width, want_keep_idx, None)
+        cfg = self._cfg(B, 1)
+        L = lib()
+        ws = _workspace(L.ypp_workspace_bytes(B, N, self.num_classes), dev, "post")
+        with torch.cuda.device(dev):
+            check(L.ypp_nms_rows(ctypes.byref(cfg), _ptr(rows), N, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                 _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                 res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                 float(img_idx_base), _stream()))
+        return res
+
+
+# ------------------------------------------------------------------------------------ mAP side
+
+def target_rows(annot: torch.Tensor, input_size, img_idx_base=0):
+    """[B,T,5] padded annots -> ([B*T,7] buffer, int32 count[1]); get_target_boxes_for_map +
+    the img_idx column (utils/yolo_utils.py:682-710, utils/yolov3_utils.py:134-137)."""
+    if annot.dim() != 3 or annot.shape[-1] != 5:
+        raise ValueError("annot must be [B, max_num_annots, 5]")
+    if not annot.is_cuda:
+        raise ValueError("annot must be a CUDA tensor")
+    annot = annot.to(torch.float32).contiguous()
+    B, T, _ = annot.shape
+    out = torch.empty((B * T, 7), dtype=torch.float32, device=annot.device)
+    cnt = torch.empty(1, dtype=torch.int32, device=annot.device)
+    with torch.cuda.device(annot.device):
+        check(lib().ypp_target_rows(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(out),
+                                    _ptr(cnt), _stream()))
+    return out, cnt
+
+
+def box_iou(box1: torch.Tensor, box2: torch.Tensor) -> torch.Tensor:
+    """utils/metrics.py:233-255: xyxy [N,4] x [M,4] -> [N,M]."""
+    if not (box1.is_cuda and box2.is_cuda):
+        raise ValueError("box_iou needs CUDA tensors")
+    a = box1.to(torch.float32).contiguous()
+    b = box2.to(torch.float32).contiguous()
+    out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
+    with torch.cuda.device(a.device):
+        check(lib().ypp_box_iou(_ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _stream()))
+    return out
+
+
+def map_match(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, iou_threshold=0.5,
+              want_tp=True):
+    """mean_average_precision / metrics_per_class on the GPU.
+    Returns (map float32[1], per_class float32[nc,4] = AP,TP,FP,FN, tp uint8[K] or None)."""
+    gt = true_boxes.reshape(-1, 7).to(torch.float32).contiguous()
+    det = pred_boxes.reshape(-1, 7).to(torch.float32).contiguous()
+    if not (gt.is_cuda and det.is_cuda):
+        raise ValueError("map_match needs CUDA tensors")
+    dev = det.device
+    G, K = gt.shape[0], det.shape[0]
+    L = lib()
+    ws = _workspace(L.ypp_map_workspace_bytes(G, K, int(num_classes)), dev, "map")
+    m = torch.empty(1, dtype=torch.float32, device=dev)
+    pc = torch.empty((int(num_classes), 4), dtype=torch.float32, device=dev)
+    tp = torch.empty(max(K, 1), dtype=torch.uint8, device=dev) if want_tp else None
+    with torch.cuda.device(dev):
+        check(L.ypp_map_match(_ptr(gt), G, _ptr(det), K, int(num_classes), float(iou_threshold), _ptr(ws),
+                              ws.numel(), _ptr(tp), _ptr(pc), _ptr(m), _stream()))
+    return m, pc, (tp[:K] if tp is not None else None)
+
+
+def launch_count(reset=False) -> int:
+    return int(lib().ypp_launch_count(int(bool(reset))))

@@ -1,0 +1,103 @@
+"""CPU: the C-ABI library loads and exports every symbol include/ypp.h declares; host-side
+logic (parameter blocks, synthetic workloads, error behaviour) -- no kernel is launched."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "ypp.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ypp_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from ypp import _lib
+    assert os.path.exists(_lib.LIB_PATH), "run __graft_entry__.build() first"
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    syms = _declared_symbols()
+    assert len(syms) >= 16
+    for s in syms:
+        assert hasattr(L, s), "libypp.so does not export %s" % s
+    assert sorted(_lib.EXPORTS) == syms
+
+
+def test_host_only_entry_points(oracle):
+    from ypp import _lib
+    L = _lib.lib()
+    assert L.ypp_version() >= 100
+    assert L.ypp_workspace_bytes(64, 10647, 20) > 64 * 10647 * (8 + 16 + 16 + 4 + 1)
+    assert L.ypp_workspace_bytes(0, 10647, 20) == 0
+    assert L.ypp_map_workspace_bytes(100, 1000, 20) > 0
+    for thr in (0.45, 0.3, 0.5, 0.7, 0.1):
+        for dbl in (0, 1):
+            assert float(L.ypp_effective_iou_thr(thr, dbl)) == oracle.effective_thr(thr, dbl)
+
+
+def test_struct_layout_matches_header():
+    from ypp import _lib
+    # ypp_scale: pointer + 3 ints + 16 floats + 2 floats, 8-byte aligned; ypp_cfg: 8 x 4 bytes
+    assert ctypes.sizeof(_lib.YppScale) == 96
+    assert ctypes.sizeof(_lib.YppCfg) == 32
+
+
+def test_errors_without_gpu():
+    from ypp import engine
+    pp = engine.PostProcessor(20, [[10, 13], [16, 30], [33, 23]], 416)
+    with pytest.raises(ValueError):
+        pp([torch.zeros(1, 75, 13, 13)])                 # CPU tensor: there is no CPU path
+    with pytest.raises(ValueError):
+        pp.decode([torch.zeros(75, 13, 13)])
+    with pytest.raises(ValueError):
+        engine.box_iou(torch.zeros(2, 4), torch.zeros(3, 4))
+
+
+def test_missing_extension_fails_loudly(monkeypatch):
+    from ypp import _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libypp.so")
+    with pytest.raises(ImportError):
+        _lib.lib()
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "pytorch-object-detection_b200")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(d, f)).read()
+                assert "oracle" not in text.lower(), os.path.join(d, f)
+
+
+def test_synth_is_deterministic_and_shaped():
+    from ypp import synth
+    w = synth.WORKLOADS["yolov3_416_voc_b64"]
+    h1 = synth.make_heads(2, w["nc"], w["grids"], g=3)
+    h2 = synth.make_heads(2, w["nc"], w["grids"], g=3)
+    assert [tuple(h.shape) for h in h1] == [(2, 75, 52, 52), (2, 75, 26, 26), (2, 75, 13, 13)]
+    assert all(torch.equal(a, b) for a, b in zip(h1, h2))
+    assert synth.boxes_per_image(w["grids"]) == 10647
+    assert synth.head_bytes_per_image(w["nc"], w["grids"]) == 1064700
+    assert synth.head_bytes_per_image(80, [76, 38, 19]) == 7732620
+    a = synth.make_annots(8, 20, g=1)
+    assert a.shape == (8, 8, 5) and (a[0, 2:] == -1).all()
+    dense = torch.sigmoid(h1[0].view(2, 3, 25, 52, 52)[:, :, 4]) > .25
+    assert 0.7 < dense.float().mean() < 0.85
+
+
+def test_scale_parameters_follow_the_reference_rounding(oracle):
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416)
+    # same python-float division + single fp32 rounding as utils/yolov3_utils.py:29-31,40
+    for i, H in enumerate([52, 26, 13]):
+        aw, ah, sw, sh = oracle.scale_params_v3(synth.YOLOV3_ANCHORS[3 * i: 3 * i + 3], 416, H, H)
+        for a, (w_, h_) in enumerate(synth.YOLOV3_ANCHORS[3 * i: 3 * i + 3]):
+            assert ctypes.c_float(w_ / (416 / H)).value == float(aw[a])
+            assert ctypes.c_float(h_ / (416 / H)).value == float(ah[a])
+        assert float(sw) == 416 / H

@@ -1,0 +1,114 @@
+"""CPU: the oracle (oracle/ypp_oracle.c) against the reference's own outputs (tests/golden/).
+
+These fixtures were produced by tests/golden/make_golden.py importing the UNMODIFIED reference;
+this is what pins the oracle.  Tolerances: decoded coordinates/scores 1e-5 relative (fp32,
+different libm), everything index-like bit-exact.
+"""
+import numpy as np
+import pytest
+
+import util
+
+
+@pytest.mark.parametrize("name", util.HEAD_CASES)
+def test_decode_and_nms_against_reference(oracle, name):
+    g = util.load(name)
+    heads = [h.numpy() for h in util.case_heads(g)]
+    nc, A, S = int(g["nc"]), int(g["A"]), int(g["input_size"])
+    anchors = util.case_anchors(g)
+    if str(g["kind"]) == "v2":
+        rows = oracle.decode_predictions_v2(heads[0], nc, anchors, S)
+    else:
+        rows = oracle.decode_multi_scale(heads, nc, anchors, S, A)
+    stride = int(g["rows_stride"])
+    ref = g["rows"]
+    sub = rows[:, ::stride]
+    assert sub.shape == ref.shape
+    assert util.rel_err(sub[..., :5], ref[..., :5]).max() <= 1e-5          # tolerance: 1e-5 relative
+    assert (sub[..., 5] != ref[..., 5]).sum() <= 2                          # argmax near-ties only
+    conf = float(g["conf"])
+    for b in range(int(g["batch"])):
+        ncand = int(g["cand_count"][b])
+        keep, onc = oracle.nms_v3_indices(rows[b], conf, 0.45, offset_mode=oracle.OFFSET_AUTO_CPU,
+                                          union_mode=oracle.UNION_SEPARATE)
+        k_ref = g["keep"][b, : int(g["keep_count"][b])]
+        # end-to-end on the oracle's own decoded rows: identical unless a score sits within an ulp
+        # of a decision; require exact equality here (holds for these seeds)
+        assert onc == ncand
+        assert np.array_equal(util.canon(keep, rows[b]), util.canon(k_ref, rows[b]))
+
+
+def test_adversarial_nms(oracle):
+    g = util.load("nms_adversarial")
+    names = sorted({k.rsplit("__", 1)[0] for k in g.files})
+    assert len(names) >= 15
+    for n in names:
+        rows, keep = g[n + "__rows"], g[n + "__keep"]
+        conf, iou = g[n + "__conf_iou"]
+        om, um = g[n + "__mode"]
+        got, _ = oracle.nms_v3_indices(rows, conf, iou, offset_mode=int(om), union_mode=int(um))
+        assert np.array_equal(got, keep), n
+        # and through the auto heuristic the CPU build of torchvision uses
+        got2, _ = oracle.nms_v3_indices(rows, conf, iou, offset_mode=oracle.OFFSET_AUTO_CPU, union_mode=int(um))
+        assert np.array_equal(got2, keep), n
+
+
+def test_trick_vs_vanilla_differ_on_cross_class(oracle):
+    g = util.load("nms_adversarial")
+    rows = g["trick_cross_class__rows"]
+    t, _ = oracle.nms_v3_indices(rows, .25, .45, offset_mode=oracle.OFFSET_TRICK)
+    v, _ = oracle.nms_v3_indices(rows, .25, .45, offset_mode=oracle.OFFSET_NONE)
+    assert len(t) == 2 and len(v) == 3
+
+
+def test_decode_edges(oracle):
+    g = util.load("decode_edges")
+    rows = oracle.decode_predictions_v3(g["head"], int(g["nc"]), g["anchors"].tolist(), int(g["input_size"]))
+    ref = g["rows"]
+    assert np.array_equal(np.isinf(rows), np.isinf(ref))
+    assert util.rel_err(rows[..., :5], ref[..., :5]).max() <= 1e-5
+    assert np.array_equal(rows[..., 5], ref[..., 5])
+
+
+def test_wrappers(oracle):
+    from ypp import synth
+    g = util.load("wrappers")
+    heads = synth.make_heads(1, 20, [52, 26, 13], g=5, mu_obj=-3.0)
+    assert [util.crc(h.numpy()) for h in heads] == [int(x) for x in g["v3_head_crc"]]
+    rows = oracle.decode_multi_scale([h.numpy() for h in heads], 20, synth.YOLOV3_ANCHORS, 416)[0]
+    out = oracle.nms_v3(rows, 0.25)
+    assert out.shape == g["v3_rows"].shape and np.allclose(out, g["v3_rows"], rtol=1e-5, atol=0)
+    h2 = synth.make_heads(1, 20, [13], A=5, g=6, mu_obj=-1.0)
+    out2 = oracle.nms_v3(oracle.decode_predictions_v2(h2[0].numpy(), 20, synth.YOLOV2_SCALED_ANCHORS, 416)[0], 0.25)
+    assert out2.shape == g["v2_rows"].shape and np.allclose(out2, g["v2_rows"], rtol=1e-5, atol=0)
+
+
+def test_map_against_reference(oracle):
+    g = util.load("map_cases")
+    annots = g["acc_annots"]
+    gt = np.concatenate([oracle.get_target_rows(a, 416, 8 * i) for i, a in enumerate(annots)])
+    assert np.array_equal(gt, g["acc_gt_rows"])
+    m, tp, pc = oracle.mean_average_precision(g["acc_gt_rows"], g["acc_det_rows"], 20, 0.5, True)
+    assert abs(float(m) - float(g["acc_map"])) <= 1e-6                     # tolerance: 1e-6 absolute
+    assert np.allclose(pc, g["acc_per_class"], atol=1e-6)
+    m, tp, pc = oracle.mean_average_precision(g["syn_gt"], g["syn_det"], int(g["syn_nc"]), 0.5, True)
+    assert abs(float(m) - float(g["syn_map"])) <= 1e-6
+    assert np.allclose(pc, g["syn_per_class"], atol=1e-6)
+    assert np.array_equal(pc[:, 1:], g["syn_per_class"][:, 1:])            # TP/FP/FN counts exact
+    assert np.array_equal(tp, g["syn_tp_oracle"])
+    assert float(oracle.mean_average_precision(g["syn_gt"], np.zeros((0, 7), np.float32), int(g["syn_nc"]))) == 0.0
+
+
+def test_iou_helpers(oracle):
+    g = util.load("iou_cases")
+    with np.errstate(invalid="ignore"):
+        assert np.array_equal(oracle.box_iou(g["a"], g["b"]), g["box_iou"], equal_nan=True)   # bit-exact
+    assert np.array_equal(oracle.bbox_iou_cxcywh(g["c1"], g["c2"]), g["bbox_iou"])
+
+
+def test_effective_threshold(oracle):
+    # .45 rounds DOWN in fp32, .3 rounds UP: only the latter changes under the CPU kernel's double compare
+    f45, f3 = np.float32(0.45), np.float32(0.3)
+    assert oracle.effective_thr(0.45, True) == float(f45) == oracle.effective_thr(0.45, False)
+    assert oracle.effective_thr(0.3, False) == float(f3)
+    assert oracle.effective_thr(0.3, True) == float(np.nextafter(f3, np.float32(-1)))

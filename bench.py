@@ -1,0 +1,421 @@
+#!/usr/bin/env python
+"""bench.py -- post-processed images/sec (decode + NMS) of the YOLO post-processing hot path.
+
+    python bench.py --gpus N --steps K --warmup W                 (ours; N>1 under torchrun)
+    python bench.py --impl reference --gpus N --steps K --warmup W  (the reference algorithm on the host cores)
+
+A step = one pass of the hot path over one batch of synthetic heads (default workload:
+YOLOv3-416 VOC, 3 scales, batch 64, dense regime: ~77% of the 10,647 boxes/image pass conf .25).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "pytorch-object-detection_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+METRIC = "post-processed images/sec (decode+NMS)"
+UNIT = "images/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="yolov3_416_voc_b64")
+    ap.add_argument("--regime", default="dense", choices=["dense", "sparse"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the sparse-regime and mAP epoch extras")
+    ap.add_argument("--ring", type=int, default=4, help="distinct input batches cycled through (> L2 in total)")
+    return ap.parse_args()
+
+
+def workload_config(args, w, n_gpus):
+    from ypp import synth
+    return {
+        "workload": args.workload, "regime": args.regime,
+        "heads": ["[%d,%d,%d,%d]" % (w["batch"], w["A"] * (5 + w["nc"]), g, g) for g in w["grids"]],
+        "batch_per_gpu": w["batch"], "global_batch": w["batch"] * n_gpus,
+        "boxes_per_image": synth.boxes_per_image(w["grids"], w["A"]), "num_classes": w["nc"],
+        "conf_threshold": w["conf"], "iou_threshold": 0.45,
+        "parallelism": "image-sharded x%d, no data-path collective" % n_gpus,
+        "l2_policy": "inputs larger than L2: ring of %d distinct batches (%.0f MB) cycled" % (
+            args.ring, args.ring * w["batch"] * synth.head_bytes_per_image(w["nc"], w["grids"], w["A"]) / 1e6),
+    }
+
+
+# ------------------------------------------------------------------------------------ clocks
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.idx = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm_sorted = sorted(sm)
+        return {"sm_mhz": sm_sorted[len(sm_sorted) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(pw)}
+
+
+# ------------------------------------------------------------------------------------ reference arm
+
+def oracle_step(O, heads_np, w, anchors):
+    """decode_predictions (+cat) and per-image nms_v3 with torchvision-CPU semantics, all host threads."""
+    if w["kind"] == "v2":
+        rows = O.decode_predictions_v2(heads_np[0], w["nc"], anchors, w["input_size"])
+    else:
+        rows = O.decode_multi_scale(heads_np, w["nc"], anchors, w["input_size"], w["A"])
+    keep, kc, cc = O.nms_v3_batch(rows, w["conf"], 0.45, offset_mode=O.OFFSET_AUTO_CPU, union_mode=O.UNION_SEPARATE)
+    return int(kc.sum()), int(cc.sum())
+
+
+def cpu_baseline(args, w, anchors, sample_images, budget_s=12.0, max_reps=3):
+    """The oracle port of the reference algorithm timed on this box's host cores, bounded sample."""
+    from oracle import oracle as O
+    from ypp import synth
+    O.build()
+    mu = 0.0 if args.regime == "dense" else -5.0
+    heads = [h.numpy() for h in synth.make_heads(sample_images, w["nc"], w["grids"], A=w["A"], g=1000, mu_obj=mu)]
+    oracle_step(O, [h[:2] for h in heads], w, anchors)        # warm the thread pool
+    best, reps, t_all = None, 0, time.perf_counter()
+    while reps < max_reps and (time.perf_counter() - t_all) < budget_s:
+        t0 = time.perf_counter()
+        oracle_step(O, heads, w, anchors)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+        reps += 1
+    return {"value": sample_images / best, "unit": UNIT, "cores": O.num_threads(), "kind": "port",
+            "sample": "%d images of %s (%s regime), oracle/ypp_oracle.c decode + per-image nms_v3 "
+                      "(torchvision-CPU semantics), OpenMP over images, best of %d" % (
+                          sample_images, args.workload, args.regime, reps)}
+
+
+def run_reference(args):
+    from oracle import oracle as O
+    from ypp import synth
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    O.build()
+    w = synth.WORKLOADS[args.workload]
+    anchors = synth.workload_anchors(w)
+    sample = 16
+    mu = 0.0 if args.regime == "dense" else -5.0
+    ring = [[h.numpy() for h in synth.make_heads(sample, w["nc"], w["grids"], A=w["A"], g=2000 + i, mu_obj=mu)]
+            for i in range(2)]
+    for i in range(args.warmup):
+        oracle_step(O, ring[i % 2], w, anchors)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        oracle_step(O, ring[i % 2], w, anchors)
+    dt = time.perf_counter() - t0
+    val = sample * args.steps / dt
+    desc = ("%d images of %s (%s regime) per step; oracle/ypp_oracle.c (C restatement of decode_predictions + "
+            "nms_v3/torchvision-CPU; the Python reference cannot travel to this box), OpenMP over images" % (
+                sample, args.workload, args.regime))
+    cfg = workload_config(args, w, args.gpus)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": cfg, "gpu_launches": 0,
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": O.num_threads(), "kind": "port", "sample": desc},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------ our arm
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from ypp import engine, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    w = synth.WORKLOADS[args.workload]
+    anchors = synth.workload_anchors(w)
+    B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
+    mu = 0.0 if args.regime == "dense" else -5.0
+    pp = engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A)
+    host_ring = [synth.make_heads(B, nc, grids, A=A, g=rank * 64 + i, mu_obj=mu) for i in range(args.ring)]
+    ring = [[h.to(dev) for h in hs] for hs in host_ring]
+    n_boxes = synth.boxes_per_image(grids, A)
+    head_bytes = synth.head_bytes_per_image(nc, grids, A)
+    res = pp(ring[0], want_keep_idx=False)            # preallocated outputs reused by every step
+    torch.cuda.synchronize()
+    K, W = args.steps, max(args.warmup, 3)
+
+    # ---- value: K steps, inputs resident in HBM, CUDA events on the launching stream
+    for i in range(W):
+        pp(ring[i % args.ring], out=res)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    if sampler:
+        sampler.start()
+    engine.launch_count(True)
+    e0.record()
+    for i in range(K):
+        pp(ring[i % args.ring], out=res)
+    e1.record()
+    torch.cuda.synchronize()
+    launches = engine.launch_count(True)
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    # keep the GPU busy a little longer so that the 200 ms sampler sees clocks under load
+    t_end = time.time() + 1.0
+    while time.time() < t_end:
+        pp(ring[0], out=res)
+    torch.cuda.synchronize()
+    clocks = sampler.stop() if sampler else None
+    value = world * B * K / (ms_total * 1e-3)
+    cand_per_img = float(res.cand_count.float().mean().item())
+    kept_per_img = float(res.keep_count.float().mean().item())
+
+    # ---- roofline of the dominant HBM kernel: D1 (decode + threshold + compaction) alone
+    for i in range(W):
+        pp.staged(ring[i % args.ring], stages=("decode",))
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(K):
+        pp.staged(ring[i % args.ring], stages=("decode",))
+    e1.record()
+    torch.cuda.synchronize()
+    d1_ms = e0.elapsed_time(e1) / K
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    alg_bytes = B * (head_bytes + 28.0 * cand_per_img)
+    achieved = alg_bytes / (d1_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "d1_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(args.workload + ":" + args.regime)
+        except Exception:
+            traffic = None
+    roofline = {"kernel": "ypp_decode_compact_kernel (D1)", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": d1_ms,
+                "bytes_per_image": "4*sum_s A(5+nc)HW + 28*n_cand = %d + 28*%.0f" % (head_bytes, cand_per_img)}
+
+    # ---- stage split (CUDA events per stage, same inputs)
+    stage_ms = {}
+    for name, stages in (("sort", ("sort",)), ("nms_gather", ("nms",))):
+        pp.staged(ring[0], stages=("decode", "sort"))
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(5):
+            pp.staged(ring[0], stages=stages)
+        e1.record()
+        torch.cuda.synchronize()
+        stage_ms[name] = e0.elapsed_time(e1) / 5
+    stage_ms["decode_compact"] = d1_ms
+
+    # ---- e2e: host (pinned) heads -> device, chain, counts + rows back to the host, every step
+    pinned = [[h.pin_memory() for h in hs] for hs in host_ring[:2]]
+    dbuf = [[torch.empty_like(h, device=dev) for h in hs] for hs in host_ring[:2]]
+    outs = [pp(ring[0]), pp(ring[0])]
+    host_cnt = torch.empty(B + 1, dtype=torch.int32).pin_memory()
+    host_rows = torch.empty((B * n_boxes, 7), dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream(device=dev)
+    main = torch.cuda.current_stream()
+    copied = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    d2h_bytes = 0
+
+    def e2e_loop(n):
+        nonlocal d2h_bytes
+        d2h_bytes = 0
+        for s in (0,):
+            with torch.cuda.stream(copy_stream):
+                for hd, hp in zip(dbuf[0], pinned[0]):
+                    hd.copy_(hp, non_blocking=True)
+                copied[0].record(copy_stream)
+        for i in range(n):
+            cur, nxt = i & 1, (i + 1) & 1
+            if i + 1 < n:                           # prefetch the next batch while this one computes
+                with torch.cuda.stream(copy_stream):
+                    if i >= 1:
+                        copy_stream.wait_event(consumed[nxt])
+                    for hd, hp in zip(dbuf[nxt], pinned[nxt]):
+                        hd.copy_(hp, non_blocking=True)
+                    copied[nxt].record(copy_stream)
+            main.wait_event(copied[cur])
+            r = pp(dbuf[cur], out=outs[cur])
+            consumed[cur].record(main)
+            host_cnt[:B].copy_(r.keep_count, non_blocking=True)
+            host_cnt[B:].copy_(r.det_total, non_blocking=True)
+            main.synchronize()                      # the user needs the count to size the row read
+            tot = int(host_cnt[B])
+            host_rows[:tot].copy_(r.det_rows[:tot], non_blocking=True)
+            main.synchronize()
+            d2h_bytes += 4 * (B + 1) + 28 * tot
+
+    e2e_loop(W)
+    barrier()
+    e0.record()
+    e2e_loop(K)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+    e2e = {"value": world * B * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * head_bytes,
+           "d2h_bytes_per_step": d2h_bytes // K, "ms_per_step": e2e_ms / K,
+           "how": "pinned host heads -> H2D on a copy stream (double buffered) -> ypp_postprocess -> "
+                  "D2H of keep counts + kept rows [K,7]; all inside the timed region"}
+
+    extras = {}
+    if not args.no_extras:
+        extras = run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args, w, anchors, sample_images=min(B, 64))
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+                "cpu_baseline": cpu, "stage_ms": stage_ms,
+                "per_image": {"candidates": cand_per_img, "kept": kept_per_img}}
+        line.update(extras)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks):
+    """Reported beside the headline: the sparse (deployment-like) regime, and the mAP epoch end
+    (all-gather of detections over NCCL + GPU TP/FP matching) on sparse-regime detections."""
+    from ypp.dist import gather_rows
+    B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
+    out = {}
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_ring = args.ring
+    sparse = [[h.to(dev) for h in synth.make_heads(B, nc, grids, A=A, g=500 + rank * 64 + i, mu_obj=-5.0)]
+              for i in range(n_ring)]
+    res = pp(sparse[0])
+    for i in range(3):
+        pp(sparse[i % n_ring], out=res)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        pp(sparse[i % n_ring], out=res)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    out["sparse_regime"] = {"value": world * B * args.steps / (ms * 1e-3), "unit": UNIT,
+                            "candidates_per_image": float(res.cand_count.float().mean().item()),
+                            "ms_per_step": ms / args.steps}
+    # mAP epoch: n_batches of B images per rank, detections accumulated on device, then gather + match
+    n_batches = 8
+    dets, gts = [], []
+    for i in range(n_batches):
+        r = pp(sparse[i % n_ring], img_idx_base=(rank * n_batches + i) * B)
+        rows = r.rows().clone()
+        dets.append(rows)
+        an = synth.make_annots(B, nc, g=rank * n_batches + i).to(dev)
+        g_rows, g_cnt = engine.target_rows(an, w["input_size"], (rank * n_batches + i) * B)
+        gts.append(g_rows[: int(g_cnt.item())].clone())
+    det_local, gt_local = torch.cat(dets), torch.cat(gts)
+    barrier()
+    e0.record()
+    det_all = gather_rows(det_local)
+    gt_all = gather_rows(gt_local)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_gather = max_over_ranks(e0.elapsed_time(e1))
+    engine.map_match(gt_all, det_all, nc)
+    torch.cuda.synchronize()
+    e0.record()
+    m, pc, _ = engine.map_match(gt_all, det_all, nc)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_match = max_over_ranks(e0.elapsed_time(e1))
+    out["map_epoch"] = {"images": world * n_batches * B, "detections": int(det_all.shape[0]),
+                        "ground_truths": int(gt_all.shape[0]), "allgather_ms": ms_gather, "match_ms": ms_match,
+                        "mAP": float(m.item()), "detections_per_s": det_all.shape[0] / (ms_match * 1e-3)}
+    return out
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_ours(a))

@@ -3,7 +3,7 @@ exchange step of the path -- a variable-length all-gather of detection / ground-
 the mAP@.5 matching.  decode -> sort -> NMS needs no communication.
 
 The reference never gathers (its metric state is rank-local, module/yolov3_detector.py:45-47);
-the parity oracle for this module is the single-process result over all images.
+parity for this module is judged against the single-process result over all images.
 Works with backend "nccl" (CUDA tensors, NVLink/NVSwitch) and "gloo" (CPU tensors, tests).
 """
 from typing import Optional, Tuple

@@ -61,51 +61,57 @@ template <> struct VecLoad<4> {
     }
 };
 
-// decode V consecutive cells of one anchor.  Returns box/score/cls for the lanes in `need`.
+// class-plane sweep for V consecutive cells: software-pipelined, 4 planes (4 x 16 B per lane
+// when V = 4) in flight while the previous 4 are folded into the running arg-max.
+template <int V>
+__device__ __forceinline__ void class_sweep(const float* __restrict__ cp, int HW, int nc, ClsTrack (&tr)[V])
+{
+#pragma unroll
+    for (int v = 0; v < V; ++v) cls_init(tr[v]);
+    float cur[4][V], nxt[4][V];
+    int c = 0;
+    if (nc >= 4) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) VecLoad<V>::ld(cp + (size_t)k * HW, cur[k]);
+        for (; c + 8 <= nc; c += 4) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) VecLoad<V>::ld(cp + (size_t)(c + 4 + k) * HW, nxt[k]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int v = 0; v < V; ++v) cls_push(tr[v], cur[k][v], c + k);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int v = 0; v < V; ++v) cur[k][v] = nxt[k][v];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int v = 0; v < V; ++v) cls_push(tr[v], cur[k][v], c + k);
+        c += 4;
+    }
+    for (; c < nc; ++c) {
+        float l0[V];
+        VecLoad<V>::ld(cp + (size_t)c * HW, l0);
+#pragma unroll
+        for (int v = 0; v < V; ++v) cls_push(tr[v], l0[v], c);
+    }
+}
+
+// decode V consecutive cells of one anchor from the already loaded t0..t3 planes and the class
+// tracks.  Fills box/score/cls for the lanes in `need`.
 template <int V>
 __device__ __forceinline__ void decode_cells(const YppDecodeParams& p, const YppScaleParams& s,
                                              const float* __restrict__ base /* channel 0, cell0 */,
-                                             int a, int cell0, unsigned need, const float (&score_obj)[V],
+                                             int a, int cell0, unsigned need,
+                                             const float (&t0)[V], const float (&t1)[V], const float (&t2)[V],
+                                             const float (&t3)[V], const ClsTrack (&tr)[V],
+                                             const float (&score_obj)[V],
                                              float4 (&box)[V], float (&score)[V], int (&cls)[V])
 {
     const int HW = s.HW;
-    float t0[V], t1[V], t2[V], t3[V];
-    VecLoad<V>::ld(base, t0);
-    VecLoad<V>::ld(base + HW, t1);
-    VecLoad<V>::ld(base + 2 * (size_t)HW, t2);
-    VecLoad<V>::ld(base + 3 * (size_t)HW, t3);
-
-    ClsTrack tr[V];
-#pragma unroll
-    for (int v = 0; v < V; ++v) cls_init(tr[v]);
     const int nc = p.nc;
-    if (nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) {
-        const float* cp = base + 5 * (size_t)HW;
-        int c = 0;
-        for (; c + 4 <= nc; c += 4) {
-            float l0[V], l1[V], l2[V], l3[V];
-            VecLoad<V>::ld(cp, l0);
-            VecLoad<V>::ld(cp + HW, l1);
-            VecLoad<V>::ld(cp + 2 * (size_t)HW, l2);
-            VecLoad<V>::ld(cp + 3 * (size_t)HW, l3);
-#pragma unroll
-            for (int v = 0; v < V; ++v) {
-                cls_push(tr[v], l0[v], c);
-                cls_push(tr[v], l1[v], c + 1);
-                cls_push(tr[v], l2[v], c + 2);
-                cls_push(tr[v], l3[v], c + 3);
-            }
-            cp += 4 * (size_t)HW;
-        }
-        for (; c < nc; ++c) {
-            float l0[V];
-            VecLoad<V>::ld(cp, l0);
-#pragma unroll
-            for (int v = 0; v < V; ++v) cls_push(tr[v], l0[v], c);
-            cp += HW;
-        }
-    }
-
     const float aw = s.aw[a], ah = s.ah[a];
     int y = cell0 / s.W;
     int x = cell0 - y * s.W;
@@ -224,10 +230,17 @@ __device__ __forceinline__ void decode_compact_tile(const YppDecodeParams& p, co
     const int cell0 = valid ? (u - a * upp) * V : 0;
     const float* base = s.head + ((size_t)(b * s.A + a) * p.C) * s.HW + cell0;
 
-    float obj[V], sobj[V];
+    // objectness and the four box planes are fetched together (one round trip); the nc class
+    // planes only when some lane of the warp holds a candidate
+    float obj[V], sobj[V], t0[V], t1[V], t2[V], t3[V];
     unsigned pass = 0;
     if (valid) {
-        VecLoad<V>::ld(base + 4 * (size_t)s.HW, obj);
+        const size_t HW = s.HW;
+        VecLoad<V>::ld(base + 4 * HW, obj);
+        VecLoad<V>::ld(base, t0);
+        VecLoad<V>::ld(base + HW, t1);
+        VecLoad<V>::ld(base + 2 * HW, t2);
+        VecLoad<V>::ld(base + 3 * HW, t3);
 #pragma unroll
         for (int v = 0; v < V; ++v) {
             sobj[v] = ypp_sigmoid(obj[v]);                       // yolov3_utils.py:50
@@ -237,10 +250,15 @@ __device__ __forceinline__ void decode_compact_tile(const YppDecodeParams& p, co
     float4 box[V];
     float score[V];
     int cls[V];
-    // warp-uniform: skip the 4+nc other planes when no lane of the warp has a candidate
     if (__any_sync(YPP_FULL_MASK, pass != 0)) {
         if (pass) {
-            decode_cells<V>(p, s, base, a, cell0, pass, sobj, box, score, cls);
+            ClsTrack tr[V];
+            if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep<V>(base + 5 * (size_t)s.HW, s.HW, p.nc, tr);
+            else {
+#pragma unroll
+                for (int v = 0; v < V; ++v) cls_init(tr[v]);
+            }
+            decode_cells<V>(p, s, base, a, cell0, pass, t0, t1, t2, t3, tr, sobj, box, score, cls);
             if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) {
 #pragma unroll
                 for (int v = 0; v < V; ++v)
@@ -251,7 +269,7 @@ __device__ __forceinline__ void decode_compact_tile(const YppDecodeParams& p, co
     compact_store<V>(p.ws, p.N, b, sm, pass, box, score, cls, s.box_base + a * s.HW + cell0);
 }
 
-__global__ void __launch_bounds__(YPP_DECODE_THREADS)
+__global__ void __launch_bounds__(YPP_DECODE_THREADS, YPP_DECODE_MINB)
 ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p)
 {
     __shared__ CompactSmem sm;
@@ -282,12 +300,20 @@ ypp_decode_dense_kernel(const __grid_constant__ YppDecodeParams p, float* __rest
     const int a = u / s.HW;
     const int cell = u - a * s.HW;
     const float* base = s.head + ((size_t)(b * s.A + a) * p.C) * s.HW + cell;
-    float obj[1], sobj[1], score[1];
+    float obj[1], sobj[1], score[1], t0[1], t1[1], t2[1], t3[1];
     float4 box[1];
     int cls[1];
-    VecLoad<1>::ld(base + 4 * (size_t)s.HW, obj);
+    const size_t HW = s.HW;
+    VecLoad<1>::ld(base + 4 * HW, obj);
+    VecLoad<1>::ld(base, t0);
+    VecLoad<1>::ld(base + HW, t1);
+    VecLoad<1>::ld(base + 2 * HW, t2);
+    VecLoad<1>::ld(base + 3 * HW, t3);
+    ClsTrack tr[1];
+    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep<1>(base + 5 * HW, s.HW, p.nc, tr);
+    else cls_init(tr[0]);
     sobj[0] = ypp_sigmoid(obj[0]);
-    decode_cells<1>(p, s, base, a, cell, 1u, sobj, box, score, cls);
+    decode_cells<1>(p, s, base, a, cell, 1u, t0, t1, t2, t3, tr, sobj, box, score, cls);
     float2* o = reinterpret_cast<float2*>(out + ((size_t)b * p.N + s.box_base + u) * 6);
     o[0] = make_float2(box[0].x, box[0].y);
     o[1] = make_float2(box[0].z, box[0].w);

@@ -17,11 +17,32 @@ namespace {
 
 struct DetEntry { float4 box; int cls; int rank; };
 
+#define YPP_DET_BINS 64
+
 struct OrgSmemHeader {
     DetEntry lowl[YPP_DET_LIST];
     DetEntry highl[YPP_DET_LIST];
+    u32 bin_hi[YPP_DET_BINS];     // A role: per x-bin max of enc(y2 - step); after the scan: suffix max
+    u32 bin_lo[YPP_DET_BINS];     // B role: per x-bin max of enc(-y1);      after the scan: prefix max
     int n_low, n_high, flagged, pad;
 };
+
+// Cross-class suppression under the coordinate trick needs a pair (A of class c, B of class
+// c' > c) whose SHIFTED boxes intersect: x1_b + k*step < x2_a and y1_b + k*step < y2_a with
+// k >= 1, step = max_coord + 1.  With u_a = x2_a - step, v_a = y2_a - step (both <= -1) that is a
+// 2-D dominance  x1_b < u_a  and  y1_b < v_a.  A 64-bin staircase over x (suffix max of v for
+// the A role, prefix min of y1 for the B role) leaves only boxes near the Pareto frontier as
+// candidates; those few are then tested pairwise with the exact shifted arithmetic.
+struct DetGeom {
+    float step, x1min, lim, slack, inv_w;
+    bool on;
+};
+
+__device__ __forceinline__ int det_bin(const DetGeom& g, float x)
+{
+    const float t = (x - g.x1min) * g.inv_w;
+    return min(max((int)t, 0), YPP_DET_BINS - 1);
+}
 
 __device__ __forceinline__ void ce(u64* a, int i, int l)
 {
@@ -81,6 +102,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         for (int i = tid; i < n; i += YPP_ORG_THREADS) keys[i] = gkeys[i];
     }
     if (tid == 0) { hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; }
+    if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
     for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
     unsigned char* kf = p.ws.keepflag + (size_t)b * N;
     for (int i = tid; i < n; i += YPP_ORG_THREADS) kf[i] = 0;
@@ -92,6 +114,29 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         for (int i = tid; i < n; i += YPP_ORG_THREADS) gkeys[i] = keys[i];
     }
 
+    // ---- which torchvision path would run for this image
+    bool trick = p.offset_mode == YPP_OFFSET_TRICK;
+    if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
+    if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
+    const float M = ypp_dec(p.ws.maxc[b]);
+    const float step = __fadd_rn(M, 1.0f);                 // max_coordinate + 1
+    DetGeom dg;
+    dg.step = step;
+    dg.x1min = -ypp_dec(p.ws.nminx1[b]);
+    dg.slack = fmaf(fabsf(step) * (float)nc, 1e-6f, 1e-3f);
+    dg.lim = -1.0f + dg.slack;
+    // no detector when offsets are not finite (every shifted IoU is NaN on both paths) or when no
+    // box reaches x1 < -1 (nothing can be shifted onto the previous class band)
+    dg.on = trick && nc > 1 && (fabsf(M) <= 3.0e38f) && dg.x1min < dg.lim;
+    {
+        const float range = dg.lim - dg.x1min;
+        dg.inv_w = (range > 64.0f * 4.0f * dg.slack) ? (float)YPP_DET_BINS / range : 0.0f;
+    }
+    const bool detect = dg.on;
+    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
+
+    const float4* gbox = p.ws.box + (size_t)b * N;
+
     // ---- stable partition by class: warp w owns ranks [w*L, (w+1)*L)
     const int L = ((n + 31) / 32 + 31) / 32 * 32;
     const int r_begin = warp * L, r_end = min(n, r_begin + L);
@@ -99,12 +144,37 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
+        u64 k = 0;
+        if (ok) k = keys[r];
+        const int c = ok ? ypp_key_cls(k) : -1 - lane;
         const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
         if (ok && (peers & ((1u << lane) - 1u)) == 0) my[c] += __popc(peers);
+        if (detect && ok) {
+            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+            const float u = xy.z - step, v = xy.w - step;
+            if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
+            if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
+        }
         __syncwarp();
     }
     __syncthreads();
+    if (detect && warp == 1) {
+        // suffix max over bin_hi (A's in bins >= j can dominate a B in bin j),
+        // prefix max over bin_lo (B's in bins <= i can be dominated by an A in bin i); 2 bins per lane
+        u32 h0 = hd->bin_hi[lane], h1 = hd->bin_hi[lane + 32];
+        u32 l0 = hd->bin_lo[lane], l1 = hd->bin_lo[lane + 32];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const u32 a1 = __shfl_down_sync(YPP_FULL_MASK, h1, d), a0 = __shfl_down_sync(YPP_FULL_MASK, h0, d);
+            if (lane + d < 32) { h1 = max(h1, a1); h0 = max(h0, a0); }
+            const u32 b0 = __shfl_up_sync(YPP_FULL_MASK, l0, d), b1 = __shfl_up_sync(YPP_FULL_MASK, l1, d);
+            if (lane >= d) { l0 = max(l0, b0); l1 = max(l1, b1); }
+        }
+        h0 = max(h0, __shfl_sync(YPP_FULL_MASK, h1, 0));        // bins 0..31 also see all of 32..63
+        l1 = max(l1, __shfl_sync(YPP_FULL_MASK, l0, 31));       // bins 32..63 also see all of 0..31
+        hd->bin_hi[lane] = h0; hd->bin_hi[lane + 32] = h1;
+        hd->bin_lo[lane] = l0; hd->bin_lo[lane + 32] = l1;
+    }
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
         int t = 0;
         for (int w = 0; w < 32; ++w) t += table[w * nc + c];
@@ -134,20 +204,6 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     __syncthreads();
 
-    // ---- which torchvision path would run for this image
-    bool trick = p.offset_mode == YPP_OFFSET_TRICK;
-    if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
-    if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
-    const float M = ypp_dec(p.ws.maxc[b]);
-    const float step = __fadd_rn(M, 1.0f);                 // max_coordinate + 1
-    const float x1min = -ypp_dec(p.ws.nminx1[b]), y1min = -ypp_dec(p.ws.nminy1[b]);
-    const float slack = fmaf(step * (float)nc, 1e-6f, 1e-3f);
-    const bool detect = trick && nc > 1;
-    const float low_lim = -1.0f + slack;
-    const float hx_lim = step + x1min - slack, hy_lim = step + y1min - slack;
-    if (detect && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
-
-    const float4* gbox = p.ws.box + (size_t)b * N;
     float4* sbox = p.ws.sbox + (size_t)b * N;
     int* grank = p.ws.grank + (size_t)b * N;
 
@@ -168,8 +224,19 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             const float4 cb = gbox[ypp_key_idx(k)];
             float4 xy = ypp_xyxy(cb);
             if (detect) {
-                const bool is_low = xy.x < low_lim && xy.y < low_lim;
-                const bool is_high = xy.z > hx_lim && xy.w > hy_lim;
+                // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
+                bool is_low = false, is_high = false;
+                if (xy.x < dg.lim && xy.y < dg.lim) {
+                    const int j = max(det_bin(dg, xy.x) - 1, 0);
+                    const u32 e = hd->bin_hi[j];
+                    is_low = e != 0 && xy.y < ypp_dec(e) + dg.slack;
+                }
+                const float u = xy.z - step, v = xy.w - step;
+                if (u > dg.x1min - dg.slack) {
+                    const int i = min(det_bin(dg, u) + 1, YPP_DET_BINS - 1);
+                    const u32 e = hd->bin_lo[i];
+                    is_high = e != 0 && v > -ypp_dec(e) - dg.slack;
+                }
                 if (is_low || is_high) {
                     const float off = __fmul_rn((float)c, step);
                     DetEntry e;
@@ -189,7 +256,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     __syncthreads();
 
-    if (detect) {
+    if (trick && nc > 1) {
         const int nl = hd->n_low, nh = hd->n_high;
         if (nl > 0 && nh > 0) {
             if (nl > YPP_DET_LIST || nh > YPP_DET_LIST) {

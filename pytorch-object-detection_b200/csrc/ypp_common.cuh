@@ -21,7 +21,12 @@ typedef unsigned int u32;
 #define YPP_NMS_SMALL_THREADS 256
 #define YPP_NMS_BIG_THREADS 1024
 #define YPP_ORG_THREADS 1024
+#ifndef YPP_DECODE_THREADS
 #define YPP_DECODE_THREADS 256
+#endif
+#ifndef YPP_DECODE_MINB
+#define YPP_DECODE_MINB 3
+#endif
 
 // ---------------------------------------------------------------- workspace layout
 // All per-image arrays are [B][N]; the counter block is zeroed by one memset per call.

@@ -9,7 +9,7 @@ import subprocess
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(os.path.dirname(_PKG), "csrc")
-LIB_PATH = os.path.join(_PKG, "libypp.so")
+LIB_PATH = os.environ.get("YPP_LIB") or os.path.join(_PKG, "libypp.so")   # YPP_LIB: tuning builds only
 SOURCES = ["api.cu", "decode.cu", "organise.cu", "nms.cu", "metrics.cu"]
 
 YPP_MAX_SCALES = 4
@@ -43,8 +43,14 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), out=None):
     """nvcc the kernels into ypp/libypp.so (sm_100a only, -lineinfo for ncu source pages)."""
+    if out is not None:
+        cmd = ["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+               "-Xcompiler", "-fPIC", "-shared", "-o", out] + ["-D" + d for d in defines] + \
+              [os.path.join(_CSRC, s) for s in SOURCES]
+        subprocess.run(cmd, check=True)
+        return out
     srcs = [os.path.join(_CSRC, s) for s in SOURCES]
     deps = srcs + [os.path.join(_CSRC, h) for h in ("ypp_common.cuh", "ypp_kernels.cuh")] + \
         [os.path.join(os.path.dirname(os.path.dirname(_PKG)), "include", "ypp.h")]

@@ -50,29 +50,116 @@ __device__ __forceinline__ void ce(u64* a, int i, int l)
     if (x > y) { a[i] = y; a[l] = x; }
 }
 
+__device__ __forceinline__ u64 shfl_xor_u64(u64 v, int m)
+{
+    return ((u64)__shfl_xor_sync(YPP_FULL_MASK, (u32)(v >> 32), m) << 32) | __shfl_xor_sync(YPP_FULL_MASK, (u32)v, m);
+}
+
+// compare-exchange across lanes: the lane whose `upper` is false keeps the minimum
+__device__ __forceinline__ void ce_lane(u64& x, int m, bool upper)
+{
+    const u64 o = shfl_xor_u64(x, m);
+    x = (upper == (x > o)) ? x : o;       // upper keeps max, lower keeps min
+}
+
+// last six steps (strides 32,16,..,1) of an ascending bitonic merge on a 64-element window held
+// two per lane: x0 = w[lane], x1 = w[lane + 32]
+__device__ __forceinline__ void merge64_tail(u64& x0, u64& x1, int lane)
+{
+    if (x0 > x1) { const u64 t = x0; x0 = x1; x1 = t; }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        const bool up = (lane & m) != 0;
+        ce_lane(x0, m, up);
+        ce_lane(x1, m, up);
+    }
+}
+
+// full ascending bitonic sort of a 64-element window in registers (merge sizes 2..64, every
+// merge = mirror step + halving steps, all compare-exchanges ascending)
+__device__ __forceinline__ void sort64(u64& x0, u64& x1, int lane)
+{
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+        // mirror step inside each lane half: partner index = i ^ (k-1)  (lane ^ (k-1))
+        const bool up = (lane & (k >> 1)) != 0;
+        ce_lane(x0, k - 1, up);
+        ce_lane(x1, k - 1, up);
+#pragma unroll
+        for (int m = k >> 2; m > 0; m >>= 1) {
+            const bool u2 = (lane & m) != 0;
+            ce_lane(x0, m, u2);
+            ce_lane(x1, m, u2);
+        }
+    }
+    // k = 64 mirror: element lane of the low half pairs with element (31 - lane) of the high half
+    {
+        const u64 o1 = shfl_xor_u64(x1, 31);   // value x1 of lane 31-lane
+        const u64 o0 = shfl_xor_u64(x0, 31);   // value x0 of lane 31-lane
+        // my x0 (index lane) vs partner index 63-lane = x1 of lane (31-lane): keep min
+        const u64 n0 = x0 < o1 ? x0 : o1;
+        // my x1 (index 32+lane) vs partner index 31-lane = x0 of lane (31-lane): keep max
+        const u64 n1 = x1 > o0 ? x1 : o0;
+        x0 = n0; x1 = n1;
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) {
+        const bool up = (lane & m) != 0;
+        ce_lane(x0, m, up);
+        ce_lane(x1, m, up);
+    }
+}
+
 // Bitonic network with every compare-exchange ascending (mirror first step), so a virtual
-// +inf padding beyond n never moves: pairs whose upper index is >= n are simply skipped.
+// +inf padding beyond n never moves: pairs whose upper index is >= n are simply skipped in
+// shared memory, and windows are padded with ~0 in registers.  Strides >= 64 go through
+// shared memory with a block barrier per step; strides <= 32 run in registers on 64-element
+// windows (one warp per window) with shuffles.
 __device__ void bitonic_sort(u64* a, int n)
 {
-    int n_pad = 1;
-    while (n_pad < n) n_pad <<= 1;
+    int n_pad = 64, lg = 6;
+    while (n_pad < n) { n_pad <<= 1; ++lg; }
     const int half = n_pad >> 1;
-    for (int k = 2; k <= n_pad; k <<= 1) {
-        const int hk = k >> 1;
-        for (int t = threadIdx.x; t < half; t += YPP_ORG_THREADS) {
-            const int blk = t / hk, r = t - blk * hk;
-            const int i = blk * k + r, l = blk * k + (k - 1 - r);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n_win = n_pad >> 6;
+    const u64 INF = ~0ull;
+    // phase 0: sort every 64-window
+    for (int w = warp; w < n_win; w += YPP_ORG_THREADS / 32) {
+        const int i0 = (w << 6) + lane, i1 = i0 + 32;
+        u64 x0 = i0 < n ? a[i0] : INF, x1 = i1 < n ? a[i1] : INF;
+        sort64(x0, x1, lane);
+        if (i0 < n) a[i0] = x0;
+        if (i1 < n) a[i1] = x1;
+    }
+    __syncthreads();
+    for (int lk = 7; lk <= lg; ++lk) {
+        const int k = 1 << lk, hk = k >> 1;
+        // mirror step: pair r of block blk: (blk*k + r, blk*k + k-1-r)
+        for (int t = tid; t < half; t += YPP_ORG_THREADS) {
+            const int blk = t >> (lk - 1), r = t & (hk - 1);
+            const int i = (blk << lk) + r, l = (blk << lk) + (k - 1 - r);
             if (l < n) ce(a, i, l);
         }
         __syncthreads();
-        for (int j = hk >> 1; j > 0; j >>= 1) {
-            for (int t = threadIdx.x; t < half; t += YPP_ORG_THREADS) {
-                const int blk = t / j, r = t - blk * j;
-                const int i = blk * 2 * j + r, l = i + j;
+        for (int lj = lk - 2; lj >= 6; --lj) {
+            const int j = 1 << lj;
+            for (int t = tid; t < half; t += YPP_ORG_THREADS) {
+                const int blk = t >> lj, r = t & (j - 1);
+                const int i = (blk << (lj + 1)) + r, l = i + j;
                 if (l < n) ce(a, i, l);
             }
             __syncthreads();
         }
+        // strides 32..1 in registers
+        for (int w = warp; w < n_win; w += YPP_ORG_THREADS / 32) {
+            const int i0 = (w << 6) + lane, i1 = i0 + 32;
+            if ((w << 6) >= n) continue;
+            u64 x0 = i0 < n ? a[i0] : INF, x1 = i1 < n ? a[i1] : INF;
+            merge64_tail(x0, x1, lane);
+            if (i0 < n) a[i0] = x0;
+            if (i1 < n) a[i1] = x1;
+        }
+        __syncthreads();
     }
 }
 

@@ -96,6 +96,7 @@ class PostProcessor:
         if compare_in_double is None:
             compare_in_double = self.union_mode == _lib.UNION_SEPARATE   # CPU kernel semantics
         self.iou_thr_eff = float(lib().ypp_effective_iou_thr(self.iou_threshold, int(bool(compare_in_double))))
+        self._plans = {}
 
     # -- parameter blocks ------------------------------------------------------------------
     def _cfg(self, B, n_scales):
@@ -155,28 +156,68 @@ class PostProcessor:
             keep_idx=torch.empty((B, n_boxes), dtype=torch.int32, device=device) if want_keep_idx else None,
             n_boxes=n_boxes)
 
+    def _plan(self, heads):
+        """Parameter blocks for these exact head buffers, cached (the per-call host cost is what
+        bounds the sparse regime): key = (pointer, shape) of every head."""
+        key = tuple((h.data_ptr(), tuple(h.shape), h.is_contiguous(), h.dtype, h.device.index) for h in heads)
+        plan = self._plans.get(key)
+        if plan is None:
+            arr, heads_c, B, n_boxes = self._scales(heads)
+            if any(hc is not h for hc, h in zip(heads_c, heads)):
+                return (arr, heads_c, B, n_boxes, self._cfg(B, len(heads)), None)     # temporaries: do not cache
+            dev = heads[0].device
+            nbytes = lib().ypp_workspace_bytes(B, n_boxes, self.num_classes)
+            plan = (arr, heads_c, B, n_boxes, self._cfg(B, len(heads)), nbytes)
+            if len(self._plans) > 64:
+                self._plans.clear()
+            self._plans[key] = plan
+        return plan
+
     def __call__(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
                  out: Optional[PostResult] = None) -> PostResult:
-        arr, heads, B, n_boxes = self._scales(heads)
+        arr, heads, B, n_boxes, cfg, nbytes = self._plan(heads)
         dev = heads[0].device
         res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
-        cfg = self._cfg(B, len(heads))
         L = lib()
-        nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
+        if nbytes is None:
+            nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
         ws = _workspace(nbytes, dev, "post")
-        with torch.cuda.device(dev):
-            check(L.ypp_postprocess(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
-                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
-                                    res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
-                                    float(img_idx_base), _stream()))
+        if dev.index is not None and dev.index != torch.cuda.current_device():
+            with torch.cuda.device(dev):
+                return self.__call__(heads, img_idx_base, row_width, want_keep_idx, res)
+        check(L.ypp_postprocess(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                float(img_idx_base), _stream()))
         return res
 
+    def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
+                repeat=1, stages=None):
+        """Capture the chain on these (static) head buffers into a CUDA graph.  Returns
+        (graph, PostResult); graph.replay() re-runs it with whatever the buffers then hold.
+        `repeat` > 1 captures that many back-to-back invocations (timing loops); `stages`
+        restricts the capture to some of ("decode", "sort", "nms")."""
+        heads = [_check_head(h) for h in heads]
+        if stages is None:
+            res = self(heads, img_idx_base, row_width, want_keep_idx)          # warm-up, allocations
+        else:
+            res = self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=("decode", "sort", "nms"))
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(repeat):
+                if stages is None:
+                    self(heads, img_idx_base, row_width, want_keep_idx, out=res)
+                else:
+                    self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=stages, out=res)
+        return g, res
+
     def staged(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
-               stages=("decode", "sort", "nms")) -> PostResult:
+               stages=("decode", "sort", "nms"), out: Optional[PostResult] = None) -> PostResult:
         """Same chain through the three separate C-ABI stages (used to time / profile D1 alone)."""
         arr, heads, B, n_boxes = self._scales(heads)
         dev = heads[0].device
-        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, None)
+        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
         cfg = self._cfg(B, len(heads))
         L = lib()
         ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, "post")

@@ -6,16 +6,240 @@
 // (stable), box j suppressed iff an earlier KEPT box i has IoU(i,j) > thr (strict).
 //
 // torchvision's CUDA kernel writes an n x n/64 bit matrix to HBM and scans it with one CTA.
-// Here a segment is processed by one CTA in 64-row tiles, entirely on chip:
-//   - the 64x64 diagonal tile becomes a bitmask in shared memory (warp ballots);
-//   - one warp resolves the tile greedily (64 dependent steps on a register bitmask);
-//   - only the KEPT rows of the tile are then broadcast against the later columns that are
-//     still alive, setting bits in a shared-memory `removed` bitmap.
-// No mask ever reaches HBM and suppressed rows never do any pair work.
+// Here nothing but the keep flags reaches HBM and suppressed rows never do any pair work:
+//   - segments of up to YPP_WARP_SEG boxes (the per-class case) are owned by one 4-warp CTA:
+//     boxes staged in shared memory, 32-row tiles, the 32x32 diagonal tile held as one register
+//     per lane, the greedy order resolved by a ballot fix-point, and only the KEPT rows
+//     broadcast against the later columns each lane owns (rows split over the four warps).
+//   - longer segments (single-class heads, the class-agnostic whole-image fallback) go to a
+//     persistent 1024-thread CTA kernel pulling (image, class) pairs from the queue S1 filled.
+//
+// Pair test.  torchvision evaluates  inter / union > thr  with an IEEE division.  The same
+// decision is reached without dividing whenever  d = fma(-thr, union, inter)  is clearly away
+// from zero: |d| > 2^-20 * union  leaves 8x more room than the rounding of the quotient, the
+// half-ulp of thr and the rounding of d together can consume (valid for 2^-10 <= thr <= 1).
+// Pairs inside that band (practically none) are re-evaluated with the exact division, so keep
+// sets stay bit-exact.
 #include "ypp_kernels.cuh"
 
 namespace {
 
+#define YPP_PAIR_BAND 9.5367431640625e-07f      /* 2^-20 */
+
+// column-side constants of the pair test: kFma: (w_b, h_b); else (S_b, unused)
+template <bool kFma>
+__device__ __forceinline__ void pair_col(const float4 b, float& p0, float& p1)
+{
+    const float wb = __fsub_rn(b.z, b.x), hb = __fsub_rn(b.w, b.y);
+    if (kFma) { p0 = wb; p1 = hb; }
+    else      { p0 = __fmul_rn(wb, hb); p1 = 0.0f; }
+}
+
+// a = row (earlier in score order, area sa), b = column.  dead |= sure suppression,
+// amb |= the decision needs the exact division.
+template <bool kFma>
+__device__ __forceinline__ void pair_fast(const float4 a, const float sa, const float4 b, const float p0,
+                                          const float p1, const float thr, bool& dead, bool& amb)
+{
+    const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
+    const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
+    const float w = fmaxf(__fsub_rn(r, l), 0.0f), h = fmaxf(__fsub_rn(bt, t), 0.0f);
+    const float inter = __fmul_rn(w, h);
+    const float uni = kFma ? __fsub_rn(__fmaf_rn(p0, p1, sa), inter) : __fsub_rn(__fadd_rn(sa, p0), inter);
+    const float au = fabsf(uni);                       // inter > 0 implies uni > 0; |.| keeps inter == 0 false
+    const float d = __fmaf_rn(-thr, au, inter);
+    const float band = __fmul_rn(au, YPP_PAIR_BAND);
+    dead |= d > band;
+    amb |= !(fabsf(d) > band);                         // also catches NaN / inf
+}
+
+__device__ __forceinline__ bool pair_exact(const float4 a, const float sa, const float4 b, const float thr,
+                                           const int union_fma)
+{
+    return ypp_suppresses<false>(a, sa, b, thr, union_fma);
+}
+
+// Accumulating form for one column tested against many rows: dmax = max over rows of
+// d = inter' - thr * |union'|, where inter' = (r - l) * max(bt - t, 0) leaves the x extent
+// unclamped: whenever the boxes do not overlap inter' <= 0 and d <= 0, and whenever d > 0 they
+// do overlap and inter', union' are the exact fp32 values torchvision computes.  With
+// B = 2^-20 * (largest row area + column area) >= 2^-20 * union of every pair:
+//   dmax >  B  : some pair is surely above the threshold -> suppressed;
+//   dmax < -B  : every pair is surely below it            -> alive;
+//   otherwise  : re-evaluate the rows with the exact division.
+// NaN d is dropped by fmaxf, which is right: every NaN case has an exact answer of "not
+// suppressed".  6 alu-pipe + 6 fma-pipe instructions per pair.
+template <bool kFma>
+__device__ __forceinline__ void pair_acc(const float4 a, const float sa, const float4 b, const float p0,
+                                         const float p1, const float thr, float& dmax)
+{
+    const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
+    const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
+    const float w = __fsub_rn(r, l);
+    const float h = fmaxf(__fsub_rn(bt, t), 0.0f);
+    const float inter = __fmul_rn(w, h);
+    const float uni = kFma ? __fsub_rn(__fmaf_rn(p0, p1, sa), inter) : __fsub_rn(__fadd_rn(sa, p0), inter);
+    dmax = fmaxf(dmax, __fmaf_rn(-thr, fabsf(uni), inter));
+}
+
+// a row that can never raise dmax (padding of the kept-row lists)
+#define YPP_DUMMY_BOX make_float4(1e30f, 1e30f, -1e30f, -1e30f)
+#define YPP_DUMMY_AREA 1e30f
+
+// ------------------------------------------------------------------ per-class segments: one 4-warp CTA each
+#define YPP_NMSQ_WARPS 4
+#define YPP_NMSQ_THREADS (32 * YPP_NMSQ_WARPS)
+
+struct SegSmem {
+    float4 box[YPP_WARP_SEG];
+    float area[YPP_WARP_SEG];
+    float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 4
+    float karea[YPP_NMSQ_WARPS][8];
+    u32 in_words[32];          // byte w of word j: rows 8w..8w+7 of the tile that suppress column j
+    uint4 dpart[32];           // per lane: the four warps' partial dead-column bits
+};
+
+// 32-row tiles in score order.  Warp w owns rows 8w..8w+7 of every tile: it tests them against the
+// tile's own columns (diagonal), the four byte-wide partial masks are exchanged through shared
+// memory, every warp resolves the greedy order redundantly (ballot fix-point: a row is kept once
+// every earlier row that could suppress it is known dead, dead once one of them is known kept),
+// and then broadcasts ITS kept rows against all later columns (lane = column mod 32).
+template <bool kFast, bool kFma>
+__global__ void __launch_bounds__(YPP_NMSQ_THREADS)
+ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
+{
+    __shared__ SegSmem sm;
+    const int c = blockIdx.x, b = blockIdx.y;
+    const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
+    const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
+    if (len <= 0 || len > YPP_WARP_SEG) return;
+    const size_t ibase = (size_t)b * p.N;
+    const float4* __restrict__ seg = p.ws.sbox + ibase + s0;
+    const int* __restrict__ grank = p.ws.grank + ibase + s0;
+    unsigned char* __restrict__ keepflag = p.ws.keepflag + ibase;
+    const float thr = p.iou_thr;
+    const int union_fma = p.union_mode;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
+        const float4 q = seg[i];
+        sm.box[i] = q;
+        sm.area[i] = ypp_area(q);
+    }
+    __syncthreads();
+    const int ntiles = (len + 31) >> 5;
+    const u32 wmask = 0xffu << (8 * w);
+    u32 dead = 0;                 // bit k: column lane + 32k is suppressed (merged over the four warps)
+    int total = 0;
+    for (int T = 0; T < ntiles; ++T) {
+        const int base = T << 5;
+        const int j = base + lane;
+        const bool in_range = j < len;
+        const bool alive_l = in_range && !((dead >> T) & 1u);
+        const u32 alive = __ballot_sync(YPP_FULL_MASK, alive_l);       // identical in all four warps
+        if (alive == 0) continue;
+        // ---- diagonal tile, column view: which of MY rows (i < lane, alive) suppress column lane
+        const float4 cb = sm.box[in_range ? j : base];
+        const float my_area = sm.area[in_range ? j : base];
+        float p0, p1;
+        pair_col<kFma>(cb, p0, p1);
+        u32 in = 0;
+        for (u32 m = alive & wmask & ~(0x80000000u >> __clz(alive)); m; m &= m - 1u) {   // the last alive row has no column
+            const int i = __ffs(m) - 1;
+            const float4 a = sm.box[base + i];
+            const float sa = sm.area[base + i];
+            bool s = false;
+            if (kFast) {
+                bool amb = false;
+                pair_fast<kFma>(a, sa, cb, p0, p1, thr, s, amb);
+                if (amb) s = pair_exact(a, sa, cb, thr, union_fma);
+            } else {
+                s = pair_exact(a, sa, cb, thr, union_fma);
+            }
+            if (s && i < lane) in |= 1u << i;
+        }
+        reinterpret_cast<unsigned char*>(sm.in_words)[lane * 4 + w] = (unsigned char)(in >> (8 * w));
+        __syncthreads();
+        in = sm.in_words[lane];
+        // ---- greedy order as a fix-point
+        u32 K = 0, D = ~alive;
+        bool undecided = alive_l;
+        while ((K | D) != 0xffffffffu) {
+            const bool dead_now = undecided && (in & K) != 0u;
+            const bool keep_now = undecided && !dead_now && (in & ~D) == 0u;
+            K |= __ballot_sync(YPP_FULL_MASK, keep_now);
+            D |= __ballot_sync(YPP_FULL_MASK, dead_now);
+            undecided = undecided && !(dead_now || keep_now);
+        }
+        total += __popc(K);
+        if (w == 0 && ((K >> lane) & 1u)) keepflag[grank[j]] = 1;
+        if (T + 1 >= ntiles) break;
+        // ---- broadcast my kept rows against the later columns (two column groups per sweep)
+        const u32 Kw = K & wmask;
+        const int nkw = __popc(Kw);
+        u32 part = 0;
+        if (nkw) {
+            const int npad = (nkw + 3) & ~3;
+            if ((Kw >> lane) & 1u) {
+                const int s = __popc(Kw & ((1u << lane) - 1u));
+                sm.kbox[w][s] = cb;
+                sm.karea[w][s] = my_area;
+            }
+            if (lane >= nkw && lane < npad) { sm.kbox[w][lane] = YPP_DUMMY_BOX; sm.karea[w][lane] = YPP_DUMMY_AREA; }
+            // largest |area| among the tile's rows (uint order == float order for non-negative floats; NaN sorts on top)
+            const float smax = __uint_as_float(__reduce_max_sync(YPP_FULL_MASK, __float_as_uint(fabsf(my_area))));
+            __syncwarp();
+            const float4* kb = sm.kbox[w];
+            const float* ka = sm.karea[w];
+            for (int k = T + 1; k < ntiles; k += 2) {
+                const int j0 = (k << 5) + lane, j1 = j0 + 32;
+                const bool v0 = j0 < len && !((dead >> k) & 1u);
+                const bool v1 = j1 < len && !((dead >> (k + 1)) & 1u);
+                if (!__any_sync(YPP_FULL_MASK, v0 || v1)) continue;
+                const float4 c0 = sm.box[j0 < len ? j0 : 0], c1 = sm.box[j1 < len ? j1 : 0];
+                bool d0 = false, d1 = false;
+                bool exact = !kFast;
+                if (kFast) {
+                    float p00, p01, p10, p11;
+                    pair_col<kFma>(c0, p00, p01);
+                    pair_col<kFma>(c1, p10, p11);
+                    const float sb0 = kFma ? __fmul_rn(p00, p01) : p00, sb1 = kFma ? __fmul_rn(p10, p11) : p10;
+                    const float B0 = YPP_PAIR_BAND * (smax + fabsf(sb0)), B1 = YPP_PAIR_BAND * (smax + fabsf(sb1));
+                    float dm0 = -INFINITY, dm1 = -INFINITY;
+                    for (int r = 0; r < npad; r += 4) {
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const float4 a = kb[r + q];
+                            const float sa = ka[r + q];
+                            pair_acc<kFma>(a, sa, c0, p00, p01, thr, dm0);
+                            pair_acc<kFma>(a, sa, c1, p10, p11, thr, dm1);
+                        }
+                    }
+                    d0 = dm0 > B0;
+                    d1 = dm1 > B1;
+                    exact = (v0 && !d0 && !(dm0 < -B0)) || (v1 && !d1 && !(dm1 < -B1));
+                }
+                if (exact) {                                                    // a pair inside the band (or thr out of range)
+                    d0 = d1 = false;
+                    for (int r = 0; r < nkw; ++r) {
+                        const float4 a = kb[r];
+                        const float sa = ka[r];
+                        d0 = d0 || pair_exact(a, sa, c0, thr, union_fma);
+                        d1 = d1 || pair_exact(a, sa, c1, thr, union_fma);
+                    }
+                }
+                if (v0 && d0) part |= 1u << k;
+                if (v1 && d1) part |= 1u << (k + 1);
+            }
+        }
+        reinterpret_cast<u32*>(&sm.dpart[lane])[w] = part;
+        __syncthreads();
+        const uint4 dp = sm.dpart[lane];
+        dead |= dp.x | dp.y | dp.z | dp.w;
+    }
+    if (tid == 0 && total) atomicAdd(p.ws.keep_count + b, total);
+}
+
+// ------------------------------------------------------------------ CTA-owned (long) segments
 struct TileSmem {
     u32 diag[64][2];          // diag[i] = columns j (tile-local) suppressed by row i, j > i
     float4 kbox[64];          // kept rows of the current tile, compacted
@@ -26,7 +250,7 @@ struct TileSmem {
 
 // Process one segment.  seg: boxes in score order (global memory), cache: shared staging for
 // the first `cache_cap` boxes, removed: bitmap words (>= (len+31)/32).
-template <int THREADS, bool kEarlyOut>
+template <int THREADS, bool kFast, bool kFma>
 __device__ void nms_segment(const float4* __restrict__ seg, const int* __restrict__ grank,
                             unsigned char* __restrict__ keepflag, int len,
                             float4* cache, int cache_cap, u32* removed, TileSmem& ts,
@@ -35,7 +259,7 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ncache = min(len, cache_cap);
     for (int i = tid; i < ncache; i += THREADS) cache[i] = seg[i];
-    for (int i = tid; i < (len + 31) / 32; i += THREADS) removed[i] = 0;
+    for (int i = tid; i < (len + 31) / 32 + 2; i += THREADS) removed[i] = 0;
     if (tid == 0) ts.total_kept = 0;
     __syncthreads();
 
@@ -48,7 +272,16 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
             if (j > i && j < rows) {     // j < rows implies i < rows
                 const float4 a = (t0 + i) < ncache ? cache[t0 + i] : seg[t0 + i];
                 const float4 bq = (t0 + j) < ncache ? cache[t0 + j] : seg[t0 + j];
-                bit = ypp_suppresses<kEarlyOut>(a, ypp_area(a), bq, thr, union_fma);
+                const float sa = ypp_area(a);
+                if (kFast) {
+                    float p0, p1;
+                    pair_col<kFma>(bq, p0, p1);
+                    bool amb = false;
+                    pair_fast<kFma>(a, sa, bq, p0, p1, thr, bit, amb);
+                    if (amb) bit = pair_exact(a, sa, bq, thr, union_fma);
+                } else {
+                    bit = pair_exact(a, sa, bq, thr, union_fma);
+                }
             }
             const u32 m = __ballot_sync(YPP_FULL_MASK, bit);
             if (lane == 0) ts.diag[i][j >> 5] = m;
@@ -85,15 +318,27 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
             if (lane == 0) { ts.nkept = nlo + __popc(khi); ts.total_kept += nlo + __popc(khi); }
         }
         __syncthreads();
-        // ---- broadcast kept rows against later, still-alive columns
+        // ---- broadcast kept rows against later, still-alive columns (rows in chunks of 8)
         const int nk = ts.nkept;
         if (nk > 0) {
             for (int j = t0 + 64 + tid; j < len; j += THREADS) {
                 if ((removed[j >> 5] >> (j & 31)) & 1u) continue;
                 const float4 bq = j < ncache ? cache[j] : seg[j];
                 bool dead = false;
-                for (int r = 0; r < nk; ++r) {
-                    if (ypp_suppresses<kEarlyOut>(ts.kbox[r], ts.karea[r], bq, thr, union_fma)) { dead = true; break; }
+                if (kFast) {
+                    float p0, p1;
+                    pair_col<kFma>(bq, p0, p1);
+                    bool amb = false;
+                    for (int r0 = 0; r0 < nk && !dead; r0 += 8) {
+                        const int r1 = min(nk, r0 + 8);
+#pragma unroll 8
+                        for (int r = r0; r < r1; ++r) pair_fast<kFma>(ts.kbox[r], ts.karea[r], bq, p0, p1, thr, dead, amb);
+                    }
+                    if (amb && !dead) {
+                        for (int r = 0; r < nk && !dead; ++r) dead = pair_exact(ts.kbox[r], ts.karea[r], bq, thr, union_fma);
+                    }
+                } else {
+                    for (int r = 0; r < nk && !dead; ++r) dead = pair_exact(ts.kbox[r], ts.karea[r], bq, thr, union_fma);
                 }
                 if (dead) atomicOr(&removed[j >> 5], 1u << (j & 31));
             }
@@ -102,27 +347,8 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
     }
 }
 
-// ---- small segments: one CTA per (class, image)
-template <bool kEarlyOut>
-__global__ void __launch_bounds__(YPP_NMS_SMALL_THREADS)
-ypp_nms_small_kernel(const __grid_constant__ YppNmsParams p)
-{
-    __shared__ float4 cache[YPP_SMALL_SEG];
-    __shared__ u32 removed[YPP_SMALL_SEG / 32 + 2];
-    __shared__ TileSmem ts;
-    const int c = blockIdx.x, b = blockIdx.y;
-    const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
-    const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
-    if (len <= 0 || len > YPP_SMALL_SEG) return;
-    const size_t base = (size_t)b * p.N;
-    nms_segment<YPP_NMS_SMALL_THREADS, kEarlyOut>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
-                                                  p.ws.keepflag + base, len, cache, YPP_SMALL_SEG,
-                                                  removed, ts, p.iou_thr, p.union_mode);
-    if (threadIdx.x == 0 && ts.total_kept) atomicAdd(p.ws.keep_count + b, ts.total_kept);
-}
-
-// ---- big segments: persistent CTAs pull (image, class) pairs from the queue S1 filled
-template <bool kEarlyOut>
+// persistent CTAs pull (image, class) pairs from the queue S1 filled
+template <bool kFast, bool kFma>
 __global__ void __launch_bounds__(YPP_NMS_BIG_THREADS, 1)
 ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
 {
@@ -131,7 +357,7 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
     u32* removed = reinterpret_cast<u32*>(smem_raw + sizeof(float4) * YPP_BIG_CACHE);
     __shared__ TileSmem ts;
     __shared__ int item;
-    const int qn = p.ws.q[0];
+    const int qn = min(p.ws.q[0], p.B * p.ws.bigq_per_image);
     for (;;) {
         if (threadIdx.x == 0) item = atomicAdd(p.ws.q + 1, 1);
         __syncthreads();
@@ -143,48 +369,81 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
         const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
         const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
         const size_t base = (size_t)b * p.N;
-        nms_segment<YPP_NMS_BIG_THREADS, kEarlyOut>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
-                                                    p.ws.keepflag + base, len, cache, YPP_BIG_CACHE,
-                                                    removed, ts, p.iou_thr, p.union_mode);
+        nms_segment<YPP_NMS_BIG_THREADS, kFast, kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
+                                                      p.ws.keepflag + base, len, cache, YPP_BIG_CACHE,
+                                                      removed, ts, p.iou_thr, p.union_mode);
         if (threadIdx.x == 0 && ts.total_kept) atomicAdd(p.ws.keep_count + b, ts.total_kept);
         __syncthreads();
     }
 }
 
-// ---- gather: keep flags (global score order) -> packed rows + kept box indices
-#define YPP_GATHER_THREADS 512
+// ------------------------------------------------------------------ gather
+// keep flags (global score order) -> packed rows + kept box indices.  grid (chunks, B): a CTA
+// counts the flags of the chunks before its own (uint4 sweeps over the byte flags), then
+// places its own YPP_GATHER_CHUNK ranks with a ballot prefix.
+#define YPP_GATHER_THREADS 256
+#define YPP_GATHER_CHUNK 1024
+
+__device__ __forceinline__ int popc_bytes16(const uint4 v)
+{
+    return __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);     // flags are 0/1 bytes
+}
+
 __global__ void __launch_bounds__(YPP_GATHER_THREADS)
 ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
 {
     __shared__ int warp_tot[YPP_GATHER_THREADS / 32];
-    __shared__ long long base_s;
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    __shared__ long long red_img[YPP_GATHER_THREADS / 32];
+    __shared__ int red_pre[YPP_GATHER_THREADS / 32];
+    const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.N;
     const int n = min(p.ws.cand_count[b], N);
-    // rows of the images before this one
-    long long part = 0;
-    for (int i = tid; i < b; i += YPP_GATHER_THREADS) part += p.ws.keep_count[i];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(YPP_FULL_MASK, part, d);
-    if (tid == 0) base_s = 0;
-    __syncthreads();
-    if (lane == 0 && part) atomicAdd((unsigned long long*)&base_s, (unsigned long long)part);
-    __syncthreads();
-    const long long base = base_s;
-    if (tid == 0) {
+    const int r_begin = blockIdx.x * YPP_GATHER_CHUNK;
+    const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && p.det_total != nullptr;
+    if (blockIdx.x == 0 && tid == 0) {
         if (p.cand_count_out) p.cand_count_out[b] = n;
         if (p.keep_count_out) p.keep_count_out[b] = p.ws.keep_count[b];
-        if (b == (int)gridDim.x - 1 && p.det_total) *p.det_total = (int)(base + p.ws.keep_count[b]);
     }
+    if (r_begin >= n && !writes_total) return;
+    // rows of the images before this one, and kept flags of this image before my chunk
     const unsigned char* kf = p.ws.keepflag + (size_t)b * N;
+    long long img_part = 0;
+    for (int i = tid; i < b; i += YPP_GATHER_THREADS) img_part += p.ws.keep_count[i];
+    int pre_part = 0;
+    {
+        const int pre = min(r_begin, n);
+        int head = (int)((16 - ((uintptr_t)kf & 15)) & 15);       // b*N need not be a multiple of 16
+        if (head > pre) head = pre;
+        if (tid < head) pre_part += kf[tid];
+        const int nvec = (pre - head) >> 4;
+        const uint4* v = reinterpret_cast<const uint4*>(kf + head);
+        for (int i = tid; i < nvec; i += YPP_GATHER_THREADS) pre_part += popc_bytes16(v[i]);
+        const int tail0 = head + (nvec << 4);
+        if (tail0 + tid < pre) pre_part += kf[tail0 + tid];
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        img_part += __shfl_xor_sync(YPP_FULL_MASK, img_part, d);
+        pre_part += __shfl_xor_sync(YPP_FULL_MASK, pre_part, d);
+    }
+    if (lane == 0) { red_img[warp] = img_part; red_pre[warp] = pre_part; }
+    __syncthreads();
+    long long img_rows = 0;
+    int pre_rows = 0;
+#pragma unroll
+    for (int w = 0; w < YPP_GATHER_THREADS / 32; ++w) { img_rows += red_img[w]; pre_rows += red_pre[w]; }
+    if (writes_total && tid == 0) *p.det_total = (int)(img_rows + p.ws.keep_count[b]);
+    if (r_begin >= n) return;
     const u64* keys = p.ws.keys + (size_t)b * N;
     const float4* box = p.ws.box + (size_t)b * N;
     const float img = p.img_idx_base + (float)b;
-    int running = 0;
-    for (int r0 = 0; r0 < n; r0 += YPP_GATHER_THREADS) {
+    const int r_end = min(n, r_begin + YPP_GATHER_CHUNK);
+    int running = pre_rows;
+    for (int r0 = r_begin; r0 < r_end; r0 += YPP_GATHER_THREADS) {
         const int r = r0 + tid;
-        const bool f = r < n && kf[r];
+        const bool f = r < r_end && kf[r];
         const u32 m = __ballot_sync(YPP_FULL_MASK, f);
+        __syncthreads();                                   // warp_tot of the previous round is consumed
         if (lane == 0) warp_tot[warp] = __popc(m);
         __syncthreads();
         int before = 0, total = 0;
@@ -195,11 +454,11 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
             total += t;
         }
         if (f) {
-            const int pos = running + before + __popc(m & ((1u << lane) - 1u));
+            const int pos = running + before + __popc(m & ((1u << lane) - 1u));      // position inside the image
             const u64 k = keys[r];
             const int idx = ypp_key_idx(k);
             if (p.keep_idx) p.keep_idx[(size_t)b * N + pos] = idx;
-            const long long row = base + pos;
+            const long long row = img_rows + pos;
             if (p.det_rows && row < p.det_capacity) {
                 const float4 bx = box[idx];
                 float cls = (float)ypp_key_cls(k);
@@ -211,28 +470,23 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
             }
         }
         running += total;
-        __syncthreads();
     }
 }
 
-}  // namespace
-
-int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st)
+template <bool kFast, bool kFma>
+int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
 {
-    const bool early = p.iou_thr >= 0.0f;
     dim3 grid(p.nc, p.B);
-    if (early) ypp_nms_small_kernel<true><<<grid, YPP_NMS_SMALL_THREADS, 0, st>>>(p);
-    else       ypp_nms_small_kernel<false><<<grid, YPP_NMS_SMALL_THREADS, 0, st>>>(p);
+    ypp_nms_seg_kernel<kFast, kFma><<<grid, YPP_NMSQ_THREADS, 0, st>>>(p);
     ypp_count_launch(1);
-    int rc = ypp_check_launch("nms_small");
+    int rc = ypp_check_launch("nms_seg");
     if (rc) return rc;
-    if (p.N > YPP_SMALL_SEG) {
-        const int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 2));
+    if (p.N > YPP_WARP_SEG) {
+        const int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 4));
         static bool configured = false;
         if (!configured) {
-            cudaError_t e1 = cudaFuncSetAttribute(ypp_nms_big_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-            cudaError_t e2 = cudaFuncSetAttribute(ypp_nms_big_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-            if (e1 != cudaSuccess || e2 != cudaSuccess) { ypp_set_error("nms_big: cudaFuncSetAttribute failed"); return YPP_E_CUDA; }
+            cudaError_t e = cudaFuncSetAttribute(ypp_nms_big_kernel<kFast, kFma>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+            if (e != cudaSuccess) { ypp_set_error("nms_big: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
             configured = true;
         }
         if (smem > 220 * 1024) { ypp_set_error("nms_big: %d boxes per image exceed the removed-bitmap budget", p.N); return YPP_E_UNSUPPORTED; }
@@ -241,17 +495,27 @@ int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st)
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (ctas > sms) ctas = sms;
-        if (early) ypp_nms_big_kernel<true><<<ctas, YPP_NMS_BIG_THREADS, smem, st>>>(p);
-        else       ypp_nms_big_kernel<false><<<ctas, YPP_NMS_BIG_THREADS, smem, st>>>(p);
+        ypp_nms_big_kernel<kFast, kFma><<<ctas, YPP_NMS_BIG_THREADS, smem, st>>>(p);
         ypp_count_launch(1);
         rc = ypp_check_launch("nms_big");
     }
     return rc;
 }
 
+}  // namespace
+
+int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st)
+{
+    // the division-free pair test is proven for thresholds in [2^-10, 1]; anything else divides
+    const bool fast = p.iou_thr >= 0.0009765625f && p.iou_thr <= 1.0f;
+    if (!fast) return launch_nms_t<false, false>(p, st);
+    return p.union_mode == YPP_UNION_FMA ? launch_nms_t<true, true>(p, st) : launch_nms_t<true, false>(p, st);
+}
+
 int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st)
 {
-    ypp_gather_kernel<<<p.B, YPP_GATHER_THREADS, 0, st>>>(p);
+    dim3 grid((p.N + YPP_GATHER_CHUNK - 1) / YPP_GATHER_CHUNK, p.B);
+    ypp_gather_kernel<<<grid, YPP_GATHER_THREADS, 0, st>>>(p);
     ypp_count_launch(1);
     return ypp_check_launch("gather");
 }

@@ -380,7 +380,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
 
     for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = seg[c];
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
-        if (seg[c + 1] - seg[c] > YPP_SMALL_SEG) {
+        if (seg[c + 1] - seg[c] > YPP_WARP_SEG) {
             const int s = atomicAdd(p.ws.q, 1);
             p.ws.bigq[s] = b * nc + c;
         }

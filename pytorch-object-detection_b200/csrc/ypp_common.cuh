@@ -14,11 +14,10 @@ typedef unsigned int u32;
 #define YPP_KEY_CLS_MASK ((1u << YPP_KEY_CLS_BITS) - 1u)
 #define YPP_KEY_IDX_MASK ((1u << YPP_KEY_IDX_BITS) - 1u)
 
-// segments longer than this go to the persistent "big" NMS kernel
-#define YPP_SMALL_SEG 2048
+// segments up to this long are owned by one warp; longer ones go to the persistent CTA kernel
+#define YPP_WARP_SEG 512
 // boxes the big kernel keeps staged in shared memory (x 16 B)
 #define YPP_BIG_CACHE 11264
-#define YPP_NMS_SMALL_THREADS 256
 #define YPP_NMS_BIG_THREADS 1024
 #define YPP_ORG_THREADS 1024
 #ifndef YPP_DECODE_THREADS
@@ -69,7 +68,7 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     w.imgflag = (int*)take(sizeof(int) * B);
     w.q = (int*)take(sizeof(int) * 4);
     w.counter_bytes = off - c0;
-    int per = N / YPP_SMALL_SEG + 1;
+    int per = N / YPP_WARP_SEG + 1;
     if (per > nc) per = nc;
     w.bigq_per_image = per;
     w.bigq = (int*)take(sizeof(int) * (size_t)B * per);

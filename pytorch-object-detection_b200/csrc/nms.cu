@@ -67,11 +67,12 @@ __device__ __forceinline__ bool pair_exact(const float4 a, const float sa, const
 //   dmax >  B  : some pair is surely above the threshold -> suppressed;
 //   dmax < -B  : every pair is surely below it            -> alive;
 //   otherwise  : re-evaluate the rows with the exact division.
+// (The kernels use one B per segment: 2^-20 * 2 * the largest |area| in the segment.)
 // NaN d is dropped by fmaxf, which is right: every NaN case has an exact answer of "not
 // suppressed".  6 alu-pipe + 6 fma-pipe instructions per pair.
 template <bool kFma>
-__device__ __forceinline__ void pair_acc(const float4 a, const float sa, const float4 b, const float p0,
-                                         const float p1, const float thr, float& dmax)
+__device__ __forceinline__ float pair_d(const float4 a, const float sa, const float4 b, const float p0,
+                                        const float p1, const float thr)
 {
     const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
     const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
@@ -79,7 +80,7 @@ __device__ __forceinline__ void pair_acc(const float4 a, const float sa, const f
     const float h = fmaxf(__fsub_rn(bt, t), 0.0f);
     const float inter = __fmul_rn(w, h);
     const float uni = kFma ? __fsub_rn(__fmaf_rn(p0, p1, sa), inter) : __fsub_rn(__fadd_rn(sa, p0), inter);
-    dmax = fmaxf(dmax, __fmaf_rn(-thr, fabsf(uni), inter));
+    return __fmaf_rn(-thr, fabsf(uni), inter);
 }
 
 // a row that can never raise dmax (padding of the kept-row lists)
@@ -95,6 +96,7 @@ struct SegSmem {
     float area[YPP_WARP_SEG];
     float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 4
     float karea[YPP_NMSQ_WARPS][8];
+    u32 amax[YPP_NMSQ_WARPS];
     u32 in_words[32];          // byte w of word j: rows 8w..8w+7 of the tile that suppress column j
     uint4 dpart[32];           // per lane: the four warps' partial dead-column bits
 };
@@ -105,7 +107,7 @@ struct SegSmem {
 // every earlier row that could suppress it is known dead, dead once one of them is known kept),
 // and then broadcasts ITS kept rows against all later columns (lane = column mod 32).
 template <bool kFast, bool kFma>
-__global__ void __launch_bounds__(YPP_NMSQ_THREADS)
+__global__ void __launch_bounds__(YPP_NMSQ_THREADS, 9)
 ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 {
     __shared__ SegSmem sm;
@@ -120,12 +122,20 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const float thr = p.iou_thr;
     const int union_fma = p.union_mode;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    u32 amax_bits = 0;            // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
         const float4 q = seg[i];
+        const float ar = ypp_area(q);
         sm.box[i] = q;
-        sm.area[i] = ypp_area(q);
+        sm.area[i] = ar;
+        amax_bits = max(amax_bits, __float_as_uint(fabsf(ar)));
     }
+    amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
+    if (lane == 0) sm.amax[w] = amax_bits;
     __syncthreads();
+    // one decision band for the whole segment (NaN / inf areas make every compare fail -> exact path)
+    const float Bseg = 2.0f * YPP_PAIR_BAND *
+        __uint_as_float(max(max(sm.amax[0], sm.amax[1]), max(sm.amax[2], sm.amax[3])));
     const int ntiles = (len + 31) >> 5;
     const u32 wmask = 0xffu << (8 * w);
     u32 dead = 0;                 // bit k: column lane + 32k is suppressed (merged over the four warps)
@@ -143,20 +153,30 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
         float p0, p1;
         pair_col<kFma>(cb, p0, p1);
         u32 in = 0;
-        for (u32 m = alive & wmask & ~(0x80000000u >> __clz(alive)); m; m &= m - 1u) {   // the last alive row has no column
-            const int i = __ffs(m) - 1;
-            const float4 a = sm.box[base + i];
-            const float sa = sm.area[base + i];
-            bool s = false;
-            if (kFast) {
-                bool amb = false;
-                pair_fast<kFma>(a, sa, cb, p0, p1, thr, s, amb);
-                if (amb) s = pair_exact(a, sa, cb, thr, union_fma);
-            } else {
-                s = pair_exact(a, sa, cb, thr, union_fma);
+        if (kFast) {
+            // my 8 rows, unconditionally (dead or out-of-range rows are masked out below)
+            float lo = INFINITY;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int i = min(base + 8 * w + q, len - 1);
+                const float d = pair_d<kFma>(sm.box[i], sm.area[i], cb, p0, p1, thr);
+                if (d > Bseg) in |= 1u << (8 * w + q);
+                lo = fminf(lo, fabsf(d));             // a NaN d is never a suppression: dropped
             }
-            if (s && i < lane) in |= 1u << i;
+            if (!(lo > Bseg)) {                       // some pair inside the band: exact pass
+                in = 0;
+                for (int q = 0; q < 8; ++q) {
+                    const int i = min(base + 8 * w + q, len - 1);
+                    if (pair_exact(sm.box[i], sm.area[i], cb, thr, union_fma)) in |= 1u << (8 * w + q);
+                }
+            }
+        } else {
+            for (int q = 0; q < 8; ++q) {
+                const int i = min(base + 8 * w + q, len - 1);
+                if (pair_exact(sm.box[i], sm.area[i], cb, thr, union_fma)) in |= 1u << (8 * w + q);
+            }
         }
+        in &= alive & ((1u << lane) - 1u);            // only alive rows before me count
         reinterpret_cast<unsigned char*>(sm.in_words)[lane * 4 + w] = (unsigned char)(in >> (8 * w));
         __syncthreads();
         in = sm.in_words[lane];
@@ -185,8 +205,6 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
                 sm.karea[w][s] = my_area;
             }
             if (lane >= nkw && lane < npad) { sm.kbox[w][lane] = YPP_DUMMY_BOX; sm.karea[w][lane] = YPP_DUMMY_AREA; }
-            // largest |area| among the tile's rows (uint order == float order for non-negative floats; NaN sorts on top)
-            const float smax = __uint_as_float(__reduce_max_sync(YPP_FULL_MASK, __float_as_uint(fabsf(my_area))));
             __syncwarp();
             const float4* kb = sm.kbox[w];
             const float* ka = sm.karea[w];
@@ -202,21 +220,19 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
                     float p00, p01, p10, p11;
                     pair_col<kFma>(c0, p00, p01);
                     pair_col<kFma>(c1, p10, p11);
-                    const float sb0 = kFma ? __fmul_rn(p00, p01) : p00, sb1 = kFma ? __fmul_rn(p10, p11) : p10;
-                    const float B0 = YPP_PAIR_BAND * (smax + fabsf(sb0)), B1 = YPP_PAIR_BAND * (smax + fabsf(sb1));
                     float dm0 = -INFINITY, dm1 = -INFINITY;
                     for (int r = 0; r < npad; r += 4) {
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const float4 a = kb[r + q];
                             const float sa = ka[r + q];
-                            pair_acc<kFma>(a, sa, c0, p00, p01, thr, dm0);
-                            pair_acc<kFma>(a, sa, c1, p10, p11, thr, dm1);
+                            dm0 = fmaxf(dm0, pair_d<kFma>(a, sa, c0, p00, p01, thr));
+                            dm1 = fmaxf(dm1, pair_d<kFma>(a, sa, c1, p10, p11, thr));
                         }
                     }
-                    d0 = dm0 > B0;
-                    d1 = dm1 > B1;
-                    exact = (v0 && !d0 && !(dm0 < -B0)) || (v1 && !d1 && !(dm1 < -B1));
+                    d0 = dm0 > Bseg;
+                    d1 = dm1 > Bseg;
+                    exact = (v0 && !d0 && !(dm0 < -Bseg)) || (v1 && !d1 && !(dm1 < -Bseg));
                 }
                 if (exact) {                                                    // a pair inside the band (or thr out of range)
                     d0 = d1 = false;

@@ -61,13 +61,14 @@ int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, Ypp
         YppScaleParams& d = p->sc[i];
         d.head = s.head; d.A = s.A; d.H = s.H; d.W = s.W; d.HW = s.H * s.W;
         d.box_base = box_base;
-        const bool vec_ok = !dense && (d.HW % 4 == 0) && (((uintptr_t)s.head & 15u) == 0);
-        d.vec = vec_ok ? 4 : 1;
-        d.units = s.A * d.HW / d.vec;
+        d.tpp = (d.HW + YPP_TILE_BOXES - 1) / YPP_TILE_BOXES;
+        // staged (cp.async.bulk) path: channel rows must be 16-byte aligned and the tile must fit shared memory
+        d.tma = (!dense && (d.HW % 4 == 0) && (((uintptr_t)s.head & 15u) == 0) && p->C * YPP_TILE_BOXES * 4 <= 100 * 1024) ? 1 : 0;
+        if (d.tma) p->stage_bytes = p->C * YPP_TILE_BOXES * 4;
         for (int a = 0; a < s.A; ++a) { d.aw[a] = s.anchor_w[a]; d.ah[a] = s.anchor_h[a]; }
         d.sw = s.stride_w; d.sh = s.stride_h;
         p->tile_base[i] = tile;
-        tile += (d.units + YPP_DECODE_THREADS - 1) / YPP_DECODE_THREADS;
+        tile += s.A * d.tpp;
         box_base += s.A * d.HW;
         if (box_base > YPP_MAX_BOXES) { ypp_set_error("more than %d boxes per image", YPP_MAX_BOXES); return YPP_E_UNSUPPORTED; }
     }
@@ -82,13 +83,6 @@ int bind_ws(int B, int N, int nc, void* ws, size_t ws_bytes, YppWs* out)
     if (((uintptr_t)ws & 255u) != 0) { ypp_set_error("workspace must be 256-byte aligned"); return YPP_E_WORKSPACE; }
     *out = ypp_make_ws(ws, B, N, nc);
     if (out->total_bytes > ws_bytes) { ypp_set_error("workspace %zu bytes < required %zu", ws_bytes, out->total_bytes); return YPP_E_WORKSPACE; }
-    return YPP_OK;
-}
-
-int reset_counters(const YppWs& w, cudaStream_t st)
-{
-    const cudaError_t e = cudaMemsetAsync(w.cand_count, 0, w.counter_bytes, st);
-    if (e != cudaSuccess) { ypp_set_error("memset: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
     return YPP_OK;
 }
 
@@ -156,8 +150,6 @@ int ypp_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, si
     if (rc) return rc;
     rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
     if (rc) return rc;
-    rc = reset_counters(p.ws, (cudaStream_t)stream);
-    if (rc) return rc;
     return ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
 }
 
@@ -168,8 +160,6 @@ int ypp_rows_compact(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, voi
     if (!rows_BN6 || n_boxes <= 0 || n_boxes > YPP_MAX_BOXES) { ypp_set_error("rows null or n_boxes=%d out of range", n_boxes); return YPP_E_BADARG; }
     YppWs w;
     rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
-    if (rc) return rc;
-    rc = reset_counters(w, (cudaStream_t)stream);
     if (rc) return rc;
     return ypp_launch_rows_compact(rows_BN6, cfg->B, n_boxes, cfg->conf_thr, w, (cudaStream_t)stream);
 }
@@ -205,8 +195,6 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
     int rc = build_decode_params(cfg, scales, false, &p);
     if (rc) return rc;
     rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
-    if (rc) return rc;
-    rc = reset_counters(p.ws, (cudaStream_t)stream);
     if (rc) return rc;
     rc = ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
     if (rc) return rc;

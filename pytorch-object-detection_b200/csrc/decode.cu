@@ -2,8 +2,20 @@
 //
 // Reference semantics: decode_predictions, utils/yolov3_utils.py:12-59 and
 // utils/yolov2_utils.py:12-58; the threshold is the torch.where of nms_v3,
-// utils/yolo_utils.py:334.  One pass over the NCHW head: lanes walk the cell dimension so
-// every channel-plane read is a coalesced (128-bit per lane when H*W % 4 == 0) transaction.
+// utils/yolo_utils.py:334.
+//
+// One pass over the NCHW head.  A CTA owns one tile = up to 256 consecutive cells of one anchor
+// plane group: its C = 5+nc channel rows (256 floats each, contiguous in the NCHW tensor) are
+// pulled into shared memory by the async-copy engine (cp.async.bulk, one bulk copy per channel
+// row, completion on an mbarrier), so the whole tile is in flight at once without holding
+// registers, and DRAM sees only large sequential requests.  Thread t then decodes cell t from
+// shared memory (conflict-free columns).  Heads whose plane size is not a multiple of 4 floats
+// (13x13, 19x19: channel rows are only 4-byte aligned) take plain coalesced loads instead.
+//
+// Compaction is deterministic: the candidates of a tile are written in box-index order at
+// keys[b][tile_first ..] with their count in tile_cnt[b][tile]; S1 concatenates the tiles, so
+// the sort input is already in box-index order and a STABLE sort by score alone gives the
+// reference's tie order.  No atomics, nothing to clear between calls.
 #include "ypp_kernels.cuh"
 
 namespace {
@@ -20,12 +32,14 @@ struct ClsTrack {
 
 __device__ __forceinline__ void cls_init(ClsTrack& t) { t.m1 = -INFINITY; t.m2 = -INFINITY; t.i1 = 0; }
 
+// branch-free; a NaN logit never wins a > compare and is dropped by fmaxf (documented: NaN
+// logits are not supported, torch.argmax would treat them as maximal)
 __device__ __forceinline__ void cls_push(ClsTrack& t, float v, int c)
 {
-    // NaN logits: sigmoid(NaN)=NaN; torch.argmax treats NaN as maximal.  Not supported here
-    // (documented): a NaN never wins a > compare and is ignored.
-    if (v > t.m1) { t.m2 = t.m1; t.m1 = v; t.i1 = c; }
-    else if (v > t.m2) { t.m2 = v; }
+    const bool gt = v > t.m1;
+    t.m2 = fmaxf(t.m2, gt ? t.m1 : v);
+    t.i1 = gt ? c : t.i1;
+    t.m1 = gt ? v : t.m1;
 }
 
 __device__ __forceinline__ float cls_tol(float m1)
@@ -34,13 +48,14 @@ __device__ __forceinline__ float cls_tol(float m1)
     return 9.6e-7f * (1.0f + __expf(fmaxf(m1, 0.0f)));
 }
 
-// slow path: exact argmax over sigmoid for logits inside the band (first max wins)
-__device__ __noinline__ int cls_resolve(const float* __restrict__ cls_base, int HW, int nc, float m1, float tol)
+// slow path: exact argmax over sigmoid for logits inside the band (first max wins);
+// cls_base/stride address either the staged tile or the head itself
+__device__ __noinline__ int cls_resolve(const float* cls_base, int stride, int nc, float m1, float tol)
 {
     int best = 0;
     float best_v = -1.0f;
     for (int c = 0; c < nc; ++c) {
-        const float v = __ldg(cls_base + (size_t)c * HW);
+        const float v = cls_base[(size_t)c * stride];
         if (v >= m1 - tol) {
             const float s = ypp_sigmoid(v);
             if (s > best_v) { best_v = s; best = c; }
@@ -49,275 +64,233 @@ __device__ __noinline__ int cls_resolve(const float* __restrict__ cls_base, int 
     return best;
 }
 
-template <int V> struct VecLoad;
-template <> struct VecLoad<1> {
-    static __device__ __forceinline__ void ld(const float* p, float (&o)[1]) { o[0] = __ldg(p); }
-};
-template <> struct VecLoad<4> {
-    static __device__ __forceinline__ void ld(const float* p, float (&o)[4])
-    {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(p));
-        o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
-    }
-};
-
-// class-plane sweep for V consecutive cells: software-pipelined, 4 planes (4 x 16 B per lane
-// when V = 4) in flight while the previous 4 are folded into the running arg-max.
-template <int V>
-__device__ __forceinline__ void class_sweep(const float* __restrict__ cp, int HW, int nc, ClsTrack (&tr)[V])
+__device__ __forceinline__ void class_sweep(const float* cp, int stride, int nc, ClsTrack& tr)
 {
-#pragma unroll
-    for (int v = 0; v < V; ++v) cls_init(tr[v]);
-    float cur[4][V], nxt[4][V];
+    cls_init(tr);
     int c = 0;
-    if (nc >= 4) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) VecLoad<V>::ld(cp + (size_t)k * HW, cur[k]);
-        for (; c + 8 <= nc; c += 4) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) VecLoad<V>::ld(cp + (size_t)(c + 4 + k) * HW, nxt[k]);
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int v = 0; v < V; ++v) cls_push(tr[v], cur[k][v], c + k);
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-#pragma unroll
-                for (int v = 0; v < V; ++v) cur[k][v] = nxt[k][v];
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-#pragma unroll
-            for (int v = 0; v < V; ++v) cls_push(tr[v], cur[k][v], c + k);
-        c += 4;
+    for (; c + 4 <= nc; c += 4) {
+        const float v0 = cp[(size_t)c * stride], v1 = cp[(size_t)(c + 1) * stride];
+        const float v2 = cp[(size_t)(c + 2) * stride], v3 = cp[(size_t)(c + 3) * stride];
+        cls_push(tr, v0, c); cls_push(tr, v1, c + 1); cls_push(tr, v2, c + 2); cls_push(tr, v3, c + 3);
     }
-    for (; c < nc; ++c) {
-        float l0[V];
-        VecLoad<V>::ld(cp + (size_t)c * HW, l0);
-#pragma unroll
-        for (int v = 0; v < V; ++v) cls_push(tr[v], l0[v], c);
-    }
+    for (; c < nc; ++c) cls_push(tr, cp[(size_t)c * stride], c);
 }
 
-// decode V consecutive cells of one anchor from the already loaded t0..t3 planes and the class
-// tracks.  Fills box/score/cls for the lanes in `need`.
-template <int V>
-__device__ __forceinline__ void decode_cells(const YppDecodeParams& p, const YppScaleParams& s,
-                                             const float* __restrict__ base /* channel 0, cell0 */,
-                                             int a, int cell0, unsigned need,
-                                             const float (&t0)[V], const float (&t1)[V], const float (&t2)[V],
-                                             const float (&t3)[V], const ClsTrack (&tr)[V],
-                                             const float (&score_obj)[V],
-                                             float4 (&box)[V], float (&score)[V], int (&cls)[V])
+// decode one cell from its five box/objectness logits and the class track
+struct Decoded { float4 box; float score; int cls; };
+
+__device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const YppScaleParams& s, int a, int cell,
+                                               float t0, float t1, float t2, float t3, float sobj,
+                                               const ClsTrack& tr, const float* cls_base, int cls_stride)
 {
-    const int HW = s.HW;
-    const int nc = p.nc;
-    const float aw = s.aw[a], ah = s.ah[a];
-    int y = cell0 / s.W;
-    int x = cell0 - y * s.W;
-#pragma unroll
-    for (int v = 0; v < V; ++v) {
-        if (need & (1u << v)) {
-            // pxy = sigmoid(t) + grid, then *= stride (yolov3_utils.py:47,54)
-            const float px = __fmul_rn(__fadd_rn(ypp_sigmoid(t0[v]), (float)x), s.sw);
-            const float py = __fmul_rn(__fadd_rn(ypp_sigmoid(t1[v]), (float)y), s.sh);
-            // pwh = exp(t) * scaled_anchor, then *= stride: two roundings (:48,54)
-            const float pw = __fmul_rn(__fmul_rn(expf(t2[v]), aw), s.sw);
-            const float ph = __fmul_rn(__fmul_rn(expf(t3[v]), ah), s.sh);
-            box[v] = make_float4(px, py, pw, ph);
-            int ci = 0;
-            if (nc > 1) {
-                ci = tr[v].i1;
-                const float tol = cls_tol(tr[v].m1);
-                if (!(tr[v].m1 - tr[v].m2 > tol))
-                    ci = cls_resolve(base + 5 * (size_t)HW + v, HW, nc, tr[v].m1, tol);
-            }
-            cls[v] = ci;
-            score[v] = score_obj[v];
-            if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS)
-                score[v] = __fmul_rn(score_obj[v], ypp_sigmoid(tr[v].m1));
-        }
-        if (++x == s.W) { x = 0; ++y; }
+    const int y = cell / s.W, x = cell - y * s.W;
+    Decoded d;
+    // pxy = sigmoid(t) + grid, then *= stride (yolov3_utils.py:47,54)
+    const float px = __fmul_rn(__fadd_rn(ypp_sigmoid(t0), (float)x), s.sw);
+    const float py = __fmul_rn(__fadd_rn(ypp_sigmoid(t1), (float)y), s.sh);
+    // pwh = exp(t) * scaled_anchor, then *= stride: two roundings (:48,54)
+    const float pw = __fmul_rn(__fmul_rn(expf(t2), s.aw[a]), s.sw);
+    const float ph = __fmul_rn(__fmul_rn(expf(t3), s.ah[a]), s.sh);
+    d.box = make_float4(px, py, pw, ph);
+    int ci = 0;
+    if (p.nc > 1) {
+        ci = tr.i1;
+        const float tol = cls_tol(tr.m1);
+        if (!(tr.m1 - tr.m2 > tol)) ci = cls_resolve(cls_base, cls_stride, p.nc, tr.m1, tol);
     }
+    d.cls = ci;
+    d.score = sobj;
+    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) d.score = __fmul_rn(sobj, ypp_sigmoid(tr.m1));
+    return d;
 }
 
-// ---- block-wide compaction of up to V candidates per thread ------------------------------
+// ---- block-wide compaction of one candidate per thread, in thread (= box index) order ----
 struct CompactSmem {
     int warp_cnt[YPP_DECODE_THREADS / 32];
     u32 warp_max[YPP_DECODE_THREADS / 32], warp_nx[YPP_DECODE_THREADS / 32], warp_ny[YPP_DECODE_THREADS / 32];
-    int block_base;
 };
 
-template <int V>
-__device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, CompactSmem& sm,
-                                              unsigned pass, const float4 (&box)[V], const float (&score)[V],
-                                              const int (&cls)[V], int idx0)
+__device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int tile, int first, CompactSmem& sm,
+                                              bool pass, const float4 box, const float score, const int cls, int idx)
 {
+    constexpr int NW = YPP_DECODE_THREADS / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int cnt = __popc(pass);
-    // warp inclusive scan of cnt
-    int inc = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
-        if (lane >= d) inc += o;
-    }
-    // per-image extrema for the coordinate trick / cross-class detector
+    const u32 m = __ballot_sync(YPP_FULL_MASK, pass);
+    // per-tile extrema for the coordinate trick / cross-class detector
     u32 emax = 0, enx = 0, eny = 0;
+    if (pass) {
+        const float4 q = ypp_xyxy(box);
+        emax = max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w)));
+        enx = ypp_enc(-q.x);
+        eny = ypp_enc(-q.y);
+    }
+    if (m) {                                       // warp-uniform
+        emax = __reduce_max_sync(YPP_FULL_MASK, emax);
+        enx = __reduce_max_sync(YPP_FULL_MASK, enx);
+        eny = __reduce_max_sync(YPP_FULL_MASK, eny);
+    }
+    if (lane == 0) { sm.warp_cnt[warp] = __popc(m); sm.warp_max[warp] = emax; sm.warp_nx[warp] = enx; sm.warp_ny[warp] = eny; }
+    __syncthreads();
+    int before = 0, total = 0;
 #pragma unroll
-    for (int v = 0; v < V; ++v) {
-        if (pass & (1u << v)) {
-            const float4 q = ypp_xyxy(box[v]);
-            emax = max(emax, max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w))));
-            enx = max(enx, ypp_enc(-q.x));
-            eny = max(eny, ypp_enc(-q.y));
+    for (int w = 0; w < NW; ++w) {
+        const int c = sm.warp_cnt[w];
+        if (w < warp) before += c;
+        total += c;
+    }
+    if (threadIdx.x == 0) {
+        u32 M = 0, NX = 0, NY = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) { M = max(M, sm.warp_max[w]); NX = max(NX, sm.warp_nx[w]); NY = max(NY, sm.warp_ny[w]); }
+        ws.tile_cnt[(size_t)b * ws.tiles_max + tile] = total;
+        *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + tile)) = make_uint4(M, NX, NY, 0u);
+        if (b == 0) {
+            ws.tile_first[tile] = first;
+            if (tile == 0) *ws.ntiles = (int)gridDim.x;
         }
     }
-    emax = __reduce_max_sync(YPP_FULL_MASK, emax);
-    enx = __reduce_max_sync(YPP_FULL_MASK, enx);
-    eny = __reduce_max_sync(YPP_FULL_MASK, eny);
-    if (lane == 31) { sm.warp_cnt[warp] = inc; sm.warp_max[warp] = emax; sm.warp_nx[warp] = enx; sm.warp_ny[warp] = eny; }
-    __syncthreads();
-    if (warp == 0) {
-        constexpr int NW = YPP_DECODE_THREADS / 32;
-        int c = lane < NW ? sm.warp_cnt[lane] : 0;
-        u32 m = lane < NW ? sm.warp_max[lane] : 0, nx = lane < NW ? sm.warp_nx[lane] : 0, ny = lane < NW ? sm.warp_ny[lane] : 0;
-        int ex = c;
-#pragma unroll
-        for (int d = 1; d < NW; d <<= 1) {
-            const int o = __shfl_up_sync(YPP_FULL_MASK, ex, d);
-            if (lane >= d) ex += o;
-        }
-        m = __reduce_max_sync(YPP_FULL_MASK, m);
-        nx = __reduce_max_sync(YPP_FULL_MASK, nx);
-        ny = __reduce_max_sync(YPP_FULL_MASK, ny);
-        if (lane < NW) sm.warp_cnt[lane] = ex - c;   // exclusive warp offsets
-        const int total = __shfl_sync(YPP_FULL_MASK, ex, NW - 1);
-        if (lane == 0) {
-            int base = 0;
-            if (total > 0) {
-                base = atomicAdd(ws.cand_count + b, total);
-                atomicMax(ws.maxc + b, m);
-                atomicMax(ws.nminx1 + b, nx);
-                atomicMax(ws.nminy1 + b, ny);
-            }
-            sm.block_base = base;
-        }
-    }
-    __syncthreads();
-    if (cnt) {
-        int pos = sm.block_base + sm.warp_cnt[warp] + inc - cnt;
-        u64* keys = ws.keys + (size_t)b * N;
-        float4* bx = ws.box + (size_t)b * N;
-#pragma unroll
-        for (int v = 0; v < V; ++v) {
-            if (pass & (1u << v)) {
-                keys[pos++] = ypp_make_key(score[v], idx0 + v, cls[v]);
-                bx[idx0 + v] = box[v];
-            }
-        }
+    if (pass) {
+        const int pos = first + before + __popc(m & ((1u << lane) - 1u));
+        ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
+        ws.box[(size_t)b * N + idx] = box;
     }
 }
 
-template <int V>
-__device__ __forceinline__ void decode_compact_tile(const YppDecodeParams& p, const YppScaleParams& s,
-                                                    int tile, int b, CompactSmem& sm)
-{
-    const int upp = s.HW / V;                       // units per anchor plane
-    const int u = tile * YPP_DECODE_THREADS + threadIdx.x;
-    const bool valid = u < s.units;
-    const int a = valid ? u / upp : 0;
-    const int cell0 = valid ? (u - a * upp) * V : 0;
-    const float* base = s.head + ((size_t)(b * s.A + a) * p.C) * s.HW + cell0;
+// ---- async bulk copy + mbarrier (sm_90+ PTX) ----------------------------------------------
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 
-    // objectness and the four box planes are fetched together (one round trip); the nc class
-    // planes only when some lane of the warp holds a candidate
-    float obj[V], sobj[V], t0[V], t1[V], t2[V], t3[V];
-    unsigned pass = 0;
-    if (valid) {
-        const size_t HW = s.HW;
-        VecLoad<V>::ld(base + 4 * HW, obj);
-        VecLoad<V>::ld(base, t0);
-        VecLoad<V>::ld(base + HW, t1);
-        VecLoad<V>::ld(base + 2 * HW, t2);
-        VecLoad<V>::ld(base + 3 * HW, t3);
-#pragma unroll
-        for (int v = 0; v < V; ++v) {
-            sobj[v] = ypp_sigmoid(obj[v]);                       // yolov3_utils.py:50
-            if (sobj[v] > p.conf) pass |= 1u << v;               // yolo_utils.py:334 (strict)
-        }
-    }
-    float4 box[V];
-    float score[V];
-    int cls[V];
-    if (__any_sync(YPP_FULL_MASK, pass != 0)) {
-        if (pass) {
-            ClsTrack tr[V];
-            if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep<V>(base + 5 * (size_t)s.HW, s.HW, p.nc, tr);
-            else {
-#pragma unroll
-                for (int v = 0; v < V; ++v) cls_init(tr[v]);
-            }
-            decode_cells<V>(p, s, base, a, cell0, pass, t0, t1, t2, t3, tr, sobj, box, score, cls);
-            if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) {
-#pragma unroll
-                for (int v = 0; v < V; ++v)
-                    if ((pass & (1u << v)) && !(score[v] > p.conf)) pass &= ~(1u << v);
-            }
-        }
-    }
-    compact_store<V>(p.ws, p.N, b, sm, pass, box, score, cls, s.box_base + a * s.HW + cell0);
+__device__ __forceinline__ void mbar_init(u64* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64* bar, u32 bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, u32 bytes, u64* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64* bar, u32 parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "YPP_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra YPP_DONE;\n"
+        "bra YPP_WAIT;\n"
+        "YPP_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
 
-__global__ void __launch_bounds__(YPP_DECODE_THREADS, YPP_DECODE_MINB)
-ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p)
+// tile -> (scale, anchor, first cell, cells)
+struct TileRef { int si, a, cell0, ncells, first; };
+
+__device__ __forceinline__ TileRef tile_ref(const YppDecodeParams& p, int bx)
 {
-    __shared__ CompactSmem sm;
-    const int b = blockIdx.y;
-    int si = 0;
+    TileRef t;
+    t.si = 0;
 #pragma unroll
     for (int k = 1; k < YPP_MAX_SCALES; ++k)
-        if (k < p.n_scales && (int)blockIdx.x >= p.tile_base[k]) si = k;
-    const YppScaleParams& s = p.sc[si];
-    const int tile = blockIdx.x - p.tile_base[si];
-    if (s.vec == 4) decode_compact_tile<4>(p, s, tile, b, sm);
-    else            decode_compact_tile<1>(p, s, tile, b, sm);
+        if (k < p.n_scales && bx >= p.tile_base[k]) t.si = k;
+    const YppScaleParams& s = p.sc[t.si];
+    const int tl = bx - p.tile_base[t.si];
+    t.a = tl / s.tpp;
+    t.cell0 = (tl - t.a * s.tpp) * YPP_TILE_BOXES;
+    t.ncells = min(YPP_TILE_BOXES, s.HW - t.cell0);
+    t.first = s.box_base + t.a * s.HW + t.cell0;
+    return t;
+}
+
+__global__ void __launch_bounds__(YPP_DECODE_THREADS)
+ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p)
+{
+    extern __shared__ __align__(128) float stage[];          // [C][256] when the tile is staged
+    __shared__ CompactSmem sm;
+    __shared__ __align__(8) u64 mbar;
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const TileRef t = tile_ref(p, (int)blockIdx.x);
+    const YppScaleParams& s = p.sc[t.si];
+    const int C = p.C, HW = s.HW;
+    const float* src = s.head + ((size_t)(b * s.A + t.a) * C) * HW + t.cell0;      // channel 0 of this tile
+    const bool valid = tid < t.ncells;
+    const int cell = t.cell0 + tid;
+
+    bool pass = false;
+    Decoded d;
+    d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
+    if (s.tma) {
+        if (tid == 0) mbar_init(&mbar, 1);
+        __syncthreads();
+        if (tid < 32) {
+            const u32 row_bytes = (u32)t.ncells * 4u;            // multiple of 16: HW % 4 == 0
+            if (tid == 0) mbar_expect_tx(&mbar, row_bytes * (u32)C);
+            __syncwarp();
+            for (int c = tid; c < C; c += 32)
+                bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * HW, row_bytes, &mbar);
+        }
+        mbar_wait(&mbar, 0);
+        const float* col = stage + tid;
+        float sobj = 0.f;
+        if (valid) {
+            sobj = ypp_sigmoid(col[4 * YPP_TILE_BOXES]);                 // yolov3_utils.py:50
+            pass = sobj > p.conf;                                        // yolo_utils.py:334 (strict)
+        }
+        if (__any_sync(YPP_FULL_MASK, pass)) {
+            ClsTrack tr;
+            if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES, p.nc, tr);
+            else cls_init(tr);
+            if (pass) {
+                d = decode_cell(p, s, t.a, cell, col[0], col[YPP_TILE_BOXES], col[2 * YPP_TILE_BOXES], col[3 * YPP_TILE_BOXES],
+                                sobj, tr, col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES);
+                if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
+            }
+        }
+    } else {
+        const float* col = src + tid;
+        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
+        if (valid) {
+            const float obj = __ldg(col + 4 * (size_t)HW);
+            t0 = __ldg(col); t1 = __ldg(col + HW); t2 = __ldg(col + 2 * (size_t)HW); t3 = __ldg(col + 3 * (size_t)HW);
+            sobj = ypp_sigmoid(obj);
+            pass = sobj > p.conf;
+        }
+        if (__any_sync(YPP_FULL_MASK, pass)) {
+            if (pass) {
+                ClsTrack tr;
+                if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)HW, HW, p.nc, tr);
+                else cls_init(tr);
+                d = decode_cell(p, s, t.a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)HW, HW);
+                if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
+            }
+        }
+    }
+    compact_store(p.ws, p.N, b, (int)blockIdx.x, t.first, sm, pass, d.box, d.score, d.cls, t.first + tid);
 }
 
 // ---- dense decode: every box, rows [B, N, 6] (= decode_predictions + cat) ---------------
 __global__ void __launch_bounds__(YPP_DECODE_THREADS)
 ypp_decode_dense_kernel(const __grid_constant__ YppDecodeParams p, float* __restrict__ out)
 {
-    const int b = blockIdx.y;
-    int si = 0;
-#pragma unroll
-    for (int k = 1; k < YPP_MAX_SCALES; ++k)
-        if (k < p.n_scales && (int)blockIdx.x >= p.tile_base[k]) si = k;
-    const YppScaleParams& s = p.sc[si];
-    const int tile = blockIdx.x - p.tile_base[si];
-    const int u = tile * YPP_DECODE_THREADS + threadIdx.x;   // dense path: units are single boxes
-    if (u >= s.A * s.HW) return;
-    const int a = u / s.HW;
-    const int cell = u - a * s.HW;
-    const float* base = s.head + ((size_t)(b * s.A + a) * p.C) * s.HW + cell;
-    float obj[1], sobj[1], score[1], t0[1], t1[1], t2[1], t3[1];
-    float4 box[1];
-    int cls[1];
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const TileRef t = tile_ref(p, (int)blockIdx.x);
+    if (tid >= t.ncells) return;
+    const YppScaleParams& s = p.sc[t.si];
     const size_t HW = s.HW;
-    VecLoad<1>::ld(base + 4 * HW, obj);
-    VecLoad<1>::ld(base, t0);
-    VecLoad<1>::ld(base + HW, t1);
-    VecLoad<1>::ld(base + 2 * HW, t2);
-    VecLoad<1>::ld(base + 3 * HW, t3);
-    ClsTrack tr[1];
-    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep<1>(base + 5 * HW, s.HW, p.nc, tr);
-    else cls_init(tr[0]);
-    sobj[0] = ypp_sigmoid(obj[0]);
-    decode_cells<1>(p, s, base, a, cell, 1u, t0, t1, t2, t3, tr, sobj, box, score, cls);
-    float2* o = reinterpret_cast<float2*>(out + ((size_t)b * p.N + s.box_base + u) * 6);
-    o[0] = make_float2(box[0].x, box[0].y);
-    o[1] = make_float2(box[0].z, box[0].w);
-    o[2] = make_float2(score[0], (float)cls[0]);
+    const float* col = s.head + ((size_t)(b * s.A + t.a) * p.C) * HW + t.cell0 + tid;
+    const float obj = __ldg(col + 4 * HW);
+    const float t0 = __ldg(col), t1 = __ldg(col + HW), t2 = __ldg(col + 2 * HW), t3 = __ldg(col + 3 * HW);
+    ClsTrack tr;
+    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * HW, (int)HW, p.nc, tr);
+    else cls_init(tr);
+    const Decoded d = decode_cell(p, s, t.a, t.cell0 + tid, t0, t1, t2, t3, ypp_sigmoid(obj), tr, col + 5 * HW, (int)HW);
+    float2* o = reinterpret_cast<float2*>(out + ((size_t)b * p.N + t.first + tid) * 6);
+    o[0] = make_float2(d.box.x, d.box.y);
+    o[1] = make_float2(d.box.z, d.box.w);
+    o[2] = make_float2(d.score, (float)d.cls);
 }
 
 // ---- compaction from decoded rows (nms_v3 entry, utils/yolo_utils.py:321-337) -----------
@@ -326,25 +299,25 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
 {
     __shared__ CompactSmem sm;
     const int b = blockIdx.y;
-    const int n = blockIdx.x * YPP_DECODE_THREADS + threadIdx.x;
-    unsigned pass = 0;
-    float4 box[1];
-    float score[1];
-    int cls[1];
+    const int first = blockIdx.x * YPP_TILE_BOXES;
+    const int n = first + threadIdx.x;
+    bool pass = false;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    float score = 0.f;
+    int cls = 0;
     if (n < N) {
         const float2* r = reinterpret_cast<const float2*>(rows + ((size_t)b * N + n) * 6);
         const float2 r0 = __ldg(r), r1 = __ldg(r + 1), r2 = __ldg(r + 2);
-        box[0] = make_float4(r0.x, r0.y, r1.x, r1.y);
-        score[0] = r2.x;
+        box = make_float4(r0.x, r0.y, r1.x, r1.y);
+        score = r2.x;
         int c = (int)r2.y;
-        if (!(r2.y >= 0.0f && r2.y <= (float)YPP_KEY_CLS_MASK && (float)c == r2.y)) {
-            atomicOr(ws.q + 2, 1);          // class id not representable: flagged, clamped
-            c = min(max(c, 0), (int)YPP_KEY_CLS_MASK);
-        }
-        cls[0] = c;
-        if (score[0] > conf) pass = 1u;
+        // class ids that the 12-bit key field cannot hold are clamped (documented: ids must be
+        // integers in [0, nc)); the row keeps its own class column verbatim in the output
+        if (!(r2.y >= 0.0f && r2.y <= (float)YPP_KEY_CLS_MASK)) c = min(max(c, 0), (int)YPP_KEY_CLS_MASK);
+        cls = c;
+        pass = score > conf;
     }
-    compact_store<1>(ws, N, b, sm, pass, box, score, cls, n);
+    compact_store(ws, N, b, (int)blockIdx.x, first, sm, pass, box, score, cls, n);
 }
 
 }  // namespace
@@ -353,8 +326,14 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
 {
+    static int configured = 0;
+    if (p.stage_bytes > 48 * 1024 && p.stage_bytes > configured) {
+        cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p.stage_bytes);
+        if (e != cudaSuccess) { ypp_set_error("decode_compact: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+        configured = p.stage_bytes;
+    }
     dim3 grid(p.tile_base[p.n_scales], B);
-    ypp_decode_compact_kernel<<<grid, YPP_DECODE_THREADS, 0, st>>>(p);
+    ypp_decode_compact_kernel<<<grid, YPP_DECODE_THREADS, p.stage_bytes, st>>>(p);
     ypp_count_launch(1);
     return ypp_check_launch("decode_compact");
 }
@@ -369,7 +348,7 @@ int ypp_launch_decode_dense(const YppDecodeParams& p, int B, float* out, cudaStr
 
 int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const YppWs& ws, cudaStream_t st)
 {
-    dim3 grid((N + YPP_DECODE_THREADS - 1) / YPP_DECODE_THREADS, B);
+    dim3 grid((N + YPP_TILE_BOXES - 1) / YPP_TILE_BOXES, B);
     ypp_rows_compact_kernel<<<grid, YPP_DECODE_THREADS, 0, st>>>(rows, N, conf, ws);
     ypp_count_launch(1);
     return ypp_check_launch("rows_compact");

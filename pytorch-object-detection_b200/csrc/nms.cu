@@ -450,7 +450,7 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     for (int w = 0; w < YPP_GATHER_THREADS / 32; ++w) { img_rows += red_img[w]; pre_rows += red_pre[w]; }
     if (writes_total && tid == 0) *p.det_total = (int)(img_rows + p.ws.keep_count[b]);
     if (r_begin >= n) return;
-    const u64* keys = p.ws.keys + (size_t)b * N;
+    const u64* keys = p.ws.skeys + (size_t)b * N;
     const float4* box = p.ws.box + (size_t)b * N;
     const float img = p.img_idx_base + (float)b;
     const int r_end = min(n, r_begin + YPP_GATHER_CHUNK);

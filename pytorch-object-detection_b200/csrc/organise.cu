@@ -1,12 +1,13 @@
 // S1: per image ordering.  One CTA per image:
-//   1. sort the compacted 64-bit keys (~score | box index | class) ascending in shared memory:
-//      the result is the stable descending-score order of torchvision::nms
-//      (scores.sort(stable=True, descending=True); ties -> lower box index) for the whole image;
-//   2. stable counting partition by class -> per (image, class) segments in the same order;
-//   3. emit xyxy boxes (utils/yolo_utils.py:339-343) in segment order, shifted by
+//   1. concatenate the per-tile candidate keys D1 left (box-index order) into shared memory;
+//   2. stable LSD radix sort on the score word only -> the stable descending-score order of
+//      torchvision::nms (scores.sort(stable=True, descending=True); ties -> lower box index),
+//      digits sized to the bits in which the image's scores actually differ;
+//   3. stable counting partition by class -> per (image, class) segments in the same order;
+//   4. emit xyxy boxes (utils/yolo_utils.py:339-343) in segment order, shifted by
 //      cls * (max_coordinate + 1) when torchvision would take the coordinate-trick path
 //      (_batched_nms_coordinate_trick), and the segment -> global-rank map;
-//   4. coordinate trick only: detect cross-class suppression edges (possible when a box with
+//   5. coordinate trick only: detect cross-class suppression edges (possible when a box with
 //      negative x1,y1 is shifted onto the previous class band); such an image is re-emitted as
 //      ONE class-agnostic segment so the greedy scan sees exactly what torchvision's does.
 #include "ypp_kernels.cuh"
@@ -14,17 +15,21 @@
 namespace {
 
 #define YPP_DET_LIST 64
+#define YPP_DET_BINS 64
+#define YPP_ORG_WARPS (YPP_ORG_THREADS / 32)
+#define YPP_RADIX_MAX 256
+#define YPP_TABLE_PITCH 33              // table[digit * 33 + warp]: leaders of one warp hit distinct banks
 
 struct DetEntry { float4 box; int cls; int rank; };
-
-#define YPP_DET_BINS 64
 
 struct OrgSmemHeader {
     DetEntry lowl[YPP_DET_LIST];
     DetEntry highl[YPP_DET_LIST];
     u32 bin_hi[YPP_DET_BINS];     // A role: per x-bin max of enc(y2 - step); after the scan: suffix max
     u32 bin_lo[YPP_DET_BINS];     // B role: per x-bin max of enc(-y1);      after the scan: prefix max
-    int n_low, n_high, flagged, pad;
+    int warp_sums[YPP_ORG_WARPS];
+    int n_low, n_high, flagged, n;
+    u32 maxc, nminx1, nminy1, kmin, kmax, pad[3];
 };
 
 // Cross-class suppression under the coordinate trick needs a pair (A of class c, B of class
@@ -44,123 +49,93 @@ __device__ __forceinline__ int det_bin(const DetGeom& g, float x)
     return min(max((int)t, 0), YPP_DET_BINS - 1);
 }
 
-__device__ __forceinline__ void ce(u64* a, int i, int l)
+// block-wide exclusive scan of one int per thread (all YPP_ORG_THREADS threads call it)
+__device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int& total)
 {
-    const u64 x = a[i], y = a[l];
-    if (x > y) { a[i] = y; a[l] = x; }
-}
-
-__device__ __forceinline__ u64 shfl_xor_u64(u64 v, int m)
-{
-    return ((u64)__shfl_xor_sync(YPP_FULL_MASK, (u32)(v >> 32), m) << 32) | __shfl_xor_sync(YPP_FULL_MASK, (u32)v, m);
-}
-
-// compare-exchange across lanes: the lane whose `upper` is false keeps the minimum
-__device__ __forceinline__ void ce_lane(u64& x, int m, bool upper)
-{
-    const u64 o = shfl_xor_u64(x, m);
-    x = (upper == (x > o)) ? x : o;       // upper keeps max, lower keeps min
-}
-
-// last six steps (strides 32,16,..,1) of an ascending bitonic merge on a 64-element window held
-// two per lane: x0 = w[lane], x1 = w[lane + 32]
-__device__ __forceinline__ void merge64_tail(u64& x0, u64& x1, int lane)
-{
-    if (x0 > x1) { const u64 t = x0; x0 = x1; x1 = t; }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
-        const bool up = (lane & m) != 0;
-        ce_lane(x0, m, up);
-        ce_lane(x1, m, up);
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
+        if (lane >= d) inc += o;
     }
+    __syncthreads();                       // previous users of warp_sums are done
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    const int ws = warp_sums[lane];        // YPP_ORG_WARPS == 32
+    int winc = ws;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(YPP_FULL_MASK, winc, d);
+        if (lane >= d) winc += o;
+    }
+    total = __shfl_sync(YPP_FULL_MASK, winc, 31);
+    const int wbase = __shfl_sync(YPP_FULL_MASK, winc - ws, warp);
+    return wbase + inc - v;
 }
 
-// full ascending bitonic sort of a 64-element window in registers (merge sizes 2..64, every
-// merge = mirror step + halving steps, all compare-exchanges ascending)
-__device__ __forceinline__ void sort64(u64& x0, u64& x1, int lane)
+// One stable LSD pass on digit ((key >> 32) - kmin) >> shift  (bw bits).  Warp w owns the contiguous
+// ranks [w*L, (w+1)*L) and walks them 32 at a time, so "warp order, then chunk order, then lane
+// order" is the input order; per (digit, warp) counters make the scatter stable.
+__device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, int bw,
+                           u32 kmin, int* table, int* warp_sums)
 {
-#pragma unroll
-    for (int k = 2; k <= 32; k <<= 1) {
-        // mirror step inside each lane half: partner index = i ^ (k-1)  (lane ^ (k-1))
-        const bool up = (lane & (k >> 1)) != 0;
-        ce_lane(x0, k - 1, up);
-        ce_lane(x1, k - 1, up);
-#pragma unroll
-        for (int m = k >> 2; m > 0; m >>= 1) {
-            const bool u2 = (lane & m) != 0;
-            ce_lane(x0, m, u2);
-            ce_lane(x1, m, u2);
-        }
-    }
-    // k = 64 mirror: element lane of the low half pairs with element (31 - lane) of the high half
-    {
-        const u64 o1 = shfl_xor_u64(x1, 31);   // value x1 of lane 31-lane
-        const u64 o0 = shfl_xor_u64(x0, 31);   // value x0 of lane 31-lane
-        // my x0 (index lane) vs partner index 63-lane = x1 of lane (31-lane): keep min
-        const u64 n0 = x0 < o1 ? x0 : o1;
-        // my x1 (index 32+lane) vs partner index 31-lane = x0 of lane (31-lane): keep max
-        const u64 n1 = x1 > o0 ? x1 : o0;
-        x0 = n0; x1 = n1;
-    }
-#pragma unroll
-    for (int m = 16; m > 0; m >>= 1) {
-        const bool up = (lane & m) != 0;
-        ce_lane(x0, m, up);
-        ce_lane(x1, m, up);
-    }
-}
-
-// Bitonic network with every compare-exchange ascending (mirror first step), so a virtual
-// +inf padding beyond n never moves: pairs whose upper index is >= n are simply skipped in
-// shared memory, and windows are padded with ~0 in registers.  Strides >= 64 go through
-// shared memory with a block barrier per step; strides <= 32 run in registers on 64-element
-// windows (one warp per window) with shuffles.
-__device__ void bitonic_sort(u64* a, int n)
-{
-    int n_pad = 64, lg = 6;
-    while (n_pad < n) { n_pad <<= 1; ++lg; }
-    const int half = n_pad >> 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n_win = n_pad >> 6;
-    const u64 INF = ~0ull;
-    // phase 0: sort every 64-window
-    for (int w = warp; w < n_win; w += YPP_ORG_THREADS / 32) {
-        const int i0 = (w << 6) + lane, i1 = i0 + 32;
-        u64 x0 = i0 < n ? a[i0] : INF, x1 = i1 < n ? a[i1] : INF;
-        sort64(x0, x1, lane);
-        if (i0 < n) a[i0] = x0;
-        if (i1 < n) a[i1] = x1;
+    const int R = 1 << bw;
+    const u32 dmask = (u32)R - 1u;
+    for (int i = tid; i < R * YPP_TABLE_PITCH; i += YPP_ORG_THREADS) table[i] = 0;
+    __syncthreads();
+    const int r_begin = warp * L, r_end = min(n, r_begin + L);
+    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
+        const int r = r0 + lane;
+        const bool ok = r < r_end;
+        int d = R + lane;                                  // matches nobody
+        if (ok) d = (int)((((u32)(src[r] >> 32) - kmin) >> shift) & dmask);
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
+        if (ok && (peers & ((1u << lane) - 1u)) == 0) table[d * YPP_TABLE_PITCH + warp] += __popc(peers);
+        __syncwarp();
     }
     __syncthreads();
-    for (int lk = 7; lk <= lg; ++lk) {
-        const int k = 1 << lk, hk = k >> 1;
-        // mirror step: pair r of block blk: (blk*k + r, blk*k + k-1-r)
-        for (int t = tid; t < half; t += YPP_ORG_THREADS) {
-            const int blk = t >> (lk - 1), r = t & (hk - 1);
-            const int i = (blk << lk) + r, l = (blk << lk) + (k - 1 - r);
-            if (l < n) ce(a, i, l);
+    // exclusive scan in (digit, warp) order; logical entry e = digit * 32 + warp
+    {
+        const int E = R * 32;
+        const int ipt = max(1, E / YPP_ORG_THREADS);       // R/32 entries per thread (R >= 32) else 1
+        const int e0 = tid * ipt;
+        int vals[YPP_RADIX_MAX / 32];
+        int sum = 0;
+#pragma unroll
+        for (int k = 0; k < YPP_RADIX_MAX / 32; ++k) {
+            vals[k] = 0;
+            const int e = e0 + k;
+            if (k < ipt && e < E) { vals[k] = table[(e >> 5) * YPP_TABLE_PITCH + (e & 31)]; sum += vals[k]; }
         }
-        __syncthreads();
-        for (int lj = lk - 2; lj >= 6; --lj) {
-            const int j = 1 << lj;
-            for (int t = tid; t < half; t += YPP_ORG_THREADS) {
-                const int blk = t >> lj, r = t & (j - 1);
-                const int i = (blk << (lj + 1)) + r, l = i + j;
-                if (l < n) ce(a, i, l);
-            }
-            __syncthreads();
+        int total;
+        int run = block_exclusive_scan(sum, warp_sums, total);
+#pragma unroll
+        for (int k = 0; k < YPP_RADIX_MAX / 32; ++k) {
+            const int e = e0 + k;
+            if (k < ipt && e < E) { table[(e >> 5) * YPP_TABLE_PITCH + (e & 31)] = run; run += vals[k]; }
         }
-        // strides 32..1 in registers
-        for (int w = warp; w < n_win; w += YPP_ORG_THREADS / 32) {
-            const int i0 = (w << 6) + lane, i1 = i0 + 32;
-            if ((w << 6) >= n) continue;
-            u64 x0 = i0 < n ? a[i0] : INF, x1 = i1 < n ? a[i1] : INF;
-            merge64_tail(x0, x1, lane);
-            if (i0 < n) a[i0] = x0;
-            if (i1 < n) a[i1] = x1;
-        }
-        __syncthreads();
     }
+    __syncthreads();
+    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
+        const int r = r0 + lane;
+        const bool ok = r < r_end;
+        u64 k = 0;
+        int d = R + lane;
+        if (ok) { k = src[r]; d = (int)((((u32)(k >> 32) - kmin) >> shift) & dmask); }
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        int base = 0;
+        if (ok) base = table[d * YPP_TABLE_PITCH + warp];
+        __syncwarp();
+        if (ok) {
+            if (rank == 0) table[d * YPP_TABLE_PITCH + warp] = base + __popc(peers);
+            dst[base + rank] = k;
+        }
+        __syncwarp();
+    }
+    __syncthreads();
 }
 
 __global__ void __launch_bounds__(YPP_ORG_THREADS, 1)
@@ -168,48 +143,115 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     OrgSmemHeader* hd = reinterpret_cast<OrgSmemHeader*>(smem_raw);
-    int* table = reinterpret_cast<int*>(smem_raw + sizeof(OrgSmemHeader));   // [32][nc]
-    int* seg = table + 32 * p.nc;                                            // [nc+1]
-    size_t koff = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)(33 * p.nc + 1);
-    koff = (koff + 15) / 16 * 16;
+    int* table = reinterpret_cast<int*>(smem_raw + sizeof(OrgSmemHeader));   // radix counters / tile offsets / class table
+    int* seg = table + 32 * p.nc;                                            // [nc+1] (class-table phase)
+    const size_t koff = (sizeof(OrgSmemHeader) + sizeof(int) * (size_t)p.table_ints + 15) / 16 * 16;
 
     const int b = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nc = p.nc, N = p.N;
-    const int n = min(p.ws.cand_count[b], N);
-    u64* gkeys = p.ws.keys + (size_t)b * N;
-    u64* keys = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : gkeys;
+    const u64* gkeys = p.ws.keys + (size_t)b * N;
+    u64* skeys = p.ws.skeys + (size_t)b * N;
+    float4* sbox = p.ws.sbox + (size_t)b * N;
+    int* grank = p.ws.grank + (size_t)b * N;
     int* gseg = p.ws.seg_start + (size_t)b * (nc + 1);
+    // ping-pong buffers of the sort: shared memory when two copies fit, else global (skeys / the
+    // not-yet-written sbox region)
+    u64* bufA = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : skeys;
+    u64* bufB = p.keys_in_smem ? bufA + N : reinterpret_cast<u64*>(sbox);
 
+    // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema
+    const int ntiles = min(*p.ws.ntiles, p.ws.tiles_max);
+    const int* tcnt = p.ws.tile_cnt + (size_t)b * p.ws.tiles_max;
+    int* tile_off = table;                                   // [ntiles + 1], dead before the first radix pass
+    if (warp == 0) {
+        const uint4* text = reinterpret_cast<const uint4*>(p.ws.tile_ext) + (size_t)b * p.ws.tiles_max;
+        int run = 0;
+        u32 M = 0, NX = 0, NY = 0;
+        for (int t0 = 0; t0 < ntiles; t0 += 32) {
+            const int t = t0 + lane;
+            const int v = t < ntiles ? tcnt[t] : 0;
+            if (v > 0) { const uint4 e = text[t]; M = max(M, e.x); NX = max(NX, e.y); NY = max(NY, e.z); }
+            int inc = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (t < ntiles) tile_off[t] = run + inc - v;
+            run += __shfl_sync(YPP_FULL_MASK, inc, 31);
+        }
+        M = __reduce_max_sync(YPP_FULL_MASK, M);
+        NX = __reduce_max_sync(YPP_FULL_MASK, NX);
+        NY = __reduce_max_sync(YPP_FULL_MASK, NY);
+        if (lane == 0) {
+            tile_off[ntiles] = run;
+            hd->n = min(run, N);
+            hd->maxc = M; hd->nminx1 = NX; hd->nminy1 = NY;
+            hd->n_low = 0; hd->n_high = 0; hd->flagged = 0;
+            hd->kmin = 0xffffffffu; hd->kmax = 0u;
+            p.ws.cand_count[b] = min(run, N);
+            p.ws.keep_count[b] = 0;
+            p.ws.imgflag[b] = 0;
+        }
+    }
+    if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
+    __syncthreads();
+    const int n = hd->n;
     if (n == 0) {
         for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = 0;
         return;
     }
-    if (p.keys_in_smem) {
-        for (int i = tid; i < n; i += YPP_ORG_THREADS) keys[i] = gkeys[i];
+    // ---- 2. gather the tiles (warp per tile), track the range of the score words
+    {
+        u32 kmin = 0xffffffffu, kmax = 0u;
+        for (int t = warp; t < ntiles; t += YPP_ORG_WARPS) {
+            const int cnt = tile_off[t + 1] - tile_off[t];
+            if (cnt <= 0) continue;
+            const u64* src = gkeys + p.ws.tile_first[t];
+            u64* dst = bufA + tile_off[t];
+            for (int i = lane; i < cnt; i += 32) {
+                const u64 k = src[i];
+                dst[i] = k;
+                const u32 hi = (u32)(k >> 32);
+                kmin = min(kmin, hi); kmax = max(kmax, hi);
+            }
+        }
+        kmin = __reduce_min_sync(YPP_FULL_MASK, kmin);
+        kmax = __reduce_max_sync(YPP_FULL_MASK, kmax);
+        if (lane == 0) { atomicMin(&hd->kmin, kmin); atomicMax(&hd->kmax, kmax); }
+        unsigned char* kf = p.ws.keepflag + (size_t)b * N;
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) kf[i] = 0;
     }
-    if (tid == 0) { hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; }
-    if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
-    for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
-    unsigned char* kf = p.ws.keepflag + (size_t)b * N;
-    for (int i = tid; i < n; i += YPP_ORG_THREADS) kf[i] = 0;
     __syncthreads();
-
-    bitonic_sort(keys, n);       // ends with __syncthreads()
-
-    if (p.keys_in_smem) {
-        for (int i = tid; i < n; i += YPP_ORG_THREADS) gkeys[i] = keys[i];
+    // ---- 3. stable sort by score word
+    const int L = ((n + 31) / 32 + 31) / 32 * 32;            // ranks per warp, multiple of 32
+    u64* keys = bufA;                                        // where the sorted keys end up
+    {
+        const u32 kmin = hd->kmin, span = hd->kmax - kmin;
+        const int bits = 32 - __clz(span);                   // 0 when every score is equal: already in order
+        const int passes = (bits + 7) / 8;
+        const int bw = passes ? (bits + passes - 1) / passes : 0;
+        u64* other = bufB;
+        for (int ps = 0; ps < passes; ++ps) {
+            radix_pass(keys, other, n, L, ps * bw, bw, kmin, table, hd->warp_sums);
+            u64* t = keys; keys = other; other = t;
+        }
+    }
+    if (keys != skeys) {
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) skeys[i] = keys[i];
+        if (!p.keys_in_smem) { __syncthreads(); keys = skeys; }   // global mode: the sbox region is about to be overwritten
     }
 
     // ---- which torchvision path would run for this image
     bool trick = p.offset_mode == YPP_OFFSET_TRICK;
     if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
     if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
-    const float M = ypp_dec(p.ws.maxc[b]);
+    const float M = ypp_dec(hd->maxc);
     const float step = __fadd_rn(M, 1.0f);                 // max_coordinate + 1
     DetGeom dg;
     dg.step = step;
-    dg.x1min = -ypp_dec(p.ws.nminx1[b]);
+    dg.x1min = -ypp_dec(hd->nminx1);
     dg.slack = fmaf(fabsf(step) * (float)nc, 1e-6f, 1e-3f);
     dg.lim = -1.0f + dg.slack;
     // no detector when offsets are not finite (every shifted IoU is NaN on both paths) or when no
@@ -220,29 +262,30 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         dg.inv_w = (range > 64.0f * 4.0f * dg.slack) ? (float)YPP_DET_BINS / range : 0.0f;
     }
     const bool detect = dg.on;
-    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
-
     const float4* gbox = p.ws.box + (size_t)b * N;
 
-    // ---- stable partition by class: warp w owns ranks [w*L, (w+1)*L)
-    const int L = ((n + 31) / 32 + 31) / 32 * 32;
+    // ---- 4a. class counting (warp w owns ranks [w*L, (w+1)*L)) and the detector's staircase bins
+    __syncthreads();                                         // table is free again
+    for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
+    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
+    __syncthreads();
     const int r_begin = warp * L, r_end = min(n, r_begin + L);
     int* my = table + warp * nc;
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        u64 k = 0;
-        if (ok) k = keys[r];
-        const int c = ok ? ypp_key_cls(k) : -1 - lane;
+        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
         const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
         if (ok && (peers & ((1u << lane) - 1u)) == 0) my[c] += __popc(peers);
-        if (detect && ok) {
-            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+        __syncwarp();
+    }
+    if (detect) {
+        for (int r = tid; r < n; r += YPP_ORG_THREADS) {
+            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(keys[r])]);
             const float u = xy.z - step, v = xy.w - step;
             if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
             if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
         }
-        __syncwarp();
     }
     __syncthreads();
     if (detect && warp == 1) {
@@ -291,55 +334,58 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     __syncthreads();
 
-    float4* sbox = p.ws.sbox + (size_t)b * N;
-    int* grank = p.ws.grank + (size_t)b * N;
-
+    // ---- 4b. stable ranking: segment position of every global rank
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        u64 k = 0;
-        int c = -1 - lane;
-        if (ok) { k = keys[r]; c = ypp_key_cls(k); }
+        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
         const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         int q = 0;
         if (ok) q = my[c] + rank;
         __syncwarp();
-        if (ok && rank == 0) my[c] += __popc(peers);
-        __syncwarp();
         if (ok) {
-            const float4 cb = gbox[ypp_key_idx(k)];
-            float4 xy = ypp_xyxy(cb);
-            if (detect) {
-                // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
-                bool is_low = false, is_high = false;
-                if (xy.x < dg.lim && xy.y < dg.lim) {
-                    const int j = max(det_bin(dg, xy.x) - 1, 0);
-                    const u32 e = hd->bin_hi[j];
-                    is_low = e != 0 && xy.y < ypp_dec(e) + dg.slack;
-                }
-                const float u = xy.z - step, v = xy.w - step;
-                if (u > dg.x1min - dg.slack) {
-                    const int i = min(det_bin(dg, u) + 1, YPP_DET_BINS - 1);
-                    const u32 e = hd->bin_lo[i];
-                    is_high = e != 0 && v > -ypp_dec(e) - dg.slack;
-                }
-                if (is_low || is_high) {
-                    const float off = __fmul_rn((float)c, step);
-                    DetEntry e;
-                    e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-                    e.cls = c; e.rank = r;
-                    if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
-                    if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
-                }
-            }
-            if (trick) {
-                const float off = __fmul_rn((float)c, step);    // idxs.to(boxes) * (max_coordinate + 1)
-                xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-            }
-            sbox[q] = xy;
+            if (rank == 0) my[c] += __popc(peers);
             grank[q] = r;
         }
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- 4c. emission in segment order (coalesced writes, independent gathers)
+    for (int q = tid; q < n; q += YPP_ORG_THREADS) {
+        const int r = grank[q];
+        const u64 k = keys[r];
+        const int c = ypp_key_cls(k);
+        float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+        if (detect) {
+            // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
+            bool is_low = false, is_high = false;
+            if (xy.x < dg.lim && xy.y < dg.lim) {
+                const int j = max(det_bin(dg, xy.x) - 1, 0);
+                const u32 e = hd->bin_hi[j];
+                is_low = e != 0 && xy.y < ypp_dec(e) + dg.slack;
+            }
+            const float u = xy.z - step, v = xy.w - step;
+            if (u > dg.x1min - dg.slack) {
+                const int i = min(det_bin(dg, u) + 1, YPP_DET_BINS - 1);
+                const u32 e = hd->bin_lo[i];
+                is_high = e != 0 && v > -ypp_dec(e) - dg.slack;
+            }
+            if (is_low || is_high) {
+                const float off = __fmul_rn((float)c, step);
+                DetEntry e;
+                e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                e.cls = c; e.rank = r;
+                if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
+                if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
+            }
+        }
+        if (trick) {
+            const float off = __fmul_rn((float)c, step);    // idxs.to(boxes) * (max_coordinate + 1)
+            xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+        }
+        sbox[q] = xy;
     }
     __syncthreads();
 
@@ -382,37 +428,47 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
         if (seg[c + 1] - seg[c] > YPP_WARP_SEG) {
             const int s = atomicAdd(p.ws.q, 1);
-            p.ws.bigq[s] = b * nc + c;
+            if (s < p.B * p.ws.bigq_per_image) p.ws.bigq[s] = b * nc + c;
         }
     }
 }
 
 }  // namespace
 
-int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem)
+// shared memory: header + max(radix table, class table, tile offsets) + (two key buffers when they fit)
+int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
 {
-    size_t fixed = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)(33 * nc + 1);
+    int tints = YPP_RADIX_MAX * YPP_TABLE_PITCH;
+    if (33 * nc + 1 > tints) tints = 33 * nc + 1;
+    const int tiles_max = N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8;
+    if (tiles_max + 1 > tints) tints = tiles_max + 1;
+    *table_ints = tints;
+    size_t fixed = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)tints;
     fixed = (fixed + 15) / 16 * 16;
     const size_t cap = 227 * 1024;
     if (fixed > cap) return -1;
-    if (fixed + (size_t)N * 8 <= cap) { *keys_in_smem = 1; return (int)(fixed + (size_t)N * 8); }
+    if (fixed + (size_t)N * 16 <= cap) { *keys_in_smem = 1; return (int)(fixed + (size_t)N * 16); }
     *keys_in_smem = 0;
     return (int)fixed;
 }
 
 int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
 {
-    int kin = 0;
-    const int smem = ypp_org_smem_bytes(p.N, p.nc, &kin);
+    int kin = 0, tints = 0;
+    const int smem = ypp_org_smem_bytes(p.N, p.nc, &kin, &tints);
     if (smem < 0) { ypp_set_error("organise: nc=%d needs more shared memory than one CTA has", p.nc); return YPP_E_UNSUPPORTED; }
     YppOrgParams q = p;
     q.keys_in_smem = kin;
+    q.table_ints = tints;
     static int configured_smem = 0;
     if (smem > configured_smem) {
         cudaError_t e = cudaFuncSetAttribute(ypp_organise_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) { ypp_set_error("organise: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
         configured_smem = 227 * 1024;
     }
+    // the long-segment queue header is the only state S1 appends to across CTAs
+    cudaError_t e = cudaMemsetAsync(p.ws.q, 0, sizeof(int) * 4, st);
+    if (e != cudaSuccess) { ypp_set_error("organise: memset: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
     ypp_organise_kernel<<<p.B, YPP_ORG_THREADS, smem, st>>>(q);
     ypp_count_launch(1);
     return ypp_check_launch("organise");

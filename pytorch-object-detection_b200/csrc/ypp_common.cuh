@@ -20,33 +20,31 @@ typedef unsigned int u32;
 #define YPP_BIG_CACHE 11264
 #define YPP_NMS_BIG_THREADS 1024
 #define YPP_ORG_THREADS 1024
-#ifndef YPP_DECODE_THREADS
-#define YPP_DECODE_THREADS 256
-#endif
-#ifndef YPP_DECODE_MINB
-#define YPP_DECODE_MINB 3
-#endif
+#define YPP_DECODE_THREADS 256     // == YPP_TILE_BOXES
 
 // ---------------------------------------------------------------- workspace layout
-// All per-image arrays are [B][N]; the counter block is zeroed by one memset per call.
+// All per-image arrays are [B][N].  Nothing needs a memset between calls: D1 owns the tile
+// records, S1 (re)initialises the per-image counters, and the 16-byte queue header is cleared
+// by the S1 launcher.
+#define YPP_TILE_BOXES 256        // boxes per D1 tile (one per thread)
 struct YppWs {
-    // counter block (zero-initialised each call)
-    int* cand_count;      // [B]
-    int* keep_count;      // [B]
-    u32* maxc;            // [B] order-encoded max over candidate x1,y1,x2,y2
-    u32* nminx1;          // [B] order-encoded max of -x1  (=> min x1)
-    u32* nminy1;          // [B] order-encoded max of -y1
+    int* cand_count;      // [B] written by S1
+    int* keep_count;      // [B] zeroed by S1, accumulated by N1
     int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge)
-    int* q;               // [4] q[0] big-segment queue length, q[1] queue head, q[2] error bits
-    size_t counter_bytes;
-    // arrays
+    int* q;               // [4] q[0] long-segment queue length, q[1] queue head
+    int* ntiles;          // [1] D1 tiles per image
+    int* tile_first;      // [T] first box index of each D1 tile (the same for every image)
+    int* tile_cnt;        // [B][T] candidates each tile produced (compacted at keys[b][tile_first ..])
+    u32* tile_ext;        // [B][T][4] order-encoded max(x1,y1,x2,y2), max(-x1), max(-y1) over the tile's candidates
     int* bigq;            // [B * bigq_per_image] entries b*nc + c
     int* seg_start;       // [B][nc+1] segment starts in class order
-    u64* keys;            // [B][N] (~enc(score))<<32 | idx<<12 | cls ; sorted in place by S1
+    u64* keys;            // [B][N] (~enc(score))<<32 | idx<<12 | cls, compacted per tile by D1 (box-index order)
+    u64* skeys;           // [B][N] the same keys in stable descending-score order (S1)
     float4* box;          // [B][N] cx,cy,w,h indexed by box index n
     float4* sbox;         // [B][N] x1,y1,x2,y2 (+ class offset) in class-segment order
     int* grank;           // [B][N] class-order position -> global score rank
     unsigned char* keepflag;  // [B][N] by global score rank
+    int tiles_max;
     int bigq_per_image;
     size_t total_bytes;
 };
@@ -59,21 +57,23 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     char* p = (char*)base;
     size_t off = 0;
     auto take = [&](size_t bytes) { char* r = p + off; off += ypp_align_up(bytes, 256); return r; };
-    size_t c0 = off;
     w.cand_count = (int*)take(sizeof(int) * B);
     w.keep_count = (int*)take(sizeof(int) * B);
-    w.maxc = (u32*)take(sizeof(u32) * B);
-    w.nminx1 = (u32*)take(sizeof(u32) * B);
-    w.nminy1 = (u32*)take(sizeof(u32) * B);
     w.imgflag = (int*)take(sizeof(int) * B);
     w.q = (int*)take(sizeof(int) * 4);
-    w.counter_bytes = off - c0;
+    w.ntiles = (int*)take(sizeof(int));
+    // a tile never spans two anchor planes, so a scale adds at most A partial tiles
+    w.tiles_max = N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8;
+    w.tile_first = (int*)take(sizeof(int) * w.tiles_max);
+    w.tile_cnt = (int*)take(sizeof(int) * (size_t)B * w.tiles_max);
+    w.tile_ext = (u32*)take(sizeof(u32) * 4 * (size_t)B * w.tiles_max);
     int per = N / YPP_WARP_SEG + 1;
     if (per > nc) per = nc;
     w.bigq_per_image = per;
     w.bigq = (int*)take(sizeof(int) * (size_t)B * per);
     w.seg_start = (int*)take(sizeof(int) * (size_t)B * (nc + 1));
     w.keys = (u64*)take(sizeof(u64) * (size_t)B * N);
+    w.skeys = (u64*)take(sizeof(u64) * (size_t)B * N);
     w.box = (float4*)take(sizeof(float4) * (size_t)B * N);
     w.sbox = (float4*)take(sizeof(float4) * (size_t)B * N);
     w.grank = (int*)take(sizeof(int) * (size_t)B * N);

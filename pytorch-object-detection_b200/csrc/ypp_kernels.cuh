@@ -6,8 +6,8 @@ struct YppScaleParams {
     const float* head;
     int A, H, W, HW;
     int box_base;        // first box index of this scale inside the image (cat order)
-    int vec;             // cells per thread: 4 when H*W % 4 == 0 and the head is 16 B aligned, else 1
-    int units;           // A*HW/vec work items per image
+    int tma;             // 1: planes staged with cp.async.bulk (H*W % 4 == 0, head 16 B aligned); 0: plain loads
+    int tpp;             // tiles per anchor plane = ceil(HW / YPP_TILE_BOXES)
     float aw[YPP_MAX_ANCHORS], ah[YPP_MAX_ANCHORS];
     float sw, sh;
 };
@@ -18,6 +18,7 @@ struct YppDecodeParams {
     int n_scales, nc, C, N;
     float conf;
     int score_mode;
+    int stage_bytes;     // dynamic shared memory of the staged path (0 when no scale uses it)
     YppWs ws;
 };
 
@@ -57,7 +58,7 @@ int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const Y
 int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st);
 int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st);
 int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st);
-int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem);
+int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints);
 
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
                            float* out, int* gt_count, cudaStream_t st);

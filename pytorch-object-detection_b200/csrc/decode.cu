@@ -4,7 +4,7 @@
 // utils/yolov2_utils.py:12-58; the threshold is the torch.where of nms_v3,
 // utils/yolo_utils.py:334.
 //
-// One pass over the NCHW head.  A CTA owns one tile = up to 256 consecutive cells of one anchor
+// One pass over the NCHW head by persistent CTAs.  A tile = up to 256 consecutive cells of one anchor
 // plane group: its C = 5+nc channel rows (256 floats each, contiguous in the NCHW tensor) are
 // pulled into shared memory by the async-copy engine (cp.async.bulk, one bulk copy per channel
 // row, completion on an mbarrier), so the whole tile is in flight at once without holding
@@ -110,12 +110,14 @@ struct CompactSmem {
     u32 warp_max[YPP_DECODE_THREADS / 32], warp_nx[YPP_DECODE_THREADS / 32], warp_ny[YPP_DECODE_THREADS / 32];
 };
 
-__device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int tile, int first, CompactSmem& sm,
-                                              bool pass, const float4 box, const float score, const int cls, int idx)
+// part 1: ballots and per-warp records (ends before the block barrier the caller places)
+struct CompactLocal { u32 m; };
+
+__device__ __forceinline__ CompactLocal compact_count(CompactSmem& sm, bool pass, const float4 box)
 {
-    constexpr int NW = YPP_DECODE_THREADS / 32;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const u32 m = __ballot_sync(YPP_FULL_MASK, pass);
+    CompactLocal cl;
+    cl.m = __ballot_sync(YPP_FULL_MASK, pass);
     // per-tile extrema for the coordinate trick / cross-class detector
     u32 emax = 0, enx = 0, eny = 0;
     if (pass) {
@@ -124,13 +126,22 @@ __device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int
         enx = ypp_enc(-q.x);
         eny = ypp_enc(-q.y);
     }
-    if (m) {                                       // warp-uniform
+    if (cl.m) {                                    // warp-uniform
         emax = __reduce_max_sync(YPP_FULL_MASK, emax);
         enx = __reduce_max_sync(YPP_FULL_MASK, enx);
         eny = __reduce_max_sync(YPP_FULL_MASK, eny);
     }
-    if (lane == 0) { sm.warp_cnt[warp] = __popc(m); sm.warp_max[warp] = emax; sm.warp_nx[warp] = enx; sm.warp_ny[warp] = eny; }
-    __syncthreads();
+    if (lane == 0) { sm.warp_cnt[warp] = __popc(cl.m); sm.warp_max[warp] = emax; sm.warp_nx[warp] = enx; sm.warp_ny[warp] = eny; }
+    return cl;
+}
+
+// part 2 (after the block barrier): tile record + stores
+__device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int tile, int ntiles, int first,
+                                              const CompactSmem& sm, const CompactLocal cl, bool pass,
+                                              const float4 box, const float score, const int cls, int idx)
+{
+    constexpr int NW = YPP_DECODE_THREADS / 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int before = 0, total = 0;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
@@ -146,11 +157,11 @@ __device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int
         *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + tile)) = make_uint4(M, NX, NY, 0u);
         if (b == 0) {
             ws.tile_first[tile] = first;
-            if (tile == 0) *ws.ntiles = (int)gridDim.x;
+            if (tile == 0) *ws.ntiles = ntiles;
         }
     }
     if (pass) {
-        const int pos = first + before + __popc(m & ((1u << lane) - 1u));
+        const int pos = first + before + __popc(cl.m & ((1u << lane) - 1u));
         ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
         ws.box[(size_t)b * N + idx] = box;
     }
@@ -205,70 +216,99 @@ __device__ __forceinline__ TileRef tile_ref(const YppDecodeParams& p, int bx)
     return t;
 }
 
-__global__ void __launch_bounds__(YPP_DECODE_THREADS)
-ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p)
+// warp 0: start the bulk copies of work item `w` (tile of image b) into stage `stg`
+__device__ __forceinline__ void issue_tile(const YppDecodeParams& p, long long w, int tiles_per_img, float* stage, u64* bar)
 {
-    extern __shared__ __align__(128) float stage[];          // [C][256] when the tile is staged
-    __shared__ CompactSmem sm;
-    __shared__ __align__(8) u64 mbar;
-    const int b = blockIdx.y, tid = threadIdx.x;
-    const TileRef t = tile_ref(p, (int)blockIdx.x);
+    const int b = (int)(w / tiles_per_img);
+    const TileRef t = tile_ref(p, (int)(w - (long long)b * tiles_per_img));
     const YppScaleParams& s = p.sc[t.si];
-    const int C = p.C, HW = s.HW;
-    const float* src = s.head + ((size_t)(b * s.A + t.a) * C) * HW + t.cell0;      // channel 0 of this tile
-    const bool valid = tid < t.ncells;
-    const int cell = t.cell0 + tid;
+    if (!s.tma) return;
+    const int lane = threadIdx.x & 31;
+    const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
+    const u32 row_bytes = (u32)t.ncells * 4u;                // multiple of 16: HW % 4 == 0
+    if (lane == 0) mbar_expect_tx(bar, row_bytes * (u32)p.C);
+    __syncwarp();
+    for (int c = lane; c < p.C; c += 32)
+        bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, bar);
+}
 
-    bool pass = false;
-    Decoded d;
-    d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
-    if (s.tma) {
-        if (tid == 0) mbar_init(&mbar, 1);
-        __syncthreads();
-        if (tid < 32) {
-            const u32 row_bytes = (u32)t.ncells * 4u;            // multiple of 16: HW % 4 == 0
-            if (tid == 0) mbar_expect_tx(&mbar, row_bytes * (u32)C);
-            __syncwarp();
-            for (int c = tid; c < C; c += 32)
-                bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * HW, row_bytes, &mbar);
-        }
-        mbar_wait(&mbar, 0);
-        const float* col = stage + tid;
-        float sobj = 0.f;
-        if (valid) {
-            sobj = ypp_sigmoid(col[4 * YPP_TILE_BOXES]);                 // yolov3_utils.py:50
-            pass = sobj > p.conf;                                        // yolo_utils.py:334 (strict)
-        }
-        if (__any_sync(YPP_FULL_MASK, pass)) {
-            ClsTrack tr;
-            if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES, p.nc, tr);
-            else cls_init(tr);
-            if (pass) {
-                d = decode_cell(p, s, t.a, cell, col[0], col[YPP_TILE_BOXES], col[2 * YPP_TILE_BOXES], col[3 * YPP_TILE_BOXES],
-                                sobj, tr, col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES);
-                if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
-            }
-        }
-    } else {
-        const float* col = src + tid;
-        float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
-        if (valid) {
-            const float obj = __ldg(col + 4 * (size_t)HW);
-            t0 = __ldg(col); t1 = __ldg(col + HW); t2 = __ldg(col + 2 * (size_t)HW); t3 = __ldg(col + 3 * (size_t)HW);
-            sobj = ypp_sigmoid(obj);
-            pass = sobj > p.conf;
-        }
-        if (__any_sync(YPP_FULL_MASK, pass)) {
-            if (pass) {
-                ClsTrack tr;
-                if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)HW, HW, p.nc, tr);
-                else cls_init(tr);
-                d = decode_cell(p, s, t.a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)HW, HW);
-                if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
-            }
-        }
+// Persistent CTAs walk the (image, tile) space with a two-stage pipeline: while tile k is decoded
+// out of one stage, the copies of tile k+1 are already in flight into the other.
+__global__ void __launch_bounds__(YPP_DECODE_THREADS)
+ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B)
+{
+    extern __shared__ __align__(128) float stage_mem[];      // [2][C][256] when some scale is staged
+    __shared__ CompactSmem sm[2];
+    __shared__ __align__(8) u64 mbar[2];
+    const int tid = threadIdx.x;
+    const int tiles_per_img = p.tile_base[p.n_scales];
+    const long long total = (long long)tiles_per_img * B;
+    const long long G = gridDim.x;
+    const int stage_floats = p.C * YPP_TILE_BOXES;
+    if (tid == 0) { mbar_init(&mbar[0], 1); mbar_init(&mbar[1], 1); }
+    __syncthreads();
+    if (tid < 32) {
+        if ((long long)blockIdx.x < total) issue_tile(p, blockIdx.x, tiles_per_img, stage_mem, &mbar[0]);
+        if ((long long)blockIdx.x + G < total) issue_tile(p, blockIdx.x + G, tiles_per_img, stage_mem + stage_floats, &mbar[1]);
     }
-    compact_store(p.ws, p.N, b, (int)blockIdx.x, t.first, sm, pass, d.box, d.score, d.cls, t.first + tid);
+    u32 uses0 = 0, uses1 = 0;                                 // completed phases of each barrier
+    int k = 0;
+    for (long long w = blockIdx.x; w < total; w += G, ++k) {
+        const int stg = k & 1;
+        const int b = (int)(w / tiles_per_img);
+        const int tile = (int)(w - (long long)b * tiles_per_img);
+        const TileRef t = tile_ref(p, tile);
+        const YppScaleParams& s = p.sc[t.si];
+        const int C = p.C, HW = s.HW;
+        const bool valid = tid < t.ncells;
+        const int cell = t.cell0 + tid;
+        bool pass = false;
+        Decoded d;
+        d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
+        if (s.tma) {
+            const u32 parity = (stg ? uses1 : uses0) & 1u;
+            mbar_wait(&mbar[stg], parity);
+            if (stg) ++uses1; else ++uses0;
+            const float* col = stage_mem + stg * stage_floats + tid;
+            float sobj = 0.f;
+            if (valid) {
+                sobj = ypp_sigmoid(col[4 * YPP_TILE_BOXES]);                 // yolov3_utils.py:50
+                pass = sobj > p.conf;                                        // yolo_utils.py:334 (strict)
+            }
+            if (__any_sync(YPP_FULL_MASK, pass)) {
+                ClsTrack tr;
+                if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES, p.nc, tr);
+                else cls_init(tr);
+                if (pass) {
+                    d = decode_cell(p, s, t.a, cell, col[0], col[YPP_TILE_BOXES], col[2 * YPP_TILE_BOXES], col[3 * YPP_TILE_BOXES],
+                                    sobj, tr, col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES);
+                    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
+                }
+            }
+        } else {
+            const float* col = s.head + ((size_t)(b * s.A + t.a) * C) * HW + cell;
+            float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
+            if (valid) {
+                const float obj = __ldg(col + 4 * (size_t)HW);
+                t0 = __ldg(col); t1 = __ldg(col + HW); t2 = __ldg(col + 2 * (size_t)HW); t3 = __ldg(col + 3 * (size_t)HW);
+                sobj = ypp_sigmoid(obj);
+                pass = sobj > p.conf;
+            }
+            if (__any_sync(YPP_FULL_MASK, pass)) {
+                if (pass) {
+                    ClsTrack tr;
+                    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)HW, HW, p.nc, tr);
+                    else cls_init(tr);
+                    d = decode_cell(p, s, t.a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)HW, HW);
+                    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
+                }
+            }
+        }
+        const CompactLocal cl = compact_count(sm[stg], pass, d.box);
+        __syncthreads();                                       // every read of this stage is done
+        if (tid < 32 && w + 2 * G < total) issue_tile(p, w + 2 * G, tiles_per_img, stage_mem + stg * stage_floats, &mbar[stg]);
+        compact_store(p.ws, p.N, b, tile, tiles_per_img, t.first, sm[stg], cl, pass, d.box, d.score, d.cls, t.first + tid);
+    }
 }
 
 // ---- dense decode: every box, rows [B, N, 6] (= decode_predictions + cat) ---------------
@@ -317,7 +357,9 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
         cls = c;
         pass = score > conf;
     }
-    compact_store(ws, N, b, (int)blockIdx.x, first, sm, pass, box, score, cls, n);
+    const CompactLocal cl = compact_count(sm, pass, box);
+    __syncthreads();
+    compact_store(ws, N, b, (int)blockIdx.x, (int)gridDim.x, first, sm, cl, pass, box, score, cls, n);
 }
 
 }  // namespace
@@ -326,14 +368,24 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
 {
-    static int configured = 0;
-    if (p.stage_bytes > 48 * 1024 && p.stage_bytes > configured) {
-        cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, p.stage_bytes);
-        if (e != cudaSuccess) { ypp_set_error("decode_compact: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
-        configured = p.stage_bytes;
+    static int configured = -1, ctas_per_sm = 0, sms = 0;
+    const int smem = 2 * p.stage_bytes;
+    if (smem != configured) {
+        if (smem > 48 * 1024) {
+            cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            if (e != cudaSuccess) { ypp_set_error("decode_compact: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+        }
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, YPP_DECODE_THREADS, smem);
+        if (e != cudaSuccess || ctas_per_sm < 1) { ypp_set_error("decode_compact: occupancy query failed"); return YPP_E_CUDA; }
+        configured = smem;
     }
-    dim3 grid(p.tile_base[p.n_scales], B);
-    ypp_decode_compact_kernel<<<grid, YPP_DECODE_THREADS, p.stage_bytes, st>>>(p);
+    const long long total = (long long)p.tile_base[p.n_scales] * B;
+    long long grid = (long long)sms * ctas_per_sm;
+    if (grid > total) grid = total;
+    ypp_decode_compact_kernel<<<(unsigned)grid, YPP_DECODE_THREADS, smem, st>>>(p, B);
     ypp_count_launch(1);
     return ypp_check_launch("decode_compact");
 }

@@ -74,6 +74,19 @@ __device__ __forceinline__ int block_exclusive_scan(int v, int* warp_sums, int& 
     return wbase + inc - v;
 }
 
+// lanes of the warp that hold the same nbits-bit value (MATCH.ANY is far slower than nbits ballots
+// when every warp of the CTA is issuing it); lanes with ok == false belong to no group
+__device__ __forceinline__ u32 same_value_lanes(int v, int nbits, bool ok)
+{
+    u32 peers = __ballot_sync(YPP_FULL_MASK, ok);
+    for (int i = 0; i < nbits; ++i) {
+        const bool bit = (v >> i) & 1;
+        const u32 bal = __ballot_sync(YPP_FULL_MASK, bit);
+        peers &= bit ? bal : ~bal;
+    }
+    return peers;
+}
+
 // One stable LSD pass on digit ((key >> 32) - kmin) >> shift  (bw bits).  Warp w owns the contiguous
 // ranks [w*L, (w+1)*L) and walks them 32 at a time, so "warp order, then chunk order, then lane
 // order" is the input order; per (digit, warp) counters make the scatter stable.
@@ -89,9 +102,9 @@ __device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, in
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        int d = R + lane;                                  // matches nobody
+        int d = 0;
         if (ok) d = (int)((((u32)(src[r] >> 32) - kmin) >> shift) & dmask);
-        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
+        const unsigned peers = same_value_lanes(d, bw, ok);
         if (ok && (peers & ((1u << lane) - 1u)) == 0) table[d * YPP_TABLE_PITCH + warp] += __popc(peers);
         __syncwarp();
     }
@@ -122,9 +135,9 @@ __device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, in
         const int r = r0 + lane;
         const bool ok = r < r_end;
         u64 k = 0;
-        int d = R + lane;
+        int d = 0;
         if (ok) { k = src[r]; d = (int)((((u32)(k >> 32) - kmin) >> shift) & dmask); }
-        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
+        const unsigned peers = same_value_lanes(d, bw, ok);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         int base = 0;
         if (ok) base = table[d * YPP_TABLE_PITCH + warp];
@@ -270,21 +283,32 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
     __syncthreads();
     const int r_begin = warp * L, r_end = min(n, r_begin + L);
+    const int cbits = 32 - __clz(max(nc - 1, 1));            // bits of a class id
     int* my = table + warp * nc;
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
-        const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
+        const int c = ok ? ypp_key_cls(keys[r]) : 0;
+        const unsigned peers = same_value_lanes(c, cbits, ok);
         if (ok && (peers & ((1u << lane) - 1u)) == 0) my[c] += __popc(peers);
         __syncwarp();
     }
     if (detect) {
-        for (int r = tid; r < n; r += YPP_ORG_THREADS) {
-            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(keys[r])]);
-            const float u = xy.z - step, v = xy.w - step;
-            if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
-            if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
+        for (int r0 = tid; r0 < n; r0 += 4 * YPP_ORG_THREADS) {      // four independent gathers in flight
+            float4 bx[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int r = r0 + j * YPP_ORG_THREADS;
+                if (r < n) bx[j] = gbox[ypp_key_idx(keys[r])];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (r0 + j * YPP_ORG_THREADS >= n) break;
+                const float4 xy = ypp_xyxy(bx[j]);
+                const float u = xy.z - step, v = xy.w - step;
+                if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
+                if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
+            }
         }
     }
     __syncthreads();
@@ -338,8 +362,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        const int c = ok ? ypp_key_cls(keys[r]) : -1 - lane;
-        const unsigned peers = __match_any_sync(YPP_FULL_MASK, c);
+        const int c = ok ? ypp_key_cls(keys[r]) : 0;
+        const unsigned peers = same_value_lanes(c, cbits, ok);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         int q = 0;
         if (ok) q = my[c] + rank;
@@ -353,11 +377,24 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     __syncthreads();
 
     // ---- 4c. emission in segment order (coalesced writes, independent gathers)
-    for (int q = tid; q < n; q += YPP_ORG_THREADS) {
-        const int r = grank[q];
-        const u64 k = keys[r];
+    for (int q0 = tid; q0 < n; q0 += 4 * YPP_ORG_THREADS) {         // four independent gathers in flight
+      int rr[4];
+      u64 kk[4];
+      float4 bx[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { const int q = q0 + j * YPP_ORG_THREADS; rr[j] = q < n ? grank[q] : 0; }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) kk[j] = keys[rr[j]];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bx[j] = gbox[ypp_key_idx(kk[j])];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int q = q0 + j * YPP_ORG_THREADS;
+        if (q >= n) break;
+        const int r = rr[j];
+        const u64 k = kk[j];
         const int c = ypp_key_cls(k);
-        float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+        float4 xy = ypp_xyxy(bx[j]);
         if (detect) {
             // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
             bool is_low = false, is_high = false;
@@ -386,6 +423,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
         }
         sbox[q] = xy;
+      }
     }
     __syncthreads();
 

@@ -67,6 +67,7 @@ int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, Ypp
         if (d.tma) p->stage_bytes = p->C * YPP_TILE_BOXES * 4;
         for (int a = 0; a < s.A; ++a) { d.aw[a] = s.anchor_w[a]; d.ah[a] = s.anchor_h[a]; }
         d.sw = s.stride_w; d.sh = s.stride_h;
+        d.inv_w = 1.0f / (float)s.W;
         p->tile_base[i] = tile;
         tile += s.A * d.tpp;
         box_base += s.A * d.HW;

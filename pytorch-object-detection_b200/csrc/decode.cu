@@ -83,7 +83,11 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
                                                float t0, float t1, float t2, float t3, float sobj,
                                                const ClsTrack& tr, const float* cls_base, int cls_stride)
 {
-    const int y = cell / s.W, x = cell - y * s.W;
+    // y = cell / W without an integer division: float estimate, then one step of correction
+    int y = __float2int_rz(__fmul_rn((float)cell, s.inv_w));
+    int x = cell - y * s.W;
+    if (x < 0) { --y; x += s.W; }
+    if (x >= s.W) { ++y; x -= s.W; }
     Decoded d;
     // pxy = sigmoid(t) + grid, then *= stride (yolov3_utils.py:47,54)
     const float px = __fmul_rn(__fadd_rn(ypp_sigmoid(t0), (float)x), s.sw);
@@ -208,9 +212,10 @@ __device__ __forceinline__ TileRef tile_ref(const YppDecodeParams& p, int bx)
     for (int k = 1; k < YPP_MAX_SCALES; ++k)
         if (k < p.n_scales && bx >= p.tile_base[k]) t.si = k;
     const YppScaleParams& s = p.sc[t.si];
-    const int tl = bx - p.tile_base[t.si];
-    t.a = tl / s.tpp;
-    t.cell0 = (tl - t.a * s.tpp) * YPP_TILE_BOXES;
+    int tl = bx - p.tile_base[t.si];
+    t.a = 0;
+    while (tl >= s.tpp) { tl -= s.tpp; ++t.a; }            // A <= 8 uniform steps instead of a division
+    t.cell0 = tl * YPP_TILE_BOXES;
     t.ncells = min(YPP_TILE_BOXES, s.HW - t.cell0);
     t.first = s.box_base + t.a * s.HW + t.cell0;
     return t;
@@ -253,10 +258,11 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
     }
     u32 uses0 = 0, uses1 = 0;                                 // completed phases of each barrier
     int k = 0;
-    for (long long w = blockIdx.x; w < total; w += G, ++k) {
+    int b = (int)(blockIdx.x / (unsigned)tiles_per_img), tile = (int)(blockIdx.x - (unsigned)b * (unsigned)tiles_per_img);
+    const int gb = (int)(gridDim.x / (unsigned)tiles_per_img), gt = (int)(gridDim.x - (unsigned)gb * (unsigned)tiles_per_img);
+    for (long long w = blockIdx.x; w < total; w += G, ++k, b += gb, tile += gt) {
+        if (tile >= tiles_per_img) { tile -= tiles_per_img; ++b; }
         const int stg = k & 1;
-        const int b = (int)(w / tiles_per_img);
-        const int tile = (int)(w - (long long)b * tiles_per_img);
         const TileRef t = tile_ref(p, tile);
         const YppScaleParams& s = p.sc[t.si];
         const int C = p.C, HW = s.HW;

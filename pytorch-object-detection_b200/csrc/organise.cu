@@ -102,11 +102,8 @@ __device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, in
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        int d = 0;
-        if (ok) d = (int)((((u32)(src[r] >> 32) - kmin) >> shift) & dmask);
-        const unsigned peers = same_value_lanes(d, bw, ok);
-        if (ok && (peers & ((1u << lane) - 1u)) == 0) table[d * YPP_TABLE_PITCH + warp] += __popc(peers);
-        __syncwarp();
+        // counting needs no order: shared-memory atomics (only this warp touches column `warp`)
+        if (ok) atomicAdd(&table[(int)((((u32)(src[r] >> 32) - kmin) >> shift) & dmask) * YPP_TABLE_PITCH + warp], 1);
     }
     __syncthreads();
     // exclusive scan in (digit, warp) order; logical entry e = digit * 32 + warp
@@ -288,10 +285,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        const int c = ok ? ypp_key_cls(keys[r]) : 0;
-        const unsigned peers = same_value_lanes(c, cbits, ok);
-        if (ok && (peers & ((1u << lane) - 1u)) == 0) my[c] += __popc(peers);
-        __syncwarp();
+        if (ok) atomicAdd(&my[ypp_key_cls(keys[r])], 1);
     }
     if (detect) {
         for (int r0 = tid; r0 < n; r0 += 4 * YPP_ORG_THREADS) {      // four independent gathers in flight

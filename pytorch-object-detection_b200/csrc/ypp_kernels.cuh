@@ -10,6 +10,7 @@ struct YppScaleParams {
     int tpp;             // tiles per anchor plane = ceil(HW / YPP_TILE_BOXES)
     float aw[YPP_MAX_ANCHORS], ah[YPP_MAX_ANCHORS];
     float sw, sh;
+    float inv_w;         // 1 / W
 };
 
 struct YppDecodeParams {

@@ -108,67 +108,78 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
     return d;
 }
 
-// ---- block-wide compaction of one candidate per thread, in thread (= box index) order ----
+// ---- block-wide compaction in box-index order ----------------------------------------------
+// A tile is split into 8 slots of 32 consecutive boxes; slot v is handled by one warp (one
+// ballot).  The decode kernel runs 4 warps x 2 boxes per thread (slots w and w + 4), the row
+// compaction kernel 8 warps x 1 box.
+#define YPP_SLOTS (YPP_TILE_BOXES / 32)
 struct CompactSmem {
-    int warp_cnt[YPP_DECODE_THREADS / 32];
-    u32 warp_max[YPP_DECODE_THREADS / 32], warp_nx[YPP_DECODE_THREADS / 32], warp_ny[YPP_DECODE_THREADS / 32];
+    int slot_cnt[YPP_SLOTS];
+    u32 slot_max[YPP_SLOTS], slot_nx[YPP_SLOTS], slot_ny[YPP_SLOTS];
 };
 
-// part 1: ballots and per-warp records (ends before the block barrier the caller places)
-struct CompactLocal { u32 m; };
-
-__device__ __forceinline__ CompactLocal compact_count(CompactSmem& sm, bool pass, const float4 box)
+// part 1: ballot and per-slot record (ends before the block barrier the caller places)
+__device__ __forceinline__ u32 compact_count(CompactSmem& sm, int slot, bool pass, const float4 box)
 {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    CompactLocal cl;
-    cl.m = __ballot_sync(YPP_FULL_MASK, pass);
-    // per-tile extrema for the coordinate trick / cross-class detector
-    u32 emax = 0, enx = 0, eny = 0;
-    if (pass) {
-        const float4 q = ypp_xyxy(box);
-        emax = max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w)));
-        enx = ypp_enc(-q.x);
-        eny = ypp_enc(-q.y);
-    }
-    if (cl.m) {                                    // warp-uniform
+    const int lane = threadIdx.x & 31;
+    const u32 m = __ballot_sync(YPP_FULL_MASK, pass);
+    if (m) {                                       // warp-uniform
+        // per-tile extrema for the coordinate trick / cross-class detector (x2 >= x1, y2 >= y1, NaN
+        // propagates into x2 / y2, so the maximum coordinate is max(x2, y2))
+        u32 emax = 0, enx = 0, eny = 0;
+        if (pass) {
+            const float4 q = ypp_xyxy(box);
+            emax = max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w)));
+            enx = ypp_enc(-q.x);
+            eny = ypp_enc(-q.y);
+        }
         emax = __reduce_max_sync(YPP_FULL_MASK, emax);
         enx = __reduce_max_sync(YPP_FULL_MASK, enx);
         eny = __reduce_max_sync(YPP_FULL_MASK, eny);
+        if (lane == 0) { sm.slot_max[slot] = emax; sm.slot_nx[slot] = enx; sm.slot_ny[slot] = eny; }
+    } else if (lane == 0) {
+        sm.slot_max[slot] = 0; sm.slot_nx[slot] = 0; sm.slot_ny[slot] = 0;
     }
-    if (lane == 0) { sm.warp_cnt[warp] = __popc(cl.m); sm.warp_max[warp] = emax; sm.warp_nx[warp] = enx; sm.warp_ny[warp] = eny; }
-    return cl;
+    if (lane == 0) sm.slot_cnt[slot] = __popc(m);
+    return m;
 }
 
-// part 2 (after the block barrier): tile record + stores
-__device__ __forceinline__ void compact_store(const YppWs& ws, int N, int b, int tile, int ntiles, int first,
-                                              const CompactSmem& sm, const CompactLocal cl, bool pass,
-                                              const float4 box, const float score, const int cls, int idx)
+// part 2 (after the block barrier): exclusive prefix of the slot counts (lane v holds slot v)
+__device__ __forceinline__ int slot_prefix(const CompactSmem& sm, int& total)
 {
-    constexpr int NW = YPP_DECODE_THREADS / 32;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int before = 0, total = 0;
+    const int lane = threadIdx.x & 31;
+    const int c = lane < YPP_SLOTS ? sm.slot_cnt[lane] : 0;
+    int inc = c;
 #pragma unroll
-    for (int w = 0; w < NW; ++w) {
-        const int c = sm.warp_cnt[w];
-        if (w < warp) before += c;
-        total += c;
+    for (int d = 1; d < YPP_SLOTS; d <<= 1) {
+        const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
+        if (lane >= d) inc += o;
     }
-    if (threadIdx.x == 0) {
-        u32 M = 0, NX = 0, NY = 0;
+    total = __shfl_sync(YPP_FULL_MASK, inc, YPP_SLOTS - 1);
+    return inc - c;                                 // lane v: candidates in the slots before v
+}
+
+__device__ __forceinline__ void tile_record(const YppWs& ws, int b, int tile, int ntiles, int first,
+                                            const CompactSmem& sm, int total)
+{
+    u32 M = 0, NX = 0, NY = 0;
 #pragma unroll
-        for (int w = 0; w < NW; ++w) { M = max(M, sm.warp_max[w]); NX = max(NX, sm.warp_nx[w]); NY = max(NY, sm.warp_ny[w]); }
-        ws.tile_cnt[(size_t)b * ws.tiles_max + tile] = total;
-        *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + tile)) = make_uint4(M, NX, NY, 0u);
-        if (b == 0) {
-            ws.tile_first[tile] = first;
-            if (tile == 0) *ws.ntiles = ntiles;
-        }
+    for (int v = 0; v < YPP_SLOTS; ++v) { M = max(M, sm.slot_max[v]); NX = max(NX, sm.slot_nx[v]); NY = max(NY, sm.slot_ny[v]); }
+    ws.tile_cnt[(size_t)b * ws.tiles_max + tile] = total;
+    *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + tile)) = make_uint4(M, NX, NY, 0u);
+    if (b == 0) {
+        ws.tile_first[tile] = first;
+        if (tile == 0) *ws.ntiles = ntiles;
     }
-    if (pass) {
-        const int pos = first + before + __popc(cl.m & ((1u << lane) - 1u));
-        ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
-        ws.box[(size_t)b * N + idx] = box;
-    }
+}
+
+__device__ __forceinline__ void candidate_store(const YppWs& ws, int N, int b, int first, int before, u32 m,
+                                                const float4 box, const float score, const int cls, int idx)
+{
+    const int lane = threadIdx.x & 31;
+    const int pos = first + before + __popc(m & ((1u << lane) - 1u));
+    ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
+    ws.box[(size_t)b * N + idx] = box;
 }
 
 // ---- async bulk copy + mbarrier (sm_90+ PTX) ----------------------------------------------
@@ -237,15 +248,48 @@ __device__ __forceinline__ void issue_tile(const YppDecodeParams& p, long long w
         bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, bar);
 }
 
-// Persistent CTAs walk the (image, tile) space with a two-stage pipeline: while tile k is decoded
-// out of one stage, the copies of tile k+1 are already in flight into the other.
-__global__ void __launch_bounds__(YPP_DECODE_THREADS)
+// one cell of a staged tile (shared-memory column `col`) or of the head itself (kStaged = false)
+template <bool kStaged>
+__device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppScaleParams& s, int a, int cell, bool valid,
+                                           const float* col, int stride, Decoded& d)
+{
+    bool pass = false;
+    float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
+    if (valid) {
+        const float obj = kStaged ? col[4 * stride] : __ldg(col + 4 * (size_t)stride);
+        if (!kStaged) { t0 = __ldg(col); t1 = __ldg(col + stride); t2 = __ldg(col + 2 * (size_t)stride); t3 = __ldg(col + 3 * (size_t)stride); }
+        sobj = ypp_sigmoid(obj);                                         // yolov3_utils.py:50
+        pass = sobj > p.conf;                                            // yolo_utils.py:334 (strict)
+    }
+#ifdef YPP_D1_NOCOMPUTE                                                  /* tuning experiment: copy pipeline only */
+    pass = false;
+#endif
+    // the staged path sweeps the classes warp-wide (shared memory reads are cheap, no divergence);
+    // the direct path only in lanes that hold a candidate (every read is a global load)
+    if (__any_sync(YPP_FULL_MASK, pass) && (kStaged || pass)) {
+        ClsTrack tr;
+        if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)stride, stride, p.nc, tr);
+        else cls_init(tr);
+        if (pass) {
+            if (kStaged) { t0 = col[0]; t1 = col[stride]; t2 = col[2 * stride]; t3 = col[3 * stride]; }
+            d = decode_cell(p, s, a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)stride, stride);
+            if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
+        }
+    }
+    return pass;
+}
+
+// Persistent CTAs (4 warps, two cells per thread) walk the (image, tile) space with a two-stage
+// pipeline: while tile k is decoded out of one stage, the copies of tile k+1 are already in flight
+// into the other.
+#define YPP_D1_THREADS 128
+__global__ void __launch_bounds__(YPP_D1_THREADS, 4)
 ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B)
 {
     extern __shared__ __align__(128) float stage_mem[];      // [2][C][256] when some scale is staged
     __shared__ CompactSmem sm[2];
     __shared__ __align__(8) u64 mbar[2];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, warp = tid >> 5;
     const int tiles_per_img = p.tile_base[p.n_scales];
     const long long total = (long long)tiles_per_img * B;
     const long long G = gridDim.x;
@@ -265,55 +309,38 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
         const int stg = k & 1;
         const TileRef t = tile_ref(p, tile);
         const YppScaleParams& s = p.sc[t.si];
-        const int C = p.C, HW = s.HW;
-        const bool valid = tid < t.ncells;
-        const int cell = t.cell0 + tid;
-        bool pass = false;
-        Decoded d;
-        d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
+        bool pass[2];
+        Decoded d[2];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) { d[h].box = make_float4(0.f, 0.f, 0.f, 0.f); d[h].score = 0.f; d[h].cls = 0; }
         if (s.tma) {
             const u32 parity = (stg ? uses1 : uses0) & 1u;
             mbar_wait(&mbar[stg], parity);
             if (stg) ++uses1; else ++uses0;
-            const float* col = stage_mem + stg * stage_floats + tid;
-            float sobj = 0.f;
-            if (valid) {
-                sobj = ypp_sigmoid(col[4 * YPP_TILE_BOXES]);                 // yolov3_utils.py:50
-                pass = sobj > p.conf;                                        // yolo_utils.py:334 (strict)
-            }
-            if (__any_sync(YPP_FULL_MASK, pass)) {
-                ClsTrack tr;
-                if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES, p.nc, tr);
-                else cls_init(tr);
-                if (pass) {
-                    d = decode_cell(p, s, t.a, cell, col[0], col[YPP_TILE_BOXES], col[2 * YPP_TILE_BOXES], col[3 * YPP_TILE_BOXES],
-                                    sobj, tr, col + 5 * YPP_TILE_BOXES, YPP_TILE_BOXES);
-                    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
-                }
+            const float* st = stage_mem + stg * stage_floats;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int ct = tid + h * YPP_D1_THREADS;
+                pass[h] = decode_one<true>(p, s, t.a, t.cell0 + ct, ct < t.ncells, st + ct, YPP_TILE_BOXES, d[h]);
             }
         } else {
-            const float* col = s.head + ((size_t)(b * s.A + t.a) * C) * HW + cell;
-            float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
-            if (valid) {
-                const float obj = __ldg(col + 4 * (size_t)HW);
-                t0 = __ldg(col); t1 = __ldg(col + HW); t2 = __ldg(col + 2 * (size_t)HW); t3 = __ldg(col + 3 * (size_t)HW);
-                sobj = ypp_sigmoid(obj);
-                pass = sobj > p.conf;
-            }
-            if (__any_sync(YPP_FULL_MASK, pass)) {
-                if (pass) {
-                    ClsTrack tr;
-                    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)HW, HW, p.nc, tr);
-                    else cls_init(tr);
-                    d = decode_cell(p, s, t.a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)HW, HW);
-                    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
-                }
+            const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int ct = tid + h * YPP_D1_THREADS;
+                pass[h] = decode_one<false>(p, s, t.a, t.cell0 + ct, ct < t.ncells, src + ct, s.HW, d[h]);
             }
         }
-        const CompactLocal cl = compact_count(sm[stg], pass, d.box);
+        const u32 m0 = compact_count(sm[stg], warp, pass[0], d[0].box);
+        const u32 m1 = compact_count(sm[stg], warp + 4, pass[1], d[1].box);
         __syncthreads();                                       // every read of this stage is done
         if (tid < 32 && w + 2 * G < total) issue_tile(p, w + 2 * G, tiles_per_img, stage_mem + stg * stage_floats, &mbar[stg]);
-        compact_store(p.ws, p.N, b, tile, tiles_per_img, t.first, sm[stg], cl, pass, d.box, d.score, d.cls, t.first + tid);
+        int tot;
+        const int pre = slot_prefix(sm[stg], tot);
+        if (tid == 0) tile_record(p.ws, b, tile, tiles_per_img, t.first, sm[stg], tot);
+        const int before0 = __shfl_sync(YPP_FULL_MASK, pre, warp), before1 = __shfl_sync(YPP_FULL_MASK, pre, warp + 4);
+        if (pass[0]) candidate_store(p.ws, p.N, b, t.first, before0, m0, d[0].box, d[0].score, d[0].cls, t.first + tid);
+        if (pass[1]) candidate_store(p.ws, p.N, b, t.first, before1, m1, d[1].box, d[1].score, d[1].cls, t.first + tid + YPP_D1_THREADS);
     }
 }
 
@@ -363,9 +390,14 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
         cls = c;
         pass = score > conf;
     }
-    const CompactLocal cl = compact_count(sm, pass, box);
+    const int warp = threadIdx.x >> 5;
+    const u32 m = compact_count(sm, warp, pass, box);
     __syncthreads();
-    compact_store(ws, N, b, (int)blockIdx.x, (int)gridDim.x, first, sm, cl, pass, box, score, cls, n);
+    int tot;
+    const int pre = slot_prefix(sm, tot);
+    if (threadIdx.x == 0) tile_record(ws, b, (int)blockIdx.x, (int)gridDim.x, first, sm, tot);
+    const int before = __shfl_sync(YPP_FULL_MASK, pre, warp);
+    if (pass) candidate_store(ws, N, b, first, before, m, box, score, cls, n);
 }
 
 }  // namespace
@@ -384,14 +416,14 @@ int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, YPP_DECODE_THREADS, smem);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, YPP_D1_THREADS, smem);
         if (e != cudaSuccess || ctas_per_sm < 1) { ypp_set_error("decode_compact: occupancy query failed"); return YPP_E_CUDA; }
         configured = smem;
     }
     const long long total = (long long)p.tile_base[p.n_scales] * B;
     long long grid = (long long)sms * ctas_per_sm;
     if (grid > total) grid = total;
-    ypp_decode_compact_kernel<<<(unsigned)grid, YPP_DECODE_THREADS, smem, st>>>(p, B);
+    ypp_decode_compact_kernel<<<(unsigned)grid, YPP_D1_THREADS, smem, st>>>(p, B);
     ypp_count_launch(1);
     return ypp_check_launch("decode_compact");
 }

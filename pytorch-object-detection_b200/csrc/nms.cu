@@ -83,6 +83,19 @@ __device__ __forceinline__ float pair_d(const float4 a, const float sa, const fl
     return __fmaf_rn(-thr, fabsf(uni), inter);
 }
 
+// box of global score rank r of image `ibase`: cxcywh -> xyxy exactly as nms_v3 does, plus the
+// coordinate trick's class offset when torchvision would apply it (S1 decided per image)
+__device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r, bool trick, float step)
+{
+    const u64 k = ws.skeys[ibase + r];
+    float4 xy = ypp_xyxy(ws.box[ibase + ypp_key_idx(k)]);
+    if (trick) {
+        const float off = __fmul_rn((float)ypp_key_cls(k), step);    // idxs.to(boxes) * (max_coordinate + 1)
+        xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+    }
+    return xy;
+}
+
 // a row that can never raise dmax (padding of the kept-row lists)
 #define YPP_DUMMY_BOX make_float4(1e30f, 1e30f, -1e30f, -1e30f)
 #define YPP_DUMMY_AREA 1e30f
@@ -116,15 +129,16 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
     if (len <= 0 || len > YPP_WARP_SEG) return;
     const size_t ibase = (size_t)b * p.N;
-    const float4* __restrict__ seg = p.ws.sbox + ibase + s0;
     const int* __restrict__ grank = p.ws.grank + ibase + s0;
     unsigned char* __restrict__ keepflag = p.ws.keepflag + ibase;
     const float thr = p.iou_thr;
     const int union_fma = p.union_mode;
+    const bool trick = (p.ws.imgflag[b] & 2) != 0;
+    const float step = p.ws.img_step[b];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     u32 amax_bits = 0;            // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
-        const float4 q = seg[i];
+        const float4 q = rank_box(p.ws, ibase, grank[i], trick, step);
         const float ar = ypp_area(q);
         sm.box[i] = q;
         sm.area[i] = ar;
@@ -385,6 +399,13 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
         const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
         const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
         const size_t base = (size_t)b * p.N;
+        {   // materialise the segment's boxes (score order) for the sweeps below
+            const bool trick = (p.ws.imgflag[b] & 2) != 0;
+            const float step = p.ws.img_step[b];
+            for (int i = threadIdx.x; i < len; i += YPP_NMS_BIG_THREADS)
+                p.ws.sbox[base + s0 + i] = rank_box(p.ws, base, p.ws.grank[base + s0 + i], trick, step);
+            __syncthreads();
+        }
         nms_segment<YPP_NMS_BIG_THREADS, kFast, kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
                                                       p.ws.keepflag + base, len, cache, YPP_BIG_CACHE,
                                                       removed, ts, p.iou_thr, p.union_mode);

@@ -4,13 +4,21 @@
 //      torchvision::nms (scores.sort(stable=True, descending=True); ties -> lower box index),
 //      digits sized to the bits in which the image's scores actually differ;
 //   3. stable counting partition by class -> per (image, class) segments in the same order;
-//   4. emit xyxy boxes (utils/yolo_utils.py:339-343) in segment order, shifted by
-//      cls * (max_coordinate + 1) when torchvision would take the coordinate-trick path
-//      (_batched_nms_coordinate_trick), and the segment -> global-rank map;
+//   4. emit the segment -> global-rank map and, per image, whether torchvision would take the
+//      coordinate-trick path (_batched_nms_coordinate_trick) and its offset step
+//      max_coordinate + 1; N1 gathers the boxes through the map, converts them to xyxy
+//      (utils/yolo_utils.py:339-343) and applies cls * step;
 //   5. coordinate trick only: detect cross-class suppression edges (possible when a box with
 //      negative x1,y1 is shifted onto the previous class band); such an image is re-emitted as
 //      ONE class-agnostic segment so the greedy scan sees exactly what torchvision's does.
 #include "ypp_kernels.cuh"
+
+#ifdef YPP_PROFILE_S1
+__device__ long long ypp_s1_clk[16];
+#define S1_MARK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) ypp_s1_clk[i] = clock64(); } while (0)
+#else
+#define S1_MARK(i) do { } while (0)
+#endif
 
 namespace {
 
@@ -20,7 +28,7 @@ namespace {
 #define YPP_RADIX_MAX 256
 #define YPP_TABLE_PITCH 33              // table[digit * 33 + warp]: leaders of one warp hit distinct banks
 
-struct DetEntry { float4 box; int cls; int rank; };
+struct DetEntry { float4 box; u64 key; int cls; int pad; };
 
 struct OrgSmemHeader {
     DetEntry lowl[YPP_DET_LIST];
@@ -170,6 +178,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     u64* bufA = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : skeys;
     u64* bufB = p.keys_in_smem ? bufA + N : reinterpret_cast<u64*>(sbox);
 
+    S1_MARK(0);
     // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema
     const int ntiles = min(*p.ws.ntiles, p.ws.tiles_max);
     const int* tcnt = p.ws.tile_cnt + (size_t)b * p.ws.tiles_max;
@@ -202,7 +211,6 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             hd->kmin = 0xffffffffu; hd->kmax = 0u;
             p.ws.cand_count[b] = min(run, N);
             p.ws.keep_count[b] = 0;
-            p.ws.imgflag[b] = 0;
         }
     }
     if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
@@ -212,6 +220,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = 0;
         return;
     }
+    S1_MARK(1);
     // ---- 2. gather the tiles (warp per tile), track the range of the score words
     {
         u32 kmin = 0xffffffffu, kmax = 0u;
@@ -234,26 +243,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         for (int i = tid; i < n; i += YPP_ORG_THREADS) kf[i] = 0;
     }
     __syncthreads();
-    // ---- 3. stable sort by score word
-    const int L = ((n + 31) / 32 + 31) / 32 * 32;            // ranks per warp, multiple of 32
-    u64* keys = bufA;                                        // where the sorted keys end up
-    {
-        const u32 kmin = hd->kmin, span = hd->kmax - kmin;
-        const int bits = 32 - __clz(span);                   // 0 when every score is equal: already in order
-        const int passes = (bits + 7) / 8;
-        const int bw = passes ? (bits + passes - 1) / passes : 0;
-        u64* other = bufB;
-        for (int ps = 0; ps < passes; ++ps) {
-            radix_pass(keys, other, n, L, ps * bw, bw, kmin, table, hd->warp_sums);
-            u64* t = keys; keys = other; other = t;
-        }
-    }
-    if (keys != skeys) {
-        for (int i = tid; i < n; i += YPP_ORG_THREADS) skeys[i] = keys[i];
-        if (!p.keys_in_smem) { __syncthreads(); keys = skeys; }   // global mode: the sbox region is about to be overwritten
-    }
-
-    // ---- which torchvision path would run for this image
+    S1_MARK(2);
+    // ---- which torchvision path would run for this image, and the geometry of the cross-class detector
     bool trick = p.offset_mode == YPP_OFFSET_TRICK;
     if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
     if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
@@ -273,56 +264,97 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     const bool detect = dg.on;
     const float4* gbox = p.ws.box + (size_t)b * N;
+    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
 
-    // ---- 4a. class counting (warp w owns ranks [w*L, (w+1)*L)) and the detector's staircase bins
+    // ---- 3. detector sweeps, BEFORE the sort: the keys are still in box-index order, so the box reads
+    // are (nearly) sequential instead of a random gather
+    if (detect) {
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(bufA[i])]);
+            const float u = xy.z - step, v = xy.w - step;
+            if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
+            if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
+        }
+        __syncthreads();
+        if (warp == 1) {
+            // suffix max over bin_hi (A's in bins >= j can dominate a B in bin j),
+            // prefix max over bin_lo (B's in bins <= i can be dominated by an A in bin i); 2 bins per lane
+            u32 h0 = hd->bin_hi[lane], h1 = hd->bin_hi[lane + 32];
+            u32 l0 = hd->bin_lo[lane], l1 = hd->bin_lo[lane + 32];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const u32 a1 = __shfl_down_sync(YPP_FULL_MASK, h1, d), a0 = __shfl_down_sync(YPP_FULL_MASK, h0, d);
+                if (lane + d < 32) { h1 = max(h1, a1); h0 = max(h0, a0); }
+                const u32 b0 = __shfl_up_sync(YPP_FULL_MASK, l0, d), b1 = __shfl_up_sync(YPP_FULL_MASK, l1, d);
+                if (lane >= d) { l0 = max(l0, b0); l1 = max(l1, b1); }
+            }
+            h0 = max(h0, __shfl_sync(YPP_FULL_MASK, h1, 0));        // bins 0..31 also see all of 32..63
+            l1 = max(l1, __shfl_sync(YPP_FULL_MASK, l0, 31));       // bins 32..63 also see all of 0..31
+            hd->bin_hi[lane] = h0; hd->bin_hi[lane + 32] = h1;
+            hd->bin_lo[lane] = l0; hd->bin_lo[lane + 32] = l1;
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+            const u64 k = bufA[i];
+            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+            // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
+            bool is_low = false, is_high = false;
+            if (xy.x < dg.lim && xy.y < dg.lim) {
+                const int j = max(det_bin(dg, xy.x) - 1, 0);
+                const u32 e = hd->bin_hi[j];
+                is_low = e != 0 && xy.y < ypp_dec(e) + dg.slack;
+            }
+            const float u = xy.z - step, v = xy.w - step;
+            if (u > dg.x1min - dg.slack) {
+                const int j = min(det_bin(dg, u) + 1, YPP_DET_BINS - 1);
+                const u32 e = hd->bin_lo[j];
+                is_high = e != 0 && v > -ypp_dec(e) - dg.slack;
+            }
+            if (is_low || is_high) {
+                const int c = ypp_key_cls(k);
+                const float off = __fmul_rn((float)c, step);
+                DetEntry e;
+                e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                e.cls = c; e.key = k;
+                if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
+                if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
+            }
+        }
+        __syncthreads();
+    }
+    S1_MARK(3);
+    // ---- 4. stable sort by score word
+    const int L = ((n + 31) / 32 + 31) / 32 * 32;            // ranks per warp, multiple of 32
+    u64* keys = bufA;                                        // where the sorted keys end up
+    {
+        const u32 kmin = hd->kmin, span = hd->kmax - kmin;
+        const int bits = 32 - __clz(span);                   // 0 when every score is equal: already in order
+        const int passes = (bits + 7) / 8;
+        const int bw = passes ? (bits + passes - 1) / passes : 0;
+        u64* other = bufB;
+        for (int ps = 0; ps < passes; ++ps) {
+            radix_pass(keys, other, n, L, ps * bw, bw, kmin, table, hd->warp_sums);
+            u64* t = keys; keys = other; other = t;
+        }
+    }
+    S1_MARK(4);
+    if (keys != skeys) {
+        for (int i = tid; i < n; i += YPP_ORG_THREADS) skeys[i] = keys[i];
+        if (!p.keys_in_smem) { __syncthreads(); keys = skeys; }
+    }
+    S1_MARK(5);
+    // ---- 5. class counting (warp w owns ranks [w*L, (w+1)*L)), segment starts
     __syncthreads();                                         // table is free again
     for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
-    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
     __syncthreads();
     const int r_begin = warp * L, r_end = min(n, r_begin + L);
     const int cbits = 32 - __clz(max(nc - 1, 1));            // bits of a class id
     int* my = table + warp * nc;
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
-        const bool ok = r < r_end;
-        if (ok) atomicAdd(&my[ypp_key_cls(keys[r])], 1);
-    }
-    if (detect) {
-        for (int r0 = tid; r0 < n; r0 += 4 * YPP_ORG_THREADS) {      // four independent gathers in flight
-            float4 bx[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int r = r0 + j * YPP_ORG_THREADS;
-                if (r < n) bx[j] = gbox[ypp_key_idx(keys[r])];
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (r0 + j * YPP_ORG_THREADS >= n) break;
-                const float4 xy = ypp_xyxy(bx[j]);
-                const float u = xy.z - step, v = xy.w - step;
-                if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
-                if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
-            }
-        }
+        if (r < r_end) atomicAdd(&my[ypp_key_cls(keys[r])], 1);
     }
     __syncthreads();
-    if (detect && warp == 1) {
-        // suffix max over bin_hi (A's in bins >= j can dominate a B in bin j),
-        // prefix max over bin_lo (B's in bins <= i can be dominated by an A in bin i); 2 bins per lane
-        u32 h0 = hd->bin_hi[lane], h1 = hd->bin_hi[lane + 32];
-        u32 l0 = hd->bin_lo[lane], l1 = hd->bin_lo[lane + 32];
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const u32 a1 = __shfl_down_sync(YPP_FULL_MASK, h1, d), a0 = __shfl_down_sync(YPP_FULL_MASK, h0, d);
-            if (lane + d < 32) { h1 = max(h1, a1); h0 = max(h0, a0); }
-            const u32 b0 = __shfl_up_sync(YPP_FULL_MASK, l0, d), b1 = __shfl_up_sync(YPP_FULL_MASK, l1, d);
-            if (lane >= d) { l0 = max(l0, b0); l1 = max(l1, b1); }
-        }
-        h0 = max(h0, __shfl_sync(YPP_FULL_MASK, h1, 0));        // bins 0..31 also see all of 32..63
-        l1 = max(l1, __shfl_sync(YPP_FULL_MASK, l0, 31));       // bins 32..63 also see all of 0..31
-        hd->bin_hi[lane] = h0; hd->bin_hi[lane + 32] = h1;
-        hd->bin_lo[lane] = l0; hd->bin_lo[lane + 32] = l1;
-    }
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
         int t = 0;
         for (int w = 0; w < 32; ++w) t += table[w * nc + c];
@@ -351,8 +383,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         for (int w = 0; w < 32; ++w) { const int t = table[w * nc + c]; table[w * nc + c] = run; run += t; }
     }
     __syncthreads();
-
-    // ---- 4b. stable ranking: segment position of every global rank
+    S1_MARK(6);
+    // ---- 6. stable ranking: segment position -> global rank (N1 gathers the boxes through it)
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
@@ -368,59 +400,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         }
         __syncwarp();
     }
-    __syncthreads();
-
-    // ---- 4c. emission in segment order (coalesced writes, independent gathers)
-    for (int q0 = tid; q0 < n; q0 += 4 * YPP_ORG_THREADS) {         // four independent gathers in flight
-      int rr[4];
-      u64 kk[4];
-      float4 bx[4];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { const int q = q0 + j * YPP_ORG_THREADS; rr[j] = q < n ? grank[q] : 0; }
-#pragma unroll
-      for (int j = 0; j < 4; ++j) kk[j] = keys[rr[j]];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) bx[j] = gbox[ypp_key_idx(kk[j])];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int q = q0 + j * YPP_ORG_THREADS;
-        if (q >= n) break;
-        const int r = rr[j];
-        const u64 k = kk[j];
-        const int c = ypp_key_cls(k);
-        float4 xy = ypp_xyxy(bx[j]);
-        if (detect) {
-            // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
-            bool is_low = false, is_high = false;
-            if (xy.x < dg.lim && xy.y < dg.lim) {
-                const int j = max(det_bin(dg, xy.x) - 1, 0);
-                const u32 e = hd->bin_hi[j];
-                is_low = e != 0 && xy.y < ypp_dec(e) + dg.slack;
-            }
-            const float u = xy.z - step, v = xy.w - step;
-            if (u > dg.x1min - dg.slack) {
-                const int i = min(det_bin(dg, u) + 1, YPP_DET_BINS - 1);
-                const u32 e = hd->bin_lo[i];
-                is_high = e != 0 && v > -ypp_dec(e) - dg.slack;
-            }
-            if (is_low || is_high) {
-                const float off = __fmul_rn((float)c, step);
-                DetEntry e;
-                e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-                e.cls = c; e.rank = r;
-                if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
-                if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
-            }
-        }
-        if (trick) {
-            const float off = __fmul_rn((float)c, step);    // idxs.to(boxes) * (max_coordinate + 1)
-            xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-        }
-        sbox[q] = xy;
-      }
-    }
-    __syncthreads();
-
+    S1_MARK(7);
+    // ---- 7. coordinate trick: exact test of the detector's candidate pairs
     if (trick && nc > 1) {
         const int nl = hd->n_low, nh = hd->n_high;
         if (nl > 0 && nh > 0) {
@@ -431,8 +412,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
                 for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) {
                     const DetEntry lo = hd->lowl[t / nh], hi = hd->highl[t % nh];
                     if (lo.cls == hi.cls) continue;
-                    const DetEntry& row = lo.rank < hi.rank ? lo : hi;
-                    const DetEntry& col = lo.rank < hi.rank ? hi : lo;
+                    const DetEntry& row = lo.key < hi.key ? lo : hi;       // smaller key = earlier in score order
+                    const DetEntry& col = lo.key < hi.key ? hi : lo;
                     const float sa = ypp_area(row.box);
                     const bool s = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
                                            : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
@@ -442,20 +423,16 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         }
         __syncthreads();
         if (hd->flagged) {
-            // class-agnostic single segment in global score order, shifted coordinates
-            for (int r = tid; r < n; r += YPP_ORG_THREADS) {
-                const u64 k = keys[r];
-                const float off = __fmul_rn((float)ypp_key_cls(k), step);
-                const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
-                sbox[r] = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-                grank[r] = r;
-            }
+            // class-agnostic single segment in global score order
+            for (int r = tid; r < n; r += YPP_ORG_THREADS) grank[r] = r;
             for (int c = tid; c <= nc; c += YPP_ORG_THREADS) seg[c] = c == 0 ? 0 : n;
-            if (tid == 0) p.ws.imgflag[b] = 1;
             __syncthreads();
         }
     }
-
+    if (tid == 0) {
+        p.ws.imgflag[b] = (hd->flagged ? 1 : 0) | (trick ? 2 : 0);
+        p.ws.img_step[b] = step;
+    }
     for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = seg[c];
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
         if (seg[c + 1] - seg[c] > YPP_WARP_SEG) {
@@ -463,6 +440,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             if (s < p.B * p.ws.bigq_per_image) p.ws.bigq[s] = b * nc + c;
         }
     }
+    S1_MARK(8);
 }
 
 }  // namespace
@@ -483,6 +461,13 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
     *keys_in_smem = 0;
     return (int)fixed;
 }
+
+#ifdef YPP_PROFILE_S1
+extern "C" int ypp_debug_s1_clocks(long long* out16)
+{
+    return (int)cudaMemcpyFromSymbol(out16, ypp_s1_clk, sizeof(long long) * 16);
+}
+#endif
 
 int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
 {

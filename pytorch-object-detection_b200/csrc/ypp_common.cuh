@@ -30,7 +30,8 @@ typedef unsigned int u32;
 struct YppWs {
     int* cand_count;      // [B] written by S1
     int* keep_count;      // [B] zeroed by S1, accumulated by N1
-    int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge)
+    int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge), bit1: coordinate trick
+    float* img_step;      // [B] max_coordinate + 1 of the image's candidates (the trick's class offset step)
     int* q;               // [4] q[0] long-segment queue length, q[1] queue head
     int* ntiles;          // [1] D1 tiles per image
     int* tile_first;      // [T] first box index of each D1 tile (the same for every image)
@@ -60,6 +61,7 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     w.cand_count = (int*)take(sizeof(int) * B);
     w.keep_count = (int*)take(sizeof(int) * B);
     w.imgflag = (int*)take(sizeof(int) * B);
+    w.img_step = (float*)take(sizeof(float) * B);
     w.q = (int*)take(sizeof(int) * 4);
     w.ntiles = (int*)take(sizeof(int));
     // a tile never spans two anchor planes, so a scale adds at most A partial tiles

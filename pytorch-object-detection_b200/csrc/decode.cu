@@ -12,8 +12,8 @@
 // shared memory (conflict-free columns).  Heads whose plane size is not a multiple of 4 floats
 // (13x13, 19x19: channel rows are only 4-byte aligned) take plain coalesced loads instead.
 //
-// Compaction is deterministic: the candidates of a tile are written in box-index order at
-// keys[b][tile_first ..] with their count in tile_cnt[b][tile]; S1 concatenates the tiles, so
+// Compaction is deterministic: the candidates of every 32-box slot are written in box-index order
+// at keys[b][slot_first ..] with their count in tile_cnt[b][slot]; S1 concatenates the slots, so
 // the sort input is already in box-index order and a STABLE sort by score alone gives the
 // reference's tie order.  No atomics, nothing to clear between calls.
 #include "ypp_kernels.cuh"
@@ -108,25 +108,18 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
     return d;
 }
 
-// ---- block-wide compaction in box-index order ----------------------------------------------
-// A tile is split into 8 slots of 32 consecutive boxes; slot v is handled by one warp (one
-// ballot).  The decode kernel runs 4 warps x 2 boxes per thread (slots w and w + 4), the row
-// compaction kernel 8 warps x 1 box.
-#define YPP_SLOTS (YPP_TILE_BOXES / 32)
-struct CompactSmem {
-    int slot_cnt[YPP_SLOTS];
-    u32 slot_max[YPP_SLOTS], slot_nx[YPP_SLOTS], slot_ny[YPP_SLOTS];
-};
-
-// part 1: ballot and per-slot record (ends before the block barrier the caller places)
-__device__ __forceinline__ u32 compact_count(CompactSmem& sm, int slot, bool pass, const float4 box)
+// ---- warp-wide compaction in box-index order ------------------------------------------------
+// The compaction unit is a SLOT of 32 consecutive boxes handled by one warp (one ballot): its
+// candidates go to keys[b][slot_first ..] in lane order, its count and extrema to the slot record.
+// S1 concatenates the slots.  No block barrier, no atomics, nothing to clear between calls.
+__device__ __forceinline__ void slot_store(const YppWs& ws, int N, int b, int slot, int nslots, int first,
+                                           bool pass, const float4 box, const float score, const int cls, int idx)
 {
     const int lane = threadIdx.x & 31;
     const u32 m = __ballot_sync(YPP_FULL_MASK, pass);
+    u32 emax = 0, enx = 0, eny = 0;
     if (m) {                                       // warp-uniform
-        // per-tile extrema for the coordinate trick / cross-class detector (x2 >= x1, y2 >= y1, NaN
-        // propagates into x2 / y2, so the maximum coordinate is max(x2, y2))
-        u32 emax = 0, enx = 0, eny = 0;
+        // extrema for the coordinate trick / cross-class detector
         if (pass) {
             const float4 q = ypp_xyxy(box);
             emax = max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w)));
@@ -136,50 +129,20 @@ __device__ __forceinline__ u32 compact_count(CompactSmem& sm, int slot, bool pas
         emax = __reduce_max_sync(YPP_FULL_MASK, emax);
         enx = __reduce_max_sync(YPP_FULL_MASK, enx);
         eny = __reduce_max_sync(YPP_FULL_MASK, eny);
-        if (lane == 0) { sm.slot_max[slot] = emax; sm.slot_nx[slot] = enx; sm.slot_ny[slot] = eny; }
-    } else if (lane == 0) {
-        sm.slot_max[slot] = 0; sm.slot_nx[slot] = 0; sm.slot_ny[slot] = 0;
     }
-    if (lane == 0) sm.slot_cnt[slot] = __popc(m);
-    return m;
-}
-
-// part 2 (after the block barrier): exclusive prefix of the slot counts (lane v holds slot v)
-__device__ __forceinline__ int slot_prefix(const CompactSmem& sm, int& total)
-{
-    const int lane = threadIdx.x & 31;
-    const int c = lane < YPP_SLOTS ? sm.slot_cnt[lane] : 0;
-    int inc = c;
-#pragma unroll
-    for (int d = 1; d < YPP_SLOTS; d <<= 1) {
-        const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
-        if (lane >= d) inc += o;
+    if (lane == 0) {
+        ws.tile_cnt[(size_t)b * ws.tiles_max + slot] = __popc(m);
+        *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + slot)) = make_uint4(emax, enx, eny, 0u);
+        if (b == 0) {
+            ws.tile_first[slot] = first;
+            if (slot == 0) *ws.ntiles = nslots;
+        }
     }
-    total = __shfl_sync(YPP_FULL_MASK, inc, YPP_SLOTS - 1);
-    return inc - c;                                 // lane v: candidates in the slots before v
-}
-
-__device__ __forceinline__ void tile_record(const YppWs& ws, int b, int tile, int ntiles, int first,
-                                            const CompactSmem& sm, int total)
-{
-    u32 M = 0, NX = 0, NY = 0;
-#pragma unroll
-    for (int v = 0; v < YPP_SLOTS; ++v) { M = max(M, sm.slot_max[v]); NX = max(NX, sm.slot_nx[v]); NY = max(NY, sm.slot_ny[v]); }
-    ws.tile_cnt[(size_t)b * ws.tiles_max + tile] = total;
-    *reinterpret_cast<uint4*>(ws.tile_ext + 4 * ((size_t)b * ws.tiles_max + tile)) = make_uint4(M, NX, NY, 0u);
-    if (b == 0) {
-        ws.tile_first[tile] = first;
-        if (tile == 0) *ws.ntiles = ntiles;
+    if (pass) {
+        const int pos = first + __popc(m & ((1u << lane) - 1u));
+        ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
+        ws.box[(size_t)b * N + idx] = box;
     }
-}
-
-__device__ __forceinline__ void candidate_store(const YppWs& ws, int N, int b, int first, int before, u32 m,
-                                                const float4 box, const float score, const int cls, int idx)
-{
-    const int lane = threadIdx.x & 31;
-    const int pos = first + before + __popc(m & ((1u << lane) - 1u));
-    ws.keys[(size_t)b * N + pos] = ypp_make_key(score, idx, cls);
-    ws.box[(size_t)b * N + idx] = box;
 }
 
 // ---- async bulk copy + mbarrier (sm_90+ PTX) ----------------------------------------------
@@ -232,22 +195,6 @@ __device__ __forceinline__ TileRef tile_ref(const YppDecodeParams& p, int bx)
     return t;
 }
 
-// warp 0: start the bulk copies of work item `w` (tile of image b) into stage `stg`
-__device__ __forceinline__ void issue_tile(const YppDecodeParams& p, long long w, int tiles_per_img, float* stage, u64* bar)
-{
-    const int b = (int)(w / tiles_per_img);
-    const TileRef t = tile_ref(p, (int)(w - (long long)b * tiles_per_img));
-    const YppScaleParams& s = p.sc[t.si];
-    if (!s.tma) return;
-    const int lane = threadIdx.x & 31;
-    const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
-    const u32 row_bytes = (u32)t.ncells * 4u;                // multiple of 16: HW % 4 == 0
-    if (lane == 0) mbar_expect_tx(bar, row_bytes * (u32)p.C);
-    __syncwarp();
-    for (int c = lane; c < p.C; c += 32)
-        bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, bar);
-}
-
 // one cell of a staged tile (shared-memory column `col`) or of the head itself (kStaged = false)
 template <bool kStaged>
 __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppScaleParams& s, int a, int cell, bool valid,
@@ -279,68 +226,81 @@ __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppSc
     return pass;
 }
 
-// Persistent CTAs (4 warps, two cells per thread) walk the (image, tile) space with a two-stage
-// pipeline: while tile k is decoded out of one stage, the copies of tile k+1 are already in flight
-// into the other.
-#define YPP_D1_THREADS 128
+// Warp-specialised persistent CTAs: 8 consumer warps + 1 producer warp, no block barrier in the
+// loop.  The producer walks the CTA's (image, tile) work items and keeps YPP_D1_STAGES tiles in
+// flight (cp.async.bulk rows -> stage, completion on full[stage]); consumer warp w decodes cells
+// 32w..32w+31 of each tile straight out of the stage, releases it on empty[stage] and compacts its
+// own slot, so warps never wait for each other -- only for data.
+#define YPP_D1_STAGES 2
+#define YPP_D1_CONSUMERS (YPP_TILE_BOXES / 32)
+#define YPP_D1_THREADS (32 * (YPP_D1_CONSUMERS + 1))
+
+__device__ __forceinline__ void mbar_arrive(u64* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
 __global__ void __launch_bounds__(YPP_D1_THREADS, 4)
 ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B)
 {
-    extern __shared__ __align__(128) float stage_mem[];      // [2][C][256] when some scale is staged
-    __shared__ CompactSmem sm[2];
-    __shared__ __align__(8) u64 mbar[2];
-    const int tid = threadIdx.x, warp = tid >> 5;
+    extern __shared__ __align__(128) float stage_mem[];      // [STAGES][C][256] when some scale is staged
+    __shared__ __align__(8) u64 full[YPP_D1_STAGES], empty[YPP_D1_STAGES];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tiles_per_img = p.tile_base[p.n_scales];
     const long long total = (long long)tiles_per_img * B;
-    const long long G = gridDim.x;
     const int stage_floats = p.C * YPP_TILE_BOXES;
-    if (tid == 0) { mbar_init(&mbar[0], 1); mbar_init(&mbar[1], 1); }
-    __syncthreads();
-    if (tid < 32) {
-        if ((long long)blockIdx.x < total) issue_tile(p, blockIdx.x, tiles_per_img, stage_mem, &mbar[0]);
-        if ((long long)blockIdx.x + G < total) issue_tile(p, blockIdx.x + G, tiles_per_img, stage_mem + stage_floats, &mbar[1]);
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < YPP_D1_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], YPP_D1_CONSUMERS); }
     }
-    u32 uses0 = 0, uses1 = 0;                                 // completed phases of each barrier
-    int k = 0;
+    __syncthreads();
     int b = (int)(blockIdx.x / (unsigned)tiles_per_img), tile = (int)(blockIdx.x - (unsigned)b * (unsigned)tiles_per_img);
     const int gb = (int)(gridDim.x / (unsigned)tiles_per_img), gt = (int)(gridDim.x - (unsigned)gb * (unsigned)tiles_per_img);
-    for (long long w = blockIdx.x; w < total; w += G, ++k, b += gb, tile += gt) {
-        if (tile >= tiles_per_img) { tile -= tiles_per_img; ++b; }
-        const int stg = k & 1;
-        const TileRef t = tile_ref(p, tile);
-        const YppScaleParams& s = p.sc[t.si];
-        bool pass[2];
-        Decoded d[2];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) { d[h].box = make_float4(0.f, 0.f, 0.f, 0.f); d[h].score = 0.f; d[h].cls = 0; }
-        if (s.tma) {
-            const u32 parity = (stg ? uses1 : uses0) & 1u;
-            mbar_wait(&mbar[stg], parity);
-            if (stg) ++uses1; else ++uses0;
-            const float* st = stage_mem + stg * stage_floats;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int ct = tid + h * YPP_D1_THREADS;
-                pass[h] = decode_one<true>(p, s, t.a, t.cell0 + ct, ct < t.ncells, st + ct, YPP_TILE_BOXES, d[h]);
-            }
-        } else {
-            const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int ct = tid + h * YPP_D1_THREADS;
-                pass[h] = decode_one<false>(p, s, t.a, t.cell0 + ct, ct < t.ncells, src + ct, s.HW, d[h]);
+    int k = 0;
+    if (warp == YPP_D1_CONSUMERS) {
+        // ---------------- producer
+        for (long long w = blockIdx.x; w < total; w += gridDim.x, ++k, b += gb, tile += gt) {
+            if (tile >= tiles_per_img) { tile -= tiles_per_img; ++b; }
+            const int stg = k % YPP_D1_STAGES, use = k / YPP_D1_STAGES;
+            if (use > 0) mbar_wait(&empty[stg], (u32)(use - 1) & 1u);        // consumers are done with this stage
+            const TileRef t = tile_ref(p, tile);
+            const YppScaleParams& s = p.sc[t.si];
+            if (s.tma) {
+                const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
+                const u32 row_bytes = (u32)t.ncells * 4u;                    // multiple of 16: HW % 4 == 0
+                float* stage = stage_mem + stg * stage_floats;
+                if (lane == 0) mbar_expect_tx(&full[stg], row_bytes * (u32)p.C);
+                __syncwarp();
+                for (int c = lane; c < p.C; c += 32)
+                    bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, &full[stg]);
+            } else if (lane == 0) {
+                mbar_arrive(&full[stg]);                                     // unstaged tile: consumers read the head directly
             }
         }
-        const u32 m0 = compact_count(sm[stg], warp, pass[0], d[0].box);
-        const u32 m1 = compact_count(sm[stg], warp + 4, pass[1], d[1].box);
-        __syncthreads();                                       // every read of this stage is done
-        if (tid < 32 && w + 2 * G < total) issue_tile(p, w + 2 * G, tiles_per_img, stage_mem + stg * stage_floats, &mbar[stg]);
-        int tot;
-        const int pre = slot_prefix(sm[stg], tot);
-        if (tid == 0) tile_record(p.ws, b, tile, tiles_per_img, t.first, sm[stg], tot);
-        const int before0 = __shfl_sync(YPP_FULL_MASK, pre, warp), before1 = __shfl_sync(YPP_FULL_MASK, pre, warp + 4);
-        if (pass[0]) candidate_store(p.ws, p.N, b, t.first, before0, m0, d[0].box, d[0].score, d[0].cls, t.first + tid);
-        if (pass[1]) candidate_store(p.ws, p.N, b, t.first, before1, m1, d[1].box, d[1].score, d[1].cls, t.first + tid + YPP_D1_THREADS);
+        return;
+    }
+    // ---------------- consumers
+    const int nslots = tiles_per_img * YPP_D1_CONSUMERS;
+    for (long long w = blockIdx.x; w < total; w += gridDim.x, ++k, b += gb, tile += gt) {
+        if (tile >= tiles_per_img) { tile -= tiles_per_img; ++b; }
+        const int stg = k % YPP_D1_STAGES, use = k / YPP_D1_STAGES;
+        const TileRef t = tile_ref(p, tile);
+        const YppScaleParams& s = p.sc[t.si];
+        const int ct = tid;                                                  // cell inside the tile (warp w: 32w..32w+31)
+        Decoded d;
+        d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
+        bool pass;
+        mbar_wait(&full[stg], (u32)use & 1u);
+        if (s.tma) {
+            pass = decode_one<true>(p, s, t.a, t.cell0 + ct, ct < t.ncells, stage_mem + stg * stage_floats + ct, YPP_TILE_BOXES, d);
+        } else {
+            const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
+            pass = decode_one<false>(p, s, t.a, t.cell0 + ct, ct < t.ncells, src + ct, s.HW, d);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[stg]);                             // this warp no longer reads the stage
+        slot_store(p.ws, p.N, b, tile * YPP_D1_CONSUMERS + warp, nslots, t.first + 32 * warp, pass,
+                   d.box, d.score, d.cls, t.first + ct);
     }
 }
 
@@ -370,10 +330,10 @@ ypp_decode_dense_kernel(const __grid_constant__ YppDecodeParams p, float* __rest
 __global__ void __launch_bounds__(YPP_DECODE_THREADS)
 ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs ws)
 {
-    __shared__ CompactSmem sm;
     const int b = blockIdx.y;
-    const int first = blockIdx.x * YPP_TILE_BOXES;
-    const int n = first + threadIdx.x;
+    const int n = blockIdx.x * YPP_DECODE_THREADS + threadIdx.x;
+    const int slot = n >> 5;
+    const int nslots = (int)gridDim.x * (YPP_DECODE_THREADS / 32);
     bool pass = false;
     float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
     float score = 0.f;
@@ -390,14 +350,7 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
         cls = c;
         pass = score > conf;
     }
-    const int warp = threadIdx.x >> 5;
-    const u32 m = compact_count(sm, warp, pass, box);
-    __syncthreads();
-    int tot;
-    const int pre = slot_prefix(sm, tot);
-    if (threadIdx.x == 0) tile_record(ws, b, (int)blockIdx.x, (int)gridDim.x, first, sm, tot);
-    const int before = __shfl_sync(YPP_FULL_MASK, pre, warp);
-    if (pass) candidate_store(ws, N, b, first, before, m, box, score, cls, n);
+    slot_store(ws, N, b, slot, nslots, slot << 5, pass, box, score, cls, n);
 }
 
 }  // namespace
@@ -407,7 +360,7 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
 {
     static int configured = -1, ctas_per_sm = 0, sms = 0;
-    const int smem = 2 * p.stage_bytes;
+    const int smem = YPP_D1_STAGES * p.stage_bytes;
     if (smem != configured) {
         if (smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

@@ -1,5 +1,5 @@
 // S1: per image ordering.  One CTA per image:
-//   1. concatenate the per-tile candidate keys D1 left (box-index order) into shared memory;
+//   1. concatenate the per-slot (32 boxes) candidate keys D1 left (box-index order) into shared memory;
 //   2. stable LSD radix sort on the score word only -> the stable descending-score order of
 //      torchvision::nms (scores.sort(stable=True, descending=True); ties -> lower box index),
 //      digits sized to the bits in which the image's scores actually differ;
@@ -183,37 +183,36 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     const int ntiles = min(*p.ws.ntiles, p.ws.tiles_max);
     const int* tcnt = p.ws.tile_cnt + (size_t)b * p.ws.tiles_max;
     int* tile_off = table;                                   // [ntiles + 1], dead before the first radix pass
-    if (warp == 0) {
+    if (tid == 0) {
+        hd->maxc = 0; hd->nminx1 = 0; hd->nminy1 = 0;
+        hd->n_low = 0; hd->n_high = 0; hd->flagged = 0;
+        hd->kmin = 0xffffffffu; hd->kmax = 0u;
+    }
+    if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
+    {
         const uint4* text = reinterpret_cast<const uint4*>(p.ws.tile_ext) + (size_t)b * p.ws.tiles_max;
         int run = 0;
         u32 M = 0, NX = 0, NY = 0;
-        for (int t0 = 0; t0 < ntiles; t0 += 32) {
-            const int t = t0 + lane;
+        for (int t0 = 0; t0 < ntiles; t0 += YPP_ORG_THREADS) {
+            const int t = t0 + tid;
             const int v = t < ntiles ? tcnt[t] : 0;
             if (v > 0) { const uint4 e = text[t]; M = max(M, e.x); NX = max(NX, e.y); NY = max(NY, e.z); }
-            int inc = v;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
-                if (lane >= d) inc += o;
-            }
-            if (t < ntiles) tile_off[t] = run + inc - v;
-            run += __shfl_sync(YPP_FULL_MASK, inc, 31);
+            int total;
+            const int ex = block_exclusive_scan(v, hd->warp_sums, total);   // syncs: the header init above is visible
+            if (t < ntiles) tile_off[t] = run + ex;
+            run += total;
         }
         M = __reduce_max_sync(YPP_FULL_MASK, M);
         NX = __reduce_max_sync(YPP_FULL_MASK, NX);
         NY = __reduce_max_sync(YPP_FULL_MASK, NY);
-        if (lane == 0) {
+        if (lane == 0 && M) { atomicMax(&hd->maxc, M); atomicMax(&hd->nminx1, NX); atomicMax(&hd->nminy1, NY); }
+        if (tid == 0) {
             tile_off[ntiles] = run;
             hd->n = min(run, N);
-            hd->maxc = M; hd->nminx1 = NX; hd->nminy1 = NY;
-            hd->n_low = 0; hd->n_high = 0; hd->flagged = 0;
-            hd->kmin = 0xffffffffu; hd->kmax = 0u;
             p.ws.cand_count[b] = min(run, N);
             p.ws.keep_count[b] = 0;
         }
     }
-    if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
     __syncthreads();
     const int n = hd->n;
     if (n == 0) {
@@ -221,17 +220,15 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         return;
     }
     S1_MARK(1);
-    // ---- 2. gather the tiles (warp per tile), track the range of the score words
+    // ---- 2. gather the slots, track the range of the score words
     {
         u32 kmin = 0xffffffffu, kmax = 0u;
-        for (int t = warp; t < ntiles; t += YPP_ORG_WARPS) {
-            const int cnt = tile_off[t + 1] - tile_off[t];
-            if (cnt <= 0) continue;
-            const u64* src = gkeys + p.ws.tile_first[t];
-            u64* dst = bufA + tile_off[t];
-            for (int i = lane; i < cnt; i += 32) {
-                const u64 k = src[i];
-                dst[i] = k;
+        for (int i = tid; i < ntiles * 32; i += YPP_ORG_THREADS) {      // slots hold <= 32 keys: one lane each
+            const int t = i >> 5;
+            const int off = tile_off[t], cnt = tile_off[t + 1] - off;
+            if (lane < cnt) {
+                const u64 k = gkeys[p.ws.tile_first[t] + lane];
+                bufA[off + lane] = k;
                 const u32 hi = (u32)(k >> 32);
                 kmin = min(kmin, hi); kmax = max(kmax, hi);
             }
@@ -450,7 +447,7 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
 {
     int tints = YPP_RADIX_MAX * YPP_TABLE_PITCH;
     if (33 * nc + 1 > tints) tints = 33 * nc + 1;
-    const int tiles_max = N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8;
+    const int tiles_max = (N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8) * (YPP_TILE_BOXES / 32);
     if (tiles_max + 1 > tints) tints = tiles_max + 1;
     *table_ints = tints;
     size_t fixed = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)tints;

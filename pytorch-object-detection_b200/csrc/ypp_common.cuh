@@ -33,10 +33,10 @@ struct YppWs {
     int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge), bit1: coordinate trick
     float* img_step;      // [B] max_coordinate + 1 of the image's candidates (the trick's class offset step)
     int* q;               // [4] q[0] long-segment queue length, q[1] queue head
-    int* ntiles;          // [1] D1 tiles per image
-    int* tile_first;      // [T] first box index of each D1 tile (the same for every image)
-    int* tile_cnt;        // [B][T] candidates each tile produced (compacted at keys[b][tile_first ..])
-    u32* tile_ext;        // [B][T][4] order-encoded max(x1,y1,x2,y2), max(-x1), max(-y1) over the tile's candidates
+    int* ntiles;          // [1] D1 slots (32 boxes, one warp) per image
+    int* tile_first;      // [T] first box index of each slot (the same for every image)
+    int* tile_cnt;        // [B][T] candidates each slot produced (compacted at keys[b][tile_first ..])
+    u32* tile_ext;        // [B][T][4] order-encoded max(x1,y1,x2,y2), max(-x1), max(-y1) over the slot's candidates
     int* bigq;            // [B * bigq_per_image] entries b*nc + c
     int* seg_start;       // [B][nc+1] segment starts in class order
     u64* keys;            // [B][N] (~enc(score))<<32 | idx<<12 | cls, compacted per tile by D1 (box-index order)
@@ -65,7 +65,7 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     w.q = (int*)take(sizeof(int) * 4);
     w.ntiles = (int*)take(sizeof(int));
     // a tile never spans two anchor planes, so a scale adds at most A partial tiles
-    w.tiles_max = N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8;
+    w.tiles_max = (N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8) * (YPP_TILE_BOXES / 32);   // 32-box slots
     w.tile_first = (int*)take(sizeof(int) * w.tiles_max);
     w.tile_cnt = (int*)take(sizeof(int) * (size_t)B * w.tiles_max);
     w.tile_ext = (u32*)take(sizeof(u32) * 4 * (size_t)B * w.tiles_max);

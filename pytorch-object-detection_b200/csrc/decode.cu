@@ -17,6 +17,7 @@
 // the sort input is already in box-index order and a STABLE sort by score alone gives the
 // reference's tie order.  No atomics, nothing to clear between calls.
 #include "ypp_kernels.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -233,14 +234,15 @@ __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppSc
 // own slot, so warps never wait for each other -- only for data.
 #define YPP_D1_STAGES 2
 #define YPP_D1_CONSUMERS (YPP_TILE_BOXES / 32)
-#define YPP_D1_THREADS (32 * (YPP_D1_CONSUMERS + 1))
+#define YPP_D1_MAX_PRODUCERS 4            /* UBLKCP issue is serialised per warp: spread the rows of a tile */
+#define YPP_D1_THREADS (32 * (YPP_D1_CONSUMERS + YPP_D1_MAX_PRODUCERS))
 
 __device__ __forceinline__ void mbar_arrive(u64* bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-__global__ void __launch_bounds__(YPP_D1_THREADS, 4)
+__global__ void __launch_bounds__(YPP_D1_THREADS, 3)
 ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B)
 {
     extern __shared__ __align__(128) float stage_mem[];      // [STAGES][C][256] when some scale is staged
@@ -251,30 +253,33 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
     const int stage_floats = p.C * YPP_TILE_BOXES;
     if (tid == 0) {
 #pragma unroll
-        for (int i = 0; i < YPP_D1_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], YPP_D1_CONSUMERS); }
+        for (int i = 0; i < YPP_D1_STAGES; ++i) { mbar_init(&full[i], (int)(blockDim.x >> 5) - YPP_D1_CONSUMERS); mbar_init(&empty[i], YPP_D1_CONSUMERS); }
     }
     __syncthreads();
     int b = (int)(blockIdx.x / (unsigned)tiles_per_img), tile = (int)(blockIdx.x - (unsigned)b * (unsigned)tiles_per_img);
     const int gb = (int)(gridDim.x / (unsigned)tiles_per_img), gt = (int)(gridDim.x - (unsigned)gb * (unsigned)tiles_per_img);
     int k = 0;
-    if (warp == YPP_D1_CONSUMERS) {
-        // ---------------- producer
+    if (warp >= YPP_D1_CONSUMERS) {
+        // ---------------- producers: warp pw copies channel rows [c_lo, c_hi) of every tile
+        const int P = (int)(blockDim.x >> 5) - YPP_D1_CONSUMERS, pw = warp - YPP_D1_CONSUMERS;
+        const int per = (p.C + P - 1) / P;
+        const int c_lo = min(p.C, pw * per), c_hi = min(p.C, c_lo + per);
         for (long long w = blockIdx.x; w < total; w += gridDim.x, ++k, b += gb, tile += gt) {
             if (tile >= tiles_per_img) { tile -= tiles_per_img; ++b; }
             const int stg = k % YPP_D1_STAGES, use = k / YPP_D1_STAGES;
             if (use > 0) mbar_wait(&empty[stg], (u32)(use - 1) & 1u);        // consumers are done with this stage
             const TileRef t = tile_ref(p, tile);
             const YppScaleParams& s = p.sc[t.si];
-            if (s.tma) {
+            if (s.tma && c_hi > c_lo) {
                 const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
                 const u32 row_bytes = (u32)t.ncells * 4u;                    // multiple of 16: HW % 4 == 0
                 float* stage = stage_mem + stg * stage_floats;
-                if (lane == 0) mbar_expect_tx(&full[stg], row_bytes * (u32)p.C);
+                if (lane == 0) mbar_expect_tx(&full[stg], row_bytes * (u32)(c_hi - c_lo));
                 __syncwarp();
-                for (int c = lane; c < p.C; c += 32)
+                for (int c = c_lo + lane; c < c_hi; c += 32)
                     bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, &full[stg]);
             } else if (lane == 0) {
-                mbar_arrive(&full[stg]);                                     // unstaged tile: consumers read the head directly
+                mbar_arrive(&full[stg]);                                     // nothing to stage: consumers read the head directly
             }
         }
         return;
@@ -361,7 +366,14 @@ int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
 {
     static int configured = -1, ctas_per_sm = 0, sms = 0;
     const int smem = YPP_D1_STAGES * p.stage_bytes;
-    if (smem != configured) {
+    // one producer warp per ~20 channel rows of a tile (env YPP_D1_PRODUCERS overrides, for tuning)
+    static int producers_env = -1;
+    if (producers_env < 0) { const char* e = getenv("YPP_D1_PRODUCERS"); producers_env = e ? atoi(e) : 0; }
+    int P = producers_env > 0 ? producers_env : (p.C + 19) / 20;
+    P = P < 1 ? 1 : (P > YPP_D1_MAX_PRODUCERS ? YPP_D1_MAX_PRODUCERS : P);
+    const int threads = 32 * (YPP_D1_CONSUMERS + P);
+    const int cfg_key = smem * 8 + P;
+    if (cfg_key != configured) {
         if (smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { ypp_set_error("decode_compact: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
@@ -369,14 +381,14 @@ int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
         int dev = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, YPP_D1_THREADS, smem);
+        cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, threads, smem);
         if (e != cudaSuccess || ctas_per_sm < 1) { ypp_set_error("decode_compact: occupancy query failed"); return YPP_E_CUDA; }
-        configured = smem;
+        configured = cfg_key;
     }
     const long long total = (long long)p.tile_base[p.n_scales] * B;
     long long grid = (long long)sms * ctas_per_sm;
     if (grid > total) grid = total;
-    ypp_decode_compact_kernel<<<(unsigned)grid, YPP_D1_THREADS, smem, st>>>(p, B);
+    ypp_decode_compact_kernel<<<(unsigned)grid, threads, smem, st>>>(p, B);
     ypp_count_launch(1);
     return ypp_check_launch("decode_compact");
 }

@@ -9,8 +9,8 @@
 //      max_coordinate + 1; N1 gathers the boxes through the map, converts them to xyxy
 //      (utils/yolo_utils.py:339-343) and applies cls * step;
 //   5. coordinate trick only: detect cross-class suppression edges (possible when a box with
-//      negative x1,y1 is shifted onto the previous class band); such an image is re-emitted as
-//      ONE class-agnostic segment so the greedy scan sees exactly what torchvision's does.
+//      negative x1,y1 is shifted onto the previous class band); the classes such an edge couples
+//      share ONE segment, so the greedy scan sees exactly what torchvision's single pass does.
 #include "ypp_kernels.cuh"
 
 #ifdef YPP_PROFILE_S1
@@ -24,6 +24,7 @@ namespace {
 
 #define YPP_DET_LIST 64
 #define YPP_DET_BINS 64
+#define YPP_DET_EDGES 64
 #define YPP_ORG_WARPS (YPP_ORG_THREADS / 32)
 #define YPP_RADIX_MAX 256
 #define YPP_TABLE_PITCH 33              // table[digit * 33 + warp]: leaders of one warp hit distinct banks
@@ -37,6 +38,8 @@ struct OrgSmemHeader {
     u32 bin_lo[YPP_DET_BINS];     // B role: per x-bin max of enc(-y1);      after the scan: prefix max
     int warp_sums[YPP_ORG_WARPS];
     int n_low, n_high, flagged, n;
+    int n_edges, epad[3];
+    u32 edges[YPP_DET_EDGES];     // (class of the earlier box << 16) | class of the box it suppresses
     u32 maxc, nminx1, nminy1, kmin, kmax, pad[3];
 };
 
@@ -185,7 +188,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     int* tile_off = table;                                   // [ntiles + 1], dead before the first radix pass
     if (tid == 0) {
         hd->maxc = 0; hd->nminx1 = 0; hd->nminy1 = 0;
-        hd->n_low = 0; hd->n_high = 0; hd->flagged = 0;
+        hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; hd->n_edges = 0;
         hd->kmin = 0xffffffffu; hd->kmax = 0u;
     }
     if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
@@ -340,8 +343,76 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         if (!p.keys_in_smem) { __syncthreads(); keys = skeys; }
     }
     S1_MARK(5);
-    // ---- 5. class counting (warp w owns ranks [w*L, (w+1)*L)), segment starts
+    // ---- 5. coordinate trick: exact test of the detector's candidate pairs.  A cross-class pair whose
+    // SHIFTED boxes suppress couples the two classes: they are merged into one segment (greedy NMS over
+    // the union in score order is then exactly what torchvision's single pass does; classes that share
+    // no such pair stay independent).  Too many candidates -> one class-agnostic segment.
     __syncthreads();                                         // table is free again
+    int* cmap = seg + nc + 1;                                // [nc] class -> segment that holds it
+    for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = c;
+    if (trick && nc > 1) {
+        const int nl = hd->n_low, nh = hd->n_high;
+        if (nl > 0 && nh > 0) {
+            const bool neg_thr = !(p.iou_thr >= 0.0f);
+            auto test_pair = [&](const DetEntry& x, const DetEntry& y) {
+                if (x.cls == y.cls) return;
+                const DetEntry& row = x.key < y.key ? x : y;               // smaller key = earlier in score order
+                const DetEntry& col = x.key < y.key ? y : x;
+                const float sa = ypp_area(row.box);
+                const bool sup = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
+                                         : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
+                if (sup) {
+                    const int e = atomicAdd(&hd->n_edges, 1);
+                    if (e < YPP_DET_EDGES) hd->edges[e] = ((u32)row.cls << 16) | (u32)col.cls;
+                }
+            };
+            const bool lo_fits = nl <= YPP_DET_LIST, hi_fits = nh <= YPP_DET_LIST;
+            if (!lo_fits && !hi_fits) {
+                if (tid == 0) hd->flagged = 1;
+            } else if (lo_fits && hi_fits) {
+                for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) test_pair(hd->lowl[t / nh], hd->highl[t % nh]);
+            } else {
+                // one role has too many candidates to list: test EVERY box against the list that fits
+                const DetEntry* lst = lo_fits ? hd->lowl : hd->highl;
+                const int nlst = lo_fits ? nl : nh;
+                for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+                    DetEntry e;
+                    e.key = keys[i];
+                    e.cls = ypp_key_cls(e.key);
+                    const float4 xy = ypp_xyxy(gbox[ypp_key_idx(e.key)]);
+                    const float off = __fmul_rn((float)e.cls, step);
+                    e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                    for (int j = 0; j < nlst; ++j) test_pair(e, lst[j]);
+                }
+            }
+        }
+        __syncthreads();
+        const int ne = hd->n_edges;
+        if (hd->flagged || ne > YPP_DET_EDGES) {
+            for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = 0;
+            if (tid == 0) hd->flagged = 1;
+        } else if (ne > 0) {
+            if (tid == 0) {                                  // union by smallest class id; a handful of edges
+                for (int e = 0; e < ne; ++e) {
+                    int a = (int)(hd->edges[e] >> 16), c2 = (int)(hd->edges[e] & 0xffffu);
+                    while (cmap[a] != a) a = cmap[a];
+                    while (cmap[c2] != c2) c2 = cmap[c2];
+                    if (a != c2) cmap[max(a, c2)] = min(a, c2);
+                }
+                hd->flagged = 1;
+            }
+            __syncthreads();
+            for (int c0 = 0; c0 < nc; c0 += YPP_ORG_THREADS) {
+                const int c = c0 + tid;
+                int r = c < nc ? c : 0;
+                while (cmap[r] != r) r = cmap[r];
+                __syncthreads();
+                if (c < nc) cmap[c] = r;
+            }
+        }
+    }
+    // ---- 6. class counting (warp w owns ranks [w*L, (w+1)*L)), segment starts
+    __syncthreads();
     for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
     __syncthreads();
     const int r_begin = warp * L, r_end = min(n, r_begin + L);
@@ -349,7 +420,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     int* my = table + warp * nc;
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
-        if (r < r_end) atomicAdd(&my[ypp_key_cls(keys[r])], 1);
+        if (r < r_end) atomicAdd(&my[cmap[ypp_key_cls(keys[r])]], 1);
     }
     __syncthreads();
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
@@ -381,11 +452,11 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     __syncthreads();
     S1_MARK(6);
-    // ---- 6. stable ranking: segment position -> global rank (N1 gathers the boxes through it)
+    // ---- 7. stable ranking: segment position -> global rank (N1 gathers the boxes through it)
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {
         const int r = r0 + lane;
         const bool ok = r < r_end;
-        const int c = ok ? ypp_key_cls(keys[r]) : 0;
+        const int c = ok ? cmap[ypp_key_cls(keys[r])] : 0;
         const unsigned peers = same_value_lanes(c, cbits, ok);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         int q = 0;
@@ -398,36 +469,11 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         __syncwarp();
     }
     S1_MARK(7);
-    // ---- 7. coordinate trick: exact test of the detector's candidate pairs
-    if (trick && nc > 1) {
-        const int nl = hd->n_low, nh = hd->n_high;
-        if (nl > 0 && nh > 0) {
-            if (nl > YPP_DET_LIST || nh > YPP_DET_LIST) {
-                if (tid == 0) hd->flagged = 1;
-            } else {
-                const bool neg_thr = !(p.iou_thr >= 0.0f);
-                for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) {
-                    const DetEntry lo = hd->lowl[t / nh], hi = hd->highl[t % nh];
-                    if (lo.cls == hi.cls) continue;
-                    const DetEntry& row = lo.key < hi.key ? lo : hi;       // smaller key = earlier in score order
-                    const DetEntry& col = lo.key < hi.key ? hi : lo;
-                    const float sa = ypp_area(row.box);
-                    const bool s = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
-                                           : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
-                    if (s) hd->flagged = 1;
-                }
-            }
-        }
-        __syncthreads();
-        if (hd->flagged) {
-            // class-agnostic single segment in global score order
-            for (int r = tid; r < n; r += YPP_ORG_THREADS) grank[r] = r;
-            for (int c = tid; c <= nc; c += YPP_ORG_THREADS) seg[c] = c == 0 ? 0 : n;
-            __syncthreads();
-        }
-    }
+    __syncthreads();
     if (tid == 0) {
-        p.ws.imgflag[b] = (hd->flagged ? 1 : 0) | (trick ? 2 : 0);
+        // bits 8.. are diagnostics: detector list lengths and suppressing cross-class pairs (each clamped to 255)
+        p.ws.imgflag[b] = (hd->flagged ? 1 : 0) | (trick ? 2 : 0) | (min(hd->n_low, 255) << 8) | (min(hd->n_high, 255) << 16) |
+                          (min(hd->n_edges, 255) << 24);
         p.ws.img_step[b] = step;
     }
     for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = seg[c];
@@ -446,7 +492,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
 int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
 {
     int tints = YPP_RADIX_MAX * YPP_TABLE_PITCH;
-    if (33 * nc + 1 > tints) tints = 33 * nc + 1;
+    if (34 * nc + 1 > tints) tints = 34 * nc + 1;
     const int tiles_max = (N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8) * (YPP_TILE_BOXES / 32);
     if (tiles_max + 1 > tints) tints = tiles_max + 1;
     *table_ints = tints;

@@ -30,7 +30,7 @@ typedef unsigned int u32;
 struct YppWs {
     int* cand_count;      // [B] written by S1
     int* keep_count;      // [B] zeroed by S1, accumulated by N1
-    int* imgflag;         // [B] bit0: whole-image class-agnostic segment (trick cross-class edge), bit1: coordinate trick
+    int* imgflag;         // [B] bit0: some classes share a segment (coordinate-trick cross-class edge), bit1: coordinate trick
     float* img_step;      // [B] max_coordinate + 1 of the image's candidates (the trick's class offset step)
     int* q;               // [4] q[0] long-segment queue length, q[1] queue head
     int* ntiles;          // [1] D1 slots (32 boxes, one warp) per image

@@ -78,6 +78,44 @@ def test_big_single_class_segment_and_whole_image_fallback(oracle, cuda):
             assert (n - 1) in set(k.tolist())
 
 
+def test_coupled_classes_share_a_segment(oracle, cuda):
+    """Trick mode with cross-class suppression: only the classes an edge couples are merged.  Many boxes
+    near max_coord overflow one detector list, which takes the every-box sweep; a dense synthetic image
+    known to hold such an edge (workload seed 64, image 44) goes through the whole chain."""
+    from ypp import engine, synth, _lib
+    rng = np.random.RandomState(11)
+    n, nc = 3000, 6
+    rows = np.concatenate([rng.uniform(0, 416, (n, 2)), rng.uniform(8, 120, (n, 2)),
+                           rng.uniform(.26, 1, (n, 1)), rng.randint(0, nc, (n, 1))], 1).astype(np.float32)
+    rows[:200, 0:2] = rng.uniform(990, 1000, (200, 2))      # a crowd near max_coord, all classes
+    rows[:200, 2:4] = rng.uniform(8, 20, (200, 2))
+    rows[:200, 4] = rng.uniform(.26, .9, 200)
+    rows[0] = [1000, 1000, 20, 20, .99, 1]
+    rows[n - 1] = [-9, -9, 20, 20, .98, 2]                  # class 2 shifted onto class 1's band
+    rows[n - 2] = [-8, -10, 20, 20, .97, 5]                 # class 5 onto class 4's band
+    rows[1] = [1001, 999, 20, 20, .995, 4]
+    t = torch.tensor(rows).to(cuda)
+    for um in ("fma", "separate"):
+        pp = engine.PostProcessor(nc, [[1, 1]], 1, 0.25, kind="v2", anchors_per_scale=1, offset_mode="trick", union_mode=um)
+        res = pp.nms_rows(t, want_keep_idx=True)
+        k = res.keep_idx[0, : int(res.keep_count[0])].cpu().numpy()
+        ref, _ = oracle.nms_v3_indices(rows, .25, .45, offset_mode=oracle.OFFSET_TRICK,
+                                       union_mode=oracle.UNION_FMA if um == "fma" else oracle.UNION_SEPARATE)
+        assert np.array_equal(k, util.canon(ref, rows)), um
+        assert (n - 1) not in set(k.tolist()) and (n - 2) not in set(k.tolist())
+    w = synth.WORKLOADS["yolov3_416_voc_b64"]
+    heads = [h[44:46].contiguous().to(cuda) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=64)]
+    pp = engine.PostProcessor(w["nc"], synth.workload_anchors(w), w["input_size"], w["conf"], kind=w["kind"],
+                              anchors_per_scale=w["A"], offset_mode="auto_cuda", union_mode="fma")
+    dec = pp.decode(heads).cpu().numpy()
+    res = pp(heads, want_keep_idx=True)
+    for b in range(2):
+        k = res.keep_idx[b, : int(res.keep_count[b])].cpu().numpy()
+        ref, _ = oracle.nms_v3_indices(dec[b], w["conf"], .45, offset_mode=_lib.OFFSET_MODES["auto_cuda"],
+                                       union_mode=_lib.UNION_MODES["fma"])
+        assert np.array_equal(k, util.canon(ref, dec[b])), b
+
+
 def test_wrappers_match_reference(cuda):
     from ypp import synth
     from ypp.compat.yolov3_utils import DecodeYoloV3, decode_predictions as dec3

@@ -83,6 +83,26 @@ __device__ __forceinline__ float pair_d(const float4 a, const float sa, const fl
     return __fmaf_rn(-thr, fabsf(uni), inter);
 }
 
+// Lean form used by the per-class segment kernel.  With c1 = 1 + thr, ta = -thr*S_a, tb = -thr*S_b:
+//   inter - thr*(S_a + S_b - inter) = c1*inter + ta + tb,
+// so a column only accumulates g = max over rows of fma(c1, inter, ta) and adds its own tb at the end.
+// The clamp of the y extent rides on the multiplier: hs = sat(h * 2^-k) (k per segment such that
+// every extent * 2^-k <= 1; power-of-two scaling is exact) and c1k = c1 * 2^k undoes it.  inter is
+// torchvision's own fp32 value; the union differs from torchvision's by a few roundings of an area,
+// |error of g + tb| <= 20 * 2^-24 * (largest |area|), inside the segment's decision band
+// 2 * 2^-20 * (largest |area|), so "beyond the band" still decides and "inside" still goes to the
+// exact division.  ta, tb use |area|: an inverted box never overlaps anything (inter <= 0), and with
+// |area| its pairs can only come out "alive" or "ask the exact form", never "suppressed".
+// 5 fma-pipe + 4 (+ half a 3-input max) alu-pipe instructions per pair.
+__device__ __forceinline__ float pair_g(const float4 a, const float ta, const float4 b, const float c1k, const float scale)
+{
+    const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
+    const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
+    const float w = __fsub_rn(r, l);
+    const float hs = __saturatef(__fmul_rn(__fsub_rn(bt, t), scale));
+    return __fmaf_rn(c1k, __fmul_rn(w, hs), ta);
+}
+
 // box of global score rank r of image `ibase`: cxcywh -> xyxy exactly as nms_v3 does, plus the
 // coordinate trick's class offset when torchvision would apply it (S1 decided per image)
 __device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r, bool trick, float step)
@@ -98,7 +118,7 @@ __device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r,
 
 // a row that can never raise dmax (padding of the kept-row lists)
 #define YPP_DUMMY_BOX make_float4(1e30f, 1e30f, -1e30f, -1e30f)
-#define YPP_DUMMY_AREA 1e30f
+#define YPP_DUMMY_TA (-1e30f)
 
 // ------------------------------------------------------------------ per-class segments: one 4-warp CTA each
 #define YPP_NMSQ_WARPS 4
@@ -108,8 +128,9 @@ struct SegSmem {
     float4 box[YPP_WARP_SEG];
     float area[YPP_WARP_SEG];
     float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 4
-    float karea[YPP_NMSQ_WARPS][8];
+    float kta[YPP_NMSQ_WARPS][8];       // -thr * area of those rows
     u32 amax[YPP_NMSQ_WARPS];
+    u32 cmax[YPP_NMSQ_WARPS];
     u32 in_words[32];          // byte w of word j: rows 8w..8w+7 of the tile that suppress column j
     uint4 dpart[32];           // per lane: the four warps' partial dead-column bits
 };
@@ -136,20 +157,30 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const bool trick = (p.ws.imgflag[b] & 2) != 0;
     const float step = p.ws.img_step[b];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    u32 amax_bits = 0;            // uint order == float order for non-negative floats; NaN sorts on top
+    u32 amax_bits = 0, cmax_bits = 0;   // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
         const float4 q = rank_box(p.ws, ibase, grank[i], trick, step);
         const float ar = ypp_area(q);
         sm.box[i] = q;
         sm.area[i] = ar;
         amax_bits = max(amax_bits, __float_as_uint(fabsf(ar)));
+        cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
+                        max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
     }
     amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
-    if (lane == 0) sm.amax[w] = amax_bits;
+    cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
+    if (lane == 0) { sm.amax[w] = amax_bits; sm.cmax[w] = cmax_bits; }
     __syncthreads();
     // one decision band for the whole segment (NaN / inf areas make every compare fail -> exact path)
-    const float Bseg = 2.0f * YPP_PAIR_BAND *
+    float Bseg = 2.0f * YPP_PAIR_BAND *
         __uint_as_float(max(max(sm.amax[0], sm.amax[1]), max(sm.amax[2], sm.amax[3])));
+    // extents are below 2^(E-125) when the largest |coordinate| has biased exponent E: scale = 2^-(E-125)
+    const int cexp = (int)(max(max(sm.cmax[0], sm.cmax[1]), max(sm.cmax[2], sm.cmax[3])) >> 23);
+    if (cexp < 67 || cexp > 187) Bseg = INFINITY;        // coordinates beyond 2^+-60 (or not finite): exact path only
+    const int cex = min(max(cexp, 67), 187);
+    const float scale = __uint_as_float((u32)(252 - cex) << 23);
+    const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cex + 2) << 23));
+    const float nthr = -thr;
     const int ntiles = (len + 31) >> 5;
     const u32 wmask = 0xffu << (8 * w);
     u32 dead = 0;                 // bit k: column lane + 32k is suppressed (merged over the four warps)
@@ -163,9 +194,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
         if (alive == 0) continue;
         // ---- diagonal tile, column view: which of MY rows (i < lane, alive) suppress column lane
         const float4 cb = sm.box[in_range ? j : base];
-        const float my_area = sm.area[in_range ? j : base];
-        float p0, p1;
-        pair_col<kFma>(cb, p0, p1);
+        const float my_ta = __fmul_rn(nthr, fabsf(sm.area[in_range ? j : base]));
         u32 in = 0;
         if (kFast) {
             // my 8 rows, unconditionally (dead or out-of-range rows are masked out below)
@@ -173,11 +202,11 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 const int i = min(base + 8 * w + q, len - 1);
-                const float d = pair_d<kFma>(sm.box[i], sm.area[i], cb, p0, p1, thr);
+                const float d = __fadd_rn(pair_g(sm.box[i], __fmul_rn(nthr, fabsf(sm.area[i])), cb, c1k, scale), my_ta);
                 if (d > Bseg) in |= 1u << (8 * w + q);
                 lo = fminf(lo, fabsf(d));             // a NaN d is never a suppression: dropped
             }
-            if (!(lo > Bseg)) {                       // some pair inside the band: exact pass
+            if (!(lo > Bseg)) {                       // some pair inside the band (or a NaN): exact pass
                 in = 0;
                 for (int q = 0; q < 8; ++q) {
                     const int i = min(base + 8 * w + q, len - 1);
@@ -216,12 +245,12 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             if ((Kw >> lane) & 1u) {
                 const int s = __popc(Kw & ((1u << lane) - 1u));
                 sm.kbox[w][s] = cb;
-                sm.karea[w][s] = my_area;
+                sm.kta[w][s] = my_ta;
             }
-            if (lane >= nkw && lane < npad) { sm.kbox[w][lane] = YPP_DUMMY_BOX; sm.karea[w][lane] = YPP_DUMMY_AREA; }
+            if (lane >= nkw && lane < npad) { sm.kbox[w][lane] = YPP_DUMMY_BOX; sm.kta[w][lane] = YPP_DUMMY_TA; }
             __syncwarp();
             const float4* kb = sm.kbox[w];
-            const float* ka = sm.karea[w];
+            const float* ka = sm.kta[w];
             for (int k = T + 1; k < ntiles; k += 2) {
                 const int j0 = (k << 5) + lane, j1 = j0 + 32;
                 const bool v0 = j0 < len && !((dead >> k) & 1u);
@@ -231,19 +260,18 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
                 bool d0 = false, d1 = false;
                 bool exact = !kFast;
                 if (kFast) {
-                    float p00, p01, p10, p11;
-                    pair_col<kFma>(c0, p00, p01);
-                    pair_col<kFma>(c1, p10, p11);
                     float dm0 = -INFINITY, dm1 = -INFINITY;
                     for (int r = 0; r < npad; r += 4) {
 #pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            const float4 a = kb[r + q];
-                            const float sa = ka[r + q];
-                            dm0 = fmaxf(dm0, pair_d<kFma>(a, sa, c0, p00, p01, thr));
-                            dm1 = fmaxf(dm1, pair_d<kFma>(a, sa, c1, p10, p11, thr));
+                        for (int q = 0; q < 4; q += 2) {
+                            const float4 a = kb[r + q], a2 = kb[r + q + 1];
+                            const float ta = ka[r + q], ta2 = ka[r + q + 1];
+                            dm0 = fmaxf(fmaxf(dm0, pair_g(a, ta, c0, c1k, scale)), pair_g(a2, ta2, c0, c1k, scale));
+                            dm1 = fmaxf(fmaxf(dm1, pair_g(a, ta, c1, c1k, scale)), pair_g(a2, ta2, c1, c1k, scale));
                         }
                     }
+                    dm0 = __fadd_rn(dm0, __fmul_rn(nthr, fabsf(sm.area[j0 < len ? j0 : 0])));
+                    dm1 = __fadd_rn(dm1, __fmul_rn(nthr, fabsf(sm.area[j1 < len ? j1 : 0])));
                     d0 = dm0 > Bseg;
                     d1 = dm1 > Bseg;
                     exact = (v0 && !d0 && !(dm0 < -Bseg)) || (v1 && !d1 && !(dm1 < -Bseg));
@@ -252,7 +280,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
                     d0 = d1 = false;
                     for (int r = 0; r < nkw; ++r) {
                         const float4 a = kb[r];
-                        const float sa = ka[r];
+                        const float sa = ypp_area(a);
                         d0 = d0 || pair_exact(a, sa, c0, thr, union_fma);
                         d1 = d1 || pair_exact(a, sa, c1, thr, union_fma);
                     }

@@ -321,6 +321,53 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             }
         }
         __syncthreads();
+        // exact test of the candidate pairs: a cross-class pair whose SHIFTED boxes suppress is an edge
+        {
+            const int nl = hd->n_low, nh = hd->n_high;
+            if (nl > 0 && nh > 0) {
+                const bool neg_thr = !(p.iou_thr >= 0.0f);
+                auto test_pair = [&](const DetEntry& x, const DetEntry& y) {
+                    if (x.cls == y.cls) return;
+                    // boxes that do not intersect have IoU 0 (or NaN): no edge unless thr is negative
+                    if (!neg_thr && !(fmaxf(x.box.x, y.box.x) < fminf(x.box.z, y.box.z) &&
+                                      fmaxf(x.box.y, y.box.y) < fminf(x.box.w, y.box.w))) return;
+                    const DetEntry& row = x.key < y.key ? x : y;               // smaller key = earlier in score order
+                    const DetEntry& col = x.key < y.key ? y : x;
+                    const float sa = ypp_area(row.box);
+                    const bool sup = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
+                                             : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
+                    if (sup) {
+                        const int e = atomicAdd(&hd->n_edges, 1);
+                        if (e < YPP_DET_EDGES) hd->edges[e] = ((u32)row.cls << 16) | (u32)col.cls;
+                    }
+                };
+                const bool lo_fits = nl <= YPP_DET_LIST, hi_fits = nh <= YPP_DET_LIST;
+                if (!lo_fits && !hi_fits) {
+                    if (tid == 0) hd->flagged = 1;
+                } else if (lo_fits && hi_fits) {
+                    for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) test_pair(hd->lowl[t / nh], hd->highl[t % nh]);
+                } else {
+                    // one role has too many candidates to list: test EVERY box that meets the role's necessary condition
+                    // against the list that fits (keys are still in box-index order: sequential box reads)
+                    const float y1min = -ypp_dec(hd->nminy1);
+                    const DetEntry* lst = lo_fits ? hd->lowl : hd->highl;
+                    const int nlst = lo_fits ? nl : nh;
+                    for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+                        DetEntry e;
+                        e.key = bufA[i];
+                        e.cls = ypp_key_cls(e.key);
+                        const float4 xy = ypp_xyxy(gbox[ypp_key_idx(e.key)]);
+                        // the role's necessary condition first (same tests as the detector sweep)
+                        if (lo_fits ? !(xy.z - step > dg.x1min - dg.slack && xy.w - step > y1min - dg.slack)
+                                    : !(xy.x < dg.lim && xy.y < dg.lim)) continue;
+                        const float off = __fmul_rn((float)e.cls, step);
+                        e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+                        for (int j = 0; j < nlst; ++j) test_pair(e, lst[j]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
     }
     S1_MARK(3);
     // ---- 4. stable sort by score word
@@ -343,49 +390,13 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         if (!p.keys_in_smem) { __syncthreads(); keys = skeys; }
     }
     S1_MARK(5);
-    // ---- 5. coordinate trick: exact test of the detector's candidate pairs.  A cross-class pair whose
-    // SHIFTED boxes suppress couples the two classes: they are merged into one segment (greedy NMS over
-    // the union in score order is then exactly what torchvision's single pass does; classes that share
-    // no such pair stay independent).  Too many candidates -> one class-agnostic segment.
+    // ---- 5. coordinate trick: an edge couples two classes: they are merged into one segment (greedy NMS
+    // over the union in score order is then exactly what torchvision's single pass does; classes that
+    // share no edge stay independent).  Too many candidates or edges -> one class-agnostic segment.
     __syncthreads();                                         // table is free again
     int* cmap = seg + nc + 1;                                // [nc] class -> segment that holds it
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = c;
     if (trick && nc > 1) {
-        const int nl = hd->n_low, nh = hd->n_high;
-        if (nl > 0 && nh > 0) {
-            const bool neg_thr = !(p.iou_thr >= 0.0f);
-            auto test_pair = [&](const DetEntry& x, const DetEntry& y) {
-                if (x.cls == y.cls) return;
-                const DetEntry& row = x.key < y.key ? x : y;               // smaller key = earlier in score order
-                const DetEntry& col = x.key < y.key ? y : x;
-                const float sa = ypp_area(row.box);
-                const bool sup = neg_thr ? ypp_suppresses<false>(row.box, sa, col.box, p.iou_thr, p.union_mode)
-                                         : ypp_suppresses<true>(row.box, sa, col.box, p.iou_thr, p.union_mode);
-                if (sup) {
-                    const int e = atomicAdd(&hd->n_edges, 1);
-                    if (e < YPP_DET_EDGES) hd->edges[e] = ((u32)row.cls << 16) | (u32)col.cls;
-                }
-            };
-            const bool lo_fits = nl <= YPP_DET_LIST, hi_fits = nh <= YPP_DET_LIST;
-            if (!lo_fits && !hi_fits) {
-                if (tid == 0) hd->flagged = 1;
-            } else if (lo_fits && hi_fits) {
-                for (int t = tid; t < nl * nh; t += YPP_ORG_THREADS) test_pair(hd->lowl[t / nh], hd->highl[t % nh]);
-            } else {
-                // one role has too many candidates to list: test EVERY box against the list that fits
-                const DetEntry* lst = lo_fits ? hd->lowl : hd->highl;
-                const int nlst = lo_fits ? nl : nh;
-                for (int i = tid; i < n; i += YPP_ORG_THREADS) {
-                    DetEntry e;
-                    e.key = keys[i];
-                    e.cls = ypp_key_cls(e.key);
-                    const float4 xy = ypp_xyxy(gbox[ypp_key_idx(e.key)]);
-                    const float off = __fmul_rn((float)e.cls, step);
-                    e.box = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
-                    for (int j = 0; j < nlst; ++j) test_pair(e, lst[j]);
-                }
-            }
-        }
         __syncthreads();
         const int ne = hd->n_edges;
         if (hd->flagged || ne > YPP_DET_EDGES) {

@@ -21,6 +21,7 @@
 // Pairs inside that band (practically none) are re-evaluated with the exact division, so keep
 // sets stay bit-exact.
 #include "ypp_kernels.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -405,7 +406,7 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
     }
 }
 
-// persistent CTAs pull (image, class) pairs from the queue S1 filled
+// persistent CTAs walk the per-image lists of long segments S1 left (bigq[b][0 .. bigcnt[b]))
 template <bool kFast, bool kFma>
 __global__ void __launch_bounds__(YPP_NMS_BIG_THREADS, 1)
 ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
@@ -414,16 +415,16 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
     float4* cache = reinterpret_cast<float4*>(smem_raw);
     u32* removed = reinterpret_cast<u32*>(smem_raw + sizeof(float4) * YPP_BIG_CACHE);
     __shared__ TileSmem ts;
-    __shared__ int item;
-    const int qn = min(p.ws.q[0], p.B * p.ws.bigq_per_image);
-    for (;;) {
-        if (threadIdx.x == 0) item = atomicAdd(p.ws.q + 1, 1);
-        __syncthreads();
-        const int it = item;
-        __syncthreads();
-        if (it >= qn) return;
-        const int e = p.ws.bigq[it];
-        const int b = e / p.nc, c = e - b * p.nc;
+    const int per = p.ws.bigq_per_image;
+    {   // nearly always there is nothing to do: find out with one round of loads
+        int any = 0;
+        for (int b = threadIdx.x; b < p.B; b += YPP_NMS_BIG_THREADS) any |= p.ws.bigcnt[b];
+        if (!__syncthreads_or(any)) return;
+    }
+    for (int it = blockIdx.x; it < p.B * per; it += gridDim.x) {
+        const int b = it / per, k = it - b * per;
+        if (k >= min(p.ws.bigcnt[b], per)) continue;          // uniform over the CTA
+        const int c = p.ws.bigq[it];
         const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
         const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
         const size_t base = (size_t)b * p.N;

@@ -1,8 +1,9 @@
 // S1: per image ordering.  One CTA per image:
 //   1. concatenate the per-slot (32 boxes) candidate keys D1 left (box-index order) into shared memory;
-//   2. stable LSD radix sort on the score word only -> the stable descending-score order of
-//      torchvision::nms (scores.sort(stable=True, descending=True); ties -> lower box index),
-//      digits sized to the bits in which the image's scores actually differ;
+//   2. sort -> the stable descending-score order of torchvision::nms (scores.sort(stable=True,
+//      descending=True); ties -> lower box index): one bucketing pass on the top bits in which the
+//      image's scores differ + ranking inside the (tiny) buckets; stable LSD radix passes on the
+//      score word when many scores tie;
 //   3. stable counting partition by class -> per (image, class) segments in the same order;
 //   4. emit the segment -> global-rank map and, per image, whether torchvision would take the
 //      coordinate-trick path (_batched_nms_coordinate_trick) and its offset step
@@ -16,8 +17,14 @@
 #ifdef YPP_PROFILE_S1
 __device__ long long ypp_s1_clk[16];
 #define S1_MARK(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) ypp_s1_clk[i] = clock64(); } while (0)
+__device__ __forceinline__ long long s1_gtime() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+// [9] longest CTA (cycles), [10] earliest CTA start, [11] latest CTA end (globaltimer ns; [10] must be preset large)
+#define S1_CTA_BEGIN() const long long s1_c0 = clock64(); if (threadIdx.x == 0) atomicMin(&ypp_s1_clk[10], s1_gtime())
+#define S1_CTA_END() do { if (threadIdx.x == 0) { atomicMax(&ypp_s1_clk[9], clock64() - s1_c0); atomicMax(&ypp_s1_clk[11], s1_gtime()); } } while (0)
 #else
 #define S1_MARK(i) do { } while (0)
+#define S1_CTA_BEGIN() do { } while (0)
+#define S1_CTA_END() do { } while (0)
 #endif
 
 namespace {
@@ -38,7 +45,7 @@ struct OrgSmemHeader {
     u32 bin_lo[YPP_DET_BINS];     // B role: per x-bin max of enc(-y1);      after the scan: prefix max
     int warp_sums[YPP_ORG_WARPS];
     int n_low, n_high, flagged, n;
-    int n_edges, epad[3];
+    int n_edges, max_bucket, n_big, epad;
     u32 edges[YPP_DET_EDGES];     // (class of the earlier box << 16) | class of the box it suppresses
     u32 maxc, nminx1, nminy1, kmin, kmax, pad[3];
 };
@@ -159,6 +166,62 @@ __device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, in
     __syncthreads();
 }
 
+// Sort by bucketing + ranking.  The keys are unique 64-bit words, so ANY sort of them is the stable
+// score order; stability of the passes themselves is not needed.  One MSD pass on the top
+// dbits <= 12 bits of the score span drops every key into its bucket with plain shared-memory
+// atomics (order inside a bucket arbitrary); buckets hold a handful of keys, so a key's final
+// place is bucket start + the number of smaller keys in its bucket.  Returns false (nothing written
+// to dst) when some bucket is too crowded for that (many tied scores): the caller takes the LSD passes.
+#define YPP_BUCKET_BITS 12
+#define YPP_BUCKET_MAX 96
+__device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int bits, u32 kmin,
+                                 int* table, OrgSmemHeader* hd)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int dbits = min(bits, YPP_BUCKET_BITS), shift = bits - dbits, R = 1 << dbits;
+    for (int i = tid; i < R; i += YPP_ORG_THREADS) table[i] = 0;
+    if (tid == 0) hd->max_bucket = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += YPP_ORG_THREADS) atomicAdd(&table[((u32)(src[i] >> 32) - kmin) >> shift], 1);
+    __syncthreads();
+    {
+        const int ipt = (R + YPP_ORG_THREADS - 1) / YPP_ORG_THREADS;         // 1..4 entries per thread
+        const int e0 = tid * ipt;
+        int vals[(1 << YPP_BUCKET_BITS) / YPP_ORG_THREADS];
+        int sum = 0, mx = 0;
+#pragma unroll
+        for (int k = 0; k < (1 << YPP_BUCKET_BITS) / YPP_ORG_THREADS; ++k) {
+            vals[k] = (k < ipt && e0 + k < R) ? table[e0 + k] : 0;
+            sum += vals[k];
+            mx = max(mx, vals[k]);
+        }
+        mx = __reduce_max_sync(YPP_FULL_MASK, mx);
+        if (lane == 0 && mx > 0) atomicMax(&hd->max_bucket, mx);
+        int total;
+        int run = block_exclusive_scan(sum, hd->warp_sums, total);           // syncs inside: max_bucket is complete after it
+        if (hd->max_bucket > YPP_BUCKET_MAX) return false;                   // uniform: every thread reads the same word
+#pragma unroll
+        for (int k = 0; k < (1 << YPP_BUCKET_BITS) / YPP_ORG_THREADS; ++k)
+            if (k < ipt && e0 + k < R) { table[e0 + k] = run; run += vals[k]; }
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+        const u64 k = src[i];
+        tmp[atomicAdd(&table[((u32)(k >> 32) - kmin) >> shift], 1)] = k;
+    }
+    __syncthreads();                       // table[d] is now the END of bucket d
+    for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+        const u64 k = tmp[i];
+        const int d = (int)(((u32)(k >> 32) - kmin) >> shift);
+        const int lo = d ? table[d - 1] : 0, hi = table[d];
+        int rank = 0;
+        for (int q = lo; q < hi; ++q) rank += tmp[q] < k;
+        dst[lo + rank] = k;
+    }
+    __syncthreads();
+    return true;
+}
+
 __global__ void __launch_bounds__(YPP_ORG_THREADS, 1)
 ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
 {
@@ -181,6 +244,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     u64* bufA = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : skeys;
     u64* bufB = p.keys_in_smem ? bufA + N : reinterpret_cast<u64*>(sbox);
 
+    S1_CTA_BEGIN();
     S1_MARK(0);
     // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema
     const int ntiles = min(*p.ws.ntiles, p.ws.tiles_max);
@@ -188,7 +252,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     int* tile_off = table;                                   // [ntiles + 1], dead before the first radix pass
     if (tid == 0) {
         hd->maxc = 0; hd->nminx1 = 0; hd->nminy1 = 0;
-        hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; hd->n_edges = 0;
+        hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; hd->n_edges = 0; hd->n_big = 0;
         hd->kmin = 0xffffffffu; hd->kmax = 0u;
     }
     if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
@@ -220,6 +284,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     const int n = hd->n;
     if (n == 0) {
         for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = 0;
+        if (tid == 0) p.ws.bigcnt[b] = 0;
         return;
     }
     S1_MARK(1);
@@ -376,12 +441,15 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     {
         const u32 kmin = hd->kmin, span = hd->kmax - kmin;
         const int bits = 32 - __clz(span);                   // 0 when every score is equal: already in order
-        const int passes = (bits + 7) / 8;
-        const int bw = passes ? (bits + passes - 1) / passes : 0;
-        u64* other = bufB;
-        for (int ps = 0; ps < passes; ++ps) {
-            radix_pass(keys, other, n, L, ps * bw, bw, kmin, table, hd->warp_sums);
-            u64* t = keys; keys = other; other = t;
+        // bucket + rank (sorted keys land back in bufA); LSD passes only when scores tie in crowds
+        if (bits > 0 && !bucket_rank_sort(bufA, bufB, bufA, n, bits, kmin, table, hd)) {
+            const int passes = (bits + 7) / 8;
+            const int bw = (bits + passes - 1) / passes;
+            u64* other = bufB;
+            for (int ps = 0; ps < passes; ++ps) {
+                radix_pass(keys, other, n, L, ps * bw, bw, kmin, table, hd->warp_sums);
+                u64* t = keys; keys = other; other = t;
+            }
         }
     }
     S1_MARK(4);
@@ -490,11 +558,14 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = seg[c];
     for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
         if (seg[c + 1] - seg[c] > YPP_WARP_SEG) {
-            const int s = atomicAdd(p.ws.q, 1);
-            if (s < p.B * p.ws.bigq_per_image) p.ws.bigq[s] = b * nc + c;
+            const int s = atomicAdd(&hd->n_big, 1);
+            if (s < p.ws.bigq_per_image) p.ws.bigq[b * p.ws.bigq_per_image + s] = c;
         }
     }
+    __syncthreads();
+    if (tid == 0) p.ws.bigcnt[b] = hd->n_big;
     S1_MARK(8);
+    S1_CTA_END();
 }
 
 }  // namespace
@@ -519,7 +590,11 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
 #ifdef YPP_PROFILE_S1
 extern "C" int ypp_debug_s1_clocks(long long* out16)
 {
-    return (int)cudaMemcpyFromSymbol(out16, ypp_s1_clk, sizeof(long long) * 16);
+    const int rc = (int)cudaMemcpyFromSymbol(out16, ypp_s1_clk, sizeof(long long) * 16);
+    long long reset[16] = {0};
+    reset[10] = 0x7fffffffffffffffLL;
+    cudaMemcpyToSymbol(ypp_s1_clk, reset, sizeof(reset));
+    return rc;
 }
 #endif
 
@@ -537,9 +612,6 @@ int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
         if (e != cudaSuccess) { ypp_set_error("organise: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
         configured_smem = 227 * 1024;
     }
-    // the long-segment queue header is the only state S1 appends to across CTAs
-    cudaError_t e = cudaMemsetAsync(p.ws.q, 0, sizeof(int) * 4, st);
-    if (e != cudaSuccess) { ypp_set_error("organise: memset: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
     ypp_organise_kernel<<<p.B, YPP_ORG_THREADS, smem, st>>>(q);
     ypp_count_launch(1);
     return ypp_check_launch("organise");

@@ -23,21 +23,20 @@ typedef unsigned int u32;
 #define YPP_DECODE_THREADS 256     // == YPP_TILE_BOXES
 
 // ---------------------------------------------------------------- workspace layout
-// All per-image arrays are [B][N].  Nothing needs a memset between calls: D1 owns the tile
-// records, S1 (re)initialises the per-image counters, and the 16-byte queue header is cleared
-// by the S1 launcher.
+// All per-image arrays are [B][N].  Nothing needs a memset between calls: D1 owns the slot
+// records and S1 (re)initialises every per-image counter and list.
 #define YPP_TILE_BOXES 256        // boxes per D1 tile (one per thread)
 struct YppWs {
     int* cand_count;      // [B] written by S1
     int* keep_count;      // [B] zeroed by S1, accumulated by N1
     int* imgflag;         // [B] bit0: some classes share a segment (coordinate-trick cross-class edge), bit1: coordinate trick
     float* img_step;      // [B] max_coordinate + 1 of the image's candidates (the trick's class offset step)
-    int* q;               // [4] q[0] long-segment queue length, q[1] queue head
+    int* bigcnt;          // [B] segments longer than YPP_WARP_SEG in the image
     int* ntiles;          // [1] D1 slots (32 boxes, one warp) per image
     int* tile_first;      // [T] first box index of each slot (the same for every image)
     int* tile_cnt;        // [B][T] candidates each slot produced (compacted at keys[b][tile_first ..])
     u32* tile_ext;        // [B][T][4] order-encoded max(x1,y1,x2,y2), max(-x1), max(-y1) over the slot's candidates
-    int* bigq;            // [B * bigq_per_image] entries b*nc + c
+    int* bigq;            // [B][bigq_per_image] their classes
     int* seg_start;       // [B][nc+1] segment starts in class order
     u64* keys;            // [B][N] (~enc(score))<<32 | idx<<12 | cls, compacted per tile by D1 (box-index order)
     u64* skeys;           // [B][N] the same keys in stable descending-score order (S1)
@@ -62,7 +61,7 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     w.keep_count = (int*)take(sizeof(int) * B);
     w.imgflag = (int*)take(sizeof(int) * B);
     w.img_step = (float*)take(sizeof(float) * B);
-    w.q = (int*)take(sizeof(int) * 4);
+    w.bigcnt = (int*)take(sizeof(int) * B);
     w.ntiles = (int*)take(sizeof(int));
     // a tile never spans two anchor planes, so a scale adds at most A partial tiles
     w.tiles_max = (N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8) * (YPP_TILE_BOXES / 32);   // 32-box slots

@@ -151,6 +151,22 @@ def test_all_scores_tied(oracle, cuda):
             assert np.all(np.diff(kidx[b, : kc[b]]) > 0)          # ties resolved by lower box index
 
 
+def test_scores_tied_in_crowds(oracle, cuda):
+    """A handful of distinct scores shared by thousands of boxes: the bucket+rank sort hands over to the
+    stable LSD passes; a few hundred distinct scores stay on the bucket path with fat buckets."""
+    from ypp import engine, _lib
+    rng = np.random.RandomState(3)
+    for levels in (7, 400):
+        n = 6000
+        rows = np.concatenate([rng.uniform(0, 416, (n, 2)), rng.uniform(8, 90, (n, 2)),
+                               0.3 + 0.6 * rng.randint(0, levels, (n, 1)) / levels, rng.randint(0, 20, (n, 1))], 1).astype(np.float32)
+        pp = engine.PostProcessor(20, [[1, 1]], 1, 0.25, kind="v2", anchors_per_scale=1, offset_mode="none", union_mode="separate")
+        res = pp.nms_rows(torch.tensor(rows).to(cuda), want_keep_idx=True)
+        k = res.keep_idx[0, : int(res.keep_count[0])].cpu().numpy()
+        ref, _ = oracle.nms_v3_indices(rows, .25, .45, offset_mode=_lib.OFFSET_MODES["none"], union_mode=_lib.UNION_MODES["separate"])
+        assert np.array_equal(k, util.canon(ref, rows)), levels
+
+
 def test_empty_and_single_image(cuda):
     from ypp import engine, synth
     heads = [h.to(cuda) for h in synth.make_heads(1, 20, [52, 26, 13], g=12, mu_obj=-60.0)]

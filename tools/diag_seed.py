@@ -38,15 +38,15 @@ for g in range(g0, g0 + 4):
         o = off[0]
         off[0] += (nbytes + 255) // 256 * 256
         return o
-    o_cand, o_keep, o_flag, o_step, o_q, o_nt = take(4 * B), take(4 * B), take(4 * B), take(4 * B), take(16), take(4)
+    o_cand, o_keep, o_flag, o_step, o_q, o_nt = take(4 * B), take(4 * B), take(4 * B), take(4 * B), take(4 * B), take(4)
     T = (N // 256 + 4 * 8 + 8) * 8
     take(4 * T); take(4 * B * T); take(16 * B * T)
     per = min(N // 512 + 1, nc)
     o_bigq = take(4 * B * per)
     o_seg = take(4 * B * (nc + 1))
     flag = ws[o_flag:o_flag + 4 * B].view(np.int32)
-    q = ws[o_q:o_q + 16].view(np.int32)
+    q = ws[o_q:o_q + 4 * B].view(np.int32).sum()
     seg = ws[o_seg:o_seg + 4 * B * (nc + 1)].view(np.int32).reshape(B, nc + 1)
     sizes = np.diff(seg, axis=1)
-    print("   flags", np.unique(flag & 3, return_counts=True), "n_low/n_high/edges of flagged", [(f >> 8 & 255, f >> 16 & 255, f >> 24 & 255) for f in flag if f & 1], "q", q, "max seg", sizes.max(), "segs>512", (sizes > 512).sum(),
+    print("   flags", np.unique(flag & 3, return_counts=True), "n_low/n_high/edges of flagged", [(f >> 8 & 255, f >> 16 & 255, f >> 24 & 255) for f in flag if f & 1], "long segments", q, "max seg", sizes.max(), "segs>512", (sizes > 512).sum(),
           "flagged imgs", np.nonzero(flag & 1)[0], "their seg sizes", sizes[(flag & 1) != 0])

@@ -11,15 +11,19 @@ w = synth.WORKLOADS[wname]
 dev = torch.device("cuda:0")
 heads = [h.to(dev) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=0, mu_obj=0.0 if regime == "dense" else -5.0)]
 pp = engine.PostProcessor(w["nc"], synth.workload_anchors(w), w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=w["A"])
-for _ in range(3):
-    pp(heads)
-torch.cuda.synchronize()
 buf = (ctypes.c_longlong * 16)()
 L = _lib.lib()
 L.ypp_debug_s1_clocks.argtypes = [ctypes.c_void_p]
+for _ in range(3):
+    pp(heads)
+torch.cuda.synchronize()
+L.ypp_debug_s1_clocks(buf)          # reads and resets the marks
+pp(heads)
+torch.cuda.synchronize()
 rc = L.ypp_debug_s1_clocks(buf)
 v = list(buf)
 names = ["tile scan", "tile gather", "detector", "radix sort", "skeys copy", "class count+seg", "rank", "flag check+out", "-", "-"]
 print("rc", rc, "total cycles", v[8] - v[0])
 for i in range(8):
     print("%-12s %8d cycles  %6.2f us @1.965GHz" % (names[i], v[i + 1] - v[i], (v[i + 1] - v[i]) / 1965.0))
+print("longest CTA %.2f us; first CTA start -> last CTA end %.2f us" % (v[9] / 1965.0, (v[11] - v[10]) / 1e3))

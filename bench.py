@@ -362,7 +362,8 @@ def run_ours(args):
 
     extras = {}
     if not args.no_extras:
-        extras = run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks)
+        extras = run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks,
+                            ring_dense=ring[0])
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -382,7 +383,7 @@ def run_ours(args):
     return 0
 
 
-def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks):
+def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks, ring_dense=None):
     """Reported beside the headline: the sparse (deployment-like) regime, and the mAP epoch end
     (all-gather of detections over NCCL + GPU TP/FP matching) on sparse-regime detections."""
     from ypp.dist import gather_rows
@@ -434,6 +435,20 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
     out["map_epoch"] = {"images": world * n_batches * B, "detections": int(det_all.shape[0]),
                         "ground_truths": int(gt_all.shape[0]), "allgather_ms": ms_gather, "match_ms": ms_match,
                         "mAP": float(m.item()), "detections_per_s": det_all.shape[0] / (ms_match * 1e-3)}
+    # detection writers: integer box columns of one dense step's kept rows
+    rows = pp(ring_dense).rows() if ring_dense is not None else det_local
+    scale = torch.tensor([[500 / w["input_size"], 375 / w["input_size"]]] * B, dtype=torch.float64)
+    engine.detection_ints(rows, "coco", scale_xy=scale)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(10):
+        engine.detection_ints(rows, "coco", scale_xy=scale)
+    e1.record()
+    torch.cuda.synchronize()
+    ms_w = e0.elapsed_time(e1) / 10
+    out["writers"] = {"rows": int(rows.shape[0]), "ms": ms_w, "rows_per_s": rows.shape[0] / (ms_w * 1e-3),
+                      "gb_per_s": rows.shape[0] * (4 * rows.shape[1] + 16) / (ms_w * 1e-3) / 1e9,
+                      "what": "ypp_detection_ints, COCO mode: 28 B row read + 16 B int4 write per detection"}
     return out
 
 

@@ -148,6 +148,22 @@ int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* w
 int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, float img_idx_base,
                     float* out_G7, int* gt_count, void* stream);
 
+/* ---- detection writers --------------------------------------------------
+ * The integer box columns the reference's detection writers put on disk, for K rows
+ * [img,]cx,cy,w,h,score,cls (row_width 7 or 6):
+ *   YPP_WRITER_PRED_FILE  make_pred_file_yolov3.py:73-86 (and the yolov2 twin):
+ *       xmin,ymin,xmax,ymax = int(cx -/+ w/2), int(cy -/+ h/2)
+ *   YPP_WRITER_COCO       yolo2coco_pred_file_yolov3.py:83-100: cx,cy,w,h are first multiplied by
+ *       (width / input_size), (height / input_size) of the row's image; bbox = int(cx - w/2),
+ *       int(cy - h/2), int(w), int(h)
+ * int() truncates toward zero; values must fit int32 (NaN -> 0, out of range saturates).
+ * scale_xy [n_img,2] (COCO only; fp32 of the Python-float ratios) is indexed by
+ * (int)row[0] - img_idx_base for 7-column rows, and by 0 for 6-column rows. */
+#define YPP_WRITER_PRED_FILE 0
+#define YPP_WRITER_COCO 1
+int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, const float* scale_xy, int n_img,
+                       float img_idx_base, int* out_K4, void* stream);
+
 /* box_iou, utils/metrics.py:233-255: xyxy [N,4] x [M,4] -> [N,M]. */
 int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream);
 

@@ -264,3 +264,39 @@ def bbox_iou_cxcywh(a, b):
     out = np.empty(a.shape[0], dtype=np.float32)
     lib().ypo_bbox_iou_cxcywh_pairs(_fp(a), _fp(b), a.shape[0], _fp(out))
     return out
+
+
+# ---- detection writers (numpy; byte/integer work) -----------------------------------------
+WRITER_PRED_FILE, WRITER_COCO = 0, 1
+
+
+def detection_ints(rows, mode=WRITER_PRED_FILE, scale_xy=None, img_idx_base=0):
+    """Integer box columns of the reference's detection writers, rows [K,6|7] -> int64 [K,4].
+
+    make_pred_file_yolov3.py:73-86: xmin = int(cx - (w / 2)), ..., xmax = int(cx + (w / 2)) on
+    0-dim fp32 tensors.  yolo2coco_pred_file_yolov3.py:83-100: cx,cy,w,h are first multiplied by
+    the Python floats width/input_size, height/input_size (fp32 tensor * Python float = fp32
+    product with the scalar rounded to fp32), bbox = int(cx - w/2), int(cy - h/2), int(w), int(h).
+    int() truncates toward zero."""
+    r = _f32(rows)
+    o = r.shape[1] - 6
+    cx, cy, w, h = r[:, o], r[:, o + 1], r[:, o + 2], r[:, o + 3]
+    two = np.float32(2)
+    if mode == WRITER_COCO:
+        s = np.asarray(scale_xy, dtype=np.float64).astype(np.float32).reshape(-1, 2)
+        img = (r[:, 0] - np.float32(img_idx_base)).astype(np.int64) if o else np.zeros(r.shape[0], np.int64)
+        sx, sy = s[img, 0], s[img, 1]
+        cx, cy, w, h = cx * sx, cy * sy, w * sx, h * sy
+        cols = [cx - w / two, cy - h / two, w, h]
+    else:
+        cols = [cx - w / two, cy - h / two, cx + w / two, cy + h / two]
+    return np.stack([np.trunc(c).astype(np.int64) for c in cols], 1)
+
+
+def pred_file_lines(boxes, class_name_list):
+    """f'{class_name} {confidence_score} {xmin} {ymin} {xmax} {ymax}\\n' per box (make_pred_file_yolov3.py:72-86)."""
+    r = _f32(boxes)
+    v = detection_ints(r, WRITER_PRED_FILE)
+    o = r.shape[1] - 6
+    return ["%s %s %d %d %d %d\n" % (class_name_list[int(r[k, o + 5])], format(float(r[k, o + 4])),
+                                     v[k, 0], v[k, 1], v[k, 2], v[k, 3]) for k in range(r.shape[0])]

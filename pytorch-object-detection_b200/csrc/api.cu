@@ -221,6 +221,19 @@ int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, floa
     return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, gt_count, (cudaStream_t)stream);
 }
 
+int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, const float* scale_xy, int n_img,
+                       float img_idx_base, int* out_K4, void* stream)
+{
+    if (K < 0 || (row_width != 6 && row_width != 7)) { ypp_set_error("detection_ints: K >= 0 and row_width 6 or 7"); return YPP_E_BADARG; }
+    if (mode != YPP_WRITER_PRED_FILE && mode != YPP_WRITER_COCO) { ypp_set_error("detection_ints: unknown mode %d", mode); return YPP_E_BADARG; }
+    if (K == 0) return YPP_OK;
+    if (!rows || !out_K4) { ypp_set_error("detection_ints: null pointer"); return YPP_E_BADARG; }
+    if (((uintptr_t)out_K4) & 15u) { ypp_set_error("detection_ints: out must be 16-byte aligned"); return YPP_E_BADARG; }
+    if (mode == YPP_WRITER_COCO && (!scale_xy || n_img <= 0)) { ypp_set_error("detection_ints: COCO mode needs scale_xy[n_img,2]"); return YPP_E_BADARG; }
+    if ((K + 255) / 256 > 0x7fffffffLL) { ypp_set_error("detection_ints: K too large"); return YPP_E_UNSUPPORTED; }
+    return ypp_launch_detection_ints(rows, (long long)K, row_width, mode, scale_xy, n_img, img_idx_base, out_K4, (cudaStream_t)stream);
+}
+
 int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream)
 {
     if (N < 0 || M < 0) { ypp_set_error("box_iou: negative size"); return YPP_E_BADARG; }

@@ -385,6 +385,39 @@ MapWs make_map_ws(void* base, long long G, long long K)
 
 int bits_for(int n) { int b = 1; while ((1 << b) < n) ++b; return b; }
 
+// ---- detection writers: the integer columns of the pred-file / COCO rows -------------------
+// make_pred_file_yolov3.py:73-86, yolo2coco_pred_file_yolov3.py:83-100.  The reference works on
+// 0-dim fp32 tensors: `w / 2`, `cx - ...` are fp32 operations, `bbox[0] * (width / input_size)`
+// multiplies by the Python-float ratio rounded to fp32, int() truncates toward zero.
+__global__ void __launch_bounds__(256)
+ypp_detection_ints_kernel(const float* __restrict__ rows, long long K, int row_width, int mode,
+                          const float* __restrict__ scale_xy, int n_img, float img_base, int* __restrict__ out)
+{
+    const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= K) return;
+    const float* r = rows + k * row_width;
+    const int o = row_width == 7 ? 1 : 0;
+    float cx = r[o], cy = r[o + 1], w = r[o + 2], h = r[o + 3];
+    int4 v;
+    if (mode == YPP_WRITER_COCO) {
+        int img = o ? (int)(r[0] - img_base) : 0;
+        img = min(max(img, 0), n_img - 1);
+        const float sx = scale_xy[2 * img], sy = scale_xy[2 * img + 1];
+        cx = __fmul_rn(cx, sx); cy = __fmul_rn(cy, sy); w = __fmul_rn(w, sx); h = __fmul_rn(h, sy);
+        v.x = __float2int_rz(__fsub_rn(cx, __fmul_rn(w, 0.5f)));
+        v.y = __float2int_rz(__fsub_rn(cy, __fmul_rn(h, 0.5f)));
+        v.z = __float2int_rz(w);
+        v.w = __float2int_rz(h);
+    } else {
+        const float hw = __fmul_rn(w, 0.5f), hh = __fmul_rn(h, 0.5f);        // x / 2 is exact either way
+        v.x = __float2int_rz(__fsub_rn(cx, hw));
+        v.y = __float2int_rz(__fsub_rn(cy, hh));
+        v.z = __float2int_rz(__fadd_rn(cx, hw));
+        v.w = __float2int_rz(__fadd_rn(cy, hh));
+    }
+    reinterpret_cast<int4*>(out)[k] = v;
+}
+
 }  // namespace
 
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
@@ -435,4 +468,13 @@ int ypp_launch_map(const float* gt, long long G, const float* det, long long K, 
     map_mean_kernel<<<1, 32, 0, st>>>(nc, G, w.gt.k[gcur], w.contrib, map);
     ypp_count_launch(2);
     return ypp_check_launch("map_match");
+}
+
+int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int mode, const float* scale_xy, int n_img,
+                              float img_base, int* out, cudaStream_t st)
+{
+    const unsigned grid = (unsigned)((K + 255) / 256);
+    ypp_detection_ints_kernel<<<grid, 256, 0, st>>>(rows, K, row_width, mode, scale_xy, n_img, img_base, out);
+    ypp_count_launch(1);
+    return ypp_check_launch("detection_ints");
 }

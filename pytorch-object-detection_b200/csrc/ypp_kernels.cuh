@@ -61,6 +61,8 @@ int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st);
 int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st);
 int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints);
 
+int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int mode, const float* scale_xy, int n_img,
+                               float img_base, int* out, cudaStream_t st);
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
                            float* out, int* gt_count, cudaStream_t st);
 int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);

@@ -37,10 +37,12 @@ class YppCfg(ctypes.Structure):
                 ("offset_mode", ctypes.c_int), ("union_mode", ctypes.c_int)]
 
 
+WRITER_MODES = {"pred_file": 0, "coco": 1}
+
 EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "ypp_decode_compact",
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
-           "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_detection_ints", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -94,6 +96,7 @@ def lib():
     L.ypp_nms_rows.argtypes = [cfgp, vp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_target_rows.argtypes = [vp, ci, ci, cf, cf, vp, vp, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
+    L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]
     L.ypp_map_workspace_bytes.argtypes = [i64, i64, ci]
     L.ypp_map_workspace_bytes.restype = ctypes.c_size_t
     L.ypp_map_match.argtypes = [vp, i64, vp, i64, ci, cf, vp, ctypes.c_size_t, vp, vp, vp, vp]
@@ -102,7 +105,8 @@ def lib():
     L.ypp_launch_count.argtypes = [ci]
     L.ypp_launch_count.restype = i64
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
-                 "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match"):
+                 "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match",
+                 "ypp_detection_ints"):
         getattr(L, name).restype = ci
     _lib = L
     return L

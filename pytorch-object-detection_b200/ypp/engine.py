@@ -313,5 +313,27 @@ def map_match(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, i
     return m, pc, (tp[:K] if tp is not None else None)
 
 
+def detection_ints(rows: torch.Tensor, mode="pred_file", scale_xy: Optional[torch.Tensor] = None, img_idx_base=0) -> torch.Tensor:
+    """Integer box columns of the reference's detection writers for rows [K,6|7] -> int32 [K,4].
+    pred_file: xmin,ymin,xmax,ymax (make_pred_file_yolov3.py:73-86); coco: xmin,ymin,w,h after scaling by
+    scale_xy[img] = fp32(width / input_size), fp32(height / input_size) (yolo2coco_pred_file_yolov3.py:83-100)."""
+    from ._lib import WRITER_MODES
+    if rows.dim() != 2 or rows.shape[1] not in (6, 7):
+        raise ValueError("rows must be [K,6] or [K,7]")
+    if not rows.is_cuda or rows.dtype != torch.float32:
+        raise ValueError("rows must be a float32 CUDA tensor")
+    rows = rows.contiguous()
+    K = rows.shape[0]
+    out = torch.empty((K, 4), dtype=torch.int32, device=rows.device)
+    n_img = 0
+    if scale_xy is not None:
+        scale_xy = scale_xy.to(device=rows.device, dtype=torch.float32).reshape(-1, 2).contiguous()
+        n_img = scale_xy.shape[0]
+    with torch.cuda.device(rows.device):
+        check(lib().ypp_detection_ints(_ptr(rows), K, rows.shape[1], WRITER_MODES[mode], _ptr(scale_xy), n_img,
+                                       float(img_idx_base), _ptr(out), _stream()))
+    return out
+
+
 def launch_count(reset=False) -> int:
     return int(lib().ypp_launch_count(int(bool(reset))))

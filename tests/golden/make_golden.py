@@ -358,8 +358,69 @@ def case_iou():
     np.savez_compressed(os.path.join(HERE, "iou_cases.npz"), a=a, b=b, box_iou=ref, c1=c1, c2=c2, bbox_iou=refc)
 
 
+# ------------------------------------------------------------------ detection writers
+
+def case_writers():
+    """The reference's writer loops are inline in CLI scripts that need a checkpoint and a dataset
+    (make_pred_file_yolov3.py:60-86, yolo2coco_pred_file_yolov3.py:66-100), so they cannot be called;
+    the loop BODIES below are those lines verbatim in meaning, run on real torch 0-dim tensors."""
+    rng = np.random.RandomState(21)
+    n = 400
+    boxes = np.concatenate([rng.uniform(-20, 436, (n, 2)), rng.uniform(0.2, 300, (n, 2)),
+                            rng.uniform(0.25, 1, (n, 1)), rng.randint(0, 20, (n, 1))], 1).astype(np.float32)
+    boxes[0, :4] = [10.5, 10.5, 21.0, 21.0]          # xmin = 0 exactly
+    boxes[1, :4] = [3.0, 4.0, 10.0, 9.5]             # negative corners truncate toward zero
+    boxes[2, :4] = [100.25, 50.75, 0.5, 0.5]
+    names = ["cls%02d" % i for i in range(20)]
+    cats = {nm: 100 + 3 * i for i, nm in enumerate(names)}
+    t = torch.tensor(boxes)
+    # make_pred_file_yolov3.py:72-86
+    lines, ints = [], []
+    for bbox in t:
+        class_name = names[int(bbox[-1])]
+        confidence_score = bbox[4]
+        cx, cy, w, h = bbox[0], bbox[1], bbox[2], bbox[3]
+        xmin = int((cx - (w / 2)))
+        ymin = int((cy - (h / 2)))
+        xmax = int((cx + (w / 2)))
+        ymax = int((cy + (h / 2)))
+        lines.append(f'{class_name} {confidence_score} {xmin} {ymin} {xmax} {ymax}\n')
+        ints.append([xmin, ymin, xmax, ymax])
+    ints = np.array(ints, dtype=np.int64)
+    check("writers:pred_file ints", np.array_equal(O.detection_ints(boxes, O.WRITER_PRED_FILE), ints))
+    check("writers:pred_file lines", O.pred_file_lines(boxes, names) == lines)
+    # yolo2coco_pred_file_yolov3.py:83-100, three images of different original sizes
+    input_size = 416
+    sizes = [(500, 375), (1280, 720), (333, 500)]
+    img_of = rng.randint(0, 3, n)
+    coco = []
+    for k, bbox in enumerate(t):
+        width, height = sizes[img_of[k]]
+        cx = bbox[0] * (width / input_size)
+        cy = bbox[1] * (height / input_size)
+        w = bbox[2] * (width / input_size)
+        h = bbox[3] * (height / input_size)
+        xmin = int((cx - (w / 2)))
+        ymin = int((cy - (h / 2)))
+        w = int(w)
+        h = int(h)
+        coco.append([xmin, ymin, w, h])
+    coco = np.array(coco, dtype=np.int64)
+    rows7 = np.concatenate([(img_of + 7).astype(np.float32)[:, None], boxes], 1)
+    scale = [[w_ / input_size, h_ / input_size] for w_, h_ in sizes]
+    check("writers:coco ints", np.array_equal(O.detection_ints(rows7, O.WRITER_COCO, scale, img_idx_base=7), coco))
+    np.savez_compressed(os.path.join(HERE, "writers.npz"), boxes=boxes, pred_ints=ints, lines=np.array(lines),
+                        img_of=img_of, sizes=np.array(sizes), input_size=input_size, coco_ints=coco,
+                        names=np.array(names), cat_ids=np.array([cats[nm] for nm in names]))
+
+
 if __name__ == "__main__":
     O.build(force=True)
+    if len(sys.argv) > 1:                      # regenerate only the named cases, e.g. `make_golden.py writers`
+        for nm in sys.argv[1:]:
+            globals()["case_" + nm]()
+        print("FAILED: %s" % FAIL if FAIL else "all golden cases agree with the oracle")
+        sys.exit(1 if FAIL else 0)
     case_decode_edges()
     case_adversarial()
     # C1: YOLOv2 416 VOC batch 8 dense (trick path, n<=1000 per image)
@@ -374,5 +435,6 @@ if __name__ == "__main__":
     case_wrappers()
     case_map()
     case_iou()
+    case_writers()
     print("FAILED: %s" % FAIL if FAIL else "all golden cases agree with the oracle")
     sys.exit(1 if FAIL else 0)

@@ -255,3 +255,47 @@ def test_library_cross_checks_torch_and_torchvision(cuda):
         keep = cand[torchvision.ops.batched_nms(xyxy, c[:, 4], c[:, 5], 0.45)]
         k = res.keep_idx[b, : int(res.keep_count[b])].long()
         assert torch.equal(k, keep), "image %d: %d vs %d kept" % (b, len(k), len(keep))
+
+
+def test_detection_writers_match_reference(oracle, cuda, tmp_path):
+    """ypp_detection_ints + the host formatting vs the stored outputs of the reference's writer loops
+    (make_pred_file_yolov3.py:72-86, yolo2coco_pred_file_yolov3.py:83-100) and vs the oracle on a big random set."""
+    import json
+    from ypp import engine
+    from ypp.compat import writers
+    g = util.load("writers")
+    names = [str(x) for x in g["names"]]
+    boxes = torch.tensor(g["boxes"]).to(cuda)
+    assert np.array_equal(engine.detection_ints(boxes, "pred_file").cpu().numpy(), g["pred_ints"])
+    assert writers.pred_file_lines(boxes, names) == [str(x) for x in g["lines"]]
+    S = int(g["input_size"])
+    sizes = g["sizes"].tolist()
+    rows7 = torch.cat([torch.tensor((g["img_of"] + 7).astype(np.float32))[:, None].to(cuda), boxes], 1)
+    cats = {nm: int(c) for nm, c in zip(names, g["cat_ids"])}
+    res = writers.coco_results(rows7, [11, 12, 13], [s[0] for s in sizes], [s[1] for s in sizes], S, cats, names, img_idx_base=7)
+    assert np.array_equal(np.array([r["bbox"] for r in res]), g["coco_ints"])
+    assert [r["image_id"] for r in res] == [11 + int(i) for i in g["img_of"]]
+    assert [r["category_id"] for r in res] == [cats[names[int(c)]] for c in g["boxes"][:, 5]]
+    assert [r["score"] for r in res] == [float(x) for x in g["boxes"][:, 4]]
+    path = writers.write_coco_results(res, str(tmp_path / "results.json"))
+    assert json.load(open(path)) == res
+    # per-image pred files of a packed batch
+    order = np.argsort(g["img_of"], kind="stable")
+    counts = np.bincount(g["img_of"], minlength=3)
+    paths = writers.write_pred_files(rows7[torch.tensor(order).to(cuda)], counts, names, str(tmp_path / "pred"))
+    want = [str(x) for x in g["lines"][order]]
+    assert "".join(open(p).read() for p in paths) == "".join(want)
+    assert [p[-9:] for p in paths] == ["00001.txt", "00002.txt", "00003.txt"]
+    # large random set against the oracle (both modes), 6- and 7-column rows
+    rng = np.random.RandomState(8)
+    n = 200000
+    big = np.concatenate([rng.randint(0, 5, (n, 1)), rng.uniform(-50, 700, (n, 2)), rng.uniform(0, 500, (n, 2)),
+                          rng.uniform(0, 1, (n, 1)), rng.randint(0, 80, (n, 1))], 1).astype(np.float32)
+    sc = [[rng.uniform(0.3, 4), rng.uniform(0.3, 4)] for _ in range(5)]
+    tb = torch.tensor(big).to(cuda)
+    assert np.array_equal(engine.detection_ints(tb, "pred_file").cpu().numpy(), oracle.detection_ints(big, oracle.WRITER_PRED_FILE))
+    assert np.array_equal(engine.detection_ints(tb, "coco", scale_xy=torch.tensor(sc, dtype=torch.float64)).cpu().numpy(),
+                          oracle.detection_ints(big, oracle.WRITER_COCO, sc))
+    assert np.array_equal(engine.detection_ints(tb[:, 1:].contiguous(), "coco", scale_xy=torch.tensor(sc[:1], dtype=torch.float64)).cpu().numpy(),
+                          oracle.detection_ints(big[:, 1:], oracle.WRITER_COCO, sc[:1]))
+    assert engine.detection_ints(tb[:0], "pred_file").shape == (0, 4)

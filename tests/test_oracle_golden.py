@@ -112,3 +112,15 @@ def test_effective_threshold(oracle):
     assert oracle.effective_thr(0.45, True) == float(f45) == oracle.effective_thr(0.45, False)
     assert oracle.effective_thr(0.3, False) == float(f3)
     assert oracle.effective_thr(0.3, True) == float(np.nextafter(f3, np.float32(-1)))
+
+
+def test_detection_writers(oracle):
+    """Pred-file lines / COCO bbox ints vs what the reference's writer loop bodies produced on torch tensors."""
+    g = util.load("writers")
+    names = [str(x) for x in g["names"]]
+    assert np.array_equal(oracle.detection_ints(g["boxes"], oracle.WRITER_PRED_FILE), g["pred_ints"])
+    assert oracle.pred_file_lines(g["boxes"], names) == [str(x) for x in g["lines"]]
+    rows7 = np.concatenate([(g["img_of"] + 7).astype(np.float32)[:, None], g["boxes"]], 1)
+    S = float(g["input_size"])
+    scale = [[w / S, h / S] for w, h in g["sizes"].tolist()]
+    assert np.array_equal(oracle.detection_ints(rows7, oracle.WRITER_COCO, scale, img_idx_base=7), g["coco_ints"])

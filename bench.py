@@ -408,7 +408,7 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                             "candidates_per_image": float(res.cand_count.float().mean().item()),
                             "ms_per_step": ms / args.steps}
     # mAP epoch: n_batches of B images per rank, detections accumulated on device, then gather + match
-    n_batches = 8
+    n_batches = 32                      # C5 shape: 2048 images per rank in batches of 64
     dets, gts = [], []
     for i in range(n_batches):
         r = pp(sparse[i % n_ring], img_idx_base=(rank * n_batches + i) * B)

@@ -128,13 +128,73 @@ __device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r,
 struct SegSmem {
     float4 box[YPP_WARP_SEG];
     float area[YPP_WARP_SEG];
-    float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 4
+    float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 2
     float kta[YPP_NMSQ_WARPS][8];       // -thr * area of those rows
     u32 amax[YPP_NMSQ_WARPS];
     u32 cmax[YPP_NMSQ_WARPS];
     u32 in_words[32];          // byte w of word j: rows 8w..8w+7 of the tile that suppress column j
     uint4 dpart[32];           // per lane: the four warps' partial dead-column bits
 };
+
+// One warp's kept rows (kb/ka, npad of them, nk real) against G groups of 32 columns starting at
+// group k (lane = column mod 32).  Returns the bits of the groups whose column in this lane died.
+template <int G, bool kFast>
+__device__ __forceinline__ u32 sweep_groups(const float4* __restrict__ sbox, const float* __restrict__ sarea, int len,
+                                            const float4* __restrict__ kb, const float* __restrict__ ka, int npad, int nk,
+                                            int k, u32 dead, float c1k, float scale, float nthr, float Bseg,
+                                            float thr, int union_fma)
+{
+    const int lane = threadIdx.x & 31;
+    bool v[G];
+    int jj[G];
+    bool any = false;
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+        const int j = ((k + g) << 5) + lane;
+        v[g] = j < len && !((dead >> (k + g)) & 1u);
+        jj[g] = j < len ? j : 0;
+        any = any || v[g];
+    }
+    if (!__any_sync(YPP_FULL_MASK, any)) return 0u;
+    float4 c[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) c[g] = sbox[jj[g]];
+    bool d[G];
+    bool exact = !kFast;
+    if (kFast) {
+        float dm[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) dm[g] = -INFINITY;
+        for (int r = 0; r < npad; r += 2) {
+            const float4 a = kb[r], a2 = kb[r + 1];
+            const float ta = ka[r], ta2 = ka[r + 1];
+#pragma unroll
+            for (int g = 0; g < G; ++g)
+                dm[g] = fmaxf(fmaxf(dm[g], pair_g(a, ta, c[g], c1k, scale)), pair_g(a2, ta2, c[g], c1k, scale));
+        }
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+            const float D = __fadd_rn(dm[g], __fmul_rn(nthr, fabsf(sarea[jj[g]])));
+            d[g] = D > Bseg;
+            exact = exact || (v[g] && !d[g] && !(D < -Bseg));
+        }
+    }
+    if (exact) {                                    // a pair inside the band (or thr out of range)
+#pragma unroll
+        for (int g = 0; g < G; ++g) d[g] = false;
+        for (int r = 0; r < nk; ++r) {
+            const float4 a = kb[r];
+            const float sa = ypp_area(a);
+#pragma unroll
+            for (int g = 0; g < G; ++g) d[g] = d[g] || pair_exact(a, sa, c[g], thr, union_fma);
+        }
+    }
+    u32 part = 0;
+#pragma unroll
+    for (int g = 0; g < G; ++g)
+        if (v[g] && d[g]) part |= 1u << (k + g);
+    return part;
+}
 
 // 32-row tiles in score order.  Warp w owns rows 8w..8w+7 of every tile: it tests them against the
 // tile's own columns (diagonal), the four byte-wide partial masks are exchanged through shared
@@ -237,12 +297,12 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
         total += __popc(K);
         if (w == 0 && ((K >> lane) & 1u)) keepflag[grank[j]] = 1;
         if (T + 1 >= ntiles) break;
-        // ---- broadcast my kept rows against the later columns (two column groups per sweep)
+        // ---- broadcast my kept rows against the later columns (four column groups per sweep)
         const u32 Kw = K & wmask;
         const int nkw = __popc(Kw);
         u32 part = 0;
         if (nkw) {
-            const int npad = (nkw + 3) & ~3;
+            const int npad = (nkw + 1) & ~1;
             if ((Kw >> lane) & 1u) {
                 const int s = __popc(Kw & ((1u << lane) - 1u));
                 sm.kbox[w][s] = cb;
@@ -252,43 +312,15 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             __syncwarp();
             const float4* kb = sm.kbox[w];
             const float* ka = sm.kta[w];
-            for (int k = T + 1; k < ntiles; k += 2) {
-                const int j0 = (k << 5) + lane, j1 = j0 + 32;
-                const bool v0 = j0 < len && !((dead >> k) & 1u);
-                const bool v1 = j1 < len && !((dead >> (k + 1)) & 1u);
-                if (!__any_sync(YPP_FULL_MASK, v0 || v1)) continue;
-                const float4 c0 = sm.box[j0 < len ? j0 : 0], c1 = sm.box[j1 < len ? j1 : 0];
-                bool d0 = false, d1 = false;
-                bool exact = !kFast;
-                if (kFast) {
-                    float dm0 = -INFINITY, dm1 = -INFINITY;
-                    for (int r = 0; r < npad; r += 4) {
-#pragma unroll
-                        for (int q = 0; q < 4; q += 2) {
-                            const float4 a = kb[r + q], a2 = kb[r + q + 1];
-                            const float ta = ka[r + q], ta2 = ka[r + q + 1];
-                            dm0 = fmaxf(fmaxf(dm0, pair_g(a, ta, c0, c1k, scale)), pair_g(a2, ta2, c0, c1k, scale));
-                            dm1 = fmaxf(fmaxf(dm1, pair_g(a, ta, c1, c1k, scale)), pair_g(a2, ta2, c1, c1k, scale));
-                        }
-                    }
-                    dm0 = __fadd_rn(dm0, __fmul_rn(nthr, fabsf(sm.area[j0 < len ? j0 : 0])));
-                    dm1 = __fadd_rn(dm1, __fmul_rn(nthr, fabsf(sm.area[j1 < len ? j1 : 0])));
-                    d0 = dm0 > Bseg;
-                    d1 = dm1 > Bseg;
-                    exact = (v0 && !d0 && !(dm0 < -Bseg)) || (v1 && !d1 && !(dm1 < -Bseg));
-                }
-                if (exact) {                                                    // a pair inside the band (or thr out of range)
-                    d0 = d1 = false;
-                    for (int r = 0; r < nkw; ++r) {
-                        const float4 a = kb[r];
-                        const float sa = ypp_area(a);
-                        d0 = d0 || pair_exact(a, sa, c0, thr, union_fma);
-                        d1 = d1 || pair_exact(a, sa, c1, thr, union_fma);
-                    }
-                }
-                if (v0 && d0) part |= 1u << k;
-                if (v1 && d1) part |= 1u << (k + 1);
+            int k = T + 1;
+            for (; k + 4 <= ntiles; k += 4)
+                part |= sweep_groups<4, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
+            if (k + 2 <= ntiles) {
+                part |= sweep_groups<2, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
+                k += 2;
             }
+            if (k < ntiles)
+                part |= sweep_groups<1, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
         }
         reinterpret_cast<u32*>(&sm.dpart[lane])[w] = part;
         __syncthreads();
@@ -448,7 +480,8 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
 // counts the flags of the chunks before its own (uint4 sweeps over the byte flags), then
 // places its own YPP_GATHER_CHUNK ranks with a ballot prefix.
 #define YPP_GATHER_THREADS 256
-#define YPP_GATHER_CHUNK 1024
+#define YPP_GATHER_ROUNDS 4
+#define YPP_GATHER_CHUNK (YPP_GATHER_ROUNDS * YPP_GATHER_THREADS)
 
 __device__ __forceinline__ int popc_bytes16(const uint4 v)
 {
@@ -458,7 +491,8 @@ __device__ __forceinline__ int popc_bytes16(const uint4 v)
 __global__ void __launch_bounds__(YPP_GATHER_THREADS)
 ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
 {
-    __shared__ int warp_tot[YPP_GATHER_THREADS / 32];
+    __shared__ int warp_tot[YPP_GATHER_ROUNDS][YPP_GATHER_THREADS / 32];
+    __shared__ float stage[YPP_GATHER_CHUNK * 7];
     __shared__ long long red_img[YPP_GATHER_THREADS / 32];
     __shared__ int red_pre[YPP_GATHER_THREADS / 32];
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -504,39 +538,70 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     const float4* box = p.ws.box + (size_t)b * N;
     const float img = p.img_idx_base + (float)b;
     const int r_end = min(n, r_begin + YPP_GATHER_CHUNK);
+    // the chunk's YPP_GATHER_ROUNDS rounds of 256 ranks at once: flags -> ballots -> one exchange of the
+    // per-(round, warp) counts -> keys -> boxes -> rows, so every load of a round overlaps the others'
+    bool f[YPP_GATHER_ROUNDS];
+    u32 m[YPP_GATHER_ROUNDS];
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
+        const int r = r_begin + u * YPP_GATHER_THREADS + tid;
+        f[u] = r < r_end && kf[r];
+    }
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
+        m[u] = __ballot_sync(YPP_FULL_MASK, f[u]);
+        if (lane == 0) warp_tot[u][warp] = __popc(m[u]);
+    }
+    __syncthreads();
+    u64 k[YPP_GATHER_ROUNDS];
+    int pos[YPP_GATHER_ROUNDS];
     int running = pre_rows;
-    for (int r0 = r_begin; r0 < r_end; r0 += YPP_GATHER_THREADS) {
-        const int r = r0 + tid;
-        const bool f = r < r_end && kf[r];
-        const u32 m = __ballot_sync(YPP_FULL_MASK, f);
-        __syncthreads();                                   // warp_tot of the previous round is consumed
-        if (lane == 0) warp_tot[warp] = __popc(m);
-        __syncthreads();
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
         int before = 0, total = 0;
 #pragma unroll
         for (int w = 0; w < YPP_GATHER_THREADS / 32; ++w) {
-            const int t = warp_tot[w];
+            const int t = warp_tot[u][w];
             if (w < warp) before += t;
             total += t;
         }
-        if (f) {
-            const int pos = running + before + __popc(m & ((1u << lane) - 1u));      // position inside the image
-            const u64 k = keys[r];
-            const int idx = ypp_key_idx(k);
-            if (p.keep_idx) p.keep_idx[(size_t)b * N + pos] = idx;
-            const long long row = img_rows + pos;
-            if (p.det_rows && row < p.det_capacity) {
-                const float4 bx = box[idx];
-                float cls = (float)ypp_key_cls(k);
-                if (p.src_rows) cls = p.src_rows[((size_t)b * N + idx) * 6 + 5];
-                float* o = p.det_rows + row * p.row_width;
-                if (p.row_width == 7) *o++ = img;
-                o[0] = bx.x; o[1] = bx.y; o[2] = bx.z; o[3] = bx.w;
-                o[4] = ypp_key_score(k); o[5] = cls;
-            }
-        }
+        pos[u] = running + before + __popc(m[u] & ((1u << lane) - 1u));      // position inside the image
         running += total;
+        k[u] = f[u] ? keys[r_begin + u * YPP_GATHER_THREADS + tid] : 0ull;
     }
+    float4 bx[YPP_GATHER_ROUNDS];
+    float cls[YPP_GATHER_ROUNDS];
+    const bool want_rows = p.det_rows != nullptr;
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
+        if (!f[u]) continue;
+        const int idx = ypp_key_idx(k[u]);
+        if (p.keep_idx) p.keep_idx[(size_t)b * N + pos[u]] = idx;
+        if (want_rows) {
+            bx[u] = box[idx];
+            cls[u] = (float)ypp_key_cls(k[u]);
+            if (p.src_rows) cls[u] = p.src_rows[((size_t)b * N + idx) * 6 + 5];
+        }
+    }
+    if (!want_rows) return;
+    // rows of the chunk are contiguous in the output: stage them in shared memory (stride 6 or 7 floats:
+    // conflict-free) and write them out as full lines instead of 7 scattered 4-byte stores per row
+    const int width = p.row_width;
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
+        if (!f[u]) continue;
+        float* o = stage + (pos[u] - pre_rows) * width;
+        if (width == 7) *o++ = img;
+        o[0] = bx[u].x; o[1] = bx[u].y; o[2] = bx[u].z; o[3] = bx[u].w;
+        o[4] = ypp_key_score(k[u]); o[5] = cls[u];
+    }
+    __syncthreads();
+    const long long first = img_rows + pre_rows;
+    long long nrows = running - pre_rows;
+    if (first + nrows > p.det_capacity) nrows = p.det_capacity > first ? p.det_capacity - first : 0;
+    float* out = p.det_rows + first * width;
+    const int nf = (int)nrows * width;
+    for (int i = tid; i < nf; i += YPP_GATHER_THREADS) out[i] = stage[i];
 }
 
 template <bool kFast, bool kFma>

@@ -291,14 +291,26 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     // ---- 2. gather the slots, track the range of the score words
     {
         u32 kmin = 0xffffffffu, kmax = 0u;
-        for (int i = tid; i < ntiles * 32; i += YPP_ORG_THREADS) {      // slots hold <= 32 keys: one lane each
-            const int t = i >> 5;
-            const int off = tile_off[t], cnt = tile_off[t + 1] - off;
-            if (lane < cnt) {
-                const u64 k = gkeys[p.ws.tile_first[t] + lane];
-                bufA[off + lane] = k;
-                const u32 hi = (u32)(k >> 32);
-                kmin = min(kmin, hi); kmax = max(kmax, hi);
+        // slots hold <= 32 keys: one lane each; four slots per thread in flight
+        for (int i0 = tid; i0 < ntiles * 32; i0 += 4 * YPP_ORG_THREADS) {
+            u64 k[4];
+            int dst[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int t = (i0 + u * YPP_ORG_THREADS) >> 5;
+                dst[u] = -1;
+                if (t < ntiles) {
+                    const int off = tile_off[t], cnt = tile_off[t + 1] - off;
+                    if (lane < cnt) { dst[u] = off + lane; k[u] = gkeys[p.ws.tile_first[t] + lane]; }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (dst[u] >= 0) {
+                    bufA[dst[u]] = k[u];
+                    const u32 hi = (u32)(k[u] >> 32);
+                    kmin = min(kmin, hi); kmax = max(kmax, hi);
+                }
             }
         }
         kmin = __reduce_min_sync(YPP_FULL_MASK, kmin);
@@ -334,13 +346,33 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     // ---- 3. detector sweeps, BEFORE the sort: the keys are still in box-index order, so the box reads
     // are (nearly) sequential instead of a random gather
     if (detect) {
-        for (int i = tid; i < n; i += YPP_ORG_THREADS) {
-            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(bufA[i])]);
-            const float u = xy.z - step, v = xy.w - step;
-            if (u > dg.x1min - dg.slack) atomicMax(&hd->bin_hi[det_bin(dg, u)], ypp_enc(v));
-            if (xy.x < dg.lim && xy.y < dg.lim) atomicMax(&hd->bin_lo[det_bin(dg, xy.x)], ypp_enc(-xy.y));
+        for (int i0 = tid; i0 < n; i0 += 4 * YPP_ORG_THREADS) {       // four box reads in flight per thread
+            float4 bx[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int i = i0 + q * YPP_ORG_THREADS;
+                if (i < n) bx[q] = gbox[ypp_key_idx(bufA[i])];
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (i0 + q * YPP_ORG_THREADS >= n) break;
+                const float4 xy = ypp_xyxy(bx[q]);
+                const float u = xy.z - step, v = xy.w - step;
+                // read first: after a few updates nearly every candidate loses to the bin's current value
+                if (u > dg.x1min - dg.slack) {
+                    const int j = det_bin(dg, u);
+                    const u32 e = ypp_enc(v);
+                    if (e > hd->bin_hi[j]) atomicMax(&hd->bin_hi[j], e);
+                }
+                if (xy.x < dg.lim && xy.y < dg.lim) {
+                    const int j = det_bin(dg, xy.x);
+                    const u32 e = ypp_enc(-xy.y);
+                    if (e > hd->bin_lo[j]) atomicMax(&hd->bin_lo[j], e);
+                }
+            }
         }
         __syncthreads();
+        S1_MARK(12);
         if (warp == 1) {
             // suffix max over bin_hi (A's in bins >= j can dominate a B in bin j),
             // prefix max over bin_lo (B's in bins <= i can be dominated by an A in bin i); 2 bins per lane
@@ -359,9 +391,20 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             hd->bin_lo[lane] = l0; hd->bin_lo[lane + 32] = l1;
         }
         __syncthreads();
-        for (int i = tid; i < n; i += YPP_ORG_THREADS) {
+        S1_MARK(13);
+        for (int i0 = tid; i0 < n; i0 += 4 * YPP_ORG_THREADS) {
+          float4 bx[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+              const int i = i0 + q * YPP_ORG_THREADS;
+              if (i < n) bx[q] = gbox[ypp_key_idx(bufA[i])];
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int i = i0 + q * YPP_ORG_THREADS;
+            if (i >= n) break;
             const u64 k = bufA[i];
-            const float4 xy = ypp_xyxy(gbox[ypp_key_idx(k)]);
+            const float4 xy = ypp_xyxy(bx[q]);
             // B role: some A in an x-bin >= mine has v_a > y1 ; A role: some B in an x-bin <= mine has y1 < v_a
             bool is_low = false, is_high = false;
             if (xy.x < dg.lim && xy.y < dg.lim) {
@@ -384,8 +427,10 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
                 if (is_low) { const int s = atomicAdd(&hd->n_low, 1); if (s < YPP_DET_LIST) hd->lowl[s] = e; }
                 if (is_high) { const int s = atomicAdd(&hd->n_high, 1); if (s < YPP_DET_LIST) hd->highl[s] = e; }
             }
+          }
         }
         __syncthreads();
+        S1_MARK(14);
         // exact test of the candidate pairs: a cross-class pair whose SHIFTED boxes suppress is an edge
         {
             const int nl = hd->n_low, nh = hd->n_high;
@@ -532,18 +577,34 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     __syncthreads();
     S1_MARK(6);
     // ---- 7. stable ranking: segment position -> global rank (N1 gathers the boxes through it)
-    for (int r0 = r_begin; r0 < r_end; r0 += 32) {
-        const int r = r0 + lane;
-        const bool ok = r < r_end;
-        const int c = ok ? cmap[ypp_key_cls(keys[r])] : 0;
-        const unsigned peers = same_value_lanes(c, cbits, ok);
-        const int rank = __popc(peers & ((1u << lane) - 1u));
-        int q = 0;
-        if (ok) q = my[c] + rank;
+    // two 32-rank chunks (A, then B) per step: B's positions also count A's lanes of the same class,
+    // found with the ballots A needs anyway
+    const u32 lt = (1u << lane) - 1u;
+    for (int r0 = r_begin; r0 < r_end; r0 += 64) {
+        const int rA = r0 + lane, rB = rA + 32;
+        const bool okA = rA < r_end, okB = rB < r_end;
+        const int cA = okA ? cmap[ypp_key_cls(keys[rA])] : 0;
+        const int cB = okB ? cmap[ypp_key_cls(keys[rB])] : 0;
+        u32 pA = __ballot_sync(YPP_FULL_MASK, okA), pB = __ballot_sync(YPP_FULL_MASK, okB);
+        u32 xB = pA, xA = pB;        // xB: A lanes of my B class; xA: B lanes of my A class
+        for (int i = 0; i < cbits; ++i) {
+            const bool bitA = (cA >> i) & 1, bitB = (cB >> i) & 1;
+            const u32 balA = __ballot_sync(YPP_FULL_MASK, bitA), balB = __ballot_sync(YPP_FULL_MASK, bitB);
+            pA &= bitA ? balA : ~balA;
+            xA &= bitA ? balB : ~balB;
+            pB &= bitB ? balB : ~balB;
+            xB &= bitB ? balA : ~balA;
+        }
+        const int rankA = __popc(pA & lt), inB = __popc(pB & lt);
+        const int baseA = okA ? my[cA] : 0, baseB = okB ? my[cB] : 0;
         __syncwarp();
-        if (ok) {
-            if (rank == 0) my[c] += __popc(peers);
-            grank[q] = r;
+        if (okA) {
+            if (rankA == 0) my[cA] = baseA + __popc(pA) + __popc(xA);
+            grank[baseA + rankA] = rA;
+        }
+        if (okB) {
+            if (inB == 0 && xB == 0u) my[cB] = baseB + __popc(pB);     // class absent from A: B's leader counts it
+            grank[baseB + __popc(xB) + inB] = rB;
         }
         __syncwarp();
     }

@@ -27,3 +27,6 @@ print("rc", rc, "total cycles", v[8] - v[0])
 for i in range(8):
     print("%-12s %8d cycles  %6.2f us @1.965GHz" % (names[i], v[i + 1] - v[i], (v[i + 1] - v[i]) / 1965.0))
 print("longest CTA %.2f us; first CTA start -> last CTA end %.2f us" % (v[9] / 1965.0, (v[11] - v[10]) / 1e3))
+if v[12]:
+    print("detector split: pass 1 %.2f, bin scan %.2f, pass 2 %.2f, pair tests %.2f us" % (
+        (v[12] - v[2]) / 1965.0, (v[13] - v[12]) / 1965.0, (v[14] - v[13]) / 1965.0, (v[3] - v[14]) / 1965.0))

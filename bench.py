@@ -437,7 +437,7 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                         "mAP": float(m.item()), "detections_per_s": det_all.shape[0] / (ms_match * 1e-3)}
     # detection writers: integer box columns of one dense step's kept rows
     rows = pp(ring_dense).rows() if ring_dense is not None else det_local
-    scale = torch.tensor([[500 / w["input_size"], 375 / w["input_size"]]] * B, dtype=torch.float64)
+    scale = torch.tensor([[500 / w["input_size"], 375 / w["input_size"]]] * B, dtype=torch.float64).float().to(dev)
     engine.detection_ints(rows, "coco", scale_xy=scale)
     torch.cuda.synchronize()
     e0.record()

@@ -232,7 +232,9 @@ __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppSc
 // flight (cp.async.bulk rows -> stage, completion on full[stage]); consumer warp w decodes cells
 // 32w..32w+31 of each tile straight out of the stage, releases it on empty[stage] and compacts its
 // own slot, so warps never wait for each other -- only for data.
+#ifndef YPP_D1_STAGES
 #define YPP_D1_STAGES 2
+#endif
 #define YPP_D1_CONSUMERS (YPP_TILE_BOXES / 32)
 #define YPP_D1_MAX_PRODUCERS 4            /* UBLKCP issue is serialised per warp: spread the rows of a tile */
 #define YPP_D1_THREADS (32 * (YPP_D1_CONSUMERS + YPP_D1_MAX_PRODUCERS))

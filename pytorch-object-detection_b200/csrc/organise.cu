@@ -239,10 +239,10 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     float4* sbox = p.ws.sbox + (size_t)b * N;
     int* grank = p.ws.grank + (size_t)b * N;
     int* gseg = p.ws.seg_start + (size_t)b * (nc + 1);
-    // ping-pong buffers of the sort: shared memory when two copies fit, else global (skeys / the
-    // not-yet-written sbox region)
+    // the two key buffers of the sort: both in shared memory when they fit, else the first one only (the
+    // second in the not-yet-written sbox region), else both global (skeys / sbox)
     u64* bufA = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : skeys;
-    u64* bufB = p.keys_in_smem ? bufA + N : reinterpret_cast<u64*>(sbox);
+    u64* bufB = p.keys_in_smem == 2 ? bufA + N : reinterpret_cast<u64*>(sbox);
 
     S1_CTA_BEGIN();
     S1_MARK(0);
@@ -643,7 +643,8 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
     fixed = (fixed + 15) / 16 * 16;
     const size_t cap = 227 * 1024;
     if (fixed > cap) return -1;
-    if (fixed + (size_t)N * 16 <= cap) { *keys_in_smem = 1; return (int)(fixed + (size_t)N * 16); }
+    if (fixed + (size_t)N * 16 <= cap) { *keys_in_smem = 2; return (int)(fixed + (size_t)N * 16); }
+    if (fixed + (size_t)N * 8 <= cap) { *keys_in_smem = 1; return (int)(fixed + (size_t)N * 8); }
     *keys_in_smem = 0;
     return (int)fixed;
 }

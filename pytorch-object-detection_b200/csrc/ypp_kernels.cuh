@@ -28,7 +28,7 @@ struct YppOrgParams {
     int B, N, nc;
     int offset_mode, union_mode;
     float iou_thr;
-    int keys_in_smem;      // 1: sort in shared memory, 0: in place in global memory
+    int keys_in_smem;      // key buffers of the sort held in shared memory: 2 (both), 1 (the first), 0
     int table_ints;        // 32 * nc
 };
 

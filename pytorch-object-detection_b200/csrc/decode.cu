@@ -109,6 +109,13 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
     return d;
 }
 
+__device__ __forceinline__ float max_nan(float a, float b)
+{
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+
 // ---- warp-wide compaction in box-index order ------------------------------------------------
 // The compaction unit is a SLOT of 32 consecutive boxes handled by one warp (one ballot): its
 // candidates go to keys[b][slot_first ..] in lane order, its count and extrema to the slot record.
@@ -123,7 +130,7 @@ __device__ __forceinline__ void slot_store(const YppWs& ws, int N, int b, int sl
         // extrema for the coordinate trick / cross-class detector
         if (pass) {
             const float4 q = ypp_xyxy(box);
-            emax = max(max(ypp_enc(q.x), ypp_enc(q.y)), max(ypp_enc(q.z), ypp_enc(q.w)));
+            emax = ypp_enc(max_nan(max_nan(q.x, q.y), max_nan(q.z, q.w)));   // a NaN coordinate stays on top, like boxes.max()
             enx = ypp_enc(-q.x);
             eny = ypp_enc(-q.y);
         }

@@ -54,6 +54,11 @@ int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, Ypp
     p->C = 5 + cfg->nc;
     p->conf = cfg->conf_thr;
     p->score_mode = cfg->score_mode;
+    // rows of a plane whose size is not a multiple of 4 floats (13x13, 19x19) start at any 4-byte offset: their
+    // copies fetch the enclosing 16-byte-aligned span, so a staged row needs up to 2 x 3 floats of slack
+    p->pitch = YPP_TILE_BOXES;
+    for (int i = 0; i < cfg->n_scales; ++i)
+        if ((sc[i].H * sc[i].W) % 4 != 0) p->pitch = YPP_TILE_BOXES + 8;
     int box_base = 0, tile = 0;
     for (int i = 0; i < cfg->n_scales; ++i) {
         const ypp_scale& s = sc[i];
@@ -62,9 +67,10 @@ int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, Ypp
         d.head = s.head; d.A = s.A; d.H = s.H; d.W = s.W; d.HW = s.H * s.W;
         d.box_base = box_base;
         d.tpp = (d.HW + YPP_TILE_BOXES - 1) / YPP_TILE_BOXES;
-        // staged (cp.async.bulk) path: channel rows must be 16-byte aligned and the tile must fit shared memory
-        d.tma = (!dense && (d.HW % 4 == 0) && (((uintptr_t)s.head & 15u) == 0) && p->C * YPP_TILE_BOXES * 4 <= 100 * 1024) ? 1 : 0;
-        if (d.tma) p->stage_bytes = p->C * YPP_TILE_BOXES * 4;
+        d.elems = (long long)cfg->B * s.A * p->C * d.HW;
+        // staged (cp.async.bulk) path: the tensor must start 16-byte aligned and the tile must fit shared memory
+        d.tma = (!dense && (((uintptr_t)s.head & 15u) == 0) && p->C * p->pitch * 4 <= 100 * 1024) ? 1 : 0;
+        if (d.tma) p->stage_bytes = p->C * p->pitch * 4;
         for (int a = 0; a < s.A; ++a) { d.aw[a] = s.anchor_w[a]; d.ah[a] = s.anchor_h[a]; }
         d.sw = s.stride_w; d.sh = s.stride_h;
         d.inv_w = 1.0f / (float)s.W;

@@ -10,7 +10,8 @@
 // row, completion on an mbarrier), so the whole tile is in flight at once without holding
 // registers, and DRAM sees only large sequential requests.  Thread t then decodes cell t from
 // shared memory (conflict-free columns).  Heads whose plane size is not a multiple of 4 floats
-// (13x13, 19x19: channel rows are only 4-byte aligned) take plain coalesced loads instead.
+// (13x13, 19x19: channel rows are only 4-byte aligned) are staged the same way: each row copy fetches
+// the enclosing span of whole 16-byte words and the consumers add the row's 0..3 float shift.
 //
 // Compaction is deterministic: the candidates of every 32-box slot are written in box-index order
 // at keys[b][slot_first ..] with their count in tile_cnt[b][slot]; S1 concatenates the slots, so
@@ -51,12 +52,12 @@ __device__ __forceinline__ float cls_tol(float m1)
 
 // slow path: exact argmax over sigmoid for logits inside the band (first max wins);
 // cls_base/stride address either the staged tile or the head itself
-__device__ __noinline__ int cls_resolve(const float* cls_base, int stride, int nc, float m1, float tol)
+__device__ __noinline__ int cls_resolve(const float* cls_base, int stride, int nc, float m1, float tol, int q, int hwm)
 {
     int best = 0;
     float best_v = -1.0f;
     for (int c = 0; c < nc; ++c) {
-        const float v = cls_base[(size_t)c * stride];
+        const float v = cls_base[(size_t)c * stride + ((q + c * hwm) & 3)];      // q = hwm = 0: rows without a shift
         if (v >= m1 - tol) {
             const float s = ypp_sigmoid(v);
             if (s > best_v) { best_v = s; best = c; }
@@ -65,16 +66,16 @@ __device__ __noinline__ int cls_resolve(const float* cls_base, int stride, int n
     return best;
 }
 
-__device__ __forceinline__ void class_sweep(const float* cp, int stride, int nc, ClsTrack& tr)
+template <class Load>
+__device__ __forceinline__ void class_sweep(Load ld, int nc, ClsTrack& tr)      // ld(c) = logit of class c
 {
     cls_init(tr);
     int c = 0;
     for (; c + 4 <= nc; c += 4) {
-        const float v0 = cp[(size_t)c * stride], v1 = cp[(size_t)(c + 1) * stride];
-        const float v2 = cp[(size_t)(c + 2) * stride], v3 = cp[(size_t)(c + 3) * stride];
+        const float v0 = ld(c), v1 = ld(c + 1), v2 = ld(c + 2), v3 = ld(c + 3);
         cls_push(tr, v0, c); cls_push(tr, v1, c + 1); cls_push(tr, v2, c + 2); cls_push(tr, v3, c + 3);
     }
-    for (; c < nc; ++c) cls_push(tr, cp[(size_t)c * stride], c);
+    for (; c < nc; ++c) cls_push(tr, ld(c), c);
 }
 
 // decode one cell from its five box/objectness logits and the class track
@@ -82,7 +83,8 @@ struct Decoded { float4 box; float score; int cls; };
 
 __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const YppScaleParams& s, int a, int cell,
                                                float t0, float t1, float t2, float t3, float sobj,
-                                               const ClsTrack& tr, const float* cls_base, int cls_stride)
+                                               const ClsTrack& tr, const float* cls_base, int cls_stride,
+                                               int cls_q = 0, int cls_hwm = 0)
 {
     // y = cell / W without an integer division: float estimate, then one step of correction
     int y = __float2int_rz(__fmul_rn((float)cell, s.inv_w));
@@ -101,7 +103,7 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
     if (p.nc > 1) {
         ci = tr.i1;
         const float tol = cls_tol(tr.m1);
-        if (!(tr.m1 - tr.m2 > tol)) ci = cls_resolve(cls_base, cls_stride, p.nc, tr.m1, tol);
+        if (!(tr.m1 - tr.m2 > tol)) ci = cls_resolve(cls_base, cls_stride, p.nc, tr.m1, tol, cls_q, cls_hwm);
     }
     d.cls = ci;
     d.score = sobj;
@@ -203,16 +205,23 @@ __device__ __forceinline__ TileRef tile_ref(const YppDecodeParams& p, int bx)
     return t;
 }
 
-// one cell of a staged tile (shared-memory column `col`) or of the head itself (kStaged = false)
-template <bool kStaged>
+// one cell of the head itself (kMode 0: global loads, stride HW), of a staged tile (1: shared-memory column
+// `col`, rows `stride` floats apart) or of a staged tile whose rows carry their own 0..3 float shift (2: row c
+// starts ((q + c * hwm) & 3) floats into its slot -- planes whose size is not a multiple of 4 floats)
+template <int kMode>
 __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppScaleParams& s, int a, int cell, bool valid,
-                                           const float* col, int stride, Decoded& d)
+                                           const float* col, int stride, int q, int hwm, Decoded& d)
 {
+    constexpr bool kStaged = kMode != 0, kShift = kMode == 2;
+    auto ld = [&](int c) -> float {
+        const float* ptr = col + (size_t)c * stride + (kShift ? ((q + c * hwm) & 3) : 0);
+        return kStaged ? *ptr : __ldg(ptr);
+    };
     bool pass = false;
     float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f, sobj = 0.f;
     if (valid) {
-        const float obj = kStaged ? col[4 * stride] : __ldg(col + 4 * (size_t)stride);
-        if (!kStaged) { t0 = __ldg(col); t1 = __ldg(col + stride); t2 = __ldg(col + 2 * (size_t)stride); t3 = __ldg(col + 3 * (size_t)stride); }
+        const float obj = ld(4);
+        if (!kStaged) { t0 = ld(0); t1 = ld(1); t2 = ld(2); t3 = ld(3); }
         sobj = ypp_sigmoid(obj);                                         // yolov3_utils.py:50
         pass = sobj > p.conf;                                            // yolo_utils.py:334 (strict)
     }
@@ -223,11 +232,12 @@ __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppSc
     // the direct path only in lanes that hold a candidate (every read is a global load)
     if (__any_sync(YPP_FULL_MASK, pass) && (kStaged || pass)) {
         ClsTrack tr;
-        if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * (size_t)stride, stride, p.nc, tr);
+        if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep([&](int c) { return ld(5 + c); }, p.nc, tr);
         else cls_init(tr);
         if (pass) {
-            if (kStaged) { t0 = col[0]; t1 = col[stride]; t2 = col[2 * stride]; t3 = col[3 * stride]; }
-            d = decode_cell(p, s, a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)stride, stride);
+            if (kStaged) { t0 = ld(0); t1 = ld(1); t2 = ld(2); t3 = ld(3); }
+            d = decode_cell(p, s, a, cell, t0, t1, t2, t3, sobj, tr, col + 5 * (size_t)stride, stride,
+                            kShift ? ((q + 5 * hwm) & 3) : 0, kShift ? hwm : 0);
             if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) pass = d.score > p.conf;
         }
     }
@@ -243,6 +253,7 @@ __device__ __forceinline__ bool decode_one(const YppDecodeParams& p, const YppSc
 #define YPP_D1_STAGES 2
 #endif
 #define YPP_D1_CONSUMERS (YPP_TILE_BOXES / 32)
+#define YPP_SHIFT_PITCH (YPP_TILE_BOXES + 8)   /* row pitch of a staged tile with shifted rows (compile-time: LDS offsets fold) */
 #define YPP_D1_MAX_PRODUCERS 4            /* UBLKCP issue is serialised per warp: spread the rows of a tile */
 #define YPP_D1_THREADS (32 * (YPP_D1_CONSUMERS + YPP_D1_MAX_PRODUCERS))
 
@@ -259,7 +270,7 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tiles_per_img = p.tile_base[p.n_scales];
     const long long total = (long long)tiles_per_img * B;
-    const int stage_floats = p.C * YPP_TILE_BOXES;
+    const int stage_floats = p.C * p.pitch;
     if (tid == 0) {
 #pragma unroll
         for (int i = 0; i < YPP_D1_STAGES; ++i) { mbar_init(&full[i], (int)(blockDim.x >> 5) - YPP_D1_CONSUMERS); mbar_init(&empty[i], YPP_D1_CONSUMERS); }
@@ -279,7 +290,8 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
             if (use > 0) mbar_wait(&empty[stg], (u32)(use - 1) & 1u);        // consumers are done with this stage
             const TileRef t = tile_ref(p, tile);
             const YppScaleParams& s = p.sc[t.si];
-            if (s.tma && c_hi > c_lo) {
+            if (s.tma && c_hi > c_lo && (s.HW & 3) == 0) {
+                // 16-byte-aligned rows: one copy of ncells floats per row
                 const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
                 const u32 row_bytes = (u32)t.ncells * 4u;                    // multiple of 16: HW % 4 == 0
                 float* stage = stage_mem + stg * stage_floats;
@@ -287,6 +299,36 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
                 __syncwarp();
                 for (int c = c_lo + lane; c < c_hi; c += 32)
                     bulk_g2s(stage + c * YPP_TILE_BOXES, src + (size_t)c * s.HW, row_bytes, &full[stg]);
+            } else if (s.tma && c_hi > c_lo) {
+                // row c of the tile = floats [e0, e0 + ncells) of the head; the copy fetches the enclosing span of
+                // whole 16-byte words [a0, a0 + n_al), so cell ct of row c lands at stage[c * 264 + (e0 & 3) + ct]
+                const long long e_tile = ((long long)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
+                float* stage = stage_mem + stg * stage_floats;
+                u32 bytes = 0;
+                for (int c = c_lo + lane; c < c_hi; c += 32) {
+                    const long long e0 = e_tile + (long long)c * s.HW;
+                    const int sh = (int)(e0 & 3);
+                    const long long a0 = e0 - sh;
+                    const int n_el = t.ncells + sh;
+                    int n_al = (n_el + 3) & ~3;
+                    if (a0 + n_al > s.elems) {                               // last words of the tensor: never read past it
+                        n_al = (int)((s.elems - a0) & ~3LL);
+                        for (int j = n_al; j < n_el; ++j) stage[c * YPP_SHIFT_PITCH + j] = __ldg(s.head + a0 + j);
+                    }
+                    bytes += (u32)n_al * 4u;
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) bytes += __shfl_xor_sync(YPP_FULL_MASK, bytes, o);
+                __syncwarp();                                                // the tail stores above are ordered before ..
+                if (lane == 0) mbar_expect_tx(&full[stg], bytes);            // .. this arrive (release) publishes them
+                __syncwarp();
+                for (int c = c_lo + lane; c < c_hi; c += 32) {
+                    const long long e0 = e_tile + (long long)c * s.HW;
+                    const long long a0 = e0 & ~3LL;
+                    int n_al = (t.ncells + (int)(e0 & 3) + 3) & ~3;
+                    if (a0 + n_al > s.elems) n_al = (int)((s.elems - a0) & ~3LL);
+                    if (n_al > 0) bulk_g2s(stage + c * YPP_SHIFT_PITCH, s.head + a0, (u32)n_al * 4u, &full[stg]);
+                }
             } else if (lane == 0) {
                 mbar_arrive(&full[stg]);                                     // nothing to stage: consumers read the head directly
             }
@@ -305,11 +347,16 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
         d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
         bool pass;
         mbar_wait(&full[stg], (u32)use & 1u);
-        if (s.tma) {
-            pass = decode_one<true>(p, s, t.a, t.cell0 + ct, ct < t.ncells, stage_mem + stg * stage_floats + ct, YPP_TILE_BOXES, d);
+        const int hwm = s.HW & 3;
+        if (s.tma && hwm == 0) {
+            pass = decode_one<1>(p, s, t.a, t.cell0 + ct, ct < t.ncells, stage_mem + stg * stage_floats + ct, YPP_TILE_BOXES, 0, 0, d);
+        } else if (s.tma) {
+            // (first float of row 0 of this tile) mod 4; unsigned wrap-around keeps the low two bits
+            const int q = (int)((((unsigned)(b * s.A + t.a) * (unsigned)p.C) * (unsigned)s.HW + (unsigned)t.cell0) & 3u);
+            pass = decode_one<2>(p, s, t.a, t.cell0 + ct, ct < t.ncells, stage_mem + stg * stage_floats + ct, YPP_SHIFT_PITCH, q, hwm, d);
         } else {
             const float* src = s.head + ((size_t)(b * s.A + t.a) * p.C) * s.HW + t.cell0;
-            pass = decode_one<false>(p, s, t.a, t.cell0 + ct, ct < t.ncells, src + ct, s.HW, d);
+            pass = decode_one<0>(p, s, t.a, t.cell0 + ct, ct < t.ncells, src + ct, s.HW, 0, 0, d);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[stg]);                             // this warp no longer reads the stage
@@ -331,7 +378,7 @@ ypp_decode_dense_kernel(const __grid_constant__ YppDecodeParams p, float* __rest
     const float obj = __ldg(col + 4 * HW);
     const float t0 = __ldg(col), t1 = __ldg(col + HW), t2 = __ldg(col + 2 * HW), t3 = __ldg(col + 3 * HW);
     ClsTrack tr;
-    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep(col + 5 * HW, (int)HW, p.nc, tr);
+    if (p.nc > 1 || p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) class_sweep([&](int c) { return __ldg(col + (5 + c) * HW); }, p.nc, tr);
     else cls_init(tr);
     const Decoded d = decode_cell(p, s, t.a, t.cell0 + tid, t0, t1, t2, t3, ypp_sigmoid(obj), tr, col + 5 * HW, (int)HW);
     float2* o = reinterpret_cast<float2*>(out + ((size_t)b * p.N + t.first + tid) * 6);

@@ -8,6 +8,7 @@ struct YppScaleParams {
     int box_base;        // first box index of this scale inside the image (cat order)
     int tma;             // 1: planes staged with cp.async.bulk (H*W % 4 == 0, head 16 B aligned); 0: plain loads
     int tpp;             // tiles per anchor plane = ceil(HW / YPP_TILE_BOXES)
+    long long elems;     // floats in the head tensor (bulk copies never read past it)
     float aw[YPP_MAX_ANCHORS], ah[YPP_MAX_ANCHORS];
     float sw, sh;
     float inv_w;         // 1 / W
@@ -19,7 +20,8 @@ struct YppDecodeParams {
     int n_scales, nc, C, N;
     float conf;
     int score_mode;
-    int stage_bytes;     // dynamic shared memory of the staged path (0 when no scale uses it)
+    int stage_bytes;     // dynamic shared memory of one stage of the staged path (0 when no scale uses it)
+    int pitch;           // floats per channel row a stage must hold: 256, or 264 when some plane's rows are not 16 B-aligned
     YppWs ws;
 };
 

@@ -14,8 +14,11 @@ ap.add_argument("--regime", default="dense")
 ap.add_argument("--steps", type=int, default=50)
 ap.add_argument("--ring", type=int, default=4)
 ap.add_argument("--stages", default="decode")
+ap.add_argument("--grids", default="", help="override the grid sizes, e.g. 52,26,12 (tuning experiments)")
 a = ap.parse_args()
-w = synth.WORKLOADS[a.workload]
+w = dict(synth.WORKLOADS[a.workload])
+if a.grids:
+    w["grids"] = [int(x) for x in a.grids.split(",")]
 dev = torch.device("cuda:0")
 mu = 0.0 if a.regime == "dense" else -5.0
 ring = [[h.to(dev) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=i, mu_obj=mu)] for i in range(a.ring)]

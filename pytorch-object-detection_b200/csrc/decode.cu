@@ -267,6 +267,7 @@ ypp_decode_compact_kernel(const __grid_constant__ YppDecodeParams p, const int B
 {
     extern __shared__ __align__(128) float stage_mem[];      // [STAGES][C][256] when some scale is staged
     __shared__ __align__(8) u64 full[YPP_D1_STAGES], empty[YPP_D1_STAGES];
+    ypp_grid_wait();       // the previous call's G may still be reading the workspace
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tiles_per_img = p.tile_base[p.n_scales];
     const long long total = (long long)tiles_per_img * B;
@@ -391,6 +392,7 @@ ypp_decode_dense_kernel(const __grid_constant__ YppDecodeParams p, float* __rest
 __global__ void __launch_bounds__(YPP_DECODE_THREADS)
 ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs ws)
 {
+    ypp_grid_wait();
     const int b = blockIdx.y;
     const int n = blockIdx.x * YPP_DECODE_THREADS + threadIdx.x;
     const int slot = n >> 5;
@@ -444,7 +446,7 @@ int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
     const long long total = (long long)p.tile_base[p.n_scales] * B;
     long long grid = (long long)sms * ctas_per_sm;
     if (grid > total) grid = total;
-    ypp_decode_compact_kernel<<<(unsigned)grid, threads, smem, st>>>(p, B);
+    ypp_launch_chain(0, ypp_decode_compact_kernel, dim3((unsigned)grid), dim3(threads), smem, st, p, B);
     ypp_count_launch(1);
     return ypp_check_launch("decode_compact");
 }
@@ -460,7 +462,7 @@ int ypp_launch_decode_dense(const YppDecodeParams& p, int B, float* out, cudaStr
 int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const YppWs& ws, cudaStream_t st)
 {
     dim3 grid((N + YPP_TILE_BOXES - 1) / YPP_TILE_BOXES, B);
-    ypp_rows_compact_kernel<<<grid, YPP_DECODE_THREADS, 0, st>>>(rows, N, conf, ws);
+    ypp_launch_chain(0, ypp_rows_compact_kernel, grid, dim3(YPP_DECODE_THREADS), 0, st, rows, N, conf, ws);
     ypp_count_launch(1);
     return ypp_check_launch("rows_compact");
 }

@@ -206,6 +206,7 @@ __global__ void __launch_bounds__(YPP_NMSQ_THREADS, 9)
 ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 {
     __shared__ SegSmem sm;
+    ypp_grid_wait();
     const int c = blockIdx.x, b = blockIdx.y;
     const int* seg_start = p.ws.seg_start + (size_t)b * (p.nc + 1);
     const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
@@ -447,6 +448,7 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
     float4* cache = reinterpret_cast<float4*>(smem_raw);
     u32* removed = reinterpret_cast<u32*>(smem_raw + sizeof(float4) * YPP_BIG_CACHE);
     __shared__ TileSmem ts;
+    ypp_grid_wait();
     const int per = p.ws.bigq_per_image;
     {   // nearly always there is nothing to do: find out with one round of loads
         int any = 0;
@@ -495,6 +497,7 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     __shared__ float stage[YPP_GATHER_CHUNK * 7];
     __shared__ long long red_img[YPP_GATHER_THREADS / 32];
     __shared__ int red_pre[YPP_GATHER_THREADS / 32];
+    ypp_grid_wait();
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.N;
     const int n = min(p.ws.cand_count[b], N);
@@ -608,7 +611,7 @@ template <bool kFast, bool kFma>
 int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
 {
     dim3 grid(p.nc, p.B);
-    ypp_nms_seg_kernel<kFast, kFma><<<grid, YPP_NMSQ_THREADS, 0, st>>>(p);
+    ypp_launch_chain(2, ypp_nms_seg_kernel<kFast, kFma>, grid, dim3(YPP_NMSQ_THREADS), 0, st, p);
     ypp_count_launch(1);
     int rc = ypp_check_launch("nms_seg");
     if (rc) return rc;
@@ -626,7 +629,7 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (ctas > sms) ctas = sms;
-        ypp_nms_big_kernel<kFast, kFma><<<ctas, YPP_NMS_BIG_THREADS, smem, st>>>(p);
+        ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, p);
         ypp_count_launch(1);
         rc = ypp_check_launch("nms_big");
     }
@@ -646,7 +649,7 @@ int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st)
 int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st)
 {
     dim3 grid((p.N + YPP_GATHER_CHUNK - 1) / YPP_GATHER_CHUNK, p.B);
-    ypp_gather_kernel<<<grid, YPP_GATHER_THREADS, 0, st>>>(p);
+    ypp_launch_chain(4, ypp_gather_kernel, grid, dim3(YPP_GATHER_THREADS), 0, st, p);
     ypp_count_launch(1);
     return ypp_check_launch("gather");
 }

@@ -244,6 +244,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     u64* bufA = p.keys_in_smem ? reinterpret_cast<u64*>(smem_raw + koff) : skeys;
     u64* bufB = p.keys_in_smem == 2 ? bufA + N : reinterpret_cast<u64*>(sbox);
 
+    ypp_grid_wait();
     S1_CTA_BEGIN();
     S1_MARK(0);
     // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema
@@ -674,7 +675,7 @@ int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
         if (e != cudaSuccess) { ypp_set_error("organise: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
         configured_smem = 227 * 1024;
     }
-    ypp_organise_kernel<<<p.B, YPP_ORG_THREADS, smem, st>>>(q);
+    ypp_launch_chain(1, ypp_organise_kernel, dim3(p.B), dim3(YPP_ORG_THREADS), smem, st, q);
     ypp_count_launch(1);
     return ypp_check_launch("organise");
 }

@@ -1,6 +1,7 @@
 // Kernel parameter blocks and host launcher prototypes (internal to libypp).
 #pragma once
 #include "ypp_common.cuh"
+#include <cstdlib>
 
 struct YppScaleParams {
     const float* head;
@@ -72,3 +73,34 @@ size_t ypp_map_ws_bytes(long long G, long long K, int nc);
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
                    cudaStream_t st);
+
+// ---- programmatic dependent launch (PDL) --------------------------------------------------
+// The chain D1 -> S1 -> N1 -> N1b -> G is five short kernels; with the attribute below the next kernel's
+// CTAs are scheduled while the previous one drains and park in ypp_grid_wait() (griddepcontrol.wait:
+// returns once the WHOLE previous grid has completed and flushed), so launch latency and CTA set-up
+// leave the critical path.  Every kernel of the chain calls ypp_grid_wait() first thing in every CTA
+// (completion then chains transitively) and releases its successor right after.  Measured on the C2
+// chain: early launch pays for D1 (after the previous call's G), N1b and G (-2 us each group) and
+// costs ~2.5 us each for S1 and N1, whose CTAs then land on the SMs in a worse order; hence the default mask.
+#ifdef __CUDACC__
+__device__ __forceinline__ void ypp_grid_wait()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+
+template <class... KArgs, class... Args>
+inline cudaError_t ypp_launch_chain(int edge, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args)
+{
+    static int pdl = -1;
+    if (pdl < 0) { const char* e = getenv("YPP_PDL"); pdl = e ? atoi(e) : 25; }     // bit per kernel: D1, S1, N1, N1b, G
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = ((pdl >> edge) & 1) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}

@@ -334,10 +334,11 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 // ------------------------------------------------------------------ CTA-owned (long) segments
 struct TileSmem {
     u32 diag[64][2];          // diag[i] = columns j (tile-local) suppressed by row i, j > i
-    float4 kbox[64];          // kept rows of the current tile, compacted
-    float karea[64];
+    float4 kbox[64];          // kept rows of the current tile, compacted (padded to an even count)
+    float karea[64];          // -thr * |area| of those rows
     int nkept;
     int total_kept;
+    u32 amax, cmax;           // largest |area| / |coordinate| of the segment (float bits)
 };
 
 // Process one segment.  seg: boxes in score order (global memory), cache: shared staging for
@@ -350,10 +351,29 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
 {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ncache = min(len, cache_cap);
-    for (int i = tid; i < ncache; i += THREADS) cache[i] = seg[i];
-    for (int i = tid; i < (len + 31) / 32 + 2; i += THREADS) removed[i] = 0;
-    if (tid == 0) ts.total_kept = 0;
+    if (tid == 0) { ts.total_kept = 0; ts.amax = 0; ts.cmax = 0; }
     __syncthreads();
+    u32 amax_bits = 0, cmax_bits = 0;
+    for (int i = tid; i < len; i += THREADS) {
+        const float4 q = seg[i];
+        if (i < ncache) cache[i] = q;
+        amax_bits = max(amax_bits, __float_as_uint(fabsf(ypp_area(q))));
+        cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
+                        max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
+    }
+    amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
+    cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
+    if (lane == 0) { atomicMax(&ts.amax, amax_bits); atomicMax(&ts.cmax, cmax_bits); }
+    for (int i = tid; i < (len + 31) / 32 + 2; i += THREADS) removed[i] = 0;
+    __syncthreads();
+    // the sweeps use the lean pair test of the per-class kernel (see pair_g): one band per segment
+    float Bseg = 2.0f * YPP_PAIR_BAND * __uint_as_float(ts.amax);
+    const int cexp = (int)(ts.cmax >> 23);
+    if (cexp < 67 || cexp > 187) Bseg = INFINITY;
+    const int cex = min(max(cexp, 67), 187);
+    const float scale = __uint_as_float((u32)(252 - cex) << 23);
+    const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cex + 2) << 23));
+    const float nthr = -thr;
 
     for (int t0 = 0; t0 < len; t0 += 64) {
         const int rows = min(64, len - t0);
@@ -397,17 +417,21 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
                 const int s = __popc(klo & ((1u << lane) - 1u));
                 const int r = t0 + lane;
                 const float4 bx = r < ncache ? cache[r] : seg[r];
-                ts.kbox[s] = bx; ts.karea[s] = ypp_area(bx);
+                ts.kbox[s] = bx; ts.karea[s] = __fmul_rn(nthr, fabsf(ypp_area(bx)));
                 keepflag[grank[r]] = 1;
             }
             if ((khi >> lane) & 1u) {
                 const int s = nlo + __popc(khi & ((1u << lane) - 1u));
                 const int r = t0 + 32 + lane;
                 const float4 bx = r < ncache ? cache[r] : seg[r];
-                ts.kbox[s] = bx; ts.karea[s] = ypp_area(bx);
+                ts.kbox[s] = bx; ts.karea[s] = __fmul_rn(nthr, fabsf(ypp_area(bx)));
                 keepflag[grank[r]] = 1;
             }
-            if (lane == 0) { ts.nkept = nlo + __popc(khi); ts.total_kept += nlo + __popc(khi); }
+            if (lane == 0) {
+                const int nk = nlo + __popc(khi);
+                ts.nkept = nk; ts.total_kept += nk;
+                if (nk < 64) { ts.kbox[nk] = YPP_DUMMY_BOX; ts.karea[nk] = YPP_DUMMY_TA; }     // rows go in pairs
+            }
         }
         __syncthreads();
         // ---- broadcast kept rows against later, still-alive columns (rows in chunks of 8)
@@ -417,20 +441,18 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
                 if ((removed[j >> 5] >> (j & 31)) & 1u) continue;
                 const float4 bq = j < ncache ? cache[j] : seg[j];
                 bool dead = false;
+                bool exact = !kFast;
                 if (kFast) {
-                    float p0, p1;
-                    pair_col<kFma>(bq, p0, p1);
-                    bool amb = false;
-                    for (int r0 = 0; r0 < nk && !dead; r0 += 8) {
-                        const int r1 = min(nk, r0 + 8);
-#pragma unroll 8
-                        for (int r = r0; r < r1; ++r) pair_fast<kFma>(ts.kbox[r], ts.karea[r], bq, p0, p1, thr, dead, amb);
-                    }
-                    if (amb && !dead) {
-                        for (int r = 0; r < nk && !dead; ++r) dead = pair_exact(ts.kbox[r], ts.karea[r], bq, thr, union_fma);
-                    }
-                } else {
-                    for (int r = 0; r < nk && !dead; ++r) dead = pair_exact(ts.kbox[r], ts.karea[r], bq, thr, union_fma);
+                    float dm = -INFINITY;
+                    for (int r = 0; r < nk; r += 2)
+                        dm = fmaxf(fmaxf(dm, pair_g(ts.kbox[r], ts.karea[r], bq, c1k, scale)),
+                                   pair_g(ts.kbox[r + 1], ts.karea[r + 1], bq, c1k, scale));
+                    const float D = __fadd_rn(dm, __fmul_rn(nthr, fabsf(ypp_area(bq))));
+                    dead = D > Bseg;
+                    exact = !dead && !(D < -Bseg);
+                }
+                if (exact) {
+                    for (int r = 0; r < nk && !dead; ++r) dead = pair_exact(ts.kbox[r], ypp_area(ts.kbox[r]), bq, thr, union_fma);
                 }
                 if (dead) atomicOr(&removed[j >> 5], 1u << (j & 31));
             }

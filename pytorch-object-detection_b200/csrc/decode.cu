@@ -422,7 +422,14 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
 {
-    static int configured = -1, ctas_per_sm = 0, sms = 0;
+    // function attributes and occupancy are per device: cache them per device (one process may drive several)
+    static int configured_d[YPP_MAX_DEVICES], ctas_d[YPP_MAX_DEVICES], sms_d[YPP_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= YPP_MAX_DEVICES) { ypp_set_error("decode_compact: device ordinal %d out of range", dev); return YPP_E_UNSUPPORTED; }
+    int& configured = configured_d[dev];
+    int& ctas_per_sm = ctas_d[dev];
+    int& sms = sms_d[dev];
     const int smem = YPP_D1_STAGES * p.stage_bytes;
     // one producer warp per ~20 channel rows of a tile (env YPP_D1_PRODUCERS overrides, for tuning)
     static int producers_env = -1;
@@ -430,14 +437,12 @@ int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st)
     int P = producers_env > 0 ? producers_env : (p.C + 19) / 20;
     P = P < 1 ? 1 : (P > YPP_D1_MAX_PRODUCERS ? YPP_D1_MAX_PRODUCERS : P);
     const int threads = 32 * (YPP_D1_CONSUMERS + P);
-    const int cfg_key = smem * 8 + P;
+    const int cfg_key = smem * 8 + P + 1;                 // never 0 (the zero-initialised cache)
     if (cfg_key != configured) {
         if (smem > 48 * 1024) {
             cudaError_t e = cudaFuncSetAttribute(ypp_decode_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { ypp_set_error("decode_compact: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
         }
-        int dev = 0;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, ypp_decode_compact_kernel, threads, smem);
         if (e != cudaSuccess || ctas_per_sm < 1) { ypp_set_error("decode_compact: occupancy query failed"); return YPP_E_CUDA; }

@@ -639,7 +639,11 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
     if (rc) return rc;
     if (p.N > YPP_WARP_SEG) {
         const int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 4));
-        static bool configured = false;
+        static bool configured_d[YPP_MAX_DEVICES];         // per device, like the attribute itself
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= YPP_MAX_DEVICES) { ypp_set_error("nms_big: device ordinal %d out of range", dev); return YPP_E_UNSUPPORTED; }
+        bool& configured = configured_d[dev];
         if (!configured) {
             cudaError_t e = cudaFuncSetAttribute(ypp_nms_big_kernel<kFast, kFma>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
             if (e != cudaSuccess) { ypp_set_error("nms_big: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
@@ -647,8 +651,6 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
         }
         if (smem > 220 * 1024) { ypp_set_error("nms_big: %d boxes per image exceed the removed-bitmap budget", p.N); return YPP_E_UNSUPPORTED; }
         int ctas = p.B * p.ws.bigq_per_image;
-        int dev = 0, sms = 148;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (ctas > sms) ctas = sms;
         ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, p);

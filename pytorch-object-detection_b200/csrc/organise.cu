@@ -669,7 +669,11 @@ int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
     YppOrgParams q = p;
     q.keys_in_smem = kin;
     q.table_ints = tints;
-    static int configured_smem = 0;
+    static int configured_d[YPP_MAX_DEVICES];              // per device, like the attribute itself
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= YPP_MAX_DEVICES) { ypp_set_error("organise: device ordinal %d out of range", dev); return YPP_E_UNSUPPORTED; }
+    int& configured_smem = configured_d[dev];
     if (smem > configured_smem) {
         cudaError_t e = cudaFuncSetAttribute(ypp_organise_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         if (e != cudaSuccess) { ypp_set_error("organise: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }

@@ -25,6 +25,7 @@ typedef unsigned int u32;
 // ---------------------------------------------------------------- workspace layout
 // All per-image arrays are [B][N].  Nothing needs a memset between calls: D1 owns the slot
 // records and S1 (re)initialises every per-image counter and list.
+#define YPP_MAX_DEVICES 64         // launcher-side per-device caches
 #define YPP_TILE_BOXES 256        // boxes per D1 tile (one per thread)
 struct YppWs {
     int* cand_count;      // [B] written by S1

@@ -174,3 +174,20 @@ def test_empty_and_single_image(cuda):
     res = pp(heads, row_width=6)
     assert int(res.det_total.item()) == 0 and res.rows().shape == (0, 6)
     assert int(res.cand_count.item()) == 0
+
+
+def test_one_process_two_devices(cuda):
+    """One process driving two GPUs: function attributes and occupancy are per device (launcher caches too)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from ypp import engine, synth
+    heads = synth.make_heads(4, 20, [52, 26, 13], g=21)
+    out = []
+    for d in (1, 0, 1):
+        dev = torch.device("cuda", d)
+        pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+        res = pp([h.to(dev) for h in heads], want_keep_idx=True)
+        torch.cuda.synchronize(dev)
+        out.append((res.keep_count.cpu(), res.rows().cpu()))
+    for kc, rows in out[1:]:
+        assert torch.equal(kc, out[0][0]) and torch.equal(rows, out[0][1])

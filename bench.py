@@ -182,6 +182,29 @@ def run_reference(args):
 
 # ------------------------------------------------------------------------------------ our arm
 
+def _bind_to_gpu_numa_node(gpu_index):
+    """Run this rank (and first-touch its pinned host buffers) on the CPUs NVML reports as local to its GPU,
+    so that with several ranks per box the H2D copies of the e2e path do not cross sockets."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        try:                                        # NVML ignores CUDA_VISIBLE_DEVICES: go through the PCI address
+            import torch
+            pr = torch.cuda.get_device_properties(gpu_index)
+            h = pynvml.nvmlDeviceGetHandleByPciBusId("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id))
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        n = (os.cpu_count() + 63) // 64
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, n)
+        cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:
+        pass                                        # affinity is an optimisation only
+
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -194,6 +217,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    _bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 

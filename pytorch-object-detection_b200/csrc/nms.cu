@@ -11,8 +11,8 @@
 //     boxes staged in shared memory, 32-row tiles, the 32x32 diagonal tile held as one register
 //     per lane, the greedy order resolved by a ballot fix-point, and only the KEPT rows
 //     broadcast against the later columns each lane owns (rows split over the four warps).
-//   - longer segments (single-class heads, the class-agnostic whole-image fallback) go to a
-//     persistent 1024-thread CTA kernel pulling (image, class) pairs from the queue S1 filled.
+//   - longer segments (single-class heads, classes a cross-class edge merged) go to a
+//     1024-thread CTA kernel walking the per-image lists of long segments S1 left.
 //
 // Pair test.  torchvision evaluates  inter / union > thr  with an IEEE division.  The same
 // decision is reached without dividing whenever  d = fma(-thr, union, inter)  is clearly away
@@ -60,31 +60,9 @@ __device__ __forceinline__ bool pair_exact(const float4 a, const float sa, const
     return ypp_suppresses<false>(a, sa, b, thr, union_fma);
 }
 
-// Accumulating form for one column tested against many rows: dmax = max over rows of
-// d = inter' - thr * |union'|, where inter' = (r - l) * max(bt - t, 0) leaves the x extent
-// unclamped: whenever the boxes do not overlap inter' <= 0 and d <= 0, and whenever d > 0 they
-// do overlap and inter', union' are the exact fp32 values torchvision computes.  With
-// B = 2^-20 * (largest row area + column area) >= 2^-20 * union of every pair:
-//   dmax >  B  : some pair is surely above the threshold -> suppressed;
-//   dmax < -B  : every pair is surely below it            -> alive;
-//   otherwise  : re-evaluate the rows with the exact division.
-// (The kernels use one B per segment: 2^-20 * 2 * the largest |area| in the segment.)
-// NaN d is dropped by fmaxf, which is right: every NaN case has an exact answer of "not
-// suppressed".  6 alu-pipe + 6 fma-pipe instructions per pair.
-template <bool kFma>
-__device__ __forceinline__ float pair_d(const float4 a, const float sa, const float4 b, const float p0,
-                                        const float p1, const float thr)
-{
-    const float l = fmaxf(a.x, b.x), t = fmaxf(a.y, b.y);
-    const float r = fminf(a.z, b.z), bt = fminf(a.w, b.w);
-    const float w = __fsub_rn(r, l);
-    const float h = fmaxf(__fsub_rn(bt, t), 0.0f);
-    const float inter = __fmul_rn(w, h);
-    const float uni = kFma ? __fsub_rn(__fmaf_rn(p0, p1, sa), inter) : __fsub_rn(__fadd_rn(sa, p0), inter);
-    return __fmaf_rn(-thr, fabsf(uni), inter);
-}
-
-// Lean form used by the per-class segment kernel.  With c1 = 1 + thr, ta = -thr*S_a, tb = -thr*S_b:
+// Lean form used by the sweeps of both kernels (the accumulating case: one column against many kept
+// rows; NaN values are dropped by fmaxf, which is right: every NaN case has an exact answer of "not
+// suppressed").  With c1 = 1 + thr, ta = -thr*S_a, tb = -thr*S_b:
 //   inter - thr*(S_a + S_b - inter) = c1*inter + ta + tb,
 // so a column only accumulates g = max over rows of fma(c1, inter, ta) and adds its own tb at the end.
 // The clamp of the y extent rides on the multiplier: hs = sat(h * 2^-k) (k per segment such that

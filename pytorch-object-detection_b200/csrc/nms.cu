@@ -105,7 +105,7 @@ __device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r,
 
 struct SegSmem {
     float4 box[YPP_WARP_SEG];
-    float area[YPP_WARP_SEG];
+    float tb[YPP_WARP_SEG];             // -thr * |area| of every box (its share of thr * union)
     float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 2
     float kta[YPP_NMSQ_WARPS][8];       // -thr * area of those rows
     u32 amax[YPP_NMSQ_WARPS];
@@ -115,29 +115,22 @@ struct SegSmem {
 };
 
 // One warp's kept rows (kb/ka, npad of them, nk real) against G groups of 32 columns starting at
-// group k (lane = column mod 32).  Returns the bits of the groups whose column in this lane died.
+// group k (lane = column mod 32).  Bit g of the lane's `dead >> k` says its column of group k+g needs no
+// work (suppressed, or past the end of the segment: those are marked dead up front and hold dummies).
+// Returns the bits of the groups whose column in this lane died.
 template <int G, bool kFast>
-__device__ __forceinline__ u32 sweep_groups(const float4* __restrict__ sbox, const float* __restrict__ sarea, int len,
+__device__ __forceinline__ u32 sweep_groups(const float4* __restrict__ sbox, const float* __restrict__ stb,
                                             const float4* __restrict__ kb, const float* __restrict__ ka, int npad, int nk,
-                                            int k, u32 dead, float c1k, float scale, float nthr, float Bseg,
-                                            float thr, int union_fma)
+                                            int k, u32 dead, float c1k, float scale, float Bseg, float thr, int union_fma)
 {
     const int lane = threadIdx.x & 31;
-    bool v[G];
-    int jj[G];
-    bool any = false;
-#pragma unroll
-    for (int g = 0; g < G; ++g) {
-        const int j = ((k + g) << 5) + lane;
-        v[g] = j < len && !((dead >> (k + g)) & 1u);
-        jj[g] = j < len ? j : 0;
-        any = any || v[g];
-    }
-    if (!__any_sync(YPP_FULL_MASK, any)) return 0u;
+    const u32 vm = ~(dead >> k) & ((1u << G) - 1u);
+    if (!__any_sync(YPP_FULL_MASK, vm != 0u)) return 0u;
+    const int j = (k << 5) + lane;
     float4 c[G];
 #pragma unroll
-    for (int g = 0; g < G; ++g) c[g] = sbox[jj[g]];
-    bool d[G];
+    for (int g = 0; g < G; ++g) c[g] = sbox[j + 32 * g];
+    u32 dbits = 0;
     bool exact = !kFast;
     if (kFast) {
         float dm[G];
@@ -150,28 +143,26 @@ __device__ __forceinline__ u32 sweep_groups(const float4* __restrict__ sbox, con
             for (int g = 0; g < G; ++g)
                 dm[g] = fmaxf(fmaxf(dm[g], pair_g(a, ta, c[g], c1k, scale)), pair_g(a2, ta2, c[g], c1k, scale));
         }
+        u32 amb = 0;
 #pragma unroll
         for (int g = 0; g < G; ++g) {
-            const float D = __fadd_rn(dm[g], __fmul_rn(nthr, fabsf(sarea[jj[g]])));
-            d[g] = D > Bseg;
-            exact = exact || (v[g] && !d[g] && !(D < -Bseg));
+            const float D = __fadd_rn(dm[g], stb[j + 32 * g]);
+            if (D > Bseg) dbits |= 1u << g;
+            if (!(fabsf(D) > Bseg)) amb |= 1u << g;               // inside the band, or NaN
         }
+        exact = (amb & vm) != 0u;
     }
     if (exact) {                                    // a pair inside the band (or thr out of range)
-#pragma unroll
-        for (int g = 0; g < G; ++g) d[g] = false;
+        dbits = 0;
         for (int r = 0; r < nk; ++r) {
             const float4 a = kb[r];
             const float sa = ypp_area(a);
 #pragma unroll
-            for (int g = 0; g < G; ++g) d[g] = d[g] || pair_exact(a, sa, c[g], thr, union_fma);
+            for (int g = 0; g < G; ++g)
+                if (pair_exact(a, sa, c[g], thr, union_fma)) dbits |= 1u << g;
         }
     }
-    u32 part = 0;
-#pragma unroll
-    for (int g = 0; g < G; ++g)
-        if (v[g] && d[g]) part |= 1u << (k + g);
-    return part;
+    return (dbits & vm) << k;
 }
 
 // 32-row tiles in score order.  Warp w owns rows 8w..8w+7 of every tile: it tests them against the
@@ -200,16 +191,18 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     u32 amax_bits = 0, cmax_bits = 0;   // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
         const float4 q = rank_box(p.ws, ibase, grank[i], trick, step);
-        const float ar = ypp_area(q);
+        const float ar = fabsf(ypp_area(q));
         sm.box[i] = q;
-        sm.area[i] = ar;
-        amax_bits = max(amax_bits, __float_as_uint(fabsf(ar)));
+        sm.tb[i] = __fmul_rn(-thr, ar);
+        amax_bits = max(amax_bits, __float_as_uint(ar));
         cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
                         max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
     }
     amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
     cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
     if (lane == 0) { sm.amax[w] = amax_bits; sm.cmax[w] = cmax_bits; }
+    // the last tile is filled up with dummies (never a valid column: marked dead below; never a live row)
+    for (int i = len + tid; i < ((len + 31) & ~31); i += YPP_NMSQ_THREADS) { sm.box[i] = YPP_DUMMY_BOX; sm.tb[i] = YPP_DUMMY_TA; }
     __syncthreads();
     // one decision band for the whole segment (NaN / inf areas make every compare fail -> exact path)
     float Bseg = 2.0f * YPP_PAIR_BAND *
@@ -220,43 +213,42 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const int cex = min(max(cexp, 67), 187);
     const float scale = __uint_as_float((u32)(252 - cex) << 23);
     const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cex + 2) << 23));
-    const float nthr = -thr;
     const int ntiles = (len + 31) >> 5;
     const u32 wmask = 0xffu << (8 * w);
-    u32 dead = 0;                 // bit k: column lane + 32k is suppressed (merged over the four warps)
+    // bit k: column lane + 32k is suppressed (merged over the four warps) or lies past the end of the segment
+    u32 dead = ((ntiles - 1) << 5) + lane >= len ? 1u << (ntiles - 1) : 0u;
     int total = 0;
     for (int T = 0; T < ntiles; ++T) {
         const int base = T << 5;
         const int j = base + lane;
-        const bool in_range = j < len;
-        const bool alive_l = in_range && !((dead >> T) & 1u);
+        const bool alive_l = !((dead >> T) & 1u);
         const u32 alive = __ballot_sync(YPP_FULL_MASK, alive_l);       // identical in all four warps
         if (alive == 0) continue;
         // ---- diagonal tile, column view: which of MY rows (i < lane, alive) suppress column lane
-        const float4 cb = sm.box[in_range ? j : base];
-        const float my_ta = __fmul_rn(nthr, fabsf(sm.area[in_range ? j : base]));
+        const float4 cb = sm.box[j];
+        const float my_ta = sm.tb[j];
         u32 in = 0;
         if (kFast) {
-            // my 8 rows, unconditionally (dead or out-of-range rows are masked out below)
+            // my 8 rows, unconditionally (dead rows and the dummies past the end are masked out below)
             float lo = INFINITY;
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
-                const int i = min(base + 8 * w + q, len - 1);
-                const float d = __fadd_rn(pair_g(sm.box[i], __fmul_rn(nthr, fabsf(sm.area[i])), cb, c1k, scale), my_ta);
+                const int i = base + 8 * w + q;
+                const float d = __fadd_rn(pair_g(sm.box[i], sm.tb[i], cb, c1k, scale), my_ta);
                 if (d > Bseg) in |= 1u << (8 * w + q);
                 lo = fminf(lo, fabsf(d));             // a NaN d is never a suppression: dropped
             }
             if (!(lo > Bseg)) {                       // some pair inside the band (or a NaN): exact pass
                 in = 0;
                 for (int q = 0; q < 8; ++q) {
-                    const int i = min(base + 8 * w + q, len - 1);
-                    if (pair_exact(sm.box[i], sm.area[i], cb, thr, union_fma)) in |= 1u << (8 * w + q);
+                    const int i = base + 8 * w + q;
+                    if (pair_exact(sm.box[i], ypp_area(sm.box[i]), cb, thr, union_fma)) in |= 1u << (8 * w + q);
                 }
             }
         } else {
             for (int q = 0; q < 8; ++q) {
-                const int i = min(base + 8 * w + q, len - 1);
-                if (pair_exact(sm.box[i], sm.area[i], cb, thr, union_fma)) in |= 1u << (8 * w + q);
+                const int i = base + 8 * w + q;
+                if (pair_exact(sm.box[i], ypp_area(sm.box[i]), cb, thr, union_fma)) in |= 1u << (8 * w + q);
             }
         }
         in &= alive & ((1u << lane) - 1u);            // only alive rows before me count
@@ -293,13 +285,13 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             const float* ka = sm.kta[w];
             int k = T + 1;
             for (; k + 4 <= ntiles; k += 4)
-                part |= sweep_groups<4, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
+                part |= sweep_groups<4, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
             if (k + 2 <= ntiles) {
-                part |= sweep_groups<2, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
+                part |= sweep_groups<2, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
                 k += 2;
             }
             if (k < ntiles)
-                part |= sweep_groups<1, kFast>(sm.box, sm.area, len, kb, ka, npad, nkw, k, dead, c1k, scale, nthr, Bseg, thr, union_fma);
+                part |= sweep_groups<1, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
         }
         reinterpret_cast<u32*>(&sm.dpart[lane])[w] = part;
         __syncthreads();

@@ -140,6 +140,44 @@ int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* w
                  float* det_rows, int row_width, int64_t det_capacity, int* det_total,
                  float img_idx_base, void* stream);
 
+/* ---- alternate semantics: the vendored Ultralytics non_max_suppression -----
+ * utils/general.py:640-731.  pred [B, n_boxes, 5+nc] rows cx,cy,w,h,obj,cls_0.. (already decoded);
+ * per image:  obj > conf_thr (:645)  ->  conf_j = cls_j * obj (:669)  ->  best class only: the first
+ * maximum, kept when conf > conf_thr (:679-680); multi_label: every (box, j) with conf_j > conf_thr in
+ * (box, j) order (:676-677)  ->  optional class filter (:683-684)  ->  the max_nms best by conf when
+ * more remain (:694-695; the reference's argsort is unstable, here ties keep (box, j) order)  ->
+ * torchvision.ops.nms on boxes + cls * max_wh (agnostic: + 0) (:698-700)  ->  the first max_det kept
+ * (:701-702).  labels (autolabelling) and merge-NMS (off in the reference) are not provided.
+ * Output rows are x1,y1,x2,y2,conf,cls (row_width 6) or img,x1,..,cls (7), image after image in NMS order.
+ * keep_idx holds box numbers (best class) or box * nc + j (multi_label).  The workspace is
+ * ypp_workspace_bytes(B, ypp_ultra_rows(n_boxes, nc, multi_label), nc). */
+typedef struct {
+    int nc, B;
+    float conf_thr;       /* strict compares, fp32 */
+    float iou_thr;        /* see ypp_effective_iou_thr */
+    int multi_label;      /* forced to 0 when nc == 1, as the reference does (:659) */
+    int agnostic;
+    int max_det;          /* <= 0: no limit */
+    int max_nms;          /* <= 0: no limit */
+    float max_wh;         /* 4096 in the reference (:656) */
+    const unsigned char* class_allow;   /* device [nc] 0/1, or NULL = every class (classes=None) */
+    int union_mode;       /* YPP_UNION_* */
+} ypp_ultra_cfg;
+
+/* rows per image the workspace must be sized for: n_boxes, or n_boxes * nc with multi_label */
+int64_t ypp_ultra_rows(int n_boxes, int nc, int multi_label);
+
+int ypp_nms_ultralytics(const ypp_ultra_cfg* cfg, const float* pred_BNC, int n_boxes, void* ws, size_t ws_bytes,
+                        int* cand_count, int* keep_count, int* keep_idx,
+                        float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+                        float img_idx_base, void* stream);
+
+/* decode_predictions of YOLO v1, utils/yolov1_utils.py:12-66: input [B, S*S*(5*num_boxes + nc)]
+ * (cell-major, per cell: nc class scores, then num_boxes x (conf, x, y, w, h)) -> out [B, S*S, 6]
+ * cx,cy,w,h,confidence,class with the box of the most confident predictor of each cell. */
+int ypp_decode_yolov1(const float* input, int B, int S, int nc, int num_boxes, float input_size,
+                      float* out_BS6, void* stream);
+
 /* ---- mAP side ------------------------------------------------------------------------ */
 
 /* get_target_boxes_for_map + the img_idx column (utils/yolo_utils.py:682-710,
@@ -166,6 +204,17 @@ int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, co
 
 /* box_iou, utils/metrics.py:233-255: xyxy [N,4] x [M,4] -> [N,M]. */
 int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream);
+
+/* ConfusionMatrix.process_batch, utils/metrics.py:122-160, for n_img images in one launch (the
+ * reference is called once per image):
+ *   det [K,6] x1,y1,x2,y2,conf,cls of all images, det_off [n_img+1] row offsets (det_off[n_img] = K)
+ *   lab [G,5] cls,x1,y1,x2,y2, lab_off [n_img+1]
+ *   matrix [(nc+1)*(nc+1)] int64, accumulated: matrix[predicted][true]; index nc = background
+ *   scratch: K * 8 bytes.  Class ids outside [0, nc) are skipped (the reference raises).
+ * Equal IoUs (unspecified in the reference: unstable argsort) go to the lower index. */
+int ypp_confusion_update(const float* det_K6, const int* det_off, const float* lab_G5, const int* lab_off, int n_img,
+                         int64_t K, int nc, float conf_thr, float iou_thr, void* scratch, size_t scratch_bytes,
+                         int64_t* matrix, void* stream);
 
 size_t ypp_map_workspace_bytes(int64_t G, int64_t K, int nc);
 

@@ -300,3 +300,133 @@ def pred_file_lines(boxes, class_name_list):
     o = r.shape[1] - 6
     return ["%s %s %d %d %d %d\n" % (class_name_list[int(r[k, o + 5])], format(float(r[k, o + 4])),
                                      v[k, 0], v[k, 1], v[k, 2], v[k, 3]) for k in range(r.shape[0])]
+
+
+# ---------------------------------------------------------------- alternate semantics
+def nms_xyxy(boxes, scores, iou_threshold, union_mode=UNION_SEPARATE, compare_in_double=None):
+    """torchvision.ops.nms on xyxy boxes: indices kept, score descending (stable)."""
+    boxes, scores = _f32(boxes), _f32(scores)
+    n = boxes.shape[0]
+    if compare_in_double is None:
+        compare_in_double = (union_mode == UNION_SEPARATE)
+    keep = np.empty(max(n, 1), dtype=np.int32)
+    k = lib().ypo_nms_xyxy(_fp(boxes), _fp(scores), n, effective_thr(iou_threshold, compare_in_double), union_mode, _ip(keep))
+    return keep[:k].copy()
+
+
+def non_max_suppression(prediction, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
+                        multi_label=False, max_det=300, max_nms=30000, max_wh=4096,
+                        union_mode=UNION_SEPARATE, compare_in_double=None, return_index=False):
+    """The vendored Ultralytics NMS, utils/general.py:640-731 (labels=() and merge=False as there).
+
+    prediction [B,n,5+nc] -> list of [k,6] xyxy,conf,cls per image.  With return_index also the row
+    number of every kept detection: box index, or box * nc + j with multi_label.  Where the
+    reference takes the max_nms best through an unstable argsort, ties keep their order here."""
+    p = _f32(prediction)
+    nc = p.shape[2] - 5
+    multi_label = bool(multi_label) and nc > 1                                   # :659
+    out, idx_out = [], []
+    two = np.float32(2)
+    for x in p:
+        sel = np.nonzero(x[:, 4] > np.float32(conf_thres))[0]                    # :645,665
+        x = x[sel].copy()
+        if x.shape[0]:
+            x[:, 5:] *= x[:, 4:5]                                                # :669
+        box = np.stack([x[:, 0] - x[:, 2] / two, x[:, 1] - x[:, 3] / two,
+                        x[:, 0] + x[:, 2] / two, x[:, 1] + x[:, 3] / two], 1) if x.shape[0] else np.zeros((0, 4), np.float32)
+        if multi_label:                                                          # :675-677
+            i, j = np.nonzero(x[:, 5:] > np.float32(conf_thres))
+            det = np.concatenate([box[i], x[i, j + 5, None], j[:, None].astype(np.float32)], 1)
+            rows = sel[i] * nc + j
+        else:                                                                    # :678-680
+            if x.shape[0]:
+                cls = np.empty(x.shape[0], np.int64)
+                conf = np.empty(x.shape[0], np.float32)
+                for r in range(x.shape[0]):          # first maximum, NaN maximal (torch.max)
+                    v = x[r, 5:]
+                    nan = np.isnan(v)
+                    cls[r] = int(np.argmax(nan)) if nan.any() else int(np.argmax(v))
+                    conf[r] = v[cls[r]]
+            else:
+                cls, conf = np.zeros(0, np.int64), np.zeros(0, np.float32)
+            m = conf > np.float32(conf_thres)
+            det = np.concatenate([box, conf[:, None], cls[:, None].astype(np.float32)], 1)[m]
+            rows = sel[m]
+        if classes is not None:                                                  # :683-684
+            m = np.isin(det[:, 5], np.asarray(classes, dtype=np.float32))
+            det, rows = det[m], rows[m]
+        n = det.shape[0]
+        if n > max_nms > 0:                                                      # :694-695
+            o = np.argsort(-det[:, 4], kind="stable")[:max_nms]
+            det, rows = det[o], rows[o]
+        c = det[:, 5:6] * np.float32(0 if agnostic else max_wh)                  # :698
+        keep = nms_xyxy(det[:, :4] + c, det[:, 4], iou_thres, union_mode, compare_in_double) if n else np.zeros(0, np.int32)
+        if max_det > 0:
+            keep = keep[:max_det]                                                # :701-702
+        out.append(det[keep].astype(np.float32).reshape(-1, 6))
+        idx_out.append(rows[keep].astype(np.int64))
+    return (out, idx_out) if return_index else out
+
+
+def decode_predictions_v1(inp, num_classes, num_boxes, input_size, S=7):
+    """YOLO v1 decode, utils/yolov1_utils.py:12-66: [B, S*S*(5*num_boxes+nc)] -> [B, S*S, 6]."""
+    x = _f32(inp).reshape(-1, S, S, num_boxes * 5 + num_classes)
+    pred = (np.float32(1) / (np.float32(1) + np.exp(-x, dtype=np.float32))).astype(np.float32)    # torch.sigmoid
+    B = pred.shape[0]
+    stride = np.float32(input_size / S)
+    conf = np.stack([pred[..., num_classes + 5 * k] for k in range(num_boxes)])          # [nb,B,S,S]
+    nan = np.isnan(conf)
+    best = np.where(nan.any(0), np.argmax(nan, 0), np.argmax(np.where(nan, -np.inf, conf), 0))
+    pbox = np.zeros((B, S, S, 4), np.float32)
+    pconf = np.zeros((B, S, S), np.float32)
+    for k in range(num_boxes):
+        hot = (best == k).astype(np.float32)
+        pbox = pbox + hot[..., None] * pred[..., num_classes + 1 + 5 * k: num_classes + 5 + 5 * k]
+        pconf = pconf + hot * pred[..., num_classes + 5 * k]
+    gx = np.arange(S, dtype=np.float32)[None, None, :]
+    gy = np.arange(S, dtype=np.float32)[None, :, None]
+    out = np.empty((B, S, S, 6), np.float32)
+    out[..., 0] = (pbox[..., 0] + gx) * stride
+    out[..., 1] = (pbox[..., 1] + gy) * stride
+    out[..., 2] = (pbox[..., 2] * np.float32(S)) * stride
+    out[..., 3] = (pbox[..., 3] * np.float32(S)) * stride
+    out[..., 4] = pconf
+    cls_p = pred[..., :num_classes]
+    cn = np.isnan(cls_p)
+    out[..., 5] = np.where(cn.any(-1), np.argmax(cn, -1), np.argmax(np.where(cn, -np.inf, cls_p), -1)).astype(np.float32)
+    return out.reshape(B, S * S, 6)
+
+
+def confusion_process_batch(matrix, detections, labels, nc, conf=0.25, iou_thres=0.45):
+    """ConfusionMatrix.process_batch, utils/metrics.py:122-160, accumulated into matrix [(nc+1),(nc+1)].
+
+    Restated without the two argsort/unique rounds (:140-145): every detection keeps the ground truth of
+    highest IoU above the threshold, then every ground truth keeps the detection of highest IoU among
+    those; equal IoUs (where the reference's unstable argsort decides) go to the lower index."""
+    det = _f32(detections).reshape(-1, 6)
+    lab = _f32(labels).reshape(-1, 5)
+    det = det[det[:, 4] > np.float32(conf)]                                      # :134
+    gt_cls = lab[:, 0].astype(np.int32)
+    det_cls = det[:, 5].astype(np.int32)
+    M, N = lab.shape[0], det.shape[0]
+    iou = box_iou(lab[:, 1:], det[:, :4]) if M and N else np.zeros((M, N), np.float32)     # :137
+    ok = iou > np.float32(iou_thres)
+    best_g = np.full(N, -1)
+    for d in range(N):
+        g = np.nonzero(ok[:, d])[0]
+        if g.size:
+            best_g[d] = g[np.argmax(iou[g, d])]
+    matched_det = np.zeros(N, bool)
+    for g in range(M):
+        d = np.nonzero(best_g == g)[0]
+        if d.size:
+            dm = d[np.argmax(iou[g, d])]
+            matrix[det_cls[dm], gt_cls[g]] += 1                                  # :151-152
+            matched_det[dm] = True
+        else:
+            matrix[nc, gt_cls[g]] += 1                                           # :153-154
+    if ok.any():                                                                 # :156 `if n:`
+        for d in range(N):
+            if not matched_det[d]:
+                matrix[det_cls[d], nc] += 1                                      # :157-159
+    return matrix

@@ -220,6 +220,67 @@ int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* w
                         img_idx_base, rows_BN6, true, true, (cudaStream_t)stream);
 }
 
+int64_t ypp_ultra_rows(int n_boxes, int nc, int multi_label)
+{
+    return (multi_label && nc > 1) ? (int64_t)n_boxes * nc : (int64_t)n_boxes;
+}
+
+int ypp_nms_ultralytics(const ypp_ultra_cfg* cfg, const float* pred_BNC, int n_boxes, void* ws, size_t ws_bytes,
+                        int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width,
+                        int64_t det_capacity, int* det_total, float img_idx_base, void* stream)
+{
+    if (!cfg || !pred_BNC) { ypp_set_error("nms_ultralytics: null pointer"); return YPP_E_BADARG; }
+    if (cfg->nc < 1 || cfg->nc > YPP_MAX_CLASSES || cfg->B < 1 || cfg->B > 65535 || n_boxes < 1) {
+        ypp_set_error("nms_ultralytics: nc=%d B=%d n_boxes=%d out of range", cfg->nc, cfg->B, n_boxes); return YPP_E_BADARG;
+    }
+    if (cfg->union_mode < 0 || cfg->union_mode > 1) { ypp_set_error("bad mode enum"); return YPP_E_BADARG; }
+    if (!(cfg->max_wh >= 0.0f)) { ypp_set_error("nms_ultralytics: max_wh must be >= 0"); return YPP_E_BADARG; }
+    if (det_rows && row_width != 6 && row_width != 7) { ypp_set_error("row_width must be 6 or 7"); return YPP_E_BADARG; }
+    const int multi = (cfg->multi_label && cfg->nc > 1) ? 1 : 0;                 // multi_label &= nc > 1
+    const int64_t rows = ypp_ultra_rows(n_boxes, cfg->nc, multi);
+    // the sort key holds 20 bits of row number; the long-segment kernel keeps one removed-bit per row in shared memory
+    if (rows > YPP_MAX_BOXES) { ypp_set_error("nms_ultralytics: %lld rows per image > %d", (long long)rows, YPP_MAX_BOXES); return YPP_E_UNSUPPORTED; }
+    const int N = (int)rows;
+    YppWs w;
+    int rc = bind_ws(cfg->B, N, cfg->nc, ws, ws_bytes, &w);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = ypp_launch_pred_compact(pred_BNC, cfg->B, n_boxes, cfg->nc, cfg->conf_thr, multi, cfg->class_allow, w, N, st);
+    if (rc) return rc;
+    YppOrgParams o;
+    memset(&o, 0, sizeof(o));
+    o.ws = w; o.B = cfg->B; o.N = N; o.nc = cfg->nc;
+    o.offset_mode = YPP_OFFSET_TRICK; o.union_mode = cfg->union_mode; o.iou_thr = cfg->iou_thr;
+    o.step_mode = 1;
+    o.fixed_step = cfg->agnostic ? 0.0f : cfg->max_wh;       // c = x[:, 5:6] * (0 if agnostic else max_wh)
+    o.max_cand = cfg->max_nms > 0 ? cfg->max_nms : 0;
+    rc = ypp_launch_organise(o, st);
+    if (rc) return rc;
+    YppNmsParams n;
+    memset(&n, 0, sizeof(n));
+    n.ws = w; n.B = cfg->B; n.N = N; n.nc = cfg->nc; n.iou_thr = cfg->iou_thr; n.union_mode = cfg->union_mode;
+    rc = ypp_launch_nms(n, st);
+    if (rc) return rc;
+    YppGatherParams g;
+    memset(&g, 0, sizeof(g));
+    g.ws = w; g.B = cfg->B; g.N = N;
+    g.cand_count_out = cand_count; g.keep_count_out = keep_count; g.keep_idx = keep_idx;
+    g.det_rows = det_rows; g.row_width = row_width; g.det_capacity = det_capacity; g.det_total = det_total;
+    g.img_idx_base = img_idx_base;
+    g.max_det = cfg->max_det > 0 ? cfg->max_det : 0;
+    g.xyxy_out = 1;
+    return ypp_launch_gather(g, st);
+}
+
+int ypp_decode_yolov1(const float* input, int B, int S, int nc, int num_boxes, float input_size, float* out_BS6, void* stream)
+{
+    if (!input || !out_BS6) { ypp_set_error("decode_yolov1: null pointer"); return YPP_E_BADARG; }
+    if (B < 1 || S < 1 || nc < 1 || num_boxes < 1 || (int64_t)B * S * S > 0x7fffffffLL) {
+        ypp_set_error("decode_yolov1: B=%d S=%d nc=%d num_boxes=%d out of range", B, S, nc, num_boxes); return YPP_E_BADARG;
+    }
+    return ypp_launch_decode_yolov1(input, B, S, nc, num_boxes, input_size, out_BS6, (cudaStream_t)stream);
+}
+
 int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, float img_idx_base, float* out_G7,
                     int* gt_count, void* stream)
 {
@@ -238,6 +299,20 @@ int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, co
     if (mode == YPP_WRITER_COCO && (!scale_xy || n_img <= 0)) { ypp_set_error("detection_ints: COCO mode needs scale_xy[n_img,2]"); return YPP_E_BADARG; }
     if ((K + 255) / 256 > 0x7fffffffLL) { ypp_set_error("detection_ints: K too large"); return YPP_E_UNSUPPORTED; }
     return ypp_launch_detection_ints(rows, (long long)K, row_width, mode, scale_xy, n_img, img_idx_base, out_K4, (cudaStream_t)stream);
+}
+
+int ypp_confusion_update(const float* det_K6, const int* det_off, const float* lab_G5, const int* lab_off, int n_img,
+                         int64_t K, int nc, float conf_thr, float iou_thr, void* scratch, size_t scratch_bytes,
+                         int64_t* matrix, void* stream)
+{
+    if (n_img < 0 || K < 0 || nc < 1) { ypp_set_error("confusion_update: bad size"); return YPP_E_BADARG; }
+    if (n_img == 0) return YPP_OK;
+    if (!det_off || !lab_off || !matrix) { ypp_set_error("confusion_update: null pointer"); return YPP_E_BADARG; }
+    if (K > 0 && (!det_K6 || !scratch || scratch_bytes < (size_t)K * 8)) {
+        ypp_set_error("confusion_update: scratch %zu bytes < %lld", scratch_bytes, (long long)K * 8); return YPP_E_WORKSPACE;
+    }
+    return ypp_launch_confusion(det_K6, det_off, lab_G5, lab_off, n_img, nc, conf_thr, iou_thr, (int*)scratch,
+                                (float*)scratch + K, (unsigned long long*)matrix, (cudaStream_t)stream);
 }
 
 int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream)

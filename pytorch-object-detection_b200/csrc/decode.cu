@@ -416,6 +416,88 @@ ypp_rows_compact_kernel(const float* __restrict__ rows, int N, float conf, YppWs
     slot_store(ws, N, b, slot, nslots, slot << 5, pass, box, score, cls, n);
 }
 
+// ---- compaction from Ultralytics-style predictions [B, n, 5+nc] (utils/general.py:640-684) ----
+// One thread per row of the workspace: a box (best class only) or a (box, class) pair (multi_label;
+// row = box * nc + j, which is the order nonzero() lists the pairs in).  A row's box is stored under
+// its own row number, so the sort / NMS / gather kernels run unchanged on n * nc "boxes".
+template <bool kMulti>
+__global__ void __launch_bounds__(YPP_DECODE_THREADS)
+ypp_pred_compact_kernel(const float* __restrict__ pred, int n_boxes, int nc, float conf,
+                        const unsigned char* __restrict__ allow, YppWs ws, int n_rows)
+{
+    ypp_grid_wait();
+    const int b = blockIdx.y;
+    const int n = blockIdx.x * YPP_DECODE_THREADS + threadIdx.x;
+    const int slot = n >> 5;
+    const int nslots = (int)gridDim.x * (YPP_DECODE_THREADS / 32);
+    const int C = 5 + nc;
+    bool pass = false;
+    float4 box = make_float4(0.f, 0.f, 0.f, 0.f);
+    float score = 0.f;
+    int cls = 0;
+    if (n < n_rows) {
+        const int i = kMulti ? n / nc : n;
+        const float* r = pred + ((size_t)b * n_boxes + i) * C;
+        const float obj = __ldg(r + 4);
+        if (obj > conf) {                                        // xc = prediction[..., 4] > conf_thres
+            if (kMulti) {
+                cls = n - i * nc;
+                score = __fmul_rn(__ldg(r + 5 + cls), obj);      // x[:, 5:] *= x[:, 4:5]
+            } else {
+                // x[:, 5:].max(1): the first maximum; a NaN is maximal (and then fails the threshold)
+                float best = __fmul_rn(__ldg(r + 5), obj);
+                for (int c = 1; c < nc; ++c) {
+                    const float v = __fmul_rn(__ldg(r + 5 + c), obj);
+                    if (v > best || (v != v && best == best)) { best = v; cls = c; }
+                }
+                score = best;
+            }
+            pass = score > conf && (allow == nullptr || allow[cls] != 0);
+            if (pass) box = make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+        }
+    }
+    slot_store(ws, n_rows, b, slot, nslots, slot << 5, pass, box, score, cls, n);
+}
+
+// ---- YOLO v1 decode (utils/yolov1_utils.py:12-66): one thread per grid cell ------------------
+__global__ void __launch_bounds__(128)
+ypp_decode_yolov1_kernel(const float* __restrict__ in, int cells_total, int S, int nc, int nb, float stride_w, float stride_h,
+                         float* __restrict__ out)
+{
+    const int t = blockIdx.x * 128 + threadIdx.x;
+    if (t >= cells_total) return;
+    const int cell = t % (S * S), gy = cell / S, gx = cell - gy * S;
+    const float* r = in + (size_t)t * (nc + 5 * nb);
+    // best predictor: torch.argmax over the confidences (first maximum, NaN maximal)
+    int k = 0;
+    float best = ypp_sigmoid(__ldg(r + nc));
+    for (int q = 1; q < nb; ++q) {
+        const float v = ypp_sigmoid(__ldg(r + nc + 5 * q));
+        if (v > best || (v != v && best == best)) { best = v; k = q; }
+    }
+    // sum over predictors of one_hot * value (:43-48): the selected value plus zeros, NaN where any is NaN
+    float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int q = 0; q < nb; ++q) {
+        const float sel = q == k ? 1.0f : 0.0f;
+#pragma unroll
+        for (int e = 0; e < 5; ++e) acc[e] = __fadd_rn(acc[e], __fmul_rn(sel, ypp_sigmoid(__ldg(r + nc + 5 * q + e))));
+    }
+    // class: argmax of the sigmoids (saturation can tie values whose logits differ)
+    int cls = 0;
+    float cb = ypp_sigmoid(__ldg(r));
+    for (int c = 1; c < nc; ++c) {
+        const float v = ypp_sigmoid(__ldg(r + c));
+        if (v > cb || (v != v && cb == cb)) { cb = v; cls = c; }
+    }
+    float* o = out + (size_t)t * 6;
+    o[0] = __fmul_rn(__fadd_rn(acc[1], (float)gx), stride_w);
+    o[1] = __fmul_rn(__fadd_rn(acc[2], (float)gy), stride_h);
+    o[2] = __fmul_rn(__fmul_rn(acc[3], (float)S), stride_w);
+    o[3] = __fmul_rn(__fmul_rn(acc[4], (float)S), stride_h);
+    o[4] = acc[0];
+    o[5] = (float)cls;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------- host launchers
@@ -470,4 +552,24 @@ int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const Y
     ypp_launch_chain(0, ypp_rows_compact_kernel, grid, dim3(YPP_DECODE_THREADS), 0, st, rows, N, conf, ws);
     ypp_count_launch(1);
     return ypp_check_launch("rows_compact");
+}
+
+int ypp_launch_pred_compact(const float* pred, int B, int n_boxes, int nc, float conf, int multi_label,
+                            const unsigned char* class_allow, const YppWs& ws, int n_rows, cudaStream_t st)
+{
+    dim3 grid((n_rows + YPP_TILE_BOXES - 1) / YPP_TILE_BOXES, B);
+    if (multi_label) ypp_launch_chain(0, ypp_pred_compact_kernel<true>, grid, dim3(YPP_DECODE_THREADS), 0, st, pred, n_boxes, nc, conf, class_allow, ws, n_rows);
+    else             ypp_launch_chain(0, ypp_pred_compact_kernel<false>, grid, dim3(YPP_DECODE_THREADS), 0, st, pred, n_boxes, nc, conf, class_allow, ws, n_rows);
+    ypp_count_launch(1);
+    return ypp_check_launch("pred_compact");
+}
+
+int ypp_launch_decode_yolov1(const float* input, int B, int S, int nc, int num_boxes, float input_size, float* out, cudaStream_t st)
+{
+    const int cells = B * S * S;
+    // stride = FloatTensor([input_size / layer_w, input_size / layer_h] * 2): Python doubles rounded to fp32
+    const float sw = (float)((double)input_size / (double)S), sh = sw;
+    ypp_decode_yolov1_kernel<<<(cells + 127) / 128, 128, 0, st>>>(input, cells, S, nc, num_boxes, sw, sh, out);
+    ypp_count_launch(1);
+    return ypp_check_launch("decode_yolov1");
 }

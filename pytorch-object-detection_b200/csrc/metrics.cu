@@ -418,6 +418,75 @@ ypp_detection_ints_kernel(const float* __restrict__ rows, long long K, int row_w
     reinterpret_cast<int4*>(out)[k] = v;
 }
 
+// ------------------------------------------------------------------ ConfusionMatrix.process_batch
+// utils/metrics.py:122-160, one CTA per image.  The reference builds the (gt, det, iou) triples with
+// iou > thr, sorts them by iou, keeps per detection its best triple, sorts again and keeps per ground
+// truth its best remaining triple.  Restated without the sorts: g*(d) = the ground truth of highest
+// iou with d (above thr), d*(g) = the detection of highest iou among those with g*(d) = g.  Ties (the
+// reference's argsort is unstable there) go to the lower index.  Then, as the reference does:
+// matched gt -> matrix[cls(d*)][cls(g)], unmatched gt -> matrix[nc][cls(g)], and ONLY IF the image has
+// any triple at all, every unmatched detection -> matrix[cls(d)][nc]  (:150-157).
+#define YPP_CM_THREADS 256
+__global__ void __launch_bounds__(YPP_CM_THREADS)
+ypp_confusion_kernel(const float* __restrict__ det, const int* __restrict__ det_off, const float* __restrict__ lab,
+                     const int* __restrict__ lab_off, int nc, float conf, float thr, int* __restrict__ bestg,
+                     float* __restrict__ bestiou, unsigned long long* __restrict__ matrix)
+{
+    __shared__ int any_match;
+    const int img = blockIdx.x, tid = threadIdx.x;
+    const int d0 = det_off[img], nd = det_off[img + 1] - d0;
+    const int l0 = lab_off[img], nl = lab_off[img + 1] - l0;
+    if (tid == 0) any_match = 0;
+    __syncthreads();
+    const int W = nc + 1;
+    for (int d = tid; d < nd; d += YPP_CM_THREADS) {
+        const float* r = det + (size_t)(d0 + d) * 6;
+        int g_best = -2;                                        // -2: below the confidence threshold (:134)
+        float i_best = 0.0f;
+        if (r[4] > conf) {
+            g_best = -1;
+            const float4 q = make_float4(r[0], r[1], r[2], r[3]);
+            const float s2 = __fmul_rn(__fsub_rn(q.z, q.x), __fsub_rn(q.w, q.y));
+            for (int g = 0; g < nl; ++g) {
+                const float* l = lab + (size_t)(l0 + g) * 5;
+                const float4 p = make_float4(l[1], l[2], l[3], l[4]);
+                const float s1 = __fmul_rn(__fsub_rn(p.z, p.x), __fsub_rn(p.w, p.y));
+                const float w = fmaxf(__fsub_rn(fminf(p.z, q.z), fmaxf(p.x, q.x)), 0.0f);
+                const float h = fmaxf(__fsub_rn(fminf(p.w, q.w), fmaxf(p.y, q.y)), 0.0f);
+                const float inter = __fmul_rn(w, h);
+                const float iou = __fdiv_rn(inter, __fsub_rn(__fadd_rn(s1, s2), inter));      // box_iou(labels, detections)
+                if (iou > thr && (g_best < 0 || iou > i_best)) { g_best = g; i_best = iou; }
+            }
+            if (g_best >= 0) any_match = 1;
+        }
+        bestg[d0 + d] = g_best;
+        bestiou[d0 + d] = i_best;
+    }
+    __syncthreads();
+    for (int g = tid; g < nl; g += YPP_CM_THREADS) {
+        int dm = -1;
+        float im = 0.0f;
+        for (int d = 0; d < nd; ++d)
+            if (bestg[d0 + d] == g) { const float v = bestiou[d0 + d]; if (dm < 0 || v > im) { dm = d; im = v; } }
+        const int gc = (int)lab[(size_t)(l0 + g) * 5];
+        if (gc < 0 || gc >= nc) continue;
+        if (dm >= 0) {
+            bestg[d0 + dm] = -3;                                 // matched: no longer equal to any g
+            const int dc = (int)det[(size_t)(d0 + dm) * 6 + 5];
+            if (dc >= 0 && dc < nc) atomicAdd(matrix + (size_t)dc * W + gc, 1ull);
+        } else {
+            atomicAdd(matrix + (size_t)nc * W + gc, 1ull);
+        }
+    }
+    __syncthreads();
+    if (!any_match) return;
+    for (int d = tid; d < nd; d += YPP_CM_THREADS) {
+        if (bestg[d0 + d] < -1) continue;                        // filtered out, or matched
+        const int dc = (int)det[(size_t)(d0 + d) * 6 + 5];
+        if (dc >= 0 && dc < nc) atomicAdd(matrix + (size_t)dc * W + nc, 1ull);
+    }
+}
+
 }  // namespace
 
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
@@ -477,4 +546,12 @@ int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int
     ypp_detection_ints_kernel<<<grid, 256, 0, st>>>(rows, K, row_width, mode, scale_xy, n_img, img_base, out);
     ypp_count_launch(1);
     return ypp_check_launch("detection_ints");
+}
+
+int ypp_launch_confusion(const float* det, const int* det_off, const float* lab, const int* lab_off, int n_img, int nc,
+                         float conf, float thr, int* bestg, float* bestiou, unsigned long long* matrix, cudaStream_t st)
+{
+    ypp_confusion_kernel<<<n_img, YPP_CM_THREADS, 0, st>>>(det, det_off, lab, lab_off, nc, conf, thr, bestg, bestiou, matrix);
+    ypp_count_launch(1);
+    return ypp_check_launch("confusion");
 }

@@ -494,16 +494,17 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     const int N = p.N;
     const int n = min(p.ws.cand_count[b], N);
     const int r_begin = blockIdx.x * YPP_GATHER_CHUNK;
+    const int cap = p.max_det > 0 ? p.max_det : 0x7fffffff;          // rows an image may contribute
     const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && p.det_total != nullptr;
     if (blockIdx.x == 0 && tid == 0) {
         if (p.cand_count_out) p.cand_count_out[b] = n;
-        if (p.keep_count_out) p.keep_count_out[b] = p.ws.keep_count[b];
+        if (p.keep_count_out) p.keep_count_out[b] = min(p.ws.keep_count[b], cap);
     }
     if (r_begin >= n && !writes_total) return;
     // rows of the images before this one, and kept flags of this image before my chunk
     const unsigned char* kf = p.ws.keepflag + (size_t)b * N;
     long long img_part = 0;
-    for (int i = tid; i < b; i += YPP_GATHER_THREADS) img_part += p.ws.keep_count[i];
+    for (int i = tid; i < b; i += YPP_GATHER_THREADS) img_part += min(p.ws.keep_count[i], cap);
     int pre_part = 0;
     {
         const int pre = min(r_begin, n);
@@ -527,8 +528,8 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     int pre_rows = 0;
 #pragma unroll
     for (int w = 0; w < YPP_GATHER_THREADS / 32; ++w) { img_rows += red_img[w]; pre_rows += red_pre[w]; }
-    if (writes_total && tid == 0) *p.det_total = (int)(img_rows + p.ws.keep_count[b]);
-    if (r_begin >= n) return;
+    if (writes_total && tid == 0) *p.det_total = (int)(img_rows + min(p.ws.keep_count[b], cap));
+    if (r_begin >= n || pre_rows >= cap) return;
     const u64* keys = p.ws.skeys + (size_t)b * N;
     const float4* box = p.ws.box + (size_t)b * N;
     const float img = p.img_idx_base + (float)b;
@@ -562,8 +563,10 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         }
         pos[u] = running + before + __popc(m[u] & ((1u << lane) - 1u));      // position inside the image
         running += total;
+        f[u] = f[u] && pos[u] < cap;                                         // max_det: later ranks are dropped
         k[u] = f[u] ? keys[r_begin + u * YPP_GATHER_THREADS + tid] : 0ull;
     }
+    running = min(running, cap);
     float4 bx[YPP_GATHER_ROUNDS];
     float cls[YPP_GATHER_ROUNDS];
     const bool want_rows = p.det_rows != nullptr;
@@ -574,6 +577,7 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         if (p.keep_idx) p.keep_idx[(size_t)b * N + pos[u]] = idx;
         if (want_rows) {
             bx[u] = box[idx];
+            if (p.xyxy_out) bx[u] = ypp_xyxy(bx[u]);
             cls[u] = (float)ypp_key_cls(k[u]);
             if (p.src_rows) cls[u] = p.src_rows[((size_t)b * N + idx) * 6 + 5];
         }

@@ -327,7 +327,16 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     if (p.offset_mode == YPP_OFFSET_AUTO_CPU) trick = 4LL * n <= 4000;
     if (p.offset_mode == YPP_OFFSET_AUTO_CUDA) trick = 4LL * n <= 100000;
     const float M = ypp_dec(hd->maxc);
-    const float step = __fadd_rn(M, 1.0f);                 // max_coordinate + 1
+    float step = __fadd_rn(M, 1.0f);                       // max_coordinate + 1
+    // fixed class offsets (boxes + cls * max_wh, one torchvision.ops.nms over everything): the class bands
+    // are disjoint as long as no coordinate exceeds step - 1, exactly the situation the detector below
+    // was built for; otherwise (or step 0 = class-agnostic, or NaN) the image is one segment
+    bool one_segment = false;
+    if (p.step_mode) {
+        trick = true;
+        step = p.fixed_step;
+        one_segment = !(M <= __fadd_rn(step, -1.0f)) || !(step > 0.0f);
+    }
     DetGeom dg;
     dg.step = step;
     dg.x1min = -ypp_dec(hd->nminx1);
@@ -335,14 +344,14 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     dg.lim = -1.0f + dg.slack;
     // no detector when offsets are not finite (every shifted IoU is NaN on both paths) or when no
     // box reaches x1 < -1 (nothing can be shifted onto the previous class band)
-    dg.on = trick && nc > 1 && (fabsf(M) <= 3.0e38f) && dg.x1min < dg.lim;
+    dg.on = trick && nc > 1 && !one_segment && (fabsf(M) <= 3.0e38f) && dg.x1min < dg.lim;
     {
         const float range = dg.lim - dg.x1min;
         dg.inv_w = (range > 64.0f * 4.0f * dg.slack) ? (float)YPP_DET_BINS / range : 0.0f;
     }
     const bool detect = dg.on;
     const float4* gbox = p.ws.box + (size_t)b * N;
-    if (trick && nc > 1 && !(step > 0.0f) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
+    if (trick && nc > 1 && (one_segment || !(step > 0.0f)) && tid == 0) hd->flagged = 1;   // degenerate offsets: be exact
 
     // ---- 3. detector sweeps, BEFORE the sort: the keys are still in box-index order, so the box reads
     // are (nearly) sequential instead of a random gather
@@ -540,7 +549,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     __syncthreads();
     for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
     __syncthreads();
-    const int r_begin = warp * L, r_end = min(n, r_begin + L);
+    const int n_in = p.max_cand > 0 ? min(n, p.max_cand) : n;        // ranks past max_cand join no segment: never kept
+    const int r_begin = warp * L, r_end = min(n_in, r_begin + L);
     const int cbits = 32 - __clz(max(nc - 1, 1));            // bits of a class id
     int* my = table + warp * nc;
     for (int r0 = r_begin; r0 < r_end; r0 += 32) {

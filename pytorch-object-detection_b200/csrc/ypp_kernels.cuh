@@ -33,6 +33,9 @@ struct YppOrgParams {
     float iou_thr;
     int keys_in_smem;      // key buffers of the sort held in shared memory: 2 (both), 1 (the first), 0
     int table_ints;        // 32 * nc
+    int step_mode;         // 0: class offset step = max coordinate + 1 (torchvision batched_nms); 1: fixed_step, always shifted
+    float fixed_step;      //    (Ultralytics: boxes + cls * max_wh, utils/general.py:698-699; 0 = agnostic)
+    int max_cand;          // > 0: only the best max_cand candidates of an image enter NMS (max_nms, utils/general.py:694-695)
 };
 
 struct YppNmsParams {
@@ -54,11 +57,16 @@ struct YppGatherParams {
     int* det_total;
     float img_idx_base;
     const float* src_rows;   // optional [B,N,6]: copy the class column verbatim (nms_rows entry)
+    int max_det;             // > 0: at most this many rows per image (utils/general.py:701-702)
+    int xyxy_out;            // rows carry x1,y1,x2,y2 instead of cx,cy,w,h
 };
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st);
 int ypp_launch_decode_dense(const YppDecodeParams& p, int B, float* out, cudaStream_t st);
 int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const YppWs& ws, cudaStream_t st);
+int ypp_launch_pred_compact(const float* pred, int B, int n_boxes, int nc, float conf, int multi_label,
+                            const unsigned char* class_allow, const YppWs& ws, int n_rows, cudaStream_t st);
+int ypp_launch_decode_yolov1(const float* input, int B, int S, int nc, int num_boxes, float input_size, float* out, cudaStream_t st);
 int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st);
 int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st);
 int ypp_launch_gather(const YppGatherParams& p, cudaStream_t st);
@@ -66,6 +74,8 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints);
 
 int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int mode, const float* scale_xy, int n_img,
                                float img_base, int* out, cudaStream_t st);
+int ypp_launch_confusion(const float* det, const int* det_off, const float* lab, const int* lab_off, int n_img, int nc,
+                         float conf, float thr, int* bestg, float* bestiou, unsigned long long* matrix, cudaStream_t st);
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
                            float* out, int* gt_count, cudaStream_t st);
 int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);

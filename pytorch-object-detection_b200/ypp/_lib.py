@@ -37,12 +37,20 @@ class YppCfg(ctypes.Structure):
                 ("offset_mode", ctypes.c_int), ("union_mode", ctypes.c_int)]
 
 
+class YppUltraCfg(ctypes.Structure):
+    _fields_ = [("nc", ctypes.c_int), ("B", ctypes.c_int), ("conf_thr", ctypes.c_float), ("iou_thr", ctypes.c_float),
+                ("multi_label", ctypes.c_int), ("agnostic", ctypes.c_int), ("max_det", ctypes.c_int),
+                ("max_nms", ctypes.c_int), ("max_wh", ctypes.c_float), ("class_allow", ctypes.c_void_p),
+                ("union_mode", ctypes.c_int)]
+
+
 WRITER_MODES = {"pred_file": 0, "coco": 1}
 
 EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "ypp_decode_compact",
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
-           "ypp_detection_ints", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
+           "ypp_confusion_update", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -97,6 +105,11 @@ def lib():
     L.ypp_target_rows.argtypes = [vp, ci, ci, cf, cf, vp, vp, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]
+    L.ypp_ultra_rows.argtypes = [ci, ci, ci]
+    L.ypp_ultra_rows.restype = i64
+    L.ypp_nms_ultralytics.argtypes = [ctypes.POINTER(YppUltraCfg), vp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
+    L.ypp_decode_yolov1.argtypes = [vp, ci, ci, ci, ci, cf, vp, vp]
+    L.ypp_confusion_update.argtypes = [vp, vp, vp, vp, ci, i64, ci, cf, cf, vp, ctypes.c_size_t, vp, vp]
     L.ypp_map_workspace_bytes.argtypes = [i64, i64, ci]
     L.ypp_map_workspace_bytes.restype = ctypes.c_size_t
     L.ypp_map_match.argtypes = [vp, i64, vp, i64, ci, cf, vp, ctypes.c_size_t, vp, vp, vp, vp]
@@ -106,7 +119,7 @@ def lib():
     L.ypp_launch_count.restype = i64
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
                  "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match",
-                 "ypp_detection_ints"):
+                 "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update"):
         getattr(L, name).restype = ci
     _lib = L
     return L

@@ -335,5 +335,94 @@ def detection_ints(rows: torch.Tensor, mode="pred_file", scale_xy: Optional[torc
     return out
 
 
+# ------------------------------------------------------------------------------------ alternate semantics
+
+def nms_ultralytics(prediction: torch.Tensor, conf_thres=0.25, iou_thres=0.45, classes=None, agnostic=False,
+                    multi_label=False, max_det=300, max_nms=30000, max_wh=4096, union_mode="fma",
+                    compare_in_double=None, row_width=6, img_idx_base=0, want_keep_idx=False) -> PostResult:
+    """The vendored Ultralytics non_max_suppression (utils/general.py:640-731) for a whole batch:
+    prediction [B, n, 5+nc] -> packed rows x1,y1,x2,y2,conf,cls.  union_mode "fma" = what the reference
+    computes on a CUDA device (torchvision's CUDA nms), "separate" = on the CPU."""
+    from ._lib import YppUltraCfg
+    if prediction.dim() != 3 or prediction.shape[2] < 6:
+        raise ValueError("prediction must be [B, n, 5+nc]")
+    if not prediction.is_cuda or prediction.dtype != torch.float32:
+        raise ValueError("prediction must be a float32 CUDA tensor (ypp has no CPU path)")
+    if not (0 <= conf_thres <= 1) or not (0 <= iou_thres <= 1):         # the reference's asserts (:648-649)
+        raise AssertionError("conf_thres and iou_thres must be in [0, 1]")
+    pred = prediction.contiguous()
+    B, n, C = pred.shape
+    nc = C - 5
+    dev = pred.device
+    um = _lib.UNION_MODES[union_mode] if isinstance(union_mode, str) else int(union_mode)
+    if compare_in_double is None:
+        compare_in_double = um == _lib.UNION_SEPARATE
+    L = lib()
+    rows = int(L.ypp_ultra_rows(n, nc, int(bool(multi_label)))) if n else 0
+    z = torch.zeros
+    if B == 0 or n == 0:
+        return PostResult(z((0, row_width), device=dev), z(1, dtype=torch.int32, device=dev),
+                          z(B, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                          z((B, 0), dtype=torch.int32, device=dev) if want_keep_idx else None, 0)
+    allow = None
+    if classes is not None:
+        allow = torch.zeros(nc, dtype=torch.uint8)
+        for c in classes:
+            if float(c) == int(c) and 0 <= int(c) < nc:
+                allow[int(c)] = 1
+        allow = allow.to(dev)
+    cfg = YppUltraCfg(nc, B, float(conf_thres), float(L.ypp_effective_iou_thr(float(iou_thres), int(bool(compare_in_double)))),
+                      int(bool(multi_label)), int(bool(agnostic)), int(max_det), int(max_nms), float(max_wh),
+                      None if allow is None else allow.data_ptr(), um)
+    per_img = min(rows, int(max_det)) if max_det > 0 else rows
+    res = PostResult(det_rows=torch.empty((B * per_img, row_width), dtype=torch.float32, device=dev),
+                     det_total=torch.empty(1, dtype=torch.int32, device=dev),
+                     keep_count=torch.empty(B, dtype=torch.int32, device=dev),
+                     cand_count=torch.empty(B, dtype=torch.int32, device=dev),
+                     keep_idx=torch.empty((B, rows), dtype=torch.int32, device=dev) if want_keep_idx else None,
+                     n_boxes=rows)
+    ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, "post")
+    with torch.cuda.device(dev):
+        check(L.ypp_nms_ultralytics(ctypes.byref(cfg), _ptr(pred), n, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), row_width,
+                                    res.det_rows.shape[0], _ptr(res.det_total), float(img_idx_base), _stream()))
+    res._keepalive = allow
+    return res
+
+
+def decode_yolov1(inp: torch.Tensor, num_classes, num_boxes, input_size, S=7) -> torch.Tensor:
+    """utils/yolov1_utils.py:12-66: [B, S*S*(5*num_boxes+nc)] -> [B, S*S, 6] cx,cy,w,h,confidence,class."""
+    if not inp.is_cuda or inp.dtype != torch.float32:
+        raise ValueError("input must be a float32 CUDA tensor (ypp has no CPU path)")
+    per = S * S * (5 * int(num_boxes) + int(num_classes))
+    x = inp.contiguous().view(-1, per)
+    B = x.shape[0]
+    out = torch.empty((B, S * S, 6), dtype=torch.float32, device=x.device)
+    if B:
+        with torch.cuda.device(x.device):
+            check(lib().ypp_decode_yolov1(_ptr(x), B, S, int(num_classes), int(num_boxes), float(input_size), _ptr(out), _stream()))
+    return out
+
+
+def confusion_update(matrix: torch.Tensor, detections: torch.Tensor, det_off: torch.Tensor, labels: torch.Tensor,
+                     lab_off: torch.Tensor, nc, conf=0.25, iou_thres=0.45) -> torch.Tensor:
+    """ConfusionMatrix.process_batch (utils/metrics.py:122-160) for len(det_off)-1 images in one launch.
+    matrix int64 [(nc+1),(nc+1)] on the device, accumulated in place."""
+    det = detections.to(torch.float32).contiguous()
+    lab = labels.to(torch.float32).contiguous()
+    dev = matrix.device
+    if matrix.dtype != torch.int64 or not matrix.is_cuda or not matrix.is_contiguous() or matrix.numel() != (nc + 1) * (nc + 1):
+        raise ValueError("matrix must be a contiguous int64 CUDA tensor [(nc+1),(nc+1)]")
+    d_off = det_off.to(device=dev, dtype=torch.int32).contiguous()
+    l_off = lab_off.to(device=dev, dtype=torch.int32).contiguous()
+    n_img = d_off.numel() - 1
+    K = det.shape[0]
+    scratch = _workspace(max(K, 1) * 8, dev, "cm")
+    with torch.cuda.device(dev):
+        check(lib().ypp_confusion_update(_ptr(det), _ptr(d_off), _ptr(lab), _ptr(l_off), n_img, K, int(nc), float(conf),
+                                         float(iou_thres), _ptr(scratch), scratch.numel(), _ptr(matrix), _stream()))
+    return matrix
+
+
 def launch_count(reset=False) -> int:
     return int(lib().ypp_launch_count(int(bool(reset))))

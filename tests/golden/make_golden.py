@@ -414,6 +414,112 @@ def case_writers():
                         names=np.array(names), cat_ids=np.array([cats[nm] for nm in names]))
 
 
+ULTRA_VARIANTS = [dict(), dict(multi_label=True), dict(agnostic=True), dict(classes=[1, 3]),
+                  dict(multi_label=True, max_det=9), dict(conf_thres=0.6, iou_thres=0.3),
+                  dict(multi_label=True, agnostic=True, classes=[0, 2, 4]), dict(max_det=5000),
+                  dict(multi_label=True, max_det=5000, conf_thres=0.1)]
+
+
+def ultra_pred(seed, B, n, nc, far=False):
+    """[B,n,5+nc] rows like the ones a YOLOv5 Detect layer emits; `far` adds boxes whose corners leave
+    [0, max_wh): classes then share coordinates after the + cls * 4096 shift."""
+    rng = np.random.RandomState(seed)
+    p = np.zeros((B, n, 5 + nc), np.float32)
+    cxy = rng.uniform(0, 640, (B, n // 4, 2))
+    p[..., 0:2] = np.repeat(cxy, 4, axis=1)[:, :n] + rng.normal(0, 6, (B, n, 2))      # crowds of ~4 around a centre
+    p[..., 2:4] = rng.uniform(8, 160, (B, n, 2))
+    p[..., 4] = rng.uniform(0, 1, (B, n))
+    p[..., 5:] = rng.uniform(0, 1, (B, n, nc)) ** 2
+    p[:, ::7, 4] = np.float32(0.8125)                    # tied objectness
+    p[:, ::7, 5:] = np.float32(0.5)                      # ... and tied class scores: first maximum, (box, j) order
+    if far:
+        k = n // 10
+        p[:, :k, 0] = rng.uniform(4000, 4200, (B, k))    # straddle the first class band's end
+        p[:, k:2 * k, 0] = rng.uniform(-80, 10, (B, k))
+        p[:, :2 * k, 2] = rng.uniform(100, 400, (B, 2 * k))
+    return p
+
+
+def case_ultralytics():
+    """utils/general.py:640-731 run as is (CPU tensors -> torchvision's CPU nms)."""
+    from utils.general import non_max_suppression as ref_nms
+    store = {}
+    for tag, far in (("near", False), ("far", True)):
+        p = ultra_pred(31 if not far else 32, 3, 600, 5, far)
+        store[tag + "_pred"] = p
+        for vi, kw in enumerate(ULTRA_VARIANTS):
+            ref = ref_nms(torch.from_numpy(p.copy()), **kw)
+            got = O.non_max_suppression(p, **kw)
+            ok = all(np.array_equal(r.numpy(), g) for r, g in zip(ref, got))
+            check("ultralytics:%s:%d %s" % (tag, vi, kw), ok, "kept %s" % [len(r) for r in ref])
+            store["%s_%d_rows" % (tag, vi)] = np.concatenate([r.numpy() for r in ref], 0)
+            store["%s_%d_counts" % (tag, vi)] = np.array([len(r) for r in ref])
+    # single class: multi_label is switched off (:659)
+    p1 = ultra_pred(33, 2, 300, 1)
+    ref = ref_nms(torch.from_numpy(p1.copy()), multi_label=True)
+    check("ultralytics:nc1", all(np.array_equal(r.numpy(), g) for r, g in zip(ref, O.non_max_suppression(p1, multi_label=True))))
+    store["nc1_pred"] = p1
+    store["nc1_rows"] = np.concatenate([r.numpy() for r in ref], 0)
+    store["nc1_counts"] = np.array([len(r) for r in ref])
+    np.savez_compressed(os.path.join(HERE, "ultralytics.npz"), **store)
+
+
+def case_yolov1():
+    """utils/yolov1_utils.py:12-66 on random logits (values differ from a libm sigmoid by an ulp: 1e-5 relative)."""
+    from utils.yolov1_utils import decode_predictions as ref_v1
+    rng = np.random.RandomState(41)
+    store = {}
+    for tag, nc, nb in (("voc_b2", 20, 2), ("nc3_b3", 3, 3)):
+        x = rng.normal(0, 2.5, (5, 7 * 7 * (5 * nb + nc))).astype(np.float32)
+        x[0, :40] = 30.0                                  # saturated sigmoids tie: first index wins
+        r = ref_v1(torch.from_numpy(x), nc, nb, 448).numpy()
+        g = O.decode_predictions_v1(x, nc, nb, 448)
+        check("yolov1:%s" % tag, np.array_equal(r[..., 5], g[..., 5]) and np.allclose(r, g, rtol=1e-5, atol=1e-6))
+        store[tag + "_in"] = x
+        store[tag + "_out"] = r
+    np.savez_compressed(os.path.join(HERE, "yolov1.npz"), **store)
+
+
+def confusion_inputs(seed, n_img, nc):
+    rng = np.random.RandomState(seed)
+    dets, labs = [], []
+    for it in range(n_img):
+        M, N = rng.randint(0, 12), rng.randint(0, 40)
+        lab = np.zeros((M, 5), np.float32)
+        xy, wh = rng.uniform(0, 300, (M, 2)), rng.uniform(20, 120, (M, 2))
+        lab[:, 0] = rng.randint(0, nc, M); lab[:, 1:3] = xy; lab[:, 3:5] = xy + wh
+        det = np.zeros((N, 6), np.float32)
+        for k in range(N):
+            if M and rng.rand() < 0.7:
+                det[k, :4] = lab[rng.randint(0, M), 1:] + rng.normal(0, 12, 4)
+            else:
+                c = rng.uniform(0, 300, 2)
+                det[k, :2] = c; det[k, 2:4] = c + rng.uniform(20, 120, 2)
+        det[:, 4] = rng.uniform(0, 1, N); det[:, 5] = rng.randint(0, nc, N)
+        if it == 3:
+            det = det[:0]
+        if it == 5:
+            det[:, :4] += 2000.0                          # no overlap at all: unmatched detections are NOT counted (:156)
+        dets.append(det); labs.append(lab)
+    return dets, labs
+
+
+def case_confusion():
+    """ConfusionMatrix.process_batch, utils/metrics.py:122-160, image by image."""
+    from utils.metrics import ConfusionMatrix
+    nc = 6
+    dets, labs = confusion_inputs(51, 40, nc)
+    cm = ConfusionMatrix(nc, conf=0.3, iou_thres=0.4)
+    m = np.zeros((nc + 1, nc + 1))
+    for d, l in zip(dets, labs):
+        cm.process_batch(torch.from_numpy(d), torch.from_numpy(l))
+        O.confusion_process_batch(m, d, l, nc, 0.3, 0.4)
+    check("confusion", np.array_equal(cm.matrix, m), "sum %d" % m.sum())
+    np.savez_compressed(os.path.join(HERE, "confusion.npz"), det=np.concatenate(dets), lab=np.concatenate(labs),
+                        det_off=np.cumsum([0] + [len(d) for d in dets]), lab_off=np.cumsum([0] + [len(l) for l in labs]),
+                        matrix=cm.matrix, nc=nc, conf=0.3, iou_thres=0.4)
+
+
 if __name__ == "__main__":
     O.build(force=True)
     if len(sys.argv) > 1:                      # regenerate only the named cases, e.g. `make_golden.py writers`
@@ -436,5 +542,8 @@ if __name__ == "__main__":
     case_map()
     case_iou()
     case_writers()
+    case_ultralytics()
+    case_yolov1()
+    case_confusion()
     print("FAILED: %s" % FAIL if FAIL else "all golden cases agree with the oracle")
     sys.exit(1 if FAIL else 0)

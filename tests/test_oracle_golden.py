@@ -124,3 +124,47 @@ def test_detection_writers(oracle):
     S = float(g["input_size"])
     scale = [[w / S, h / S] for w, h in g["sizes"].tolist()]
     assert np.array_equal(oracle.detection_ints(rows7, oracle.WRITER_COCO, scale, img_idx_base=7), g["coco_ints"])
+
+
+# ---------------------------------------------------------------- alternate semantics
+ULTRA_VARIANTS = [dict(), dict(multi_label=True), dict(agnostic=True), dict(classes=[1, 3]),
+                  dict(multi_label=True, max_det=9), dict(conf_thres=0.6, iou_thres=0.3),
+                  dict(multi_label=True, agnostic=True, classes=[0, 2, 4]), dict(max_det=5000),
+                  dict(multi_label=True, max_det=5000, conf_thres=0.1)]
+
+
+def _split(rows, counts):
+    off = np.concatenate([[0], np.cumsum(counts)])
+    return [rows[off[i]: off[i + 1]] for i in range(len(counts))]
+
+
+def test_ultralytics_nms(oracle):
+    """utils/general.py:640-731 as run by the reference (CPU), every option combination of the fixture."""
+    g = util.load("ultralytics")
+    for tag in ("near", "far"):
+        for vi, kw in enumerate(ULTRA_VARIANTS):
+            want = _split(g["%s_%d_rows" % (tag, vi)], g["%s_%d_counts" % (tag, vi)])
+            got = oracle.non_max_suppression(g[tag + "_pred"], **kw)
+            assert [len(x) for x in got] == [len(x) for x in want], (tag, kw)
+            assert all(np.array_equal(a, b) for a, b in zip(got, want)), (tag, kw)
+    got = oracle.non_max_suppression(g["nc1_pred"], multi_label=True)
+    assert all(np.array_equal(a, b) for a, b in zip(got, _split(g["nc1_rows"], g["nc1_counts"])))
+
+
+def test_yolov1_decode(oracle):
+    g = util.load("yolov1")
+    for tag, nc, nb in (("voc_b2", 20, 2), ("nc3_b3", 3, 3)):
+        got = oracle.decode_predictions_v1(g[tag + "_in"], nc, nb, 448)
+        want = g[tag + "_out"]
+        assert np.array_equal(got[..., 5], want[..., 5])
+        np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-6)      # sigmoid differs by an ulp between libms
+
+
+def test_confusion_matrix(oracle):
+    g = util.load("confusion")
+    nc = int(g["nc"])
+    m = np.zeros((nc + 1, nc + 1))
+    do, lo = g["det_off"], g["lab_off"]
+    for i in range(len(do) - 1):
+        oracle.confusion_process_batch(m, g["det"][do[i]: do[i + 1]], g["lab"][lo[i]: lo[i + 1]], nc, float(g["conf"]), float(g["iou_thres"]))
+    assert np.array_equal(m, g["matrix"])

@@ -103,15 +103,44 @@ __device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r,
 #define YPP_NMSQ_WARPS 4
 #define YPP_NMSQ_THREADS (32 * YPP_NMSQ_WARPS)
 
-struct SegSmem {
-    float4 box[YPP_WARP_SEG];
+// sweep-and-prune path of the per-class kernel (see nms_sparse below)
+#define YPP_SP_BINS 256
+#define YPP_SP_MIN_LEN 192
+#define YPP_SP_EDGES 1024
+#define YPP_SP_ROUNDS 24
+#define YPP_SP_LONG 32              /* ranges this long are swept by a whole warp (even) */
+
+struct SegDense {
     float tb[YPP_WARP_SEG];             // -thr * |area| of every box (its share of thr * union)
     float4 kbox[YPP_NMSQ_WARPS][8];     // per warp: its kept rows of the current tile, padded to a multiple of 2
     float kta[YPP_NMSQ_WARPS][8];       // -thr * area of those rows
-    u32 amax[YPP_NMSQ_WARPS];
-    u32 cmax[YPP_NMSQ_WARPS];
     u32 in_words[32];          // byte w of word j: rows 8w..8w+7 of the tile that suppress column j
     uint4 dpart[32];           // per lane: the four warps' partial dead-column bits
+};
+
+struct SegSparse {
+    u32 hist[YPP_SP_BINS];              // boxes per x1 bin, then the scatter cursors
+    u32 edges[YPP_SP_EDGES];            // (earlier rank << 16) | later rank of every pair with IoU > thr
+    float tb[YPP_WARP_SEG];             // -thr * |area| by position
+    u32 rowlist[YPP_WARP_SEG];          // position | end of its range << 16, longest range first
+    unsigned short bstart[YPP_SP_BINS + 2];     // first position of every bin
+    unsigned short rk[YPP_WARP_SEG];    // position (x1 order) -> rank inside the segment (score order)
+    unsigned char state[YPP_WARP_SEG];  // by rank: 0 undecided, 1 kept, 2 suppressed
+    unsigned char pend[YPP_WARP_SEG];   // some undecided earlier box could still suppress me
+    unsigned char kill[YPP_WARP_SEG];   // a kept earlier box suppresses me
+    int wtot[YPP_NMSQ_WARPS];
+    u32 xlo[YPP_NMSQ_WARPS], xhi[YPP_NMSQ_WARPS];
+};
+
+struct SegSmem {
+    float4 box[YPP_WARP_SEG];           // score order (tile sweeps) or x1 order (sweep-and-prune)
+    union {
+        SegDense d;
+        SegSparse s;
+    };
+    u32 amax[YPP_NMSQ_WARPS];
+    u32 cmax[YPP_NMSQ_WARPS];
+    int nedges;
 };
 
 // One warp's kept rows (kb/ka, npad of them, nk real) against G groups of 32 columns starting at
@@ -165,6 +194,266 @@ __device__ __forceinline__ u32 sweep_groups(const float4* __restrict__ sbox, con
     return (dbits & vm) << k;
 }
 
+// ---- sweep-and-prune path -------------------------------------------------------------------
+// The tile sweeps below test every (kept row, later column) pair: len^2/2 pair tests per segment, and
+// on detector output nearly all of them are between boxes that do not even touch.  Greedy NMS only
+// needs the EDGES (i earlier than j, IoU(i, j) > thr); which pairs are looked at, and in what order,
+// is free as long as no edge is missed.  So for segments of ordinary boxes (finite, x2 > x1, y2 > y1):
+//   1. counting sort of the boxes by x1 into YPP_SP_BINS bins over the segment's x1 range;
+//   2. every box p only meets the boxes after it in that order whose bin starts before
+//        xe = x1 + (1 - 0.9 thr) * w_p   (every step rounded up).
+//      For x1_c >= x1_p:  IoU <= overlap_x / max(w_p, w_c) <= 1 - (x1_c - x1_p) / w_p, so a column
+//      beyond xe has IoU <= 0.9 thr in exact arithmetic, which no rounding of the fp32 quotient (a few
+//      2^-24 relative; the union never cancels) lifts above thr.  Boxes of p's own bin after p are
+//      always met, whatever their x1;
+//   3. one thread per box, boxes handed out in order of decreasing range length (a second counting
+//      sort), so the lanes of a warp run loops of nearly the same length.  The pair test is the lean
+//      form of the tile sweeps (pair_g + the segment's decision band); the rare pair inside the band
+//      is decided by the exact division with the EARLIER box as torchvision's row (the fma form of
+//      the union is not symmetric);
+//   4. the greedy order over the edge list as a fix-point: a box is kept once every earlier box with
+//      an edge to it is known suppressed, suppressed once one of them is known kept.
+// Anything unusual - a box that is not ordinary, coordinates or areas outside the lean test's range,
+// more than YPP_SP_EDGES edges (crowds of overlapping boxes), a dependency chain deeper than
+// YPP_SP_ROUNDS - returns false with nothing written, and the segment goes through the tile sweeps.
+// On the C2 dense workload (409 boxes per segment, 18 edges) this path does 11 % of the pair tests.
+#ifdef YPP_SP_STATS
+// tuning build only: 0 attempts, 1 done, 2 not ordinary, 3 edge overflow, 4 too deep, 5 pair tests, 6 edges, 7 rounds,
+// 8.. clock cycles of CTA phases (load, sorts, sweep, resolve), 12 sweep iterations of warp 0
+__device__ unsigned long long ypp_sp_stats[16];
+#define SP_STAT(i, v) atomicAdd(&ypp_sp_stats[i], (unsigned long long)(v))
+#define SP_CLOCK(var) const long long var = clock64()
+#else
+#define SP_STAT(i, v)
+#define SP_CLOCK(var)
+#endif
+
+__device__ __forceinline__ int sp_bin(const float x, const float xmin, const float inv)
+{
+    const float v = __fmul_rn(__fsub_rn(x, xmin), inv);          // monotone in x; NaN (0 * inf) -> bin 0
+    return (int)fminf(fmaxf(v, 0.0f), (float)(YPP_SP_BINS - 1));
+}
+__device__ __forceinline__ int sp_bin_end(const float x, const float xmin, const float inv)
+{
+    const float v = __fmul_rn(__fsub_rn(x, xmin), inv);          // >= sp_bin(x); NaN -> last bin
+    return !(v < (float)YPP_SP_BINS) ? YPP_SP_BINS - 1 : max((int)v, 0);
+}
+
+// hist[256] -> exclusive offsets in place (the scatter cursors); optionally kept in bstart as well
+__device__ __forceinline__ void sp_scan(SegSparse& s, const int tid, const bool keep_starts, const int len)
+{
+    const int lane = tid & 31, w = tid >> 5;
+    const int h0 = (int)s.hist[2 * tid], h1 = (int)s.hist[2 * tid + 1];
+    int incl = h0 + h1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(YPP_FULL_MASK, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s.wtot[w] = incl;
+    __syncthreads();
+    int off = incl - (h0 + h1);
+    for (int k = 0; k < w; ++k) off += s.wtot[k];
+    if (keep_starts) {
+        s.bstart[2 * tid] = (unsigned short)off;
+        s.bstart[2 * tid + 1] = (unsigned short)(off + h0);
+        if (tid == 0) s.bstart[YPP_SP_BINS] = (unsigned short)len;
+    }
+    s.hist[2 * tid] = (u32)off;
+    s.hist[2 * tid + 1] = (u32)(off + h0);
+    __syncthreads();
+}
+
+// one pair of the sweep: box a (position order, rank ra) against the box at position c
+template <bool kFma>
+__device__ __forceinline__ void sp_pair(SegSmem& sm, const float4 a, const float ta, const int ra, const int c,
+                                        const float c1k, const float scale, const float Bseg, const float thr, int& ntests)
+{
+    const float4 bq = sm.box[c];
+#ifdef YPP_SP_STATS
+    ++ntests;
+#endif
+    const float D = __fadd_rn(pair_g(a, ta, bq, c1k, scale), sm.s.tb[c]);
+    if (D < -Bseg) return;                              // surely not suppressed (no NaN: everything is finite)
+    const int rb = sm.s.rk[c];
+    bool dead = D > Bseg;
+    if (!dead) {                                        // inside the band: the exact division decides
+        const bool a_first = ra < rb;
+        const float4 hi = a_first ? a : bq, lo = a_first ? bq : a;
+        dead = pair_exact(hi, ypp_area(hi), lo, thr, kFma ? 1 : 0);
+    }
+    if (dead) {
+        const int e = atomicAdd(&sm.nedges, 1);
+        if (e < YPP_SP_EDGES) sm.s.edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
+    }
+}
+
+template <bool kFma>
+__device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size_t ibase, const int* __restrict__ grank,
+                                        unsigned char* __restrict__ keepflag, const int len, const int b,
+                                        const bool trick, const float step, const float thr)
+{
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    SegSparse& S = sm.s;
+    SP_CLOCK(t0);
+    if (tid == 0) SP_STAT(0, 1);
+    // ---- boxes in score order -> registers; ordinary? x1 range, largest |area| and |coordinate|
+    float4 q[4];
+    bool odd = false;
+    u32 xlo = 0xffffffffu, xhi = 0u, amax_bits = 0u, cmax_bits = 0u;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int i = tid + u * YPP_NMSQ_THREADS;
+        q[u] = make_float4(0.f, 0.f, 1.f, 1.f);
+        if (i < len) {
+            q[u] = rank_box(ws, ibase, grank[i], trick, step);
+            const float bw = __fsub_rn(q[u].z, q[u].x), bh = __fsub_rn(q[u].w, q[u].y);
+            const bool ok = bw > 0.0f && bh > 0.0f && bw < INFINITY && bh < INFINITY &&
+                            fabsf(q[u].x) < INFINITY && fabsf(q[u].y) < INFINITY;
+            odd |= !ok;
+            const u32 e = ypp_enc(q[u].x);
+            xlo = min(xlo, e); xhi = max(xhi, e);
+            amax_bits = max(amax_bits, __float_as_uint(fabsf(__fmul_rn(bw, bh))));
+            cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q[u].x))), max(__float_as_uint(fabsf(q[u].y)),
+                            max(__float_as_uint(fabsf(q[u].z)), __float_as_uint(fabsf(q[u].w)))));
+        }
+    }
+    xlo = __reduce_min_sync(YPP_FULL_MASK, xlo);
+    xhi = __reduce_max_sync(YPP_FULL_MASK, xhi);
+    amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
+    cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
+    if (lane == 0) { S.xlo[w] = xlo; S.xhi[w] = xhi; sm.amax[w] = amax_bits; sm.cmax[w] = cmax_bits; }
+    for (int i = tid; i < YPP_SP_BINS; i += YPP_NMSQ_THREADS) S.hist[i] = 0;
+    if (tid == 0) sm.nedges = 0;
+    if (__syncthreads_or(odd)) { if (tid == 0) SP_STAT(2, 1); return false; }
+    // the lean pair test's constants, exactly as the tile sweeps derive them
+    const float Bseg = 2.0f * YPP_PAIR_BAND *
+        __uint_as_float(max(max(sm.amax[0], sm.amax[1]), max(sm.amax[2], sm.amax[3])));
+    const int cexp = (int)(max(max(sm.cmax[0], sm.cmax[1]), max(sm.cmax[2], sm.cmax[3])) >> 23);
+    if (cexp < 67 || cexp > 187 || !(Bseg < INFINITY)) { if (tid == 0) SP_STAT(2, 1); return false; }    // uniform
+    const float scale = __uint_as_float((u32)(252 - cexp) << 23);
+    const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cexp + 2) << 23));
+    const float xmin = ypp_dec(min(min(S.xlo[0], S.xlo[1]), min(S.xlo[2], S.xlo[3])));
+    const float xmax = ypp_dec(max(max(S.xhi[0], S.xhi[1]), max(S.xhi[2], S.xhi[3])));
+    const float inv = __fdiv_rn((float)YPP_SP_BINS, __fsub_rn(xmax, xmin));      // inf when every x1 is the same: one bin
+    SP_CLOCK(t1);
+    // ---- counting sort by x1 bin
+    int mybin[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        mybin[u] = sp_bin(q[u].x, xmin, inv);
+        if (tid + u * YPP_NMSQ_THREADS < len) atomicAdd(&S.hist[mybin[u]], 1u);
+    }
+    __syncthreads();
+    sp_scan(S, tid, true, len);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int i = tid + u * YPP_NMSQ_THREADS;
+        if (i < len) {
+            const int pos = (int)atomicAdd(&S.hist[mybin[u]], 1u);
+            sm.box[pos] = q[u];
+            S.tb[pos] = __fmul_rn(-thr, fabsf(ypp_area(q[u])));
+            S.rk[pos] = (unsigned short)i;
+        }
+        if (i < YPP_WARP_SEG) { S.state[i] = 0; S.pend[i] = 0; S.kill[i] = 0; }
+    }
+    __syncthreads();
+    // ---- range of every box; boxes in order of decreasing range length
+    for (int i = tid; i < YPP_SP_BINS; i += YPP_NMSQ_THREADS) S.hist[i] = 0;
+    __syncthreads();
+    const float ct = __fsub_ru(1.0f, __fmul_rd(0.9f, thr));
+    u32 myrow[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+        const int pr = tid + u * YPP_NMSQ_THREADS;
+        mybin[u] = YPP_SP_BINS - 1;
+        myrow[u] = 0;
+        if (pr < len) {
+            const float4 a = sm.box[pr];
+            const float xe = __fadd_ru(a.x, __fmul_ru(ct, __fsub_ru(a.z, a.x)));
+            const int cend = S.bstart[sp_bin_end(xe, xmin, inv) + 1];
+            const int cnt = max(cend - pr - 1, 0);
+            mybin[u] = YPP_SP_BINS - 1 - min(cnt >> 1, YPP_SP_BINS - 1);
+            myrow[u] = (u32)pr | ((u32)cend << 16);
+            atomicAdd(&S.hist[mybin[u]], 1u);
+        }
+    }
+    __syncthreads();
+    sp_scan(S, tid, false, len);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+        if (tid + u * YPP_NMSQ_THREADS < len) S.rowlist[atomicAdd(&S.hist[mybin[u]], 1u)] = myrow[u];
+    __syncthreads();
+    SP_CLOCK(t2);
+    // ---- sweep.  Ranges of YPP_SP_LONG boxes and more: one warp per box, lanes over its range (the few
+    // very wide boxes meet most of the segment; handed to single threads they would be the whole run time);
+    // the others: one thread per box
+    {
+        int ntests = 0;
+        const int nlong = (int)S.hist[YPP_SP_BINS - 1 - YPP_SP_LONG / 2];      // cursor of that bin after the scatter = its end
+        for (int k = w; k < nlong; k += YPP_NMSQ_WARPS) {
+            const u32 row = S.rowlist[k];
+            const int pr = (int)(row & 0xffffu), cend = (int)(row >> 16);
+            const float4 a = sm.box[pr];
+            const float ta = S.tb[pr];
+            const int ra = S.rk[pr];
+            for (int c = pr + 1 + lane; c < cend; c += 32)
+                sp_pair<kFma>(sm, a, ta, ra, c, c1k, scale, Bseg, thr, ntests);
+        }
+        for (int k = nlong + tid; k < len; k += YPP_NMSQ_THREADS) {
+            const u32 row = S.rowlist[k];
+            const int pr = (int)(row & 0xffffu), cend = (int)(row >> 16);
+            if (pr + 1 >= cend) continue;
+            const float4 a = sm.box[pr];
+            const float ta = S.tb[pr];
+            const int ra = S.rk[pr];
+            for (int c = pr + 1; c < cend; ++c)
+                sp_pair<kFma>(sm, a, ta, ra, c, c1k, scale, Bseg, thr, ntests);
+            if (*(volatile int*)&sm.nedges >= YPP_SP_EDGES) break;
+        }
+#ifdef YPP_SP_STATS
+        SP_STAT(5, ntests);
+#endif
+    }
+    __syncthreads();
+    SP_CLOCK(t3);
+    const int ne = sm.nedges;
+    if (ne > YPP_SP_EDGES) { if (tid == 0) SP_STAT(3, 1); return false; }
+    if (tid == 0) SP_STAT(6, ne);
+    // ---- greedy order over the edges
+    bool settled = ne == 0;
+    for (int round = 0; !settled && round < YPP_SP_ROUNDS; ++round) {
+        for (int e = tid; e < ne; e += YPP_NMSQ_THREADS) {
+            const u32 ed = S.edges[e];
+            const int st = S.state[ed >> 16];
+            if (st == 1) S.kill[ed & 0xffffu] = 1;
+            else if (st == 0) S.pend[ed & 0xffffu] = 1;
+        }
+        __syncthreads();
+        bool open = false;
+        for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
+            if (S.state[i] == 0) {
+                if (S.kill[i]) S.state[i] = 2;
+                else if (!S.pend[i]) S.state[i] = 1;
+                else open = true;
+            }
+            S.pend[i] = 0;
+        }
+        settled = !__syncthreads_or(open);
+        if (tid == 0) SP_STAT(7, 1);
+    }
+    if (!settled) { if (tid == 0) SP_STAT(4, 1); return false; }
+#ifdef YPP_SP_STATS
+    if (tid == 0) { SP_STAT(1, 1); SP_STAT(8, t1 - t0); SP_STAT(9, t2 - t1); SP_STAT(10, t3 - t2); SP_STAT(11, clock64() - t3); }
+#endif
+    int kept = 0;
+    for (int i = tid; i < len; i += YPP_NMSQ_THREADS)
+        if (S.state[i] != 2) { keepflag[grank[i]] = 1; ++kept; }      // ne == 0: every state is still 0
+    kept = __reduce_add_sync(YPP_FULL_MASK, kept);
+    if (lane == 0 && kept) atomicAdd(ws.keep_count + b, kept);
+    return true;
+}
+
 // 32-row tiles in score order.  Warp w owns rows 8w..8w+7 of every tile: it tests them against the
 // tile's own columns (diagonal), the four byte-wide partial masks are exchanged through shared
 // memory, every warp resolves the greedy order redundantly (ballot fix-point: a row is kept once
@@ -188,12 +477,16 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const bool trick = (p.ws.imgflag[b] & 2) != 0;
     const float step = p.ws.img_step[b];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (kFast && thr >= 0.0f && len >= p.sparse_min_len) {        // uniform over the CTA
+        if (nms_sparse<kFma>(sm, p.ws, ibase, grank, keepflag, len, b, trick, step, thr)) return;
+        __syncthreads();
+    }
     u32 amax_bits = 0, cmax_bits = 0;   // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
         const float4 q = rank_box(p.ws, ibase, grank[i], trick, step);
         const float ar = fabsf(ypp_area(q));
         sm.box[i] = q;
-        sm.tb[i] = __fmul_rn(-thr, ar);
+        sm.d.tb[i] = __fmul_rn(-thr, ar);
         amax_bits = max(amax_bits, __float_as_uint(ar));
         cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
                         max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
@@ -202,7 +495,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
     if (lane == 0) { sm.amax[w] = amax_bits; sm.cmax[w] = cmax_bits; }
     // the last tile is filled up with dummies (never a valid column: marked dead below; never a live row)
-    for (int i = len + tid; i < ((len + 31) & ~31); i += YPP_NMSQ_THREADS) { sm.box[i] = YPP_DUMMY_BOX; sm.tb[i] = YPP_DUMMY_TA; }
+    for (int i = len + tid; i < ((len + 31) & ~31); i += YPP_NMSQ_THREADS) { sm.box[i] = YPP_DUMMY_BOX; sm.d.tb[i] = YPP_DUMMY_TA; }
     __syncthreads();
     // one decision band for the whole segment (NaN / inf areas make every compare fail -> exact path)
     float Bseg = 2.0f * YPP_PAIR_BAND *
@@ -226,7 +519,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
         if (alive == 0) continue;
         // ---- diagonal tile, column view: which of MY rows (i < lane, alive) suppress column lane
         const float4 cb = sm.box[j];
-        const float my_ta = sm.tb[j];
+        const float my_ta = sm.d.tb[j];
         u32 in = 0;
         if (kFast) {
             // my 8 rows, unconditionally (dead rows and the dummies past the end are masked out below)
@@ -234,7 +527,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 const int i = base + 8 * w + q;
-                const float d = __fadd_rn(pair_g(sm.box[i], sm.tb[i], cb, c1k, scale), my_ta);
+                const float d = __fadd_rn(pair_g(sm.box[i], sm.d.tb[i], cb, c1k, scale), my_ta);
                 if (d > Bseg) in |= 1u << (8 * w + q);
                 lo = fminf(lo, fabsf(d));             // a NaN d is never a suppression: dropped
             }
@@ -252,9 +545,9 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             }
         }
         in &= alive & ((1u << lane) - 1u);            // only alive rows before me count
-        reinterpret_cast<unsigned char*>(sm.in_words)[lane * 4 + w] = (unsigned char)(in >> (8 * w));
+        reinterpret_cast<unsigned char*>(sm.d.in_words)[lane * 4 + w] = (unsigned char)(in >> (8 * w));
         __syncthreads();
-        in = sm.in_words[lane];
+        in = sm.d.in_words[lane];
         // ---- greedy order as a fix-point
         u32 K = 0, D = ~alive;
         bool undecided = alive_l;
@@ -276,26 +569,26 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             const int npad = (nkw + 1) & ~1;
             if ((Kw >> lane) & 1u) {
                 const int s = __popc(Kw & ((1u << lane) - 1u));
-                sm.kbox[w][s] = cb;
-                sm.kta[w][s] = my_ta;
+                sm.d.kbox[w][s] = cb;
+                sm.d.kta[w][s] = my_ta;
             }
-            if (lane >= nkw && lane < npad) { sm.kbox[w][lane] = YPP_DUMMY_BOX; sm.kta[w][lane] = YPP_DUMMY_TA; }
+            if (lane >= nkw && lane < npad) { sm.d.kbox[w][lane] = YPP_DUMMY_BOX; sm.d.kta[w][lane] = YPP_DUMMY_TA; }
             __syncwarp();
-            const float4* kb = sm.kbox[w];
-            const float* ka = sm.kta[w];
+            const float4* kb = sm.d.kbox[w];
+            const float* ka = sm.d.kta[w];
             int k = T + 1;
             for (; k + 4 <= ntiles; k += 4)
-                part |= sweep_groups<4, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
+                part |= sweep_groups<4, kFast>(sm.box, sm.d.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
             if (k + 2 <= ntiles) {
-                part |= sweep_groups<2, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
+                part |= sweep_groups<2, kFast>(sm.box, sm.d.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
                 k += 2;
             }
             if (k < ntiles)
-                part |= sweep_groups<1, kFast>(sm.box, sm.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
+                part |= sweep_groups<1, kFast>(sm.box, sm.d.tb, kb, ka, npad, nkw, k, dead, c1k, scale, Bseg, thr, union_fma);
         }
-        reinterpret_cast<u32*>(&sm.dpart[lane])[w] = part;
+        reinterpret_cast<u32*>(&sm.d.dpart[lane])[w] = part;
         __syncthreads();
-        const uint4 dp = sm.dpart[lane];
+        const uint4 dp = sm.d.dpart[lane];
         dead |= dp.x | dp.y | dp.z | dp.w;
     }
     if (tid == 0 && total) atomicAdd(p.ws.keep_count + b, total);
@@ -636,8 +929,23 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
 
 }  // namespace
 
-int ypp_launch_nms(const YppNmsParams& p, cudaStream_t st)
+#ifdef YPP_SP_STATS
+extern "C" int ypp_debug_sp_stats(unsigned long long* out16, int reset)
 {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out16, ypp_sp_stats, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(ypp_sp_stats, z, sizeof(z)); }
+    return 0;
+}
+#endif
+
+int ypp_launch_nms(const YppNmsParams& p0, cudaStream_t st)
+{
+    // YPP_SPARSE_MIN: shortest per-class segment that tries the sweep-and-prune path (0 = never; tuning knob)
+    static int sparse_min = -1;
+    if (sparse_min < 0) { const char* e = getenv("YPP_SPARSE_MIN"); sparse_min = e ? atoi(e) : YPP_SP_MIN_LEN; if (sparse_min < 0) sparse_min = 0; }
+    YppNmsParams p = p0;
+    p.sparse_min_len = sparse_min > 0 ? sparse_min : 0x7fffffff;
     // the division-free pair test is proven for thresholds in [2^-10, 1]; anything else divides
     const bool fast = p.iou_thr >= 0.0009765625f && p.iou_thr <= 1.0f;
     if (!fast) return launch_nms_t<false, false>(p, st);

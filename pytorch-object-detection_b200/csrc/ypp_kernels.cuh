@@ -43,6 +43,7 @@ struct YppNmsParams {
     int B, N, nc;
     float iou_thr;
     int union_mode;
+    int sparse_min_len;    // per-class segments at least this long try the sweep-and-prune path first
 };
 
 struct YppGatherParams {

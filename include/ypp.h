@@ -134,6 +134,30 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
                     float* det_rows, int row_width, int64_t det_capacity, int* det_total,
                     float img_idx_base, void* stream);
 
+/* ---- the head's 1x1 convolution fused with the decode ---------------------------
+ * Every detector ends each scale in nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
+ * (models/detector/yolov3.py:56,62,68; yolov2.py; yolov4_tiny.py) and hands its output to
+ * decode_predictions (utils/yolov3_utils.py:12).  These entry points take the INPUT of that
+ * convolution instead and never materialise the head: one tcgen05 (TF32 products, fp32
+ * accumulation - cuDNN's arithmetic for this layer under torch's default allow_tf32) kernel per scale
+ * decodes, thresholds and compacts the accumulator tiles.  scales[i].head is ignored. */
+typedef struct {
+    const float* feature;   /* [B, H, W, Cin] fp32, channels-last (x.permute(0,2,3,1).contiguous() of the
+                               conv input, or a torch.channels_last tensor's storage); 16-byte aligned */
+    const float* weight;    /* [A*(5+nc), Cin] fp32: conv.weight.reshape(A*(5+nc), Cin); 16-byte aligned */
+    int cin;                /* multiple of 4 */
+    float* head_out;        /* optional [B, A*(5+nc), H, W]: the head tensor, for inspection / parity */
+} ypp_head_src;
+
+/* = the convolutions + ypp_decode_compact */
+int ypp_head_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src,
+                            void* ws, size_t ws_bytes, void* stream);
+/* = the convolutions + ypp_postprocess */
+int ypp_head_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src,
+                         void* ws, size_t ws_bytes, int* cand_count, int* keep_count, int* keep_idx,
+                         float* det_rows, int row_width, int64_t det_capacity, int* det_total,
+                         float img_idx_base, void* stream);
+
 /* nms_v3 on decoded rows [B, n_boxes, 6] (utils/yolo_utils.py:321-348), batched. */
 int ypp_nms_rows(const ypp_cfg* cfg, const float* rows_BN6, int n_boxes, void* ws, size_t ws_bytes,
                  int* cand_count, int* keep_count, int* keep_idx,

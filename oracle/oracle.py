@@ -430,3 +430,15 @@ def confusion_process_batch(matrix, detections, labels, nc, conf=0.25, iou_thres
             if not matched_det[d]:
                 matrix[det_cls[d], nc] += 1                                      # :157-159
     return matrix
+
+
+def head_conv1x1(feature, weight):
+    """The head's last layer, nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False) (models/detector/yolov3.py:56,62,68):
+    feature [B, Cin, H, W], weight [AC, Cin(,1,1)] -> (head [B, AC, H, W] in float64, bound), where
+    bound = sum_k |x_k| |w_k| per output element: the tensor core cuts both factors to 10 mantissa bits
+    (each loses up to 2^-10 relative), so |tf32 head - exact head| <= 2^-9 * bound * (1 + eps)."""
+    x = np.asarray(feature, dtype=np.float64)
+    w = np.asarray(weight, dtype=np.float64).reshape(np.asarray(weight).shape[0], -1)
+    head = np.einsum("bkhw,ck->bchw", x, w)
+    bound = np.einsum("bkhw,ck->bchw", np.abs(x), np.abs(w))
+    return head, bound

@@ -43,7 +43,7 @@ int check_cfg(const ypp_cfg* cfg)
     return YPP_OK;
 }
 
-int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, YppDecodeParams* p)
+int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, YppDecodeParams* p, bool need_head = true)
 {
     int rc = check_cfg(cfg);
     if (rc) return rc;
@@ -62,7 +62,7 @@ int build_decode_params(const ypp_cfg* cfg, const ypp_scale* sc, bool dense, Ypp
     int box_base = 0, tile = 0;
     for (int i = 0; i < cfg->n_scales; ++i) {
         const ypp_scale& s = sc[i];
-        if (!s.head || s.A < 1 || s.A > YPP_MAX_ANCHORS || s.H < 1 || s.W < 1) { ypp_set_error("scale %d: bad head/A/H/W", i); return YPP_E_BADARG; }
+        if ((need_head && !s.head) || s.A < 1 || s.A > YPP_MAX_ANCHORS || s.H < 1 || s.W < 1) { ypp_set_error("scale %d: bad head/A/H/W", i); return YPP_E_BADARG; }
         YppScaleParams& d = p->sc[i];
         d.head = s.head; d.A = s.A; d.H = s.H; d.W = s.W; d.HW = s.H * s.W;
         d.box_base = box_base;
@@ -204,6 +204,40 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
     rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
     if (rc) return rc;
     rc = ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
+    if (rc) return rc;
+    return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, nullptr, true, true, (cudaStream_t)stream);
+}
+
+// the heads' 1x1 convolutions fused with D1: one tcgen05 kernel per scale writes the slot records
+static int head_decode_all(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
+                           YppDecodeParams* p, cudaStream_t st)
+{
+    int rc = build_decode_params(cfg, scales, false, p, false);
+    if (rc) return rc;
+    if (!src) { ypp_set_error("head sources are null"); return YPP_E_BADARG; }
+    for (int i = 0; i < cfg->n_scales; ++i)
+        if (!src[i].feature || !src[i].weight || src[i].cin < 1) { ypp_set_error("scale %d: feature / weight / cin missing", i); return YPP_E_BADARG; }
+    rc = bind_ws(cfg->B, p->N, cfg->nc, ws, ws_bytes, &p->ws);
+    if (rc) return rc;
+    for (int i = 0; i < cfg->n_scales && !rc; ++i)
+        rc = ypp_launch_head_decode(*p, cfg->B, i, src[i].feature, src[i].weight, src[i].cin, src[i].head_out, st);
+    return rc;
+}
+
+int ypp_head_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
+                            void* stream)
+{
+    YppDecodeParams p;
+    return head_decode_all(cfg, scales, src, ws, ws_bytes, &p, (cudaStream_t)stream);
+}
+
+int ypp_head_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
+                         int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width,
+                         int64_t det_capacity, int* det_total, float img_idx_base, void* stream)
+{
+    YppDecodeParams p;
+    int rc = head_decode_all(cfg, scales, src, ws, ws_bytes, &p, (cudaStream_t)stream);
     if (rc) return rc;
     return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
                         img_idx_base, nullptr, true, true, (cudaStream_t)stream);

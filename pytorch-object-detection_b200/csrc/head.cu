@@ -1,0 +1,244 @@
+// F1: the detection head's 1x1 convolution fused with D1.
+//
+// Reference: every scale ends in  nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
+// (models/detector/yolov3.py:53-69, yolov4_tiny.py, yolov2.py) whose output [B, A(5+nc), H, W] is what
+// decode_predictions reads (utils/yolov3_utils.py:12-59).  A 1x1 convolution is the GEMM
+//     head[b, hw, c] = sum_k feature[b, hw, k] * weight[c, k]
+// so here the head tensor never exists in HBM: the accumulator tile of 128 cells x A(5+nc) channels is
+// decoded, thresholded and compacted straight out of tensor memory into the same slot records D1
+// writes, and S1 -> N1 -> G run unchanged.
+//
+// sm_100a design: one CTA per (image, 128 cells).  A = feature tile [128 cells x 32 channels] and
+// B = weight tile [N x 32 channels] (N = A(5+nc) rounded up to 16), both K-major, arrive by TMA
+// (cp.async.bulk.tensor, 128-byte swizzle) into a 4-stage ring; one thread issues
+// tcgen05.mma.kind::tf32 (M 128, N, K 8) four times per stage into a TMEM accumulator and commits
+// the stage back to the producer; after the last commit four warps read their 32 TMEM lanes
+// (tcgen05.ld 32x32b), park the tile channel-major in the (now idle) ring and run D1's own
+// decode_one / slot_store on it, so everything downstream of the accumulator is bit-identical to
+// D1 fed the same head values.  Features are channels-last ([B, H, W, Cin], torch.channels_last):
+// K-major rows of any H*W, 16-byte aligned for Cin % 4 == 0.
+// Arithmetic: TF32 products, fp32 accumulation - what cuDNN does for this convolution under
+// torch.backends.cudnn.allow_tf32 (the default); parity is stated against that, see tests.
+#include "decode_common.cuh"
+#include <cuda.h>
+#include <cstdlib>
+
+#define YPP_HEAD_STAGES 4
+#define YPP_HEAD_BM 128            /* cells per CTA = UMMA M = TMEM lanes */
+#define YPP_HEAD_BK 32             /* fp32 channels per stage row: 128 bytes = one swizzle span */
+#define YPP_HEAD_THREADS 192       /* warps 0-3 epilogue (TMEM lanes 32w..), 4 TMA producer, 5 MMA issuer + TMEM owner */
+#define YPP_HEAD_A_BYTES (YPP_HEAD_BM * YPP_HEAD_BK * 4)
+
+struct YppHeadParams {
+    YppDecodeParams d;
+    int si;                 // the scale this launch handles
+    int cin;                // input channels (K)
+    int ac;                 // A * (5 + nc): real output channels
+    int n_pad;              // UMMA N: ac rounded up to a multiple of 16
+    int tmem_cols;          // power of two >= max(32, n_pad)
+    u32 idesc;              // tcgen05 instruction descriptor (tf32 x tf32 -> f32, K-major A and B, M 128, N n_pad)
+    float* head_out;        // optional [B, ac, H, W]: the head tensor itself
+};
+
+namespace {
+
+__device__ __forceinline__ void tma_load_3d(u32 dst, const CUtensorMap* tm, int c0, int c1, int c2, u64* bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst), "l"((u64)tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(u32 dst, const CUtensorMap* tm, int c0, int c1, u64* bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"((u64)tm), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+// shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups 1024 bytes apart
+__device__ __forceinline__ u64 umma_desc(u32 saddr)
+{
+    return (u64)((saddr & 0x3ffffu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void umma_tf32(u32 tmem_d, u64 da, u64 db, u32 idesc, u32 accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(u64* bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(u32 taddr, u32 (&v)[16])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__global__ void __launch_bounds__(YPP_HEAD_THREADS)
+ypp_head_decode_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                       const __grid_constant__ YppHeadParams hp)
+{
+    extern __shared__ unsigned char ring_raw[];
+    __shared__ __align__(8) u64 full[YPP_HEAD_STAGES], empty[YPP_HEAD_STAGES], accum;
+    __shared__ u32 tmem_slot;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const YppDecodeParams& p = hp.d;
+    const YppScaleParams& s = p.sc[hp.si];
+    const int b = blockIdx.y, cell0 = blockIdx.x * YPP_HEAD_BM;
+    const bool has_cells = cell0 < s.HW;                     // 2 * tpp tiles per plane cover every D1 slot, some past the end
+    const int nk = (hp.cin + YPP_HEAD_BK - 1) / YPP_HEAD_BK;
+    const u32 stage_bytes = YPP_HEAD_A_BYTES + (u32)hp.n_pad * (YPP_HEAD_BK * 4);
+    unsigned char* ring = ring_raw + ((1024u - (smem_u32(ring_raw) & 1023u)) & 1023u);      // swizzle atoms are 1024-byte aligned
+    const u32 ring_addr = smem_u32(ring);
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < YPP_HEAD_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        mbar_init(&accum, 1);
+    }
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(hp.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const u32 tmem = tmem_slot;
+    ypp_grid_wait();                                          // the previous call's G may still be reading the workspace
+
+    if (has_cells && warp == 4 && lane == 0) {
+        // ---------------- TMA producer
+        for (int kc = 0; kc < nk; ++kc) {
+            const int st = kc % YPP_HEAD_STAGES, use = kc / YPP_HEAD_STAGES;
+            if (use > 0) mbar_wait(&empty[st], (u32)(use - 1) & 1u);
+            mbar_expect_tx(&full[st], stage_bytes);
+            const u32 dst = ring_addr + (u32)st * stage_bytes;
+            tma_load_3d(dst, &tm_a, kc * YPP_HEAD_BK, cell0, b, &full[st]);              // cells past H*W arrive as zeros
+            tma_load_2d(dst + YPP_HEAD_A_BYTES, &tm_b, kc * YPP_HEAD_BK, 0, &full[st]);   // rows past ac arrive as zeros
+        }
+    } else if (has_cells && warp == 5 && lane == 0) {
+        // ---------------- MMA issuer
+        for (int kc = 0; kc < nk; ++kc) {
+            const int st = kc % YPP_HEAD_STAGES, use = kc / YPP_HEAD_STAGES;
+            mbar_wait(&full[st], (u32)use & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const u32 a_addr = ring_addr + (u32)st * stage_bytes, b_addr = a_addr + YPP_HEAD_A_BYTES;
+#pragma unroll
+            for (int k = 0; k < YPP_HEAD_BK / 8; ++k)          // UMMA K = 8 tf32 = 32 bytes along the swizzled row
+                umma_tf32(tmem, umma_desc(a_addr + 32u * k), umma_desc(b_addr + 32u * k), hp.idesc, (u32)(kc | k));
+            umma_commit(&empty[st]);                          // the stage is free once these four have read it
+        }
+        umma_commit(&accum);
+    } else if (warp < 4) {
+        // ---------------- epilogue: thread = TMEM lane = cell
+        float* stg = reinterpret_cast<float*>(ring);          // [ac][128] channel-major, in the ring (idle by then)
+        const int ct = tid, cell = cell0 + ct;
+        if (has_cells) {
+            mbar_wait(&accum, 0u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int j = 0; j < hp.n_pad / 16; ++j) {
+                u32 v[16];
+                tmem_ld16(tmem + ((u32)(warp * 32) << 16) + (u32)(j * 16), v);
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (j * 16 + i < hp.ac) stg[(j * 16 + i) * YPP_HEAD_BM + ct] = __uint_as_float(v[i]);
+            }
+            __syncwarp();
+            if (hp.head_out != nullptr && cell < s.HW)
+                for (int c = 0; c < hp.ac; ++c)
+                    hp.head_out[((size_t)b * hp.ac + c) * s.HW + cell] = stg[c * YPP_HEAD_BM + ct];
+        }
+        const int nslots = p.tile_base[p.n_scales] * (YPP_TILE_BOXES / 32);
+        const int wslot = ((cell0 & (YPP_TILE_BOXES - 1)) >> 5) + warp;
+        for (int a = 0; a < s.A; ++a) {
+            Decoded d;
+            d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
+            const bool pass = decode_one<1>(p, s, a, cell, cell < s.HW, stg + a * p.C * YPP_HEAD_BM + ct, YPP_HEAD_BM, 0, 0, d);
+            const int tile = p.tile_base[hp.si] + a * s.tpp + cell0 / YPP_TILE_BOXES;
+            const int first = s.box_base + a * s.HW + cell0;
+            slot_store(p.ws, p.N, b, tile * (YPP_TILE_BOXES / 32) + wslot, nslots, first + 32 * warp, pass,
+                       d.box, d.score, d.cls, first + ct);
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 5)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(hp.tmem_cols) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled()
+{
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)ptr;
+    }
+    return fn;
+}
+
+}  // namespace
+
+int ypp_launch_head_decode(const YppDecodeParams& p, int B, int si, const float* feature, const float* weight, int cin,
+                           float* head_out, cudaStream_t st)
+{
+    const YppScaleParams& s = p.sc[si];
+    const int ac = s.A * p.C;
+    const int n_pad = (ac + 15) & ~15;
+    if (n_pad > 256) { ypp_set_error("head_decode: A*(5+nc) = %d exceeds one UMMA tile (256)", ac); return YPP_E_UNSUPPORTED; }
+    if (cin < 4 || (cin & 3) != 0) { ypp_set_error("head_decode: Cin = %d must be a positive multiple of 4", cin); return YPP_E_UNSUPPORTED; }
+    if (((uintptr_t)feature & 15u) != 0 || ((uintptr_t)weight & 15u) != 0) { ypp_set_error("head_decode: feature / weight must be 16-byte aligned"); return YPP_E_BADARG; }
+    EncodeTiledFn enc = encode_tiled();
+    if (!enc) { ypp_set_error("head_decode: cuTensorMapEncodeTiled is not available from this driver"); return YPP_E_CUDA; }
+    CUtensorMap tm_a, tm_b;
+    {   // features [B][HW][Cin], box 1 x 128 x 32
+        const cuuint64_t dims[3] = {(cuuint64_t)cin, (cuuint64_t)s.HW, (cuuint64_t)B};
+        const cuuint64_t strides[2] = {(cuuint64_t)cin * 4, (cuuint64_t)s.HW * cin * 4};
+        const cuuint32_t box[3] = {YPP_HEAD_BK, YPP_HEAD_BM, 1}, es[3] = {1, 1, 1};
+        const CUresult r = enc(&tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)feature, dims, strides, box, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the features failed (%d)", (int)r); return YPP_E_CUDA; }
+    }
+    {   // weight [ac][Cin], box n_pad x 32
+        const cuuint64_t dims[2] = {(cuuint64_t)cin, (cuuint64_t)ac};
+        const cuuint64_t strides[1] = {(cuuint64_t)cin * 4};
+        const cuuint32_t box[2] = {YPP_HEAD_BK, (cuuint32_t)n_pad}, es[2] = {1, 1};
+        const CUresult r = enc(&tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)weight, dims, strides, box, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the weight failed (%d)", (int)r); return YPP_E_CUDA; }
+    }
+    YppHeadParams hp;
+    hp.d = p;
+    hp.si = si; hp.cin = cin; hp.ac = ac; hp.n_pad = n_pad;
+    hp.tmem_cols = 32;
+    while (hp.tmem_cols < n_pad) hp.tmem_cols <<= 1;
+    // c_format f32 (1 << 4), a/b format tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
+    hp.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((u32)(n_pad >> 3) << 17) | ((u32)(YPP_HEAD_BM >> 4) << 24);
+    hp.head_out = head_out;
+    const int smem = YPP_HEAD_STAGES * (YPP_HEAD_A_BYTES + n_pad * YPP_HEAD_BK * 4) + 1024;
+    static int configured_d[YPP_MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= YPP_MAX_DEVICES) { ypp_set_error("head_decode: device ordinal %d out of range", dev); return YPP_E_UNSUPPORTED; }
+    if (configured_d[dev] < smem) {
+        cudaError_t e = cudaFuncSetAttribute(ypp_head_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) { ypp_set_error("head_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+        configured_d[dev] = smem;
+    }
+    dim3 grid(2 * s.tpp, B);
+    ypp_head_decode_kernel<<<grid, YPP_HEAD_THREADS, smem, st>>>(tm_a, tm_b, hp);
+    ypp_count_launch(1);
+    return ypp_check_launch("head_decode");
+}

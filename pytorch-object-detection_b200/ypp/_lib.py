@@ -10,7 +10,7 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(os.path.dirname(_PKG), "csrc")
 LIB_PATH = os.environ.get("YPP_LIB") or os.path.join(_PKG, "libypp.so")   # YPP_LIB: tuning builds only
-SOURCES = ["api.cu", "decode.cu", "organise.cu", "nms.cu", "metrics.cu"]
+SOURCES = ["api.cu", "decode.cu", "head.cu", "organise.cu", "nms.cu", "metrics.cu"]
 
 YPP_MAX_SCALES = 4
 YPP_MAX_ANCHORS = 8
@@ -44,13 +44,18 @@ class YppUltraCfg(ctypes.Structure):
                 ("union_mode", ctypes.c_int)]
 
 
+class YppHeadSrc(ctypes.Structure):
+    _fields_ = [("feature", ctypes.c_void_p), ("weight", ctypes.c_void_p), ("cin", ctypes.c_int),
+                ("head_out", ctypes.c_void_p)]
+
+
 WRITER_MODES = {"pred_file": 0, "coco": 1}
 
 EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "ypp_decode_compact",
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
-           "ypp_confusion_update", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -62,7 +67,7 @@ def build(force=False, verbose=False, defines=(), out=None):
         subprocess.run(cmd, check=True)
         return out
     srcs = [os.path.join(_CSRC, s) for s in SOURCES]
-    deps = srcs + [os.path.join(_CSRC, h) for h in ("ypp_common.cuh", "ypp_kernels.cuh")] + \
+    deps = srcs + [os.path.join(_CSRC, h) for h in ("ypp_common.cuh", "ypp_kernels.cuh", "decode_common.cuh")] + \
         [os.path.join(os.path.dirname(os.path.dirname(_PKG)), "include", "ypp.h")]
     if not force and os.path.exists(LIB_PATH):
         t = os.path.getmtime(LIB_PATH)
@@ -101,6 +106,9 @@ def lib():
     L.ypp_sort_segments.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp]
     L.ypp_nms.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_postprocess.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
+    hsp = ctypes.POINTER(YppHeadSrc)
+    L.ypp_head_decode_compact.argtypes = [cfgp, scp, hsp, vp, ctypes.c_size_t, vp]
+    L.ypp_head_postprocess.argtypes = [cfgp, scp, hsp, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_nms_rows.argtypes = [cfgp, vp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_target_rows.argtypes = [vp, ci, ci, cf, cf, vp, vp, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
@@ -119,7 +127,8 @@ def lib():
     L.ypp_launch_count.restype = i64
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
                  "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match",
-                 "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update"):
+                 "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update",
+                 "ypp_head_decode_compact", "ypp_head_postprocess"):
         getattr(L, name).restype = ci
     _lib = L
     return L

@@ -191,6 +191,76 @@ class PostProcessor:
                                 float(img_idx_base), _stream()))
         return res
 
+    def from_features(self, features: Sequence[torch.Tensor], weights: Sequence[torch.Tensor], img_idx_base=0,
+                      row_width=7, want_keep_idx=False, want_heads=False, stages=("decode", "sort", "nms"),
+                      out: Optional[PostResult] = None):
+        """The chain fed by the INPUTS of the heads' 1x1 convolutions: features[i] is the
+        [B, Cin, H, W] tensor the reference passes to nn.Conv2d(Cin, A*(5+nc), 1, bias=False)
+        (models/detector/yolov3.py:56,62,68), weights[i] that layer's weight [A*(5+nc), Cin, 1, 1].  The
+        head tensors are never written: one tcgen05 TF32 kernel per scale decodes the accumulator tiles.
+        Features are read channels-last; a torch.channels_last tensor is used in place, anything else is
+        converted first (one extra pass).  want_heads=True also returns the head tensors the kernel saw."""
+        n = len(features)
+        if n != len(weights) or n < 1 or n > _lib.YPP_MAX_SCALES:
+            raise ValueError("features and weights must be equally long lists of 1..%d tensors" % _lib.YPP_MAX_SCALES)
+        dev = features[0].device
+        B = features[0].shape[0]
+        arr = (YppScale * n)()
+        src = (_lib.YppHeadSrc * n)()
+        keep_alive, heads_out, n_boxes = [], [], 0
+        AC = self.A * (5 + self.num_classes)
+        for i, (x, w) in enumerate(zip(features, weights)):
+            if x.dim() != 4 or not x.is_cuda or x.dtype != torch.float32 or x.shape[0] != B or x.device != dev:
+                raise ValueError("feature %d must be a float32 CUDA tensor [B, Cin, H, W] on one device" % i)
+            _, Cin, H, W = x.shape
+            w2 = w.reshape(w.shape[0], -1)
+            if w2.shape != (AC, Cin) or w.dtype != torch.float32 or w.device != dev:
+                raise ValueError("weight %d must be float32 [%d, %d(,1,1)] on the features' device" % (i, AC, Cin))
+            xl = x.permute(0, 2, 3, 1)
+            if not xl.is_contiguous():
+                xl = xl.contiguous()                       # NCHW input: one transposing pass
+            w2 = w2.contiguous()
+            keep_alive += [xl, w2]
+            an = self.anchors[self.A * i: self.A * i + self.A]
+            if len(an) != self.A:
+                raise ValueError("not enough anchors for scale %d" % i)
+            stride_h, stride_w = self.input_size / H, self.input_size / W
+            s = arr[i]
+            s.head = None
+            s.A, s.H, s.W = self.A, H, W
+            for a, (w_, h_) in enumerate(an):
+                if self.kind == "v2":
+                    s.anchor_w[a], s.anchor_h[a] = w_, h_
+                else:
+                    s.anchor_w[a], s.anchor_h[a] = w_ / stride_w, h_ / stride_h
+            s.stride_w, s.stride_h = stride_w, stride_h
+            src[i].feature, src[i].weight, src[i].cin = xl.data_ptr(), w2.data_ptr(), Cin
+            if want_heads:
+                heads_out.append(torch.empty((B, AC, H, W), dtype=torch.float32, device=dev))
+                src[i].head_out = heads_out[-1].data_ptr()
+            n_boxes += self.A * H * W
+        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
+        cfg = self._cfg(B, n)
+        L = lib()
+        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, "post")
+        with torch.cuda.device(dev):
+            if tuple(stages) == ("decode", "sort", "nms"):
+                check(L.ypp_head_postprocess(ctypes.byref(cfg), arr, src, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                             _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                             res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                             float(img_idx_base), _stream()))
+            else:
+                if "decode" in stages:
+                    check(L.ypp_head_decode_compact(ctypes.byref(cfg), arr, src, _ptr(ws), ws.numel(), _stream()))
+                if "sort" in stages:
+                    check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
+                if "nms" in stages:
+                    check(L.ypp_nms(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                    res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                    float(img_idx_base), _stream()))
+        return (res, heads_out) if want_heads else res
+
     def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
                 repeat=1, stages=None):
         """Capture the chain on these (static) head buffers into a CUDA graph.  Returns

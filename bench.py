@@ -495,7 +495,77 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                               "gb_per_s": pred.numel() * 4 / (ms_u * 1e-3) / 1e9,
                               "what": "ypp_nms_ultralytics, conf .25 / iou .45 / max_det 300, best class, input resident in HBM"}
     del pred
+    if len(grids) == 3 and w["kind"] == "v3":
+        out["fused_head"] = fused_head_extra(torch, engine, dev, w, anchors)
     return out
+
+
+def fused_head_extra(torch, engine, dev, w, anchors, cins=(256, 512, 1024)):
+    """the heads' 1x1 convolutions fused with decode+compaction (tcgen05 TF32 kernel F1) on the
+    reference's channel counts (models/detector/yolov3.py:56,62,68), against cuDNN's convolution + the unfused chain.
+    Features channels-last and resident, 3 distinct batches cycled (> L2), weights scaled to the workload's head statistics."""
+    B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
+    AC = A * (5 + nc)
+    g = torch.Generator("cpu").manual_seed(4242)
+    ring = [[torch.randn(B, c, h, h, generator=g).to(dev).contiguous(memory_format=torch.channels_last)
+             for c, h in zip(cins, grids)] for _ in range(3)]
+    row_std = torch.tensor(([1.0, 1.0, 0.5, 0.5, 1.5] + [1.0] * nc) * A).reshape(AC, 1, 1, 1)
+    weights = [(torch.randn(AC, c, 1, 1, generator=g) * row_std / c ** 0.5).to(dev) for c in cins]
+    wcl = [x.contiguous(memory_format=torch.channels_last) for x in weights]
+    pp = engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A)
+    res = pp.from_features(ring[0], weights)
+    hcl = [torch.empty((B, AC, h, h), device=dev).contiguous(memory_format=torch.channels_last) for h in grids]
+    hnchw = [torch.empty((B, AC, h, h), device=dev) for h in grids]
+    state = {"i": 0}
+
+    def fused(stages):
+        def f():
+            state["i"] += 1
+            pp.from_features(ring[state["i"] % 3], weights, stages=stages, out=res)
+        return f
+
+    def cudnn():
+        state["i"] += 1
+        for x, ww, o, oc in zip(ring[state["i"] % 3], wcl, hcl, hnchw):
+            torch.ops.aten.convolution.out(x, ww, None, [1, 1], [0, 0], [1, 1], False, [0, 0], 1, out=o)
+            oc.copy_(o)                      # the contiguous NCHW head the reference's decode (and D1) reads
+
+    def unfused():
+        cudnn()
+        pp(hnchw, out=res)
+
+    def timed(fn, per_graph=6, n=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for _ in range(per_graph):
+                fn()
+        gr.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            gr.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (n * per_graph)
+
+    t_f1, t_chain = timed(fused(("decode",))), timed(fused(("decode", "sort", "nms")))
+    t_conv, t_unf = timed(cudnn), timed(unfused)
+    feat_bytes = sum(B * c * h * h * 4 for c, h in zip(cins, grids))
+    cand = float(res.cand_count.float().mean().item())
+    alg = feat_bytes + sum(AC * c * 4 for c in cins) + 28.0 * cand * B
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak = float(json.load(open(peaks_path))["hbm_gbs"]) if os.path.exists(peaks_path) else 6650.0
+    return {"kernel": "ypp_head_decode_kernel (F1: TMA + tcgen05 kind::tf32 + TMEM epilogue)", "cin": list(cins),
+            "f1_ms": t_f1, "f1_gb_per_s": alg / (t_f1 * 1e-3) / 1e9, "f1_frac_of_hbm_peak": alg / (t_f1 * 1e-3) / 1e9 / peak,
+            "algorithmic_bytes": alg, "fused_chain_ms": t_chain, "fused_chain_images_per_s": B / (t_chain * 1e-3),
+            "cudnn_conv_plus_nchw_copy_ms": t_conv, "cudnn_plus_unfused_chain_ms": t_unf,
+            "cudnn_plus_unfused_images_per_s": B / (t_unf * 1e-3), "candidates_per_image": cand,
+            "allow_tf32": bool(torch.backends.cudnn.allow_tf32),
+            "what": "input of the heads' 1x1 convs [B,H,W,Cin] fp32 resident in HBM -> kept rows; CUDA-graph timed"}
 
 
 if __name__ == "__main__":

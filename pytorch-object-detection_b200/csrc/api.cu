@@ -209,7 +209,7 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
                         img_idx_base, nullptr, true, true, (cudaStream_t)stream);
 }
 
-// the heads' 1x1 convolutions fused with D1: one tcgen05 kernel per scale writes the slot records
+// the heads' 1x1 convolutions fused with D1: one tcgen05 kernel over every scale writes the slot records
 static int head_decode_all(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
                            YppDecodeParams* p, cudaStream_t st)
 {
@@ -220,9 +220,12 @@ static int head_decode_all(const ypp_cfg* cfg, const ypp_scale* scales, const yp
         if (!src[i].feature || !src[i].weight || src[i].cin < 1) { ypp_set_error("scale %d: feature / weight / cin missing", i); return YPP_E_BADARG; }
     rc = bind_ws(cfg->B, p->N, cfg->nc, ws, ws_bytes, &p->ws);
     if (rc) return rc;
-    for (int i = 0; i < cfg->n_scales && !rc; ++i)
-        rc = ypp_launch_head_decode(*p, cfg->B, i, src[i].feature, src[i].weight, src[i].cin, src[i].head_out, st);
-    return rc;
+    const float* feat[YPP_MAX_SCALES];
+    const float* wgt[YPP_MAX_SCALES];
+    float* hout[YPP_MAX_SCALES];
+    int cin[YPP_MAX_SCALES];
+    for (int i = 0; i < cfg->n_scales; ++i) { feat[i] = src[i].feature; wgt[i] = src[i].weight; hout[i] = src[i].head_out; cin[i] = src[i].cin; }
+    return ypp_launch_head_decode(*p, cfg->B, feat, wgt, cin, hout, st);
 }
 
 int ypp_head_decode_compact(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,

@@ -8,9 +8,9 @@
 // decoded, thresholded and compacted straight out of tensor memory into the same slot records D1
 // writes, and S1 -> N1 -> G run unchanged.
 //
-// sm_100a design: one CTA per (image, 128 cells).  A = feature tile [128 cells x 32 channels] and
+// sm_100a design: one launch over every scale, one CTA per (image, 128 cells), widest scale first.  A = feature tile [128 cells x 32 channels] and
 // B = weight tile [N x 32 channels] (N = A(5+nc) rounded up to 16), both K-major, arrive by TMA
-// (cp.async.bulk.tensor, 128-byte swizzle) into a 4-stage ring; one thread issues
+// (cp.async.bulk.tensor, 128-byte swizzle) into a small ring of stages; one thread issues
 // tcgen05.mma.kind::tf32 (M 128, N, K 8) four times per stage into a TMEM accumulator and commits
 // the stage back to the producer; after the last commit four warps read their 32 TMEM lanes
 // (tcgen05.ld 32x32b), park the tile channel-major in the (now idle) ring and run D1's own
@@ -22,8 +22,10 @@
 #include "decode_common.cuh"
 #include <cuda.h>
 #include <cstdlib>
+#include <cstring>
 
-#define YPP_HEAD_STAGES 4
+#define YPP_HEAD_STAGES 4            /* most stages of the TMA ring */
+#define YPP_HEAD_DEFAULT_STAGES 2    /* 4 CTAs per SM with two stages each beat 2 CTAs with four (72 vs 77 us on C2) */
 #define YPP_HEAD_BM 128            /* cells per CTA = UMMA M = TMEM lanes */
 #define YPP_HEAD_BK 32             /* fp32 channels per stage row: 128 bytes = one swizzle span */
 #define YPP_HEAD_THREADS 192       /* warps 0-3 epilogue (TMEM lanes 32w..), 4 TMA producer, 5 MMA issuer + TMEM owner */
@@ -31,13 +33,20 @@
 
 struct YppHeadParams {
     YppDecodeParams d;
-    int si;                 // the scale this launch handles
-    int cin;                // input channels (K)
+    int order[YPP_MAX_SCALES];          // scales in the order their tiles are handed out (most input channels first)
+    int tile_start[YPP_MAX_SCALES + 1]; // blockIdx.x ranges of order[0], order[1], ...
+    int cin[YPP_MAX_SCALES];            // input channels (K) per scale
+    float* head_out[YPP_MAX_SCALES];    // optional [B, ac, H, W]: the head tensor itself
     int ac;                 // A * (5 + nc): real output channels
     int n_pad;              // UMMA N: ac rounded up to a multiple of 16
     int tmem_cols;          // power of two >= max(32, n_pad)
+    int stages;             // depth of the TMA ring (<= YPP_HEAD_STAGES)
     u32 idesc;              // tcgen05 instruction descriptor (tf32 x tf32 -> f32, K-major A and B, M 128, N n_pad)
-    float* head_out;        // optional [B, ac, H, W]: the head tensor itself
+};
+
+struct YppHeadMaps {
+    CUtensorMap a[YPP_MAX_SCALES];      // features [B][HW][Cin], box 1 x 128 x 32
+    CUtensorMap b[YPP_MAX_SCALES];      // weight [ac][Cin], box n_pad x 32
 };
 
 namespace {
@@ -80,18 +89,25 @@ __device__ __forceinline__ void tmem_ld16(u32 taddr, u32 (&v)[16])
 }
 
 __global__ void __launch_bounds__(YPP_HEAD_THREADS)
-ypp_head_decode_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                       const __grid_constant__ YppHeadParams hp)
+ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_constant__ YppHeadParams hp)
 {
     extern __shared__ unsigned char ring_raw[];
     __shared__ __align__(8) u64 full[YPP_HEAD_STAGES], empty[YPP_HEAD_STAGES], accum;
     __shared__ u32 tmem_slot;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const YppDecodeParams& p = hp.d;
-    const YppScaleParams& s = p.sc[hp.si];
-    const int b = blockIdx.y, cell0 = blockIdx.x * YPP_HEAD_BM;
+    int oi = 0;
+#pragma unroll
+    for (int k = 1; k < YPP_MAX_SCALES; ++k)
+        if (k < p.n_scales && (int)blockIdx.x >= hp.tile_start[k]) oi = k;
+    const int si = hp.order[oi];
+    const YppScaleParams& s = p.sc[si];
+    const CUtensorMap* tm_a = &tm.a[si];
+    const CUtensorMap* tm_b = &tm.b[si];
+    const int b = blockIdx.y, cell0 = ((int)blockIdx.x - hp.tile_start[oi]) * YPP_HEAD_BM;
     const bool has_cells = cell0 < s.HW;                     // 2 * tpp tiles per plane cover every D1 slot, some past the end
-    const int nk = (hp.cin + YPP_HEAD_BK - 1) / YPP_HEAD_BK;
+    const int nk = (hp.cin[si] + YPP_HEAD_BK - 1) / YPP_HEAD_BK;
+    const int nst = hp.stages;
     const u32 stage_bytes = YPP_HEAD_A_BYTES + (u32)hp.n_pad * (YPP_HEAD_BK * 4);
     unsigned char* ring = ring_raw + ((1024u - (smem_u32(ring_raw) & 1023u)) & 1023u);      // swizzle atoms are 1024-byte aligned
     const u32 ring_addr = smem_u32(ring);
@@ -113,17 +129,17 @@ ypp_head_decode_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
     if (has_cells && warp == 4 && lane == 0) {
         // ---------------- TMA producer
         for (int kc = 0; kc < nk; ++kc) {
-            const int st = kc % YPP_HEAD_STAGES, use = kc / YPP_HEAD_STAGES;
+            const int st = kc % nst, use = kc / nst;
             if (use > 0) mbar_wait(&empty[st], (u32)(use - 1) & 1u);
             mbar_expect_tx(&full[st], stage_bytes);
             const u32 dst = ring_addr + (u32)st * stage_bytes;
-            tma_load_3d(dst, &tm_a, kc * YPP_HEAD_BK, cell0, b, &full[st]);              // cells past H*W arrive as zeros
-            tma_load_2d(dst + YPP_HEAD_A_BYTES, &tm_b, kc * YPP_HEAD_BK, 0, &full[st]);   // rows past ac arrive as zeros
+            tma_load_3d(dst, tm_a, kc * YPP_HEAD_BK, cell0, b, &full[st]);              // cells past H*W arrive as zeros
+            tma_load_2d(dst + YPP_HEAD_A_BYTES, tm_b, kc * YPP_HEAD_BK, 0, &full[st]);   // rows past ac arrive as zeros
         }
     } else if (has_cells && warp == 5 && lane == 0) {
         // ---------------- MMA issuer
         for (int kc = 0; kc < nk; ++kc) {
-            const int st = kc % YPP_HEAD_STAGES, use = kc / YPP_HEAD_STAGES;
+            const int st = kc % nst, use = kc / nst;
             mbar_wait(&full[st], (u32)use & 1u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const u32 a_addr = ring_addr + (u32)st * stage_bytes, b_addr = a_addr + YPP_HEAD_A_BYTES;
@@ -148,9 +164,10 @@ ypp_head_decode_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
                     if (j * 16 + i < hp.ac) stg[(j * 16 + i) * YPP_HEAD_BM + ct] = __uint_as_float(v[i]);
             }
             __syncwarp();
-            if (hp.head_out != nullptr && cell < s.HW)
+            float* ho = hp.head_out[si];
+            if (ho != nullptr && cell < s.HW)
                 for (int c = 0; c < hp.ac; ++c)
-                    hp.head_out[((size_t)b * hp.ac + c) * s.HW + cell] = stg[c * YPP_HEAD_BM + ct];
+                    ho[((size_t)b * hp.ac + c) * s.HW + cell] = stg[c * YPP_HEAD_BM + ct];
         }
         const int nslots = p.tile_base[p.n_scales] * (YPP_TILE_BOXES / 32);
         const int wslot = ((cell0 & (YPP_TILE_BOXES - 1)) >> 5) + warp;
@@ -158,7 +175,7 @@ ypp_head_decode_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_co
             Decoded d;
             d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
             const bool pass = decode_one<1>(p, s, a, cell, cell < s.HW, stg + a * p.C * YPP_HEAD_BM + ct, YPP_HEAD_BM, 0, 0, d);
-            const int tile = p.tile_base[hp.si] + a * s.tpp + cell0 / YPP_TILE_BOXES;
+            const int tile = p.tile_base[si] + a * s.tpp + cell0 / YPP_TILE_BOXES;
             const int first = s.box_base + a * s.HW + cell0;
             slot_store(p.ws, p.N, b, tile * (YPP_TILE_BOXES / 32) + wslot, nslots, first + 32 * warp, pass,
                        d.box, d.score, d.cls, first + ct);
@@ -189,45 +206,64 @@ EncodeTiledFn encode_tiled()
 
 }  // namespace
 
-int ypp_launch_head_decode(const YppDecodeParams& p, int B, int si, const float* feature, const float* weight, int cin,
-                           float* head_out, cudaStream_t st)
+int ypp_launch_head_decode(const YppDecodeParams& p, int B, const float* const* feature, const float* const* weight,
+                           const int* cin, float* const* head_out, cudaStream_t st)
 {
-    const YppScaleParams& s = p.sc[si];
-    const int ac = s.A * p.C;
+    const int A = p.sc[0].A;
+    const int ac = A * p.C;
     const int n_pad = (ac + 15) & ~15;
     if (n_pad > 256) { ypp_set_error("head_decode: A*(5+nc) = %d exceeds one UMMA tile (256)", ac); return YPP_E_UNSUPPORTED; }
-    if (cin < 4 || (cin & 3) != 0) { ypp_set_error("head_decode: Cin = %d must be a positive multiple of 4", cin); return YPP_E_UNSUPPORTED; }
-    if (((uintptr_t)feature & 15u) != 0 || ((uintptr_t)weight & 15u) != 0) { ypp_set_error("head_decode: feature / weight must be 16-byte aligned"); return YPP_E_BADARG; }
     EncodeTiledFn enc = encode_tiled();
     if (!enc) { ypp_set_error("head_decode: cuTensorMapEncodeTiled is not available from this driver"); return YPP_E_CUDA; }
-    CUtensorMap tm_a, tm_b;
-    {   // features [B][HW][Cin], box 1 x 128 x 32
-        const cuuint64_t dims[3] = {(cuuint64_t)cin, (cuuint64_t)s.HW, (cuuint64_t)B};
-        const cuuint64_t strides[2] = {(cuuint64_t)cin * 4, (cuuint64_t)s.HW * cin * 4};
-        const cuuint32_t box[3] = {YPP_HEAD_BK, YPP_HEAD_BM, 1}, es[3] = {1, 1, 1};
-        const CUresult r = enc(&tm_a, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)feature, dims, strides, box, es,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the features failed (%d)", (int)r); return YPP_E_CUDA; }
-    }
-    {   // weight [ac][Cin], box n_pad x 32
-        const cuuint64_t dims[2] = {(cuuint64_t)cin, (cuuint64_t)ac};
-        const cuuint64_t strides[1] = {(cuuint64_t)cin * 4};
-        const cuuint32_t box[2] = {YPP_HEAD_BK, (cuuint32_t)n_pad}, es[2] = {1, 1};
-        const CUresult r = enc(&tm_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)weight, dims, strides, box, es,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the weight failed (%d)", (int)r); return YPP_E_CUDA; }
-    }
+    YppHeadMaps tm;
+    memset(&tm, 0, sizeof(tm));
     YppHeadParams hp;
+    memset(&hp, 0, sizeof(hp));
     hp.d = p;
-    hp.si = si; hp.cin = cin; hp.ac = ac; hp.n_pad = n_pad;
+    for (int i = 0; i < p.n_scales; ++i) {
+        const YppScaleParams& s = p.sc[i];
+        if (s.A != A) { ypp_set_error("head_decode: every scale must have the same number of anchors"); return YPP_E_UNSUPPORTED; }
+        if (cin[i] < 4 || (cin[i] & 3) != 0) { ypp_set_error("head_decode: Cin = %d must be a positive multiple of 4", cin[i]); return YPP_E_UNSUPPORTED; }
+        if (((uintptr_t)feature[i] & 15u) != 0 || ((uintptr_t)weight[i] & 15u) != 0) { ypp_set_error("head_decode: feature / weight must be 16-byte aligned"); return YPP_E_BADARG; }
+        {   // features [B][HW][Cin], box 1 x 128 x 32
+            const cuuint64_t dims[3] = {(cuuint64_t)cin[i], (cuuint64_t)s.HW, (cuuint64_t)B};
+            const cuuint64_t strides[2] = {(cuuint64_t)cin[i] * 4, (cuuint64_t)s.HW * cin[i] * 4};
+            const cuuint32_t box[3] = {YPP_HEAD_BK, YPP_HEAD_BM, 1}, es[3] = {1, 1, 1};
+            const CUresult r = enc(&tm.a[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)feature[i], dims, strides, box, es,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the features failed (%d)", (int)r); return YPP_E_CUDA; }
+        }
+        {   // weight [ac][Cin], box n_pad x 32
+            const cuuint64_t dims[2] = {(cuuint64_t)cin[i], (cuuint64_t)ac};
+            const cuuint64_t strides[1] = {(cuuint64_t)cin[i] * 4};
+            const cuuint32_t box[2] = {YPP_HEAD_BK, (cuuint32_t)n_pad}, es[2] = {1, 1};
+            const CUresult r = enc(&tm.b[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)weight[i], dims, strides, box, es,
+                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) { ypp_set_error("head_decode: tensor map of the weight failed (%d)", (int)r); return YPP_E_CUDA; }
+        }
+        hp.cin[i] = cin[i];
+        hp.head_out[i] = head_out ? head_out[i] : nullptr;
+        hp.order[i] = i;
+    }
+    // the longest K loops first: their CTAs run longest, the short ones fill the tail
+    for (int i = 1; i < p.n_scales; ++i)
+        for (int j = i; j > 0 && hp.cin[hp.order[j]] > hp.cin[hp.order[j - 1]]; --j) { const int t = hp.order[j]; hp.order[j] = hp.order[j - 1]; hp.order[j - 1] = t; }
+    int tiles = 0;
+    for (int i = 0; i < p.n_scales; ++i) { hp.tile_start[i] = tiles; tiles += 2 * p.sc[hp.order[i]].tpp; }
+    for (int i = p.n_scales; i <= YPP_MAX_SCALES; ++i) hp.tile_start[i] = tiles;
+    hp.ac = ac; hp.n_pad = n_pad;
     hp.tmem_cols = 32;
     while (hp.tmem_cols < n_pad) hp.tmem_cols <<= 1;
+    static int stages_env = -1;
+    if (stages_env < 0) { const char* e = getenv("YPP_HEAD_STAGES"); stages_env = e ? atoi(e) : 0; }
+    hp.stages = stages_env >= 1 && stages_env <= YPP_HEAD_STAGES ? stages_env : YPP_HEAD_DEFAULT_STAGES;
     // c_format f32 (1 << 4), a/b format tf32 (2 << 7, 2 << 10), K-major both, N >> 3 at bit 17, M >> 4 at bit 24
     hp.idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((u32)(n_pad >> 3) << 17) | ((u32)(YPP_HEAD_BM >> 4) << 24);
-    hp.head_out = head_out;
-    const int smem = YPP_HEAD_STAGES * (YPP_HEAD_A_BYTES + n_pad * YPP_HEAD_BK * 4) + 1024;
+    int smem = hp.stages * (YPP_HEAD_A_BYTES + n_pad * YPP_HEAD_BK * 4);
+    if (smem < ac * YPP_HEAD_BM * 4) smem = ac * YPP_HEAD_BM * 4;        // the epilogue parks the whole tile in the ring
+    smem += 1024;
     static int configured_d[YPP_MAX_DEVICES];
     int dev = 0;
     cudaGetDevice(&dev);
@@ -237,8 +273,8 @@ int ypp_launch_head_decode(const YppDecodeParams& p, int B, int si, const float*
         if (e != cudaSuccess) { ypp_set_error("head_decode: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
         configured_d[dev] = smem;
     }
-    dim3 grid(2 * s.tpp, B);
-    ypp_head_decode_kernel<<<grid, YPP_HEAD_THREADS, smem, st>>>(tm_a, tm_b, hp);
+    dim3 grid(tiles, B);
+    ypp_head_decode_kernel<<<grid, YPP_HEAD_THREADS, smem, st>>>(tm, hp);
     ypp_count_launch(1);
     return ypp_check_launch("head_decode");
 }

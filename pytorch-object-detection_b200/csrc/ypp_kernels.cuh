@@ -63,8 +63,8 @@ struct YppGatherParams {
 };
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st);
-int ypp_launch_head_decode(const YppDecodeParams& p, int B, int si, const float* feature, const float* weight, int cin,
-                           float* head_out, cudaStream_t st);
+int ypp_launch_head_decode(const YppDecodeParams& p, int B, const float* const* feature, const float* const* weight,
+                           const int* cin, float* const* head_out, cudaStream_t st);
 int ypp_launch_decode_dense(const YppDecodeParams& p, int B, float* out, cudaStream_t st);
 int ypp_launch_rows_compact(const float* rows, int B, int N, float conf, const YppWs& ws, cudaStream_t st);
 int ypp_launch_pred_compact(const float* pred, int B, int n_boxes, int nc, float conf, int multi_label,

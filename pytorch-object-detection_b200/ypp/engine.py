@@ -80,8 +80,9 @@ class PostProcessor:
 
     def __init__(self, num_classes, anchors, input_size, conf_threshold=0.25, iou_threshold=0.45,
                  kind="v3", anchors_per_scale=None, offset_mode="auto_cuda", union_mode="fma",
-                 score_mode="obj", compare_in_double=None):
+                 score_mode="obj", compare_in_double=None, ws_tag="post"):
         self.num_classes = int(num_classes)
+        self.ws_tag = ws_tag            # scratch buffer name: processors used from different streams need their own
         self.anchors = [list(map(float, a)) for a in anchors]
         self.input_size = input_size
         self.conf_threshold = float(conf_threshold)
@@ -181,7 +182,7 @@ class PostProcessor:
         L = lib()
         if nbytes is None:
             nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
-        ws = _workspace(nbytes, dev, "post")
+        ws = _workspace(nbytes, dev, self.ws_tag)
         if dev.index is not None and dev.index != torch.cuda.current_device():
             with torch.cuda.device(dev):
                 return self.__call__(heads, img_idx_base, row_width, want_keep_idx, res)
@@ -242,7 +243,7 @@ class PostProcessor:
         res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
         cfg = self._cfg(B, n)
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, "post")
+        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
         with torch.cuda.device(dev):
             if tuple(stages) == ("decode", "sort", "nms"):
                 check(L.ypp_head_postprocess(ctypes.byref(cfg), arr, src, _ptr(ws), ws.numel(), _ptr(res.cand_count),
@@ -290,7 +291,7 @@ class PostProcessor:
         res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
         cfg = self._cfg(B, len(heads))
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, "post")
+        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
         with torch.cuda.device(dev):
             if "decode" in stages:
                 check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
@@ -322,7 +323,7 @@ class PostProcessor:
         res = self._outputs(B, N, dev, row_width, want_keep_idx, None)
         cfg = self._cfg(B, 1)
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, N, self.num_classes), dev, "post")
+        ws = _workspace(L.ypp_workspace_bytes(B, N, self.num_classes), dev, self.ws_tag)
         with torch.cuda.device(dev):
             check(L.ypp_nms_rows(ctypes.byref(cfg), _ptr(rows), N, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                  _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
@@ -451,7 +452,7 @@ def nms_ultralytics(prediction: torch.Tensor, conf_thres=0.25, iou_thres=0.45, c
                      cand_count=torch.empty(B, dtype=torch.int32, device=dev),
                      keep_idx=torch.empty((B, rows), dtype=torch.int32, device=dev) if want_keep_idx else None,
                      n_boxes=rows)
-    ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, "post")
+    ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, self.ws_tag)
     with torch.cuda.device(dev):
         check(L.ypp_nms_ultralytics(ctypes.byref(cfg), _ptr(pred), n, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                     _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), row_width,

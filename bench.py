@@ -36,6 +36,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the sparse-regime and mAP epoch extras")
     ap.add_argument("--ring", type=int, default=4, help="distinct input batches cycled through (> L2 in total)")
+    ap.add_argument("--in-flight", type=int, default=2,
+                    help="steps in flight: each on its own stream with its own workspace and outputs (must divide --ring)")
     return ap.parse_args()
 
 
@@ -48,6 +50,7 @@ def workload_config(args, w, n_gpus):
         "boxes_per_image": synth.boxes_per_image(w["grids"], w["A"]), "num_classes": w["nc"],
         "conf_threshold": w["conf"], "iou_threshold": 0.45,
         "parallelism": "image-sharded x%d, no data-path collective" % n_gpus,
+        "steps_in_flight": max(1, args.in_flight),
         "l2_policy": "inputs larger than L2: ring of %d distinct batches (%.0f MB) cycled" % (
             args.ring, args.ring * w["batch"] * synth.head_bytes_per_image(w["nc"], w["grids"], w["A"]) / 1e6),
     }
@@ -247,20 +250,46 @@ def run_ours(args):
     # ---- value: K steps, inputs resident in HBM, CUDA events on the launching stream.
     # Each step replays the CUDA graph of the chain captured on that ring entry (PostProcessor.graphed):
     # the chain is 6 short launches, so eager launches would time the host, not the GPU.
+    # NS steps are in flight at a time, each on its own stream with its own workspace and output buffers: S1 is one
+    # CTA per image (64 of the 148 SMs at batch 64), so the neighbouring step's kernels fill the rest of the machine.
+    NS = max(1, args.in_flight)
+    if args.ring % NS != 0:
+        raise SystemExit("bench.py: --in-flight must divide --ring")
+    pps = [pp] + [engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A,
+                                       ws_tag="post%d" % k) for k in range(1, NS)]
     engine.launch_count(True)
-    graphs = [pp.graphed(hs) for hs in ring]
+    graphs = [pps[i % NS].graphed(hs) for i, hs in enumerate(ring)]
     launches_per_step = engine.launch_count(True) // (2 * len(ring))      # warm-up call + captured call
     res = graphs[0][1]
-    for i in range(W):
-        graphs[i % args.ring][0].replay()
+    streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
+    main = torch.cuda.current_stream()
+
+    def run_steps(n):
+        """n steps, step i on stream i % NS (ring entry i % ring was captured with that stream's workspace)."""
+        for st in streams:
+            st.wait_stream(main)
+        for i in range(n):
+            with torch.cuda.stream(streams[i % NS]):
+                graphs[i % args.ring][0].replay()
+        for st in streams:
+            main.wait_stream(st)
+
+    run_steps(W)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # one step at a time on one stream (the latency of a step), before the clocks are sampled
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(K):
+        graphs[i % args.ring][0].replay()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_single = e0.elapsed_time(e1) / K
     sampler = ClockSampler(local) if rank == 0 else None
     barrier()
     if sampler:
         sampler.start()
     e0.record()
-    for i in range(K):
-        graphs[i % args.ring][0].replay()
+    run_steps(K)
     e1.record()
     torch.cuda.synchronize()
     launches = launches_per_step * K
@@ -399,6 +428,8 @@ def run_ours(args):
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "cpu_baseline": cpu, "stage_ms": stage_ms,
+                "single_stream": {"ms_per_step": ms_single, "value": world * B / (ms_single * 1e-3), "unit": UNIT,
+                                  "what": "the same K steps one at a time on one stream: the latency of a step"},
                 "per_image": {"candidates": cand_per_img, "kept": kept_per_img}}
         line.update(extras)
         print(json.dumps(line))

@@ -452,7 +452,7 @@ def nms_ultralytics(prediction: torch.Tensor, conf_thres=0.25, iou_thres=0.45, c
                      cand_count=torch.empty(B, dtype=torch.int32, device=dev),
                      keep_idx=torch.empty((B, rows), dtype=torch.int32, device=dev) if want_keep_idx else None,
                      n_boxes=rows)
-    ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, self.ws_tag)
+    ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, "post")
     with torch.cuda.device(dev):
         check(L.ypp_nms_ultralytics(ctypes.byref(cfg), _ptr(pred), n, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                     _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), row_width,

@@ -228,15 +228,17 @@ __device__ unsigned long long ypp_sp_stats[16];
 #define SP_CLOCK(var)
 #endif
 
+template <int kBins>
 __device__ __forceinline__ int sp_bin(const float x, const float xmin, const float inv)
 {
     const float v = __fmul_rn(__fsub_rn(x, xmin), inv);          // monotone in x; NaN (0 * inf) -> bin 0
-    return (int)fminf(fmaxf(v, 0.0f), (float)(YPP_SP_BINS - 1));
+    return (int)fminf(fmaxf(v, 0.0f), (float)(kBins - 1));
 }
+template <int kBins>
 __device__ __forceinline__ int sp_bin_end(const float x, const float xmin, const float inv)
 {
     const float v = __fmul_rn(__fsub_rn(x, xmin), inv);          // >= sp_bin(x); NaN -> last bin
-    return !(v < (float)YPP_SP_BINS) ? YPP_SP_BINS - 1 : max((int)v, 0);
+    return !(v < (float)kBins) ? kBins - 1 : max((int)v, 0);
 }
 
 // hist[256] -> exclusive offsets in place (the scatter cursors); optionally kept in bstart as well
@@ -341,7 +343,7 @@ __device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size
     int mybin[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-        mybin[u] = sp_bin(q[u].x, xmin, inv);
+        mybin[u] = sp_bin<YPP_SP_BINS>(q[u].x, xmin, inv);
         if (tid + u * YPP_NMSQ_THREADS < len) atomicAdd(&S.hist[mybin[u]], 1u);
     }
     __syncthreads();
@@ -371,7 +373,7 @@ __device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size
         if (pr < len) {
             const float4 a = sm.box[pr];
             const float xe = __fadd_ru(a.x, __fmul_ru(ct, __fsub_ru(a.z, a.x)));
-            const int cend = S.bstart[sp_bin_end(xe, xmin, inv) + 1];
+            const int cend = S.bstart[sp_bin_end<YPP_SP_BINS>(xe, xmin, inv) + 1];
             const int cnt = max(cend - pr - 1, 0);
             mybin[u] = YPP_SP_BINS - 1 - min(cnt >> 1, YPP_SP_BINS - 1);
             myrow[u] = (u32)pr | ((u32)cend << 16);
@@ -724,6 +726,170 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
     }
 }
 
+// ---- sweep-and-prune for long segments -----------------------------------------------------
+// The same idea as nms_sparse for the segments the 1024-thread CTAs own (single-class heads, merged
+// classes): x1 counting sort into YPP_BSP_BINS bins, per-box range from the IoU bound, lean pair test,
+// edge list, fix-point.  At these lengths every range is long, so every box is swept by a warp (lanes
+// over its range); the boxes live in the dynamic shared memory the tile sweeps use as their cache
+// (19 + 3 bytes per box: up to YPP_BSP_MAX boxes).  Returns false with nothing written when the
+// segment is too long, holds a box that is not ordinary, overflows the edge list or resolves too
+// deep; nms_segment (tile sweeps) then takes it.
+#define YPP_BSP_BINS 1024
+#define YPP_BIG_SMEM_MAX (222 * 1024)  /* dynamic shared memory of the long-segment kernel */
+#define YPP_BSP_EDGES 4096
+#define YPP_BSP_FIXED (4 * YPP_BSP_EDGES + 4 * YPP_BSP_BINS + 2 * (YPP_BSP_BINS + 2) + 64)
+
+struct BigSparseHdr {
+    u32 xlo, xhi, amax, cmax;
+    int nedges, odd;
+    int wtot[YPP_NMS_BIG_THREADS / 32];
+};
+
+template <bool kFma>
+__device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __restrict__ grank,
+                               unsigned char* __restrict__ keepflag, const int len, unsigned char* smem,
+                               const int smem_bytes, BigSparseHdr& H, const float thr, int& kept_total)
+{
+    constexpr int T = YPP_NMS_BIG_THREADS;
+    static_assert(T == YPP_BSP_BINS, "the bin scan gives every thread one bin");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if ((long long)len * 21 + YPP_BSP_FIXED > smem_bytes || len > 65535) return false;      // uniform
+    // carve: boxes | edges | hist | bstart | rk | state | pend | kill
+    float4* box = reinterpret_cast<float4*>(smem);
+    u32* edges = reinterpret_cast<u32*>(smem + (size_t)len * 16);
+    u32* hist = edges + YPP_BSP_EDGES;
+    unsigned short* bstart = reinterpret_cast<unsigned short*>(hist + YPP_BSP_BINS);
+    unsigned short* rk = bstart + YPP_BSP_BINS + 2;
+    unsigned char* state = reinterpret_cast<unsigned char*>(rk + len + (len & 1));
+    unsigned char* pend = state + len;
+    unsigned char* kill = pend + len;
+    if (tid == 0) { H.xlo = 0xffffffffu; H.xhi = 0u; H.amax = 0u; H.cmax = 0u; H.nedges = 0; H.odd = 0; }
+    for (int i = tid; i < YPP_BSP_BINS; i += T) hist[i] = 0;
+    __syncthreads();
+    // ---- pass 1: ordinary? x1 range, largest |area| and |coordinate|
+    {
+        bool odd = false;
+        u32 xlo = 0xffffffffu, xhi = 0u, amax_bits = 0u, cmax_bits = 0u;
+        for (int i = tid; i < len; i += T) {
+            const float4 q = seg[i];
+            const float bw = __fsub_rn(q.z, q.x), bh = __fsub_rn(q.w, q.y);
+            odd |= !(bw > 0.0f && bh > 0.0f && bw < INFINITY && bh < INFINITY && fabsf(q.x) < INFINITY && fabsf(q.y) < INFINITY);
+            const u32 e = ypp_enc(q.x);
+            xlo = min(xlo, e); xhi = max(xhi, e);
+            amax_bits = max(amax_bits, __float_as_uint(fabsf(__fmul_rn(bw, bh))));
+            cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
+                            max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
+        }
+        xlo = __reduce_min_sync(YPP_FULL_MASK, xlo);
+        xhi = __reduce_max_sync(YPP_FULL_MASK, xhi);
+        amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
+        cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
+        if (lane == 0) {
+            atomicMin(&H.xlo, xlo); atomicMax(&H.xhi, xhi); atomicMax(&H.amax, amax_bits); atomicMax(&H.cmax, cmax_bits);
+        }
+        if (__syncthreads_or(odd)) return false;
+    }
+    const float Bseg = 2.0f * YPP_PAIR_BAND * __uint_as_float(H.amax);
+    const int cexp = (int)(H.cmax >> 23);
+    if (cexp < 67 || cexp > 187 || !(Bseg < INFINITY)) return false;                     // uniform
+    const float scale = __uint_as_float((u32)(252 - cexp) << 23);
+    const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cexp + 2) << 23));
+    const float xmin = ypp_dec(H.xlo), xmax = ypp_dec(H.xhi);
+    const float inv = __fdiv_rn((float)YPP_BSP_BINS, __fsub_rn(xmax, xmin));
+    // ---- pass 2: histogram, scan (one bin per thread), pass 3: scatter
+    for (int i = tid; i < len; i += T) atomicAdd(&hist[sp_bin<YPP_BSP_BINS>(seg[i].x, xmin, inv)], 1u);
+    __syncthreads();
+    {
+        const int h = (int)hist[tid];
+        int incl = h;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(YPP_FULL_MASK, incl, d);
+            if (lane >= d) incl += o;
+        }
+        if (lane == 31) H.wtot[warp] = incl;
+        __syncthreads();
+        int off = incl - h;
+        for (int k = 0; k < warp; ++k) off += H.wtot[k];
+        bstart[tid] = (unsigned short)off;
+        if (tid == 0) bstart[YPP_BSP_BINS] = (unsigned short)len;
+        hist[tid] = (u32)off;
+    }
+    __syncthreads();
+    for (int i = tid; i < len; i += T) {
+        const float4 q = seg[i];
+        const int pos = (int)atomicAdd(&hist[sp_bin<YPP_BSP_BINS>(q.x, xmin, inv)], 1u);
+        box[pos] = q;
+        rk[pos] = (unsigned short)i;
+        state[i] = 0; pend[i] = 0; kill[i] = 0;
+    }
+    __syncthreads();
+    // ---- sweep: a warp per box, lanes over its range
+    {
+        const float ct = __fsub_ru(1.0f, __fmul_rd(0.9f, thr));
+        const float nthr = -thr;
+        for (int pr = warp; pr < len; pr += T / 32) {
+            if (*(volatile int*)&H.nedges >= YPP_BSP_EDGES) break;
+            const float4 a = box[pr];
+            const float xe = __fadd_ru(a.x, __fmul_ru(ct, __fsub_ru(a.z, a.x)));
+            const int cend = bstart[sp_bin_end<YPP_BSP_BINS>(xe, xmin, inv) + 1];
+            const float ta = __fmul_rn(nthr, fabsf(ypp_area(a)));
+            const int ra = rk[pr];
+            for (int c = pr + 1 + lane; c < cend; c += 32) {
+                const float4 bq = box[c];
+                const float D = __fadd_rn(pair_g(a, ta, bq, c1k, scale), __fmul_rn(nthr, fabsf(ypp_area(bq))));
+                if (D < -Bseg) continue;
+                const int rb = rk[c];
+                bool dead = D > Bseg;
+                if (!dead) {
+                    const bool a_first = ra < rb;
+                    const float4 hi = a_first ? a : bq, lo = a_first ? bq : a;
+                    dead = pair_exact(hi, ypp_area(hi), lo, thr, kFma ? 1 : 0);
+                }
+                if (dead) {
+                    const int e = atomicAdd(&H.nedges, 1);
+                    if (e < YPP_BSP_EDGES) edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int ne = H.nedges;
+    if (ne > YPP_BSP_EDGES) return false;
+    // ---- greedy order over the edges
+    bool settled = ne == 0;
+    for (int round = 0; !settled && round < YPP_SP_ROUNDS; ++round) {
+        for (int e = tid; e < ne; e += T) {
+            const u32 ed = edges[e];
+            const int st = state[ed >> 16];
+            if (st == 1) kill[ed & 0xffffu] = 1;
+            else if (st == 0) pend[ed & 0xffffu] = 1;
+        }
+        __syncthreads();
+        bool open = false;
+        for (int i = tid; i < len; i += T) {
+            if (state[i] == 0) {
+                if (kill[i]) state[i] = 2;
+                else if (!pend[i]) state[i] = 1;
+                else open = true;
+            }
+            pend[i] = 0;
+        }
+        settled = !__syncthreads_or(open);
+    }
+    if (!settled) return false;
+    int kept = 0;
+    for (int i = tid; i < len; i += T)
+        if (state[i] != 2) { keepflag[grank[i]] = 1; ++kept; }
+    kept = __reduce_add_sync(YPP_FULL_MASK, kept);
+    if (lane == 0) H.wtot[warp] = kept;
+    __syncthreads();
+    kept_total = 0;
+    for (int k = 0; k < T / 32; ++k) kept_total += H.wtot[k];
+    __syncthreads();                              // the shared memory is reused by the CTA's next segment
+    return true;
+}
+
 // persistent CTAs walk the per-image lists of long segments S1 left (bigq[b][0 .. bigcnt[b]))
 template <bool kFast, bool kFma>
 __global__ void __launch_bounds__(YPP_NMS_BIG_THREADS, 1)
@@ -733,6 +899,7 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
     float4* cache = reinterpret_cast<float4*>(smem_raw);
     u32* removed = reinterpret_cast<u32*>(smem_raw + sizeof(float4) * YPP_BIG_CACHE);
     __shared__ TileSmem ts;
+    __shared__ BigSparseHdr bsh;
     ypp_grid_wait();
     const int per = p.ws.bigq_per_image;
     {   // nearly always there is nothing to do: find out with one round of loads
@@ -752,6 +919,15 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
             const float step = p.ws.img_step[b];
             for (int i = threadIdx.x; i < len; i += YPP_NMS_BIG_THREADS)
                 p.ws.sbox[base + s0 + i] = rank_box(p.ws, base, p.ws.grank[base + s0 + i], trick, step);
+            __syncthreads();
+        }
+        if (kFast && p.iou_thr >= 0.0f && p.sparse_min_len != 0x7fffffff) {
+            int kept = 0;
+            if (nms_big_sparse<kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0, p.ws.keepflag + base, len, smem_raw,
+                                     p.big_smem_bytes, bsh, p.iou_thr, kept)) {
+                if (threadIdx.x == 0 && kept) atomicAdd(p.ws.keep_count + b, kept);
+                continue;                                   // uniform over the CTA
+            }
             __syncthreads();
         }
         nms_segment<YPP_NMS_BIG_THREADS, kFast, kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
@@ -905,22 +1081,26 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
     int rc = ypp_check_launch("nms_seg");
     if (rc) return rc;
     if (p.N > YPP_WARP_SEG) {
-        const int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 4));
+        int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 4));
+        const int want = (int)((long long)p.N * 21 + YPP_BSP_FIXED);        // the sweep-and-prune layout for a whole image
+        if (smem < want) smem = want < YPP_BIG_SMEM_MAX ? want : YPP_BIG_SMEM_MAX;
         static bool configured_d[YPP_MAX_DEVICES];         // per device, like the attribute itself
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         if (dev < 0 || dev >= YPP_MAX_DEVICES) { ypp_set_error("nms_big: device ordinal %d out of range", dev); return YPP_E_UNSUPPORTED; }
         bool& configured = configured_d[dev];
         if (!configured) {
-            cudaError_t e = cudaFuncSetAttribute(ypp_nms_big_kernel<kFast, kFma>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+            cudaError_t e = cudaFuncSetAttribute(ypp_nms_big_kernel<kFast, kFma>, cudaFuncAttributeMaxDynamicSharedMemorySize, YPP_BIG_SMEM_MAX);
             if (e != cudaSuccess) { ypp_set_error("nms_big: cudaFuncSetAttribute failed: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
             configured = true;
         }
-        if (smem > 220 * 1024) { ypp_set_error("nms_big: %d boxes per image exceed the removed-bitmap budget", p.N); return YPP_E_UNSUPPORTED; }
+        if (smem > YPP_BIG_SMEM_MAX) { ypp_set_error("nms_big: %d boxes per image exceed the removed-bitmap budget", p.N); return YPP_E_UNSUPPORTED; }
         int ctas = p.B * p.ws.bigq_per_image;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         if (ctas > sms) ctas = sms;
-        ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, p);
+        YppNmsParams pb = p;
+        pb.big_smem_bytes = smem;
+        ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, pb);
         ypp_count_launch(1);
         rc = ypp_check_launch("nms_big");
     }

@@ -44,6 +44,7 @@ struct YppNmsParams {
     float iou_thr;
     int union_mode;
     int sparse_min_len;    // per-class segments at least this long try the sweep-and-prune path first
+    int big_smem_bytes;    // dynamic shared memory of the long-segment kernel (its sweep-and-prune path sizes itself by it)
 };
 
 struct YppGatherParams {

@@ -731,13 +731,13 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
 // classes): x1 counting sort into YPP_BSP_BINS bins, per-box range from the IoU bound, lean pair test,
 // edge list, fix-point.  At these lengths every range is long, so every box is swept by a warp (lanes
 // over its range); the boxes live in the dynamic shared memory the tile sweeps use as their cache
-// (19 + 3 bytes per box: up to YPP_BSP_MAX boxes).  Returns false with nothing written when the
+// (18 + 3 bytes per box, up to ~9700 boxes; the edge list takes the rest).  Returns false with nothing written when the
 // segment is too long, holds a box that is not ordinary, overflows the edge list or resolves too
 // deep; nms_segment (tile sweeps) then takes it.
 #define YPP_BSP_BINS 1024
 #define YPP_BIG_SMEM_MAX (222 * 1024)  /* dynamic shared memory of the long-segment kernel */
-#define YPP_BSP_EDGES 4096
-#define YPP_BSP_FIXED (4 * YPP_BSP_EDGES + 4 * YPP_BSP_BINS + 2 * (YPP_BSP_BINS + 2) + 64)
+#define YPP_BSP_MIN_EDGES 2048          /* the edge list takes whatever shared memory the boxes leave; at least this */
+#define YPP_BSP_FIXED (4 * YPP_BSP_BINS + 2 * (YPP_BSP_BINS + 2) + 64)
 
 struct BigSparseHdr {
     u32 xlo, xhi, amax, cmax;
@@ -753,16 +753,19 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
     constexpr int T = YPP_NMS_BIG_THREADS;
     static_assert(T == YPP_BSP_BINS, "the bin scan gives every thread one bin");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if ((long long)len * 21 + YPP_BSP_FIXED > smem_bytes || len > 65535) return false;      // uniform
-    // carve: boxes | edges | hist | bstart | rk | state | pend | kill
+    if (len > 65535) return false;                                                          // uniform
+    const long long spare = (long long)smem_bytes - (long long)len * 21 - YPP_BSP_FIXED;
+    if (spare < 4 * YPP_BSP_MIN_EDGES) return false;                                        // uniform
+    const int ecap = (int)(spare / 4);
+    // carve: boxes | hist | bstart | rk | state | pend | kill | edges
     float4* box = reinterpret_cast<float4*>(smem);
-    u32* edges = reinterpret_cast<u32*>(smem + (size_t)len * 16);
-    u32* hist = edges + YPP_BSP_EDGES;
+    u32* hist = reinterpret_cast<u32*>(smem + (size_t)len * 16);
     unsigned short* bstart = reinterpret_cast<unsigned short*>(hist + YPP_BSP_BINS);
     unsigned short* rk = bstart + YPP_BSP_BINS + 2;
     unsigned char* state = reinterpret_cast<unsigned char*>(rk + len + (len & 1));
     unsigned char* pend = state + len;
     unsigned char* kill = pend + len;
+    u32* edges = reinterpret_cast<u32*>(smem + (((size_t)(kill + len - smem) + 15) & ~(size_t)15));
     if (tid == 0) { H.xlo = 0xffffffffu; H.xhi = 0u; H.amax = 0u; H.cmax = 0u; H.nedges = 0; H.odd = 0; }
     for (int i = tid; i < YPP_BSP_BINS; i += T) hist[i] = 0;
     __syncthreads();
@@ -829,7 +832,7 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
         const float ct = __fsub_ru(1.0f, __fmul_rd(0.9f, thr));
         const float nthr = -thr;
         for (int pr = warp; pr < len; pr += T / 32) {
-            if (*(volatile int*)&H.nedges >= YPP_BSP_EDGES) break;
+            if (*(volatile int*)&H.nedges >= ecap) break;
             const float4 a = box[pr];
             const float xe = __fadd_ru(a.x, __fmul_ru(ct, __fsub_ru(a.z, a.x)));
             const int cend = bstart[sp_bin_end<YPP_BSP_BINS>(xe, xmin, inv) + 1];
@@ -848,14 +851,14 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
                 }
                 if (dead) {
                     const int e = atomicAdd(&H.nedges, 1);
-                    if (e < YPP_BSP_EDGES) edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
+                    if (e < ecap) edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
                 }
             }
         }
     }
     __syncthreads();
     const int ne = H.nedges;
-    if (ne > YPP_BSP_EDGES) return false;
+    if (ne > ecap) return false;
     // ---- greedy order over the edges
     bool settled = ne == 0;
     for (int round = 0; !settled && round < YPP_SP_ROUNDS; ++round) {
@@ -1082,7 +1085,7 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
     if (rc) return rc;
     if (p.N > YPP_WARP_SEG) {
         int smem = (int)(sizeof(float4) * YPP_BIG_CACHE + sizeof(u32) * ((size_t)p.N / 32 + 4));
-        const int want = (int)((long long)p.N * 21 + YPP_BSP_FIXED);        // the sweep-and-prune layout for a whole image
+        const int want = (int)((long long)p.N * 21 + YPP_BSP_FIXED + 4 * 16384);        // the sweep-and-prune layout for a whole image
         if (smem < want) smem = want < YPP_BIG_SMEM_MAX ? want : YPP_BIG_SMEM_MAX;
         static bool configured_d[YPP_MAX_DEVICES];         // per device, like the attribute itself
         int dev = 0, sms = 148;

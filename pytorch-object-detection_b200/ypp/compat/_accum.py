@@ -54,9 +54,17 @@ class MeanAveragePrecisionBase:
     def all_pred_boxes_variable(self):
         return self._pred.view() if self.img_idx else 0
 
-    def _update(self, y_true, heads):
+    def update_state_features(self, y_true, features, weights):
+        """update_state fed by the INPUTS of the heads' 1x1 convolutions and their weights (the fused head,
+        PostProcessor.from_features): the head tensors are never materialised."""
+        self._update(y_true, list(features), list(weights))
+
+    def _update(self, y_true, heads, weights=None):
         dev = heads[0].device
-        res = self._pp(heads, img_idx_base=self.img_idx, row_width=7)
+        if weights is None:
+            res = self._pp(heads, img_idx_base=self.img_idx, row_width=7)
+        else:
+            res = self._pp.from_features(heads, weights, img_idx_base=self.img_idx, row_width=7)
         gt_rows, gt_cnt = engine.target_rows(y_true.to(dev, non_blocking=True), self.input_size, self.img_idx)
         n_det, n_gt = torch.cat([res.det_total, gt_cnt]).tolist()      # the one host sync per batch
         self._pred.append(res.det_rows[:n_det])

@@ -36,6 +36,12 @@ class DecodeYoloV3(nn.Module):
         """Batched generalisation: list of per-image [K_b,6] tensors."""
         return self._pp(list(x), row_width=6).per_image()
 
+    def forward_features(self, features, weights):
+        """forward() fed by the inputs of the heads' 1x1 convolutions (models/detector/yolov3.py:56,62,68) and those
+        layers' weights instead of their outputs: convolution, decode and NMS without the head tensors."""
+        assert features[0].size(0) == 1
+        return self._pp.from_features(list(features), list(weights), row_width=6).rows()
+
 
 class MeanAveragePrecision(MeanAveragePrecisionBase):
     def __init__(self, num_classes, anchors, input_size, conf_threshold, **modes):

@@ -101,3 +101,34 @@ def test_scale_parameters_follow_the_reference_rounding(oracle):
             assert ctypes.c_float(w_ / (416 / H)).value == float(aw[a])
             assert ctypes.c_float(h_ / (416 / H)).value == float(ah[a])
         assert float(sw) == 416 / H
+
+
+def test_head_entry_points_check_their_arguments_before_any_launch():
+    """ypp_head_decode_compact / ypp_head_postprocess (the fused head): struct layout and the
+    argument errors that are raised before CUDA is touched."""
+    from ypp import _lib
+    L = _lib.lib()
+    assert ctypes.sizeof(_lib.YppHeadSrc) == 32            # two pointers, int (+ padding), pointer
+    cfg = _lib.YppCfg(20, 2, 1, 0.25, 0.45, 0, 3, 1)
+    sc = (_lib.YppScale * 1)()
+    sc[0].A, sc[0].H, sc[0].W = 3, 13, 13
+    assert L.ypp_head_decode_compact(ctypes.byref(cfg), sc, None, None, 0, None) == -1        # YPP_E_BADARG: no sources
+    assert b"null" in L.ypp_last_error()
+    src = (_lib.YppHeadSrc * 1)()
+    assert L.ypp_head_decode_compact(ctypes.byref(cfg), sc, src, None, 0, None) == -1         # feature / weight missing
+    src[0].feature, src[0].weight, src[0].cin = 256, 512, 64
+    assert L.ypp_head_decode_compact(ctypes.byref(cfg), sc, src, None, 0, None) == -3         # YPP_E_WORKSPACE
+    assert L.ypp_head_postprocess(ctypes.byref(cfg), sc, src, None, 0, None, None, None, None, 7, 0, None, 0.0, None) == -3
+
+
+def test_oracle_head_conv_is_the_reference_layer(oracle):
+    """oracle.head_conv1x1 against the layer itself, nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
+    (models/detector/yolov3.py:56) run by torch on the CPU in fp32: equal within fp32 accumulation error."""
+    g = torch.Generator().manual_seed(0)
+    conv = torch.nn.Conv2d(48, 75, 1, 1, bias=False)
+    x = torch.randn(2, 48, 13, 13, generator=g).relu_()
+    with torch.no_grad():
+        y = conv(x).numpy()
+    exact, bound = oracle.head_conv1x1(x.numpy(), conv.weight.detach().numpy())
+    assert exact.shape == y.shape
+    assert (np.abs(y - exact) <= 2.0 ** -20 * bound + 1e-7).all()

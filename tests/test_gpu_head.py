@@ -84,3 +84,27 @@ def test_fused_head_argument_errors(cuda):
         pp.from_features([x], [w])
     with pytest.raises(ValueError):
         pp.from_features([torch.randn(1, 32, 13, 13, device=cuda)], [torch.randn(70, 32, 1, 1, device=cuda)])
+
+
+def test_compat_entry_points_for_features(oracle, cuda):
+    """DecodeYoloV3.forward_features and MeanAveragePrecision.update_state_features equal forward / update_state
+    fed the head tensors the fused kernel itself produced."""
+    from ypp import engine
+    from ypp.compat.yolov3_utils import DecodeYoloV3, MeanAveragePrecision
+    from ypp import synth
+    feats, weights = _inputs(1, [64, 96, 128], [52, 26, 13], 75, seed=9)
+    df, dw = [f.to(cuda) for f in feats], [w.to(cuda) for w in weights]
+    dec = DecodeYoloV3(20, ANCH9, 416, conf_threshold=0.25)
+    pp = engine.PostProcessor(20, ANCH9, 416, 0.25)
+    _, heads = pp.from_features(df, dw, want_heads=True)
+    assert torch.equal(dec.forward_features(df, dw), dec(heads))
+    feats, weights = _inputs(4, [64, 96, 128], [52, 26, 13], 75, seed=10)
+    df, dw = [f.to(cuda) for f in feats], [w.to(cuda) for w in weights]
+    _, heads = pp.from_features(df, dw, want_heads=True)
+    annot = synth.make_annots(4, 20, g=2).to(cuda)
+    m1, m2 = MeanAveragePrecision(20, ANCH9, 416, 0.25), MeanAveragePrecision(20, ANCH9, 416, 0.25)
+    m1.update_state_features(annot, df, dw)
+    m2.update_state(annot, heads)
+    assert torch.equal(m1.all_pred_boxes_variable, m2.all_pred_boxes_variable)
+    assert torch.equal(m1.all_true_boxes_variable, m2.all_true_boxes_variable)
+    assert float(m1.result()) == float(m2.result())

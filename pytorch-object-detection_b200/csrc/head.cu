@@ -12,8 +12,8 @@
 // B = weight tile [N x 32 channels] (N = A(5+nc) rounded up to 16), both K-major, arrive by TMA
 // (cp.async.bulk.tensor, 128-byte swizzle) into a small ring of stages; one thread issues
 // tcgen05.mma.kind::tf32 (M 128, N, K 8) four times per stage into a TMEM accumulator and commits
-// the stage back to the producer; after the last commit four warps read their 32 TMEM lanes
-// (tcgen05.ld 32x32b), park the tile channel-major in the (now idle) ring and run D1's own
+// the stage back to the producer; after the last commit eight warps read the TMEM lanes
+// (tcgen05.ld 32x32b, two warps per lane quarter), park the tile channel-major in the (now idle) ring and run D1's own
 // decode_one / slot_store on it, so everything downstream of the accumulator is bit-identical to
 // D1 fed the same head values.  Features are channels-last ([B, H, W, Cin], torch.channels_last):
 // K-major rows of any H*W, 16-byte aligned for Cin % 4 == 0.
@@ -28,7 +28,10 @@
 #define YPP_HEAD_DEFAULT_STAGES 2    /* 4 CTAs per SM with two stages each beat 2 CTAs with four (72 vs 77 us on C2) */
 #define YPP_HEAD_BM 128            /* cells per CTA = UMMA M = TMEM lanes */
 #define YPP_HEAD_BK 32             /* fp32 channels per stage row: 128 bytes = one swizzle span */
-#define YPP_HEAD_THREADS 192       /* warps 0-3 epilogue (TMEM lanes 32w..), 4 TMA producer, 5 MMA issuer + TMEM owner */
+#define YPP_HEAD_EPI_WARPS 8       /* epilogue warps: warp w reads TMEM lanes 32 (w % 4) .., two warps per lane quarter */
+#define YPP_HEAD_PRODUCER YPP_HEAD_EPI_WARPS          /* the TMA producer warp */
+#define YPP_HEAD_MMA (YPP_HEAD_EPI_WARPS + 1)        /* the MMA issuer, owner of the TMEM allocation */
+#define YPP_HEAD_THREADS (32 * (YPP_HEAD_EPI_WARPS + 2))
 #define YPP_HEAD_A_BYTES (YPP_HEAD_BM * YPP_HEAD_BK * 4)
 
 struct YppHeadParams {
@@ -88,7 +91,7 @@ __device__ __forceinline__ void tmem_ld16(u32 taddr, u32 (&v)[16])
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-__global__ void __launch_bounds__(YPP_HEAD_THREADS)
+__global__ void __launch_bounds__(YPP_HEAD_THREADS, 4)
 ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_constant__ YppHeadParams hp)
 {
     extern __shared__ unsigned char ring_raw[];
@@ -111,12 +114,22 @@ ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_cons
     const u32 stage_bytes = YPP_HEAD_A_BYTES + (u32)hp.n_pad * (YPP_HEAD_BK * 4);
     unsigned char* ring = ring_raw + ((1024u - (smem_u32(ring_raw) & 1023u)) & 1023u);      // swizzle atoms are 1024-byte aligned
     const u32 ring_addr = smem_u32(ring);
-    if (tid == 0) {
+    int kc0 = 0;
+    if (warp == YPP_HEAD_PRODUCER && lane == 0) {
 #pragma unroll
         for (int i = 0; i < YPP_HEAD_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
         mbar_init(&accum, 1);
+        // the first loads leave before the TMEM allocation and the block barrier below: nobody else touches the
+        // mbarriers until then, and the features are read-only (no need for the grid dependency either)
+        if (has_cells)
+            for (; kc0 < nk && kc0 < nst; ++kc0) {
+                mbar_expect_tx(&full[kc0], stage_bytes);
+                const u32 dst = ring_addr + (u32)kc0 * stage_bytes;
+                tma_load_3d(dst, tm_a, kc0 * YPP_HEAD_BK, cell0, b, &full[kc0]);
+                tma_load_2d(dst + YPP_HEAD_A_BYTES, tm_b, kc0 * YPP_HEAD_BK, 0, &full[kc0]);
+            }
     }
-    if (warp == 5) {
+    if (warp == YPP_HEAD_MMA) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)), "r"(hp.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -126,9 +139,9 @@ ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_cons
     const u32 tmem = tmem_slot;
     ypp_grid_wait();                                          // the previous call's G may still be reading the workspace
 
-    if (has_cells && warp == 4 && lane == 0) {
-        // ---------------- TMA producer
-        for (int kc = 0; kc < nk; ++kc) {
+    if (has_cells && warp == YPP_HEAD_PRODUCER && lane == 0) {
+        // ---------------- TMA producer (the first ring-full is already in flight)
+        for (int kc = kc0; kc < nk; ++kc) {
             const int st = kc % nst, use = kc / nst;
             if (use > 0) mbar_wait(&empty[st], (u32)(use - 1) & 1u);
             mbar_expect_tx(&full[st], stage_bytes);
@@ -136,7 +149,7 @@ ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_cons
             tma_load_3d(dst, tm_a, kc * YPP_HEAD_BK, cell0, b, &full[st]);              // cells past H*W arrive as zeros
             tma_load_2d(dst + YPP_HEAD_A_BYTES, tm_b, kc * YPP_HEAD_BK, 0, &full[st]);   // rows past ac arrive as zeros
         }
-    } else if (has_cells && warp == 5 && lane == 0) {
+    } else if (has_cells && warp == YPP_HEAD_MMA && lane == 0) {
         // ---------------- MMA issuer
         for (int kc = 0; kc < nk; ++kc) {
             const int st = kc % nst, use = kc / nst;
@@ -149,41 +162,46 @@ ypp_head_decode_kernel(const __grid_constant__ YppHeadMaps tm, const __grid_cons
             umma_commit(&empty[st]);                          // the stage is free once these four have read it
         }
         umma_commit(&accum);
-    } else if (warp < 4) {
-        // ---------------- epilogue: thread = TMEM lane = cell
-        float* stg = reinterpret_cast<float*>(ring);          // [ac][128] channel-major, in the ring (idle by then)
-        const int ct = tid, cell = cell0 + ct;
+    } else if (warp < YPP_HEAD_EPI_WARPS) {
+        // ---------------- epilogue.  Warps q and q + 4 share the TMEM lane quarter q (cells 32q .. 32q+31 of the
+        // tile) and split its column chunks; the tile is parked channel-major in the ring (idle by then), after
+        // which any warp can decode any 32-cell slot: the 4 A slots of the tile are dealt round-robin to the warps.
+        float* stg = reinterpret_cast<float*>(ring);          // [ac][128]
+        const int q = warp & 3, g = warp >> 2;
         if (has_cells) {
+            const int ct = q * 32 + lane, cell = cell0 + ct;
             mbar_wait(&accum, 0u);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int j = 0; j < hp.n_pad / 16; ++j) {
+            for (int j = g; j < hp.n_pad / 16; j += YPP_HEAD_EPI_WARPS / 4) {
                 u32 v[16];
-                tmem_ld16(tmem + ((u32)(warp * 32) << 16) + (u32)(j * 16), v);
+                tmem_ld16(tmem + ((u32)(q * 32) << 16) + (u32)(j * 16), v);
 #pragma unroll
                 for (int i = 0; i < 16; ++i)
                     if (j * 16 + i < hp.ac) stg[(j * 16 + i) * YPP_HEAD_BM + ct] = __uint_as_float(v[i]);
             }
-            __syncwarp();
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * YPP_HEAD_EPI_WARPS) : "memory");     // the epilogue warps only
             float* ho = hp.head_out[si];
             if (ho != nullptr && cell < s.HW)
-                for (int c = 0; c < hp.ac; ++c)
+                for (int c = g; c < hp.ac; c += YPP_HEAD_EPI_WARPS / 4)
                     ho[((size_t)b * hp.ac + c) * s.HW + cell] = stg[c * YPP_HEAD_BM + ct];
         }
         const int nslots = p.tile_base[p.n_scales] * (YPP_TILE_BOXES / 32);
-        const int wslot = ((cell0 & (YPP_TILE_BOXES - 1)) >> 5) + warp;
-        for (int a = 0; a < s.A; ++a) {
+        for (int sl = warp; sl < 4 * s.A; sl += YPP_HEAD_EPI_WARPS) {
+            const int a = sl >> 2, qq = sl & 3;
+            const int ct = qq * 32 + lane, cell = cell0 + ct;
             Decoded d;
             d.box = make_float4(0.f, 0.f, 0.f, 0.f); d.score = 0.f; d.cls = 0;
             const bool pass = decode_one<1>(p, s, a, cell, cell < s.HW, stg + a * p.C * YPP_HEAD_BM + ct, YPP_HEAD_BM, 0, 0, d);
             const int tile = p.tile_base[si] + a * s.tpp + cell0 / YPP_TILE_BOXES;
+            const int wslot = ((cell0 & (YPP_TILE_BOXES - 1)) >> 5) + qq;
             const int first = s.box_base + a * s.HW + cell0;
-            slot_store(p.ws, p.N, b, tile * (YPP_TILE_BOXES / 32) + wslot, nslots, first + 32 * warp, pass,
+            slot_store(p.ws, p.N, b, tile * (YPP_TILE_BOXES / 32) + wslot, nslots, first + 32 * qq, pass,
                        d.box, d.score, d.cls, first + ct);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 5)
+    if (warp == YPP_HEAD_MMA)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(hp.tmem_cols) : "memory");
 }
 

@@ -35,8 +35,8 @@ def parse_args():
     ap.add_argument("--regime", default="dense", choices=["dense", "sparse"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the sparse-regime and mAP epoch extras")
-    ap.add_argument("--ring", type=int, default=4, help="distinct input batches cycled through (> L2 in total)")
-    ap.add_argument("--in-flight", type=int, default=2,
+    ap.add_argument("--ring", type=int, default=6, help="distinct input batches cycled through (> L2 in total)")
+    ap.add_argument("--in-flight", type=int, default=3,
                     help="steps in flight: each on its own stream with its own workspace and outputs (must divide --ring)")
     return ap.parse_args()
 

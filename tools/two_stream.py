@@ -9,12 +9,12 @@ from ypp import engine, synth  # noqa: E402
 
 w = synth.WORKLOADS["yolov3_416_voc_b64"]
 dev = torch.device("cuda:0")
-ring = [[h.to(dev) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=i)] for i in range(6)]
-for ns in (1, 2, 3):
+ring = [[h.to(dev) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=i)] for i in range(12)]
+for ns in (1, 2, 3, 4, 6):
     pps = [engine.PostProcessor(w["nc"], synth.workload_anchors(w), w["input_size"], w["conf"], kind=w["kind"],
                                 anchors_per_scale=w["A"], ws_tag="post%d" % k) for k in range(ns)]
     streams = [torch.cuda.Stream() for _ in range(ns)]
-    graphs = [pps[i % ns].graphed(ring[i]) for i in range(6)]
+    graphs = [pps[i % ns].graphed(ring[i]) for i in range(12)]
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     K = 120
@@ -25,7 +25,7 @@ for ns in (1, 2, 3):
             s.wait_stream(main)
         for i in range(K):
             with torch.cuda.stream(streams[i % ns]):
-                graphs[i % 6][0].replay()
+                graphs[i % 12][0].replay()
         for s in streams:
             main.wait_stream(s)
         e1.record(main)

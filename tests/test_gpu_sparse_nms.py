@@ -90,3 +90,21 @@ def test_sweep_and_prune_batch_of_random_segments(oracle, cuda):
     for b in range(B):
         ref, _ = oracle.nms_v3_indices(rows[b], .25, .45, offset_mode=oracle.OFFSET_AUTO_CUDA, union_mode=oracle.UNION_FMA)
         assert np.array_equal(ki[b, : kc[b]], util.canon(ref, rows[b])), b
+
+
+def test_sweep_and_prune_against_torchvision_on_the_same_device(cuda):
+    """Not the oracle: torchvision.ops.batched_nms on CUDA (what nms_v3 calls, utils/yolo_utils.py:346) on the
+    same hand-made inputs; defaults (auto_cuda + fma) are the arithmetic of that kernel."""
+    torchvision = pytest.importorskip("torchvision")
+    from ypp import engine
+    for name, rows in _cases().items():
+        nc = int(rows[:, 5].max()) + 1
+        t = torch.tensor(rows).to(cuda)
+        pp = engine.PostProcessor(nc, [[1, 1]], 1, 0.25, kind="v2", anchors_per_scale=1)
+        res = pp.nms_rows(t, want_keep_idx=True)
+        k = res.keep_idx[0, : int(res.keep_count[0])].long()
+        cand = torch.where(t[:, 4] > 0.25)[0]
+        c = t[cand]
+        xyxy = torch.stack([c[:, 0] - c[:, 2] / 2, c[:, 1] - c[:, 3] / 2, c[:, 0] + c[:, 2] / 2, c[:, 1] + c[:, 3] / 2], 1)
+        keep = cand[torchvision.ops.batched_nms(xyxy, c[:, 4], c[:, 5], 0.45)]
+        assert torch.equal(k, keep), (name, len(k), len(keep))

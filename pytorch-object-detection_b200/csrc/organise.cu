@@ -172,17 +172,36 @@ __device__ void radix_pass(const u64* src, u64* dst, int n, int L, int shift, in
 // atomics (order inside a bucket arbitrary); buckets hold a handful of keys, so a key's final
 // place is bucket start + the number of smaller keys in its bucket.  Returns false (nothing written
 // to dst) when some bucket is too crowded for that (many tied scores): the caller takes the LSD passes.
+// Two bucket functions, both monotone in the key: kLinear = false, the top dbits of the score WORD (equal
+// buckets per binade: right for scores spread over many binades, e.g. conf 0.001 on a trained net);
+// kLinear = true, the score VALUE mapped linearly onto the buckets (right for scores spread evenly over
+// their range: half of a uniform sample shares the top binade, 27 keys per bucket on C4 against 5.5).
+// The caller tries the linear one first with a tight limit, then the word one, then the LSD passes.
 #define YPP_BUCKET_BITS 12
 #define YPP_BUCKET_MAX 96
-__device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int bits, u32 kmin,
+#define YPP_BUCKET_MAX_LINEAR 32
+template <bool kLinear>
+__device__ __forceinline__ int bucket_of(const u64 k, const u32 kmin, const int shift, const float smax, const float scale, const int R)
+{
+    if (!kLinear) return (int)(((u32)(k >> 32) - kmin) >> shift);
+    const float v = __fmul_rn(__fsub_rn(smax, ypp_key_score(k)), scale);      // 0 for the best score, grows with the key
+    return min(max((int)v, 0), R - 1);
+}
+
+template <bool kLinear>
+__device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int bits, u32 kmin, u32 kmax,
                                  int* table, OrgSmemHeader* hd)
 {
     const int tid = threadIdx.x, lane = tid & 31;
-    const int dbits = min(bits, YPP_BUCKET_BITS), shift = bits - dbits, R = 1 << dbits;
+    const int dbits = kLinear ? YPP_BUCKET_BITS : min(bits, YPP_BUCKET_BITS), shift = bits - dbits, R = 1 << dbits;
+    const float smax = ypp_dec(~kmin), smin = ypp_dec(~kmax);               // smallest key word = largest score
+    const float scale = __fdiv_rn((float)R - 0.5f, __fsub_rn(smax, smin));
+    if (kLinear && !(scale > 0.0f && scale < INFINITY)) return false;       // uniform: no finite score range
+    const int limit = kLinear ? YPP_BUCKET_MAX_LINEAR : YPP_BUCKET_MAX;
     for (int i = tid; i < R; i += YPP_ORG_THREADS) table[i] = 0;
     if (tid == 0) hd->max_bucket = 0;
     __syncthreads();
-    for (int i = tid; i < n; i += YPP_ORG_THREADS) atomicAdd(&table[((u32)(src[i] >> 32) - kmin) >> shift], 1);
+    for (int i = tid; i < n; i += YPP_ORG_THREADS) atomicAdd(&table[bucket_of<kLinear>(src[i], kmin, shift, smax, scale, R)], 1);
     __syncthreads();
     {
         const int ipt = (R + YPP_ORG_THREADS - 1) / YPP_ORG_THREADS;         // 1..4 entries per thread
@@ -199,7 +218,7 @@ __device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int 
         if (lane == 0 && mx > 0) atomicMax(&hd->max_bucket, mx);
         int total;
         int run = block_exclusive_scan(sum, hd->warp_sums, total);           // syncs inside: max_bucket is complete after it
-        if (hd->max_bucket > YPP_BUCKET_MAX) return false;                   // uniform: every thread reads the same word
+        if (hd->max_bucket > limit) return false;                            // uniform: every thread reads the same word
 #pragma unroll
         for (int k = 0; k < (1 << YPP_BUCKET_BITS) / YPP_ORG_THREADS; ++k)
             if (k < ipt && e0 + k < R) { table[e0 + k] = run; run += vals[k]; }
@@ -207,12 +226,12 @@ __device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int 
     __syncthreads();
     for (int i = tid; i < n; i += YPP_ORG_THREADS) {
         const u64 k = src[i];
-        tmp[atomicAdd(&table[((u32)(k >> 32) - kmin) >> shift], 1)] = k;
+        tmp[atomicAdd(&table[bucket_of<kLinear>(k, kmin, shift, smax, scale, R)], 1)] = k;
     }
     __syncthreads();                       // table[d] is now the END of bucket d
     for (int i = tid; i < n; i += YPP_ORG_THREADS) {
         const u64 k = tmp[i];
-        const int d = (int)(((u32)(k >> 32) - kmin) >> shift);
+        const int d = bucket_of<kLinear>(k, kmin, shift, smax, scale, R);
         const int lo = d ? table[d - 1] : 0, hi = table[d];
         int rank = 0;
         for (int q = lo; q < hi; ++q) rank += tmp[q] < k;
@@ -497,7 +516,8 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         const u32 kmin = hd->kmin, span = hd->kmax - kmin;
         const int bits = 32 - __clz(span);                   // 0 when every score is equal: already in order
         // bucket + rank (sorted keys land back in bufA); LSD passes only when scores tie in crowds
-        if (bits > 0 && !bucket_rank_sort(bufA, bufB, bufA, n, bits, kmin, table, hd)) {
+        if (bits > 0 && !bucket_rank_sort<true>(bufA, bufB, bufA, n, bits, kmin, hd->kmax, table, hd) &&
+            !bucket_rank_sort<false>(bufA, bufB, bufA, n, bits, kmin, hd->kmax, table, hd)) {
             const int passes = (bits + 7) / 8;
             const int bw = (bits + passes - 1) / passes;
             u64* other = bufB;

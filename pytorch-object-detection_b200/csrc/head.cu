@@ -8,15 +8,15 @@
 // decoded, thresholded and compacted straight out of tensor memory into the same slot records D1
 // writes, and S1 -> N1 -> G run unchanged.
 //
-// sm_100a design: one launch over every scale, one CTA per (image, 128 cells), widest scale first.  A = feature tile [128 cells x 32 channels] and
-// B = weight tile [N x 32 channels] (N = A(5+nc) rounded up to 16), both K-major, arrive by TMA
-// (cp.async.bulk.tensor, 128-byte swizzle) into a small ring of stages; one thread issues
-// tcgen05.mma.kind::tf32 (M 128, N, K 8) four times per stage into a TMEM accumulator and commits
-// the stage back to the producer; after the last commit eight warps read the TMEM lanes
-// (tcgen05.ld 32x32b, two warps per lane quarter), park the tile channel-major in the (now idle) ring and run D1's own
-// decode_one / slot_store on it, so everything downstream of the accumulator is bit-identical to
-// D1 fed the same head values.  Features are channels-last ([B, H, W, Cin], torch.channels_last):
-// K-major rows of any H*W, 16-byte aligned for Cin % 4 == 0.
+// sm_100a design: one launch over every scale, one CTA per (image, 128 cells), widest scale first.
+// A = feature tile [128 cells x 32 channels] and B = weight tile [N x 32 channels] (N = A(5+nc) rounded
+// up to 16), both K-major, arrive by TMA (cp.async.bulk.tensor, 128-byte swizzle) into a small ring of
+// stages; one thread issues tcgen05.mma.kind::tf32 (M 128, N, K 8) four times per stage into a TMEM
+// accumulator and commits the stage back to the producer; after the last commit eight warps read the
+// TMEM lanes (tcgen05.ld 32x32b, two warps per lane quarter), park the tile channel-major in the (now
+// idle) ring and run D1's own decode_one / slot_store on it, so everything downstream of the
+// accumulator is bit-identical to D1 fed the same head values.  Features are channels-last
+// ([B, H, W, Cin], torch.channels_last): K-major rows of any H*W, 16-byte aligned for Cin % 4 == 0.
 // Arithmetic: TF32 products, fp32 accumulation - what cuDNN does for this convolution under
 // torch.backends.cudnn.allow_tf32 (the default); parity is stated against that, see tests.
 #include "decode_common.cuh"

@@ -1,4 +1,5 @@
-"""Tuning build (-DYPP_SP_STATS): how the sweep-and-prune path of N1 fares on a workload."""
+"""Tuning build (-DYPP_SP_STATS): how the sweep-and-prune path of N1 fares on a workload (attempts, ways out,
+pair tests, edges, rounds).  The phase clocks include the counters' own global atomics: read them as shares at most."""
 import ctypes
 import os
 import subprocess

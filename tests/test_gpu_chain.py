@@ -167,6 +167,29 @@ def test_scores_tied_in_crowds(oracle, cuda):
         assert np.array_equal(k, util.canon(ref, rows)), levels
 
 
+def test_score_distributions_of_both_bucket_functions(oracle, cuda):
+    """The sort's two bucket functions and the hand-over between them: scores spread evenly over their range
+    (value-linear buckets), spread over many binades (the linear buckets overflow, score-word buckets take over),
+    one huge outlier (a linear range that is all outlier), an infinite score (no finite range at all)."""
+    from ypp import engine, _lib
+    rng = np.random.RandomState(17)
+    n = 9000
+    base = np.concatenate([rng.uniform(0, 416, (n, 2)), rng.uniform(8, 60, (n, 2)), np.zeros((n, 1)),
+                           rng.randint(0, 20, (n, 1))], 1).astype(np.float32)
+    cases = {"even": rng.uniform(0.001, 1.0, n), "binades": np.exp(-rng.uniform(0, 12, n)),
+             "outlier": rng.uniform(0.001, 1.0, n), "infinite": rng.uniform(0.001, 1.0, n)}
+    cases["outlier"][123] = 1e30
+    cases["infinite"][77] = np.inf
+    for name, sc in cases.items():
+        rows = base.copy()
+        rows[:, 4] = sc.astype(np.float32)
+        pp = engine.PostProcessor(20, [[1, 1]], 1, 0.0005, kind="v2", anchors_per_scale=1, offset_mode="none", union_mode="fma")
+        res = pp.nms_rows(torch.tensor(rows).to(cuda), want_keep_idx=True)
+        k = res.keep_idx[0, : int(res.keep_count[0])].cpu().numpy()
+        ref, _ = oracle.nms_v3_indices(rows, .0005, .45, offset_mode=_lib.OFFSET_MODES["none"], union_mode=_lib.UNION_MODES["fma"])
+        assert np.array_equal(k, util.canon(ref, rows)), name
+
+
 def test_empty_and_single_image(cuda):
     from ypp import engine, synth
     heads = [h.to(cuda) for h in synth.make_heads(1, 20, [52, 26, 13], g=12, mu_obj=-60.0)]

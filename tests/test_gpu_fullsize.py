@@ -100,3 +100,23 @@ def test_full_size_default_modes_match_torchvision_on_device(cuda, name):
         # the vanilla path's final score sort is not stable: canonicalise to (score desc, index asc)
         order = torch.tensor(np.lexsort((want.cpu().numpy(), -r[want, 4].cpu().numpy())), device=cuda)
         assert torch.equal(res.keep_idx[b, : int(kc[b])].long(), want[order]), (name, b)
+
+
+@pytest.mark.parametrize("n", [25000, 25001, 60000])
+def test_large_single_image_and_the_cuda_heuristic_flip(oracle, cuda, n):
+    """torchvision's CUDA heuristic takes the coordinate trick up to 25 000 candidates (4 n <= 100 000) and the
+    per-class loop above; 60 000 boxes no longer fit the sort's shared-memory key buffers.  Every box passes the
+    threshold, 80 classes, one cross-class pair that only the trick suppresses."""
+    from ypp import engine, _lib
+    rng = np.random.RandomState(n)
+    rows = np.concatenate([rng.uniform(0, 1200, (n, 2)), rng.uniform(8, 90, (n, 2)),
+                           rng.permutation(n).reshape(n, 1) / (2.0 * n) + 0.3, rng.randint(0, 80, (n, 1))], 1).astype(np.float32)
+    rows[0] = [1290, 1290, 20, 20, .99, 0]          # max coordinate 1300
+    rows[1] = [-9, -9, 20, 20, .98, 1]              # class 1 at negative coordinates: lands on it under the trick
+    pp = engine.PostProcessor(80, [[1, 1]], 1, 0.25, kind="v2", anchors_per_scale=1)      # auto_cuda + fma
+    res = pp.nms_rows(torch.tensor(rows).to(cuda), want_keep_idx=True)
+    k = res.keep_idx[0, : int(res.keep_count[0])].cpu().numpy()
+    ref, ncand = oracle.nms_v3_indices(rows, .25, .45, offset_mode=_lib.OFFSET_MODES["auto_cuda"], union_mode=_lib.UNION_MODES["fma"])
+    assert ncand == n == int(res.cand_count[0])
+    assert np.array_equal(k, util.canon(ref, rows))
+    assert (1 in set(k.tolist())) == (n > 25000)    # suppressed by the trick only

@@ -6,13 +6,17 @@
 // (stable), box j suppressed iff an earlier KEPT box i has IoU(i,j) > thr (strict).
 //
 // torchvision's CUDA kernel writes an n x n/64 bit matrix to HBM and scans it with one CTA.
-// Here nothing but the keep flags reaches HBM and suppressed rows never do any pair work:
-//   - segments of up to YPP_WARP_SEG boxes (the per-class case) are owned by one 4-warp CTA:
-//     boxes staged in shared memory, 32-row tiles, the 32x32 diagonal tile held as one register
-//     per lane, the greedy order resolved by a ballot fix-point, and only the KEPT rows
-//     broadcast against the later columns each lane owns (rows split over the four warps).
-//   - longer segments (single-class heads, classes a cross-class edge merged) go to a
-//     1024-thread CTA kernel walking the per-image lists of long segments S1 left.
+// Here nothing but the keep flags reaches HBM.  Two ways through a segment, same result:
+//   - sweep-and-prune (segments of ordinary boxes, see nms_sparse / nms_big_sparse): greedy NMS only
+//     needs the edges (i before j, IoU > thr), so the boxes are counting-sorted by x1, every box
+//     meets only the later boxes inside the x1 range an IoU above thr allows, the edges go to a
+//     list in shared memory and the greedy order is a fix-point over that list;
+//   - tile sweeps (anything else, or when the edge list overflows): tiles in score order, the
+//     diagonal tile resolved by a ballot fix-point, and only the KEPT rows broadcast against the
+//     later, still-alive columns, so suppressed rows never do any pair work.
+// Segments of up to YPP_WARP_SEG boxes (the per-class case) are owned by one 4-warp CTA; longer
+// ones (single-class heads, classes a cross-class edge merged) go to a 1024-thread CTA kernel
+// walking the per-image lists of long segments S1 left.
 //
 // Pair test.  torchvision evaluates  inter / union > thr  with an IEEE division.  The same
 // decision is reached without dividing whenever  d = fma(-thr, union, inter)  is clearly away

@@ -127,6 +127,18 @@ int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes,
             float* det_rows, int row_width, int64_t det_capacity, int* det_total,
             float img_idx_base, void* stream);
 
+/* ypp_nms in append mode: the accumulation `self.all_pred_boxes_variable = torch.cat([self.all_pred_boxes_variable,
+ * pred_boxes])` of MeanAveragePrecision.update_state (utils/yolov3_utils.py:139-144) done by the gather itself,
+ * with no host read of the row count between batches.  det_rows is the whole accumulator ([det_capacity,
+ * row_width]); this call's rows land after the *cursor_in rows already there and *cursor_out receives
+ * *cursor_in + rows of this call.  cursor_in and cursor_out are device int64 words and must be DIFFERENT words
+ * (blocks of the gather read the one while another writes the other): alternate between two.  Rows past
+ * det_capacity are dropped while the cursor still counts them, so the caller sizes det_capacity for the worst
+ * case (B * n_boxes rows per call) between two reads of the cursor. */
+int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count,
+                   float* det_rows, int row_width, int64_t det_capacity, const int64_t* cursor_in,
+                   int64_t* cursor_out, float img_idx_base, void* stream);
+
 /* The three stages above, back to back, from the heads (DecodeYoloV3/V2.forward and the body
  * of MeanAveragePrecision.update_state: utils/yolov3_utils.py:73-90,108-146). */
 int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,
@@ -209,6 +221,12 @@ int ypp_decode_yolov1(const float* input, int B, int S, int nc, int num_boxes, f
  * (image, slot) order; rows with sum <= 0 are dropped.  gt_count [1] out.  out needs B*T rows. */
 int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, float img_idx_base,
                     float* out_G7, int* gt_count, void* stream);
+
+/* The same in append mode (`self.all_true_boxes_variable = torch.cat(...)`, utils/yolov3_utils.py:141-145):
+ * out_G7 is the whole accumulator [capacity,7]; rows go after the *cursor rows already there and *cursor
+ * (device int64, in/out - the kernel is one block) is advanced.  A call adds at most B*T rows. */
+int ypp_target_rows_append(const float* annot_BT5, int B, int T, float input_size, float img_idx_base,
+                           float* out_G7, int64_t capacity, int64_t* cursor, void* stream);
 
 /* ---- detection writers --------------------------------------------------
  * The integer box columns the reference's detection writers put on disk, for K rows

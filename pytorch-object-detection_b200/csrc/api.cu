@@ -95,7 +95,8 @@ int bind_ws(int B, int N, int nc, void* ws, size_t ws_bytes, YppWs* out)
 
 int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int* keep_count, int* keep_idx,
                  float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
-                 const float* src_rows, bool do_sort, bool do_nms, cudaStream_t st)
+                 const float* src_rows, bool do_sort, bool do_nms, cudaStream_t st,
+                 const long long* cursor_in = nullptr, long long* cursor_out = nullptr)
 {
     int rc = YPP_OK;
     if (do_sort) {
@@ -119,6 +120,7 @@ int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int
         g.cand_count_out = cand_count; g.keep_count_out = keep_count; g.keep_idx = keep_idx;
         g.det_rows = det_rows; g.row_width = row_width; g.det_capacity = det_capacity; g.det_total = det_total;
         g.img_idx_base = img_idx_base; g.src_rows = src_rows;
+        g.cursor_in = cursor_in; g.cursor_out = cursor_out;
         rc = ypp_launch_gather(g, st);
     }
     return rc;
@@ -192,6 +194,23 @@ int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* can
     if (rc) return rc;
     return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
                         img_idx_base, nullptr, false, true, (cudaStream_t)stream);
+}
+
+int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count,
+                   float* det_rows, int row_width, int64_t det_capacity, const int64_t* cursor_in, int64_t* cursor_out,
+                   float img_idx_base, void* stream)
+{
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    if (!det_rows || !cursor_in || !cursor_out || cursor_in == cursor_out) {
+        ypp_set_error("nms_append: det_rows and two different cursor words are required"); return YPP_E_BADARG;
+    }
+    YppWs w;
+    rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
+    if (rc) return rc;
+    return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr,
+                        img_idx_base, nullptr, false, true, (cudaStream_t)stream, (const long long*)cursor_in,
+                        (long long*)cursor_out);
 }
 
 int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
@@ -322,7 +341,16 @@ int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, floa
                     int* gt_count, void* stream)
 {
     if (!annot_BT5 || !out_G7 || !gt_count || B <= 0 || T <= 0) { ypp_set_error("target_rows: bad argument"); return YPP_E_BADARG; }
-    return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, gt_count, (cudaStream_t)stream);
+    return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, gt_count, (long long)B * T, nullptr,
+                                  nullptr, (cudaStream_t)stream);
+}
+
+int ypp_target_rows_append(const float* annot_BT5, int B, int T, float input_size, float img_idx_base, float* out_G7,
+                           int64_t capacity, int64_t* cursor, void* stream)
+{
+    if (!annot_BT5 || !out_G7 || !cursor || B <= 0 || T <= 0 || capacity < 0) { ypp_set_error("target_rows_append: bad argument"); return YPP_E_BADARG; }
+    return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, nullptr, capacity, (const long long*)cursor,
+                                  (long long*)cursor, (cudaStream_t)stream);
 }
 
 int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, const float* scale_xy, int n_img,

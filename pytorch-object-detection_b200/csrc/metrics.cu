@@ -20,11 +20,13 @@ namespace {
 // ------------------------------------------------------------------ GT ingest
 __global__ void __launch_bounds__(1024)
 ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float input_size, float img_base,
-                       float* __restrict__ out, int* __restrict__ gt_count)
+                       float* __restrict__ out, int* __restrict__ gt_count, long long capacity,
+                       const long long* cursor_in, long long* cursor_out)
 {
     __shared__ int warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = B * T;
+    const long long base = cursor_in ? *cursor_in : 0;      // append mode: rows already in `out`
     int running = 0;
     for (int i0 = 0; i0 < total; i0 += 1024) {
         const int i = i0 + tid;
@@ -41,8 +43,9 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
         __syncthreads();
         int before = 0, tot = 0;
         for (int w = 0; w < 32; ++w) { const int t = warp_tot[w]; if (w < warp) before += t; tot += t; }
-        if (ok) {
-            float* o = out + (size_t)(running + before + __popc(m & ((1u << lane) - 1u))) * 7;
+        const long long row = base + running + before + __popc(m & ((1u << lane) - 1u));
+        if (ok && row < capacity) {
+            float* o = out + (size_t)row * 7;
             o[0] = img_base + (float)(i / T);
             o[1] = __fmul_rn(r0, input_size); o[2] = __fmul_rn(r1, input_size);
             o[3] = __fmul_rn(r2, input_size); o[4] = __fmul_rn(r3, input_size);
@@ -51,7 +54,10 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
         running += tot;
         __syncthreads();
     }
-    if (tid == 0) *gt_count = running;
+    if (tid == 0) {
+        if (gt_count) *gt_count = running;
+        if (cursor_out) *cursor_out = base + running;       // one block: may be the word cursor_in points at
+    }
 }
 
 // ------------------------------------------------------------------ box_iou (N x M)
@@ -490,9 +496,11 @@ ypp_confusion_kernel(const float* __restrict__ det, const int* __restrict__ det_
 }  // namespace
 
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
-                           float* out, int* gt_count, cudaStream_t st)
+                           float* out, int* gt_count, long long capacity, const long long* cursor_in,
+                           long long* cursor_out, cudaStream_t st)
 {
-    ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count);
+    ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count, capacity, cursor_in,
+                                               cursor_out);
     ypp_count_launch(1);
     return ypp_check_launch("target_rows");
 }

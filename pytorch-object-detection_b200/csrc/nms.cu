@@ -971,7 +971,8 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     const int n = min(p.ws.cand_count[b], N);
     const int r_begin = blockIdx.x * YPP_GATHER_CHUNK;
     const int cap = p.max_det > 0 ? p.max_det : 0x7fffffff;          // rows an image may contribute
-    const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && p.det_total != nullptr;
+    const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && (p.det_total != nullptr || p.cursor_out != nullptr);
+    const long long base = p.cursor_in ? *p.cursor_in : 0;          // append mode: rows already in det_rows
     if (blockIdx.x == 0 && tid == 0) {
         if (p.cand_count_out) p.cand_count_out[b] = n;
         if (p.keep_count_out) p.keep_count_out[b] = min(p.ws.keep_count[b], cap);
@@ -1004,7 +1005,11 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     int pre_rows = 0;
 #pragma unroll
     for (int w = 0; w < YPP_GATHER_THREADS / 32; ++w) { img_rows += red_img[w]; pre_rows += red_pre[w]; }
-    if (writes_total && tid == 0) *p.det_total = (int)(img_rows + min(p.ws.keep_count[b], cap));
+    if (writes_total && tid == 0) {
+        const long long rows = img_rows + min(p.ws.keep_count[b], cap);
+        if (p.det_total) *p.det_total = (int)rows;
+        if (p.cursor_out) *p.cursor_out = base + rows;               // never the word cursor_in points at
+    }
     if (r_begin >= n || pre_rows >= cap) return;
     const u64* keys = p.ws.skeys + (size_t)b * N;
     const float4* box = p.ws.box + (size_t)b * N;
@@ -1071,7 +1076,7 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         o[4] = ypp_key_score(k[u]); o[5] = cls[u];
     }
     __syncthreads();
-    const long long first = img_rows + pre_rows;
+    const long long first = base + img_rows + pre_rows;
     long long nrows = running - pre_rows;
     if (first + nrows > p.det_capacity) nrows = p.det_capacity > first ? p.det_capacity - first : 0;
     float* out = p.det_rows + first * width;

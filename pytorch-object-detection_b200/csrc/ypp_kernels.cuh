@@ -61,6 +61,8 @@ struct YppGatherParams {
     const float* src_rows;   // optional [B,N,6]: copy the class column verbatim (nms_rows entry)
     int max_det;             // > 0: at most this many rows per image (utils/general.py:701-702)
     int xyxy_out;            // rows carry x1,y1,x2,y2 instead of cx,cy,w,h
+    const long long* cursor_in;   // optional: rows already in det_rows; this call's rows go after them
+    long long* cursor_out;        // optional: *cursor_in + rows of this call (a different word than cursor_in)
 };
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st);
@@ -81,7 +83,8 @@ int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int
 int ypp_launch_confusion(const float* det, const int* det_off, const float* lab, const int* lab_off, int n_img, int nc,
                          float conf, float thr, int* bestg, float* bestiou, unsigned long long* matrix, cudaStream_t st);
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
-                           float* out, int* gt_count, cudaStream_t st);
+                           float* out, int* gt_count, long long capacity, const long long* cursor_in,
+                           long long* cursor_out, cudaStream_t st);
 int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);
 size_t ypp_map_ws_bytes(long long G, long long K, int nc);
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,

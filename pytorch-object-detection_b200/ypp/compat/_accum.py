@@ -33,7 +33,8 @@ class MeanAveragePrecisionBase:
     """reset_states / update_state / result with the reference's public attributes
     (utils/yolov3_utils.py:93-149, utils/yolov2_utils.py:81-128)."""
 
-    def __init__(self, num_classes, anchors, input_size, conf_threshold, kind, **modes):
+    def __init__(self, num_classes, anchors, input_size, conf_threshold, kind, sync_every=16, **modes):
+        self.sync_every = sync_every
         self.num_classes = num_classes
         self.anchors = anchors
         self.input_size = input_size
@@ -42,17 +43,17 @@ class MeanAveragePrecisionBase:
         self.reset_states()
 
     def reset_states(self):
-        self._true = _GrowBuf()
-        self._pred = _GrowBuf()
+        self._true = None          # RowAccumulators, made on the first batch's device
+        self._pred = None
         self.img_idx = 0
 
     @property
     def all_true_boxes_variable(self):
-        return self._true.view() if self.img_idx else 0
+        return self._true.view() if self._true is not None else 0
 
     @property
     def all_pred_boxes_variable(self):
-        return self._pred.view() if self.img_idx else 0
+        return self._pred.view() if self._pred is not None else 0
 
     def update_state_features(self, y_true, features, weights):
         """update_state fed by the INPUTS of the heads' 1x1 convolutions and their weights (the fused head,
@@ -61,16 +62,16 @@ class MeanAveragePrecisionBase:
 
     def _update(self, y_true, heads, weights=None):
         dev = heads[0].device
-        if weights is None:
-            res = self._pp(heads, img_idx_base=self.img_idx, row_width=7)
-        else:
-            res = self._pp.from_features(heads, weights, img_idx_base=self.img_idx, row_width=7)
-        gt_rows, gt_cnt = engine.target_rows(y_true.to(dev, non_blocking=True), self.input_size, self.img_idx)
-        n_det, n_gt = torch.cat([res.det_total, gt_cnt]).tolist()      # the one host sync per batch
-        self._pred.append(res.det_rows[:n_det])
-        self._true.append(gt_rows[:n_gt])
+        if self._pred is None:
+            self._pred = engine.RowAccumulator(dev, self.sync_every)
+            self._true = engine.RowAccumulator(dev, 64 * self.sync_every)
+        # both appends happen on the device behind the accumulators' cursors: no host read per batch
+        self._pp.accumulate(self._pred, heads, weights, img_idx_base=self.img_idx)
+        engine.target_rows_append(self._true, y_true.to(dev, non_blocking=True), self.input_size, self.img_idx)
         self.img_idx += int(y_true.size(0))
 
     def result(self):
         from .yolo_utils import mean_average_precision
+        if self._pred is None:
+            raise RuntimeError("result() before any update_state()")
         return mean_average_precision(self._true.view(), self._pred.view(), self.num_classes)

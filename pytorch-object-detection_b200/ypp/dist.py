@@ -81,8 +81,8 @@ class ShardedMeanAveragePrecision:
         self._acc._update(y_true, list(y_preds) if isinstance(y_preds, (list, tuple)) else [y_preds])
 
     def gathered(self):
-        det = gather_rows(self._acc._pred.view() if self._acc._pred.buf is not None else self._empty(), self.group)
-        gt = gather_rows(self._acc._true.view() if self._acc._true.buf is not None else self._empty(), self.group)
+        det = gather_rows(self._acc._pred.view() if self._acc._pred is not None else self._empty(), self.group)
+        gt = gather_rows(self._acc._true.view() if self._acc._true is not None else self._empty(), self.group)
         return gt, det
 
     def _empty(self):

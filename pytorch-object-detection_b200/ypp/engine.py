@@ -68,6 +68,55 @@ class PostResult:
         return out
 
 
+class RowAccumulator:
+    """[n, 7] rows growing on the device with the row count kept ON the device: what
+    `self.all_pred_boxes_variable = torch.cat([...])` (utils/yolov3_utils.py:139-146) builds, without a host
+    read of the count per batch.  The kernels append behind a device cursor (ypp_nms_append /
+    ypp_target_rows_append); the host only tracks an upper bound of the rows (worst case per append) and reads
+    the cursor when that bound reaches the capacity - once per `sync_every` appends at most."""
+
+    def __init__(self, device, sync_every=16):
+        self.device = torch.device(device)
+        self.sync_every = max(1, int(sync_every))
+        self.cur = torch.zeros(2, dtype=torch.int64, device=self.device)   # two words: see ypp_nms_append
+        self.k = 0                                                         # appends so far: the live word is k & 1
+        self.buf = None
+        self.bound = 0                                                     # rows <= bound, known without a sync
+        self.syncs = 0
+
+    def count(self) -> int:
+        self.syncs += 1
+        n = int(self.cur[self.k & 1].item())
+        self.bound = n
+        return n
+
+    def reserve(self, worst: int):
+        """Room for `worst` more rows; reads the cursor only when the bound says they might not fit."""
+        cap = 0 if self.buf is None else self.buf.shape[0]
+        if self.bound + worst > cap:
+            n = self.count() if self.buf is not None else 0
+            if n + worst > cap:
+                nb = torch.empty((max(n + worst * self.sync_every, 2 * cap, 1024), 7), dtype=torch.float32, device=self.device)
+                if n:
+                    nb[:n] = self.buf[:n]
+                self.buf = nb
+        self.bound += worst
+
+    def cursors(self, in_place=False):
+        """(pointer to the live word, pointer to the word the next append writes)."""
+        base = self.cur.data_ptr()
+        if in_place:
+            return base + 8 * (self.k & 1), base + 8 * (self.k & 1)
+        a, b = base + 8 * (self.k & 1), base + 8 * ((self.k + 1) & 1)
+        self.k += 1
+        return a, b
+
+    def view(self) -> torch.Tensor:
+        if self.buf is None:
+            return torch.empty((0, 7), dtype=torch.float32, device=self.device)
+        return self.buf[: self.count()]
+
+
 class PostProcessor:
     """decode -> threshold/compact -> sort -> per-class NMS -> rows for a batch of heads.
 
@@ -98,6 +147,7 @@ class PostProcessor:
             compare_in_double = self.union_mode == _lib.UNION_SEPARATE   # CPU kernel semantics
         self.iou_thr_eff = float(lib().ypp_effective_iou_thr(self.iou_threshold, int(bool(compare_in_double))))
         self._plans = {}
+        self._scratch = {}
 
     # -- parameter blocks ------------------------------------------------------------------
     def _cfg(self, B, n_scales):
@@ -262,6 +312,39 @@ class PostProcessor:
                                     float(img_idx_base), _stream()))
         return (res, heads_out) if want_heads else res
 
+    def accumulate(self, acc: RowAccumulator, heads: Sequence[torch.Tensor], weights=None, img_idx_base=0):
+        """The chain with the gather appending to `acc` (7-column rows) instead of filling a per-call buffer:
+        nothing is read back, so a validation loop queues batch after batch.  weights given: `heads` are the
+        INPUTS of the heads' 1x1 convolutions (from_features)."""
+        if weights is None:
+            _, hc, B, n_boxes, _, _ = self._plan(heads)
+            dev = hc[0].device
+        else:
+            B = heads[0].shape[0]
+            n_boxes = sum(self.A * f.shape[2] * f.shape[3] for f in heads)
+            dev = heads[0].device
+        if acc.device != dev:
+            raise ValueError("accumulator and heads are on different devices")
+        sc = self._scratch.get((B, dev))
+        if sc is None:
+            z = torch.empty
+            sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                            z(B, dtype=torch.int32, device=dev), None, n_boxes)
+            self._scratch[(B, dev)] = sc
+        if weights is None:
+            self.staged(heads, stages=("decode", "sort"), out=sc)
+        else:
+            self.from_features(heads, weights, stages=("decode", "sort"), out=sc)
+        L = lib()
+        cfg = self._cfg(B, len(heads))
+        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
+        with torch.cuda.device(dev):
+            acc.reserve(B * n_boxes)
+            cin, cout = acc.cursors()
+            check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),
+                                   _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream()))
+        return sc
+
     def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
                 repeat=1, stages=None):
         """Capture the chain on these (static) head buffers into a CUDA graph.  Returns
@@ -349,6 +432,21 @@ def target_rows(annot: torch.Tensor, input_size, img_idx_base=0):
         check(lib().ypp_target_rows(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(out),
                                     _ptr(cnt), _stream()))
     return out, cnt
+
+
+def target_rows_append(acc: RowAccumulator, annot: torch.Tensor, input_size, img_idx_base=0):
+    """target_rows appending to `acc` behind its device cursor (no count comes back)."""
+    if annot.dim() != 3 or annot.shape[-1] != 5:
+        raise ValueError("annot must be [B, max_num_annots, 5]")
+    if not annot.is_cuda or annot.device != acc.device:
+        raise ValueError("annot must be a CUDA tensor on the accumulator's device")
+    annot = annot.to(torch.float32).contiguous()
+    B, T, _ = annot.shape
+    with torch.cuda.device(annot.device):
+        acc.reserve(B * T)
+        cin, _ = acc.cursors(in_place=True)
+        check(lib().ypp_target_rows_append(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(acc.buf),
+                                           acc.buf.shape[0], cin, _stream()))
 
 
 def box_iou(box1: torch.Tensor, box2: torch.Tensor) -> torch.Tensor:

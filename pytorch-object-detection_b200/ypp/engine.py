@@ -316,8 +316,10 @@ class PostProcessor:
         """The chain with the gather appending to `acc` (7-column rows) instead of filling a per-call buffer:
         nothing is read back, so a validation loop queues batch after batch.  weights given: `heads` are the
         INPUTS of the heads' 1x1 convolutions (from_features)."""
+        plan = None
         if weights is None:
-            _, hc, B, n_boxes, _, _ = self._plan(heads)
+            plan = self._plan(heads)
+            _, hc, B, n_boxes, _, _ = plan
             dev = hc[0].device
         else:
             B = heads[0].shape[0]
@@ -331,14 +333,18 @@ class PostProcessor:
             sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
                             z(B, dtype=torch.int32, device=dev), None, n_boxes)
             self._scratch[(B, dev)] = sc
-        if weights is None:
-            self.staged(heads, stages=("decode", "sort"), out=sc)
-        else:
-            self.from_features(heads, weights, stages=("decode", "sort"), out=sc)
         L = lib()
-        cfg = self._cfg(B, len(heads))
-        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
+        if plan is None:
+            self.from_features(heads, weights, stages=("decode", "sort"), out=sc)
+            cfg = self._cfg(B, len(heads))
+            nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
+        else:
+            arr, cfg, nbytes = plan[0], plan[4], plan[5] or L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
+        ws = _workspace(nbytes, dev, self.ws_tag)
         with torch.cuda.device(dev):
+            if plan is not None:                      # the cached parameter blocks of these head buffers
+                check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
+                check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
             acc.reserve(B * n_boxes)
             cin, cout = acc.cursors()
             check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),

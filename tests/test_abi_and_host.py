@@ -121,6 +121,20 @@ def test_head_entry_points_check_their_arguments_before_any_launch():
     assert L.ypp_head_postprocess(ctypes.byref(cfg), sc, src, None, 0, None, None, None, None, 7, 0, None, 0.0, None) == -3
 
 
+def test_append_entry_points_check_their_arguments_before_any_launch():
+    """ypp_nms_append needs the accumulator and two DIFFERENT cursor words; ypp_target_rows_append its cursor."""
+    from ypp import _lib
+    L = _lib.lib()
+    cfg = _lib.YppCfg(20, 2, 1, 0.25, 0.45, 0, 3, 1)
+    c = ctypes.byref(cfg)
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, None, 7, 0, 64, 72, 0.0, None) == -1       # no det_rows
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 64, 0.0, None) == -1       # one word twice
+    assert b"cursor" in L.ypp_last_error()
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 72, 0.0, None) == -3       # YPP_E_WORKSPACE
+    assert L.ypp_target_rows_append(1024, 2, 8, 416.0, 0.0, 2048, 16, None, None) == -1             # no cursor
+    assert L.ypp_target_rows_append(1024, 0, 8, 416.0, 0.0, 2048, 16, 64, None) == -1               # B = 0
+
+
 def test_oracle_head_conv_is_the_reference_layer(oracle):
     """oracle.head_conv1x1 against the layer itself, nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
     (models/detector/yolov3.py:56) run by torch on the CPU in fp32: equal within fp32 accumulation error."""

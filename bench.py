@@ -492,15 +492,26 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                             "ms_per_step": ms / args.steps, "steps_in_flight": NS, "single_stream_ms_per_step": ms_one}
     # mAP epoch: n_batches of B images per rank, detections accumulated on device, then gather + match
     n_batches = 32                      # C5 shape: 2048 images per rank in batches of 64
-    dets, gts = [], []
-    for i in range(n_batches):
-        r = pp(sparse[i % n_ring], img_idx_base=(rank * n_batches + i) * B)
-        rows = r.rows().clone()
-        dets.append(rows)
-        an = synth.make_annots(B, nc, g=rank * n_batches + i).to(dev)
-        g_rows, g_cnt = engine.target_rows(an, w["input_size"], (rank * n_batches + i) * B)
-        gts.append(g_rows[: int(g_cnt.item())].clone())
-    det_local, gt_local = torch.cat(dets), torch.cat(gts)
+    # the accumulation is MeanAveragePrecision.update_state's: the gather and the GT ingest append behind device
+    # cursors (ypp_nms_append / ypp_target_rows_append), the host reads nothing back between batches
+    annots = [synth.make_annots(B, nc, g=rank * n_batches + i).to(dev) for i in range(n_batches)]
+
+    def accumulate():
+        acc_d, acc_g = engine.RowAccumulator(dev), engine.RowAccumulator(dev, 1024)
+        for i in range(n_batches):
+            base = (rank * n_batches + i) * B
+            pp.accumulate(acc_d, sparse[i % n_ring], img_idx_base=base)
+            engine.target_rows_append(acc_g, annots[i], w["input_size"], base)
+        return acc_d, acc_g
+
+    accumulate()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    acc_d, acc_g = accumulate()
+    torch.cuda.synchronize()
+    ms_acc = (time.perf_counter() - t0) * 1e3 / n_batches
+    det_local, gt_local = acc_d.view().clone(), acc_g.view().clone()
+    del acc_d, acc_g
     barrier()
     e0.record()
     det_all = gather_rows(det_local)
@@ -516,7 +527,8 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
     torch.cuda.synchronize()
     ms_match = max_over_ranks(e0.elapsed_time(e1))
     out["map_epoch"] = {"images": world * n_batches * B, "detections": int(det_all.shape[0]),
-                        "ground_truths": int(gt_all.shape[0]), "allgather_ms": ms_gather, "match_ms": ms_match,
+                        "ground_truths": int(gt_all.shape[0]), "accumulate_ms_per_batch": ms_acc,
+                        "allgather_ms": ms_gather, "match_ms": ms_match,
                         "mAP": float(m.item()), "detections_per_s": det_all.shape[0] / (ms_match * 1e-3)}
     # detection writers: integer box columns of one dense step's kept rows
     rows = pp(ring_dense).rows() if ring_dense is not None else det_local

@@ -3,6 +3,7 @@
 PyTorch is used for device memory (caching allocator), the current CUDA stream and, in
 ypp.dist, torch.distributed.  All arithmetic happens in libypp.so (csrc/*.cu).
 """
+import contextlib
 import ctypes
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
@@ -13,8 +14,25 @@ from . import _lib
 from ._lib import YppCfg, YppScale, check, lib
 
 
+# the per-call host cost is what bounds small batches: the current device and stream come from the two C getters
+# torch.cuda's Python helpers wrap (an order of magnitude cheaper); fall back to the public API if they move
+_cur_dev = getattr(torch._C, "_cuda_getDevice", None) or torch.cuda.current_device
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+_NULL_CTX = contextlib.nullcontext()
+
+
 def _stream():
+    if _raw_stream is not None:
+        return ctypes.c_void_p(_raw_stream(_cur_dev()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _on(device):
+    """Context that makes `device` current; nothing to do (and nothing to pay) when it already is."""
+    idx = device.index
+    if idx is None or idx == _cur_dev():
+        return _NULL_CTX
+    return torch.cuda.device(device)
 
 
 def _ptr(t: Optional[torch.Tensor]):
@@ -27,7 +45,7 @@ _ws_cache = {}
 def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
     """One scratch buffer per (device, tag), grown on demand; safe because every consumer is
     ordered on the current stream."""
-    key = (device.index if device.index is not None else torch.cuda.current_device(), tag)
+    key = (device.index if device.index is not None else _cur_dev(), tag)
     buf = _ws_cache.get(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
@@ -191,7 +209,7 @@ class PostProcessor:
         arr, heads, B, n_boxes = self._scales(heads)
         out = torch.empty((B, n_boxes, 6), dtype=torch.float32, device=heads[0].device)
         cfg = self._cfg(B, len(heads))
-        with torch.cuda.device(heads[0].device):
+        with _on(heads[0].device):
             check(lib().ypp_decode_dense(ctypes.byref(cfg), arr, _ptr(out), _stream()))
         return out
 
@@ -233,8 +251,8 @@ class PostProcessor:
         if nbytes is None:
             nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
         ws = _workspace(nbytes, dev, self.ws_tag)
-        if dev.index is not None and dev.index != torch.cuda.current_device():
-            with torch.cuda.device(dev):
+        if dev.index is not None and dev.index != _cur_dev():
+            with _on(dev):
                 return self.__call__(heads, img_idx_base, row_width, want_keep_idx, res)
         check(L.ypp_postprocess(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                 _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
@@ -294,7 +312,7 @@ class PostProcessor:
         cfg = self._cfg(B, n)
         L = lib()
         ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
-        with torch.cuda.device(dev):
+        with _on(dev):
             if tuple(stages) == ("decode", "sort", "nms"):
                 check(L.ypp_head_postprocess(ctypes.byref(cfg), arr, src, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                              _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
@@ -341,7 +359,7 @@ class PostProcessor:
         else:
             arr, cfg, nbytes = plan[0], plan[4], plan[5] or L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
         ws = _workspace(nbytes, dev, self.ws_tag)
-        with torch.cuda.device(dev):
+        with _on(dev):
             if plan is not None:                      # the cached parameter blocks of these head buffers
                 check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
                 check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
@@ -381,7 +399,7 @@ class PostProcessor:
         cfg = self._cfg(B, len(heads))
         L = lib()
         ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
-        with torch.cuda.device(dev):
+        with _on(dev):
             if "decode" in stages:
                 check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
             if "sort" in stages:
@@ -413,7 +431,7 @@ class PostProcessor:
         cfg = self._cfg(B, 1)
         L = lib()
         ws = _workspace(L.ypp_workspace_bytes(B, N, self.num_classes), dev, self.ws_tag)
-        with torch.cuda.device(dev):
+        with _on(dev):
             check(L.ypp_nms_rows(ctypes.byref(cfg), _ptr(rows), N, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                  _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
                                  res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
@@ -434,7 +452,7 @@ def target_rows(annot: torch.Tensor, input_size, img_idx_base=0):
     B, T, _ = annot.shape
     out = torch.empty((B * T, 7), dtype=torch.float32, device=annot.device)
     cnt = torch.empty(1, dtype=torch.int32, device=annot.device)
-    with torch.cuda.device(annot.device):
+    with _on(annot.device):
         check(lib().ypp_target_rows(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(out),
                                     _ptr(cnt), _stream()))
     return out, cnt
@@ -448,7 +466,7 @@ def target_rows_append(acc: RowAccumulator, annot: torch.Tensor, input_size, img
         raise ValueError("annot must be a CUDA tensor on the accumulator's device")
     annot = annot.to(torch.float32).contiguous()
     B, T, _ = annot.shape
-    with torch.cuda.device(annot.device):
+    with _on(annot.device):
         acc.reserve(B * T)
         cin, _ = acc.cursors(in_place=True)
         check(lib().ypp_target_rows_append(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(acc.buf),
@@ -462,7 +480,7 @@ def box_iou(box1: torch.Tensor, box2: torch.Tensor) -> torch.Tensor:
     a = box1.to(torch.float32).contiguous()
     b = box2.to(torch.float32).contiguous()
     out = torch.empty((a.shape[0], b.shape[0]), dtype=torch.float32, device=a.device)
-    with torch.cuda.device(a.device):
+    with _on(a.device):
         check(lib().ypp_box_iou(_ptr(a), a.shape[0], _ptr(b), b.shape[0], _ptr(out), _stream()))
     return out
 
@@ -482,7 +500,7 @@ def map_match(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, i
     m = torch.empty(1, dtype=torch.float32, device=dev)
     pc = torch.empty((int(num_classes), 4), dtype=torch.float32, device=dev)
     tp = torch.empty(max(K, 1), dtype=torch.uint8, device=dev) if want_tp else None
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(L.ypp_map_match(_ptr(gt), G, _ptr(det), K, int(num_classes), float(iou_threshold), _ptr(ws),
                               ws.numel(), _ptr(tp), _ptr(pc), _ptr(m), _stream()))
     return m, pc, (tp[:K] if tp is not None else None)
@@ -504,7 +522,7 @@ def detection_ints(rows: torch.Tensor, mode="pred_file", scale_xy: Optional[torc
     if scale_xy is not None:
         scale_xy = scale_xy.to(device=rows.device, dtype=torch.float32).reshape(-1, 2).contiguous()
         n_img = scale_xy.shape[0]
-    with torch.cuda.device(rows.device):
+    with _on(rows.device):
         check(lib().ypp_detection_ints(_ptr(rows), K, rows.shape[1], WRITER_MODES[mode], _ptr(scale_xy), n_img,
                                        float(img_idx_base), _ptr(out), _stream()))
     return out
@@ -557,7 +575,7 @@ def nms_ultralytics(prediction: torch.Tensor, conf_thres=0.25, iou_thres=0.45, c
                      keep_idx=torch.empty((B, rows), dtype=torch.int32, device=dev) if want_keep_idx else None,
                      n_boxes=rows)
     ws = _workspace(L.ypp_workspace_bytes(B, rows, nc), dev, "post")
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(L.ypp_nms_ultralytics(ctypes.byref(cfg), _ptr(pred), n, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                     _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), row_width,
                                     res.det_rows.shape[0], _ptr(res.det_total), float(img_idx_base), _stream()))
@@ -574,7 +592,7 @@ def decode_yolov1(inp: torch.Tensor, num_classes, num_boxes, input_size, S=7) ->
     B = x.shape[0]
     out = torch.empty((B, S * S, 6), dtype=torch.float32, device=x.device)
     if B:
-        with torch.cuda.device(x.device):
+        with _on(x.device):
             check(lib().ypp_decode_yolov1(_ptr(x), B, S, int(num_classes), int(num_boxes), float(input_size), _ptr(out), _stream()))
     return out
 
@@ -593,7 +611,7 @@ def confusion_update(matrix: torch.Tensor, detections: torch.Tensor, det_off: to
     n_img = d_off.numel() - 1
     K = det.shape[0]
     scratch = _workspace(max(K, 1) * 8, dev, "cm")
-    with torch.cuda.device(dev):
+    with _on(dev):
         check(lib().ypp_confusion_update(_ptr(det), _ptr(d_off), _ptr(lab), _ptr(l_off), n_img, K, int(nc), float(conf),
                                          float(iou_thres), _ptr(scratch), scratch.numel(), _ptr(matrix), _stream()))
     return matrix

@@ -139,6 +139,11 @@ int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, i
                    float* det_rows, int row_width, int64_t det_capacity, const int64_t* cursor_in,
                    int64_t* cursor_out, float img_idx_base, void* stream);
 
+/* ypp_postprocess with the gather in append mode (one call per batch of a validation loop). */
+int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
+                           int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
+                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream);
+
 /* The three stages above, back to back, from the heads (DecodeYoloV3/V2.forward and the body
  * of MeanAveragePrecision.update_state: utils/yolov3_utils.py:73-90,108-146). */
 int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,

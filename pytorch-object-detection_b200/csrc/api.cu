@@ -228,6 +228,25 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
                         img_idx_base, nullptr, true, true, (cudaStream_t)stream);
 }
 
+int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
+                           int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
+                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream)
+{
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, false, &p);
+    if (rc) return rc;
+    if (!det_rows || !cursor_in || !cursor_out || cursor_in == cursor_out) {
+        ypp_set_error("postprocess_append: det_rows and two different cursor words are required"); return YPP_E_BADARG;
+    }
+    rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
+    if (rc) return rc;
+    rc = ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
+    if (rc) return rc;
+    return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr,
+                        img_idx_base, nullptr, true, true, (cudaStream_t)stream, (const long long*)cursor_in,
+                        (long long*)cursor_out);
+}
+
 // the heads' 1x1 convolutions fused with D1: one tcgen05 kernel over every scale writes the slot records
 static int head_decode_all(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
                            YppDecodeParams* p, cudaStream_t st)

@@ -55,7 +55,7 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
-           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -112,6 +112,7 @@ def lib():
     L.ypp_nms_rows.argtypes = [cfgp, vp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_target_rows.argtypes = [vp, ci, ci, cf, cf, vp, vp, vp]
     L.ypp_target_rows_append.argtypes = [vp, ci, ci, cf, cf, vp, i64, vp, vp]
+    L.ypp_postprocess_append.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]

@@ -360,13 +360,15 @@ class PostProcessor:
             arr, cfg, nbytes = plan[0], plan[4], plan[5] or L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
         ws = _workspace(nbytes, dev, self.ws_tag)
         with _on(dev):
-            if plan is not None:                      # the cached parameter blocks of these head buffers
-                check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
-                check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
             acc.reserve(B * n_boxes)
             cin, cout = acc.cursors()
-            check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),
-                                   _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream()))
+            if plan is not None:                      # the cached parameter blocks of these head buffers: one call
+                check(L.ypp_postprocess_append(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(sc.cand_count),
+                                               _ptr(sc.keep_count), _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout,
+                                               float(img_idx_base), _stream()))
+            else:
+                check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),
+                                       _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream()))
         return sc
 
     def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,

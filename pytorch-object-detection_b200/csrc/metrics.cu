@@ -26,6 +26,10 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
     __shared__ int warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = B * T;
+    // In append mode the kernel sits between two chains of a validation loop and depends on neither: it is
+    // launched early (PDL), lets the next chain's D1 be scheduled at once, and only waits for the kernel before it
+    // on its way out, so that "this kernel is complete" still implies "everything before it is complete".
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const long long base = cursor_in ? *cursor_in : 0;      // append mode: rows already in `out`
     int running = 0;
     for (int i0 = 0; i0 < total; i0 += 1024) {
@@ -58,6 +62,7 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
         if (gt_count) *gt_count = running;
         if (cursor_out) *cursor_out = base + running;       // one block: may be the word cursor_in points at
     }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // ------------------------------------------------------------------ box_iou (N x M)
@@ -499,8 +504,12 @@ int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, f
                            float* out, int* gt_count, long long capacity, const long long* cursor_in,
                            long long* cursor_out, cudaStream_t st)
 {
-    ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count, capacity, cursor_in,
-                                               cursor_out);
+    if (cursor_in)      // append mode: the buffers are the accumulator's own, nothing of the kernel before is read
+        ypp_launch_chain(0, ypp_target_rows_kernel, dim3(1), dim3(1024), 0, st, annot, B, T, input_size, img_base, out, gt_count,
+                         capacity, cursor_in, cursor_out);
+    else
+        ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count, capacity, cursor_in,
+                                                   cursor_out);
     ypp_count_launch(1);
     return ypp_check_launch("target_rows");
 }

@@ -212,6 +212,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from ypp import engine, synth
+    from ypp import _lib
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -223,6 +224,11 @@ def run_ours(args):
     _bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    if not os.path.exists(_lib.LIB_PATH):       # a snapshot taken before __graft_entry__.build(): compile, never fall back
+        if local == 0:
+            _lib.build()
+    if world > 1:
+        dist.barrier()
 
     def barrier():
         if world > 1:

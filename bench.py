@@ -576,6 +576,22 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                               "what": "ypp_nms_ultralytics, conf .25 / iou .45 / max_det 300, best class, input resident in HBM"}
     del pred
     if len(grids) == 3 and w["kind"] == "v3":
+        # the reference's own calling shape: DecodeYoloV3.forward on ONE image (utils/yolov3_utils.py:73-90), the sized
+        # [K,6] tensor returned to the caller (so each call ends with a host read of K); wall clock, heads resident
+        from ypp.compat.yolov3_utils import DecodeYoloV3
+        dec = DecodeYoloV3(nc, anchors, w["input_size"], w["conf"])
+        one = [[h[:1].contiguous() for h in hs] for hs in sparse]
+        for i in range(20):
+            k = dec(one[i % n_ring]).shape[0]
+        torch.cuda.synchronize()
+        n_calls = 300
+        t0 = time.perf_counter()
+        for i in range(n_calls):
+            k = dec(one[i % n_ring]).shape[0]
+        torch.cuda.synchronize()
+        ms_d = (time.perf_counter() - t0) * 1e3 / n_calls
+        out["decode_module_b1"] = {"ms_per_call": ms_d, "images_per_s": 1e3 / ms_d, "kept_last": int(k),
+                                   "what": "ypp.compat.yolov3_utils.DecodeYoloV3.forward, batch 1, sparse regime, result sized on the host"}
         out["fused_head"] = fused_head_extra(torch, engine, dev, w, anchors)
     return out
 

@@ -111,3 +111,21 @@ def test_accumulator_from_features_and_result(cuda):
     assert torch.equal(m.all_true_boxes_variable, torch.cat(gts))
     want = engine.map_match(torch.cat(gts), torch.cat(dets), 20)[0]
     assert float(m.result()) == float(want)
+
+
+def test_append_on_a_device_that_is_not_current(cuda):
+    """One process, two GPUs: the accumulators live on cuda:1 while cuda:0 is current."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from ypp import engine, synth
+    d1 = torch.device("cuda", 1)
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    batches = [[h.to(d1) for h in hs] for hs in _batches(cuda, 3)]
+    want = torch.cat([pp(h, img_idx_base=4 * i).rows().clone() for i, h in enumerate(batches)])
+    acc, gt = engine.RowAccumulator(d1, 2), engine.RowAccumulator(d1)
+    for i, h in enumerate(batches):
+        pp.accumulate(acc, h, img_idx_base=4 * i)
+        engine.target_rows_append(gt, synth.make_annots(4, 20, g=i).to(d1), 416, 4 * i)
+    assert torch.cuda.current_device() == 0
+    assert torch.equal(acc.view(), want) and want.device == d1
+    assert gt.view().shape[0] == sum(int((synth.make_annots(4, 20, g=i)[..., 0] >= 0).sum()) for i in range(3))

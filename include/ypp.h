@@ -151,6 +151,24 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
                     float* det_rows, int row_width, int64_t det_capacity, int* det_total,
                     float img_idx_base, void* stream);
 
+/* Any contiguous part of the chain as ONE call: stages is a mask of YPP_STAGE_* (DECODE = D1, SORT = S1,
+ * SUPPRESS = N1 (+ the long-segment kernel), ROWS = the row gather G).  The state between stages lives in
+ * the workspace, so a chain may be cut anywhere and continued by a later call on the same workspace (on any
+ * stream that is ordered after the first).  What it is for: several batches in flight, each on its own
+ * stream and workspace, with only the ROWS stages - which append behind one device cursor and therefore run
+ * in batch order - chained by events (the validation loop of module/yolov3_detector.py:33-47 without the
+ * host ever waiting for the device).  scales is read when DECODE is set (n_boxes may then be 0 = derive it);
+ * the outputs and cursors when ROWS is set, with the meaning they have in ypp_nms / ypp_nms_append
+ * (cursor_in == cursor_out == NULL: plain mode). */
+#define YPP_STAGE_DECODE 1
+#define YPP_STAGE_SORT 2
+#define YPP_STAGE_SUPPRESS 4
+#define YPP_STAGE_ROWS 8
+int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, void* ws, size_t ws_bytes, int stages,
+                   int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width,
+                   int64_t det_capacity, int* det_total, const int64_t* cursor_in, int64_t* cursor_out,
+                   float img_idx_base, void* stream);
+
 /* ---- the head's 1x1 convolution fused with the decode ---------------------------
  * Every detector ends each scale in nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
  * (models/detector/yolov3.py:56,62,68; yolov2.py; yolov4_tiny.py) and hands its output to

@@ -96,7 +96,7 @@ int bind_ws(int B, int N, int nc, void* ws, size_t ws_bytes, YppWs* out)
 int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int* keep_count, int* keep_idx,
                  float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
                  const float* src_rows, bool do_sort, bool do_nms, cudaStream_t st,
-                 const long long* cursor_in = nullptr, long long* cursor_out = nullptr)
+                 const long long* cursor_in = nullptr, long long* cursor_out = nullptr, bool do_rows = true)
 {
     int rc = YPP_OK;
     if (do_sort) {
@@ -108,12 +108,14 @@ int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int
         if (rc) return rc;
     }
     if (do_nms) {
-        if (det_rows && row_width != 6 && row_width != 7) { ypp_set_error("row_width must be 6 or 7"); return YPP_E_BADARG; }
         YppNmsParams n;
         memset(&n, 0, sizeof(n));
         n.ws = w; n.B = cfg->B; n.N = N; n.nc = cfg->nc; n.iou_thr = cfg->iou_thr; n.union_mode = cfg->union_mode;
         rc = ypp_launch_nms(n, st);
         if (rc) return rc;
+    }
+    if (do_rows) {
+        if (det_rows && row_width != 6 && row_width != 7) { ypp_set_error("row_width must be 6 or 7"); return YPP_E_BADARG; }
         YppGatherParams g;
         memset(&g, 0, sizeof(g));
         g.ws = w; g.B = cfg->B; g.N = N;
@@ -181,7 +183,7 @@ int ypp_sort_segments(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes
     rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
     if (rc) return rc;
     return run_sort_nms(cfg, n_boxes, w, nullptr, nullptr, nullptr, nullptr, 7, 0, nullptr, 0.f, nullptr, true, false,
-                        (cudaStream_t)stream);
+                        (cudaStream_t)stream, nullptr, nullptr, false);
 }
 
 int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count, int* keep_idx,
@@ -245,6 +247,41 @@ int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws
     return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr,
                         img_idx_base, nullptr, true, true, (cudaStream_t)stream, (const long long*)cursor_in,
                         (long long*)cursor_out);
+}
+
+int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, void* ws, size_t ws_bytes, int stages,
+                   int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width, int64_t det_capacity,
+                   int* det_total, const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream)
+{
+    if (stages <= 0 || stages > 15) { ypp_set_error("run_stages: stages=%d is not a mask of YPP_STAGE_*", stages); return YPP_E_BADARG; }
+    if ((cursor_in == nullptr) != (cursor_out == nullptr) || (cursor_in && (const int64_t*)cursor_out == cursor_in)) {
+        ypp_set_error("run_stages: append mode needs two different cursor words"); return YPP_E_BADARG;
+    }
+    if (cursor_in && !det_rows) { ypp_set_error("run_stages: append mode needs det_rows"); return YPP_E_BADARG; }
+    YppWs w;
+    int rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (stages & YPP_STAGE_DECODE) {
+        YppDecodeParams p;
+        rc = build_decode_params(cfg, scales, false, &p);
+        if (rc) return rc;
+        if (n_boxes > 0 && n_boxes != p.N) { ypp_set_error("run_stages: n_boxes=%d but the scales hold %d boxes", n_boxes, p.N); return YPP_E_BADARG; }
+        n_boxes = p.N;
+        rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
+        if (rc) return rc;
+        rc = ypp_launch_decode_compact(p, cfg->B, st);
+        if (rc) return rc;
+        w = p.ws;
+    } else {
+        rc = check_cfg(cfg);
+        if (rc) return rc;
+        if (n_boxes <= 0 || n_boxes > YPP_MAX_BOXES) { ypp_set_error("run_stages: n_boxes=%d out of range", n_boxes); return YPP_E_BADARG; }
+        rc = bind_ws(cfg->B, n_boxes, cfg->nc, ws, ws_bytes, &w);
+        if (rc) return rc;
+    }
+    return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, nullptr, (stages & YPP_STAGE_SORT) != 0, (stages & YPP_STAGE_SUPPRESS) != 0, st,
+                        (const long long*)cursor_in, (long long*)cursor_out, (stages & YPP_STAGE_ROWS) != 0);
 }
 
 // the heads' 1x1 convolutions fused with D1: one tcgen05 kernel over every scale writes the slot records

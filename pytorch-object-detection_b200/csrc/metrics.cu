@@ -26,10 +26,12 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
     __shared__ int warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int total = B * T;
-    // In append mode the kernel sits between two chains of a validation loop and depends on neither: it is
-    // launched early (PDL), lets the next chain's D1 be scheduled at once, and only waits for the kernel before it
-    // on its way out, so that "this kernel is complete" still implies "everything before it is complete".
+    // In append mode the kernel sits between two chains of a validation loop and is launched early (PDL): its CTA is
+    // scheduled while the kernel ahead drains and it lets the next chain's D1 be scheduled at once.  Every global
+    // read and write - the annotations, the cursor word the previous ground-truth kernel wrote, the rows - comes
+    // after griddepcontrol.wait, i.e. after the whole grid ahead has completed and flushed.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const long long base = cursor_in ? *cursor_in : 0;      // append mode: rows already in `out`
     int running = 0;
     for (int i0 = 0; i0 < total; i0 += 1024) {
@@ -62,7 +64,6 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
         if (gt_count) *gt_count = running;
         if (cursor_out) *cursor_out = base + running;       // one block: may be the word cursor_in points at
     }
-    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // ------------------------------------------------------------------ box_iou (N x M)

@@ -19,6 +19,10 @@ SCORE_OBJ, SCORE_OBJ_TIMES_CLS = 0, 1
 OFFSET_NONE, OFFSET_TRICK, OFFSET_AUTO_CPU, OFFSET_AUTO_CUDA = 0, 1, 2, 3
 UNION_SEPARATE, UNION_FMA = 0, 1
 
+STAGE_DECODE, STAGE_SORT, STAGE_SUPPRESS, STAGE_ROWS = 1, 2, 4, 8
+STAGES = {"decode": STAGE_DECODE, "sort": STAGE_SORT, "suppress": STAGE_SUPPRESS, "rows": STAGE_ROWS,
+          "nms": STAGE_SUPPRESS | STAGE_ROWS}
+
 OFFSET_MODES = {"none": OFFSET_NONE, "trick": OFFSET_TRICK, "auto_cpu": OFFSET_AUTO_CPU,
                 "auto_cuda": OFFSET_AUTO_CUDA}
 UNION_MODES = {"separate": UNION_SEPARATE, "fma": UNION_FMA}
@@ -55,7 +59,7 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
-           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -114,6 +118,7 @@ def lib():
     L.ypp_target_rows_append.argtypes = [vp, ci, ci, cf, cf, vp, i64, vp, vp]
     L.ypp_postprocess_append.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
+    L.ypp_run_stages.argtypes = [cfgp, scp, ci, vp, ctypes.c_size_t, ci, vp, vp, vp, vp, ci, i64, vp, vp, vp, cf, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]
     L.ypp_ultra_rows.argtypes = [ci, ci, ci]
@@ -131,7 +136,8 @@ def lib():
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
                  "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match",
                  "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update",
-                 "ypp_head_decode_compact", "ypp_head_postprocess"):
+                 "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_run_stages", "ypp_nms_append",
+                 "ypp_postprocess_append", "ypp_target_rows_append"):
         getattr(L, name).restype = ci
     _lib = L
     return L

@@ -29,7 +29,30 @@ class _GrowBuf:
         return self.buf[: self.n]
 
 
-class MeanAveragePrecisionBase:
+class LiveParams:
+    """The reference reads num_classes / anchors / input_size / conf_threshold from the object on every call
+    (utils/yolov3_utils.py:79,88,113-125), so assigning one of them after construction changes the next call.
+    Same here: assigning any name in `_live` drops the processor, and the next call builds one from the current
+    values.  (Mutating the anchors list in place is not seen; assign a new list.)"""
+    _live = ("num_classes", "anchors", "scaled_anchors", "input_size", "conf_threshold")
+
+    def __setattr__(self, name, value):
+        if name in self._live:
+            self.__dict__.pop("_pp", None)
+        super().__setattr__(name, value)
+
+    def __getattr__(self, name):
+        if name == "_pp":
+            pp = self._make_processor()
+            self.__dict__["_pp"] = pp
+            return pp
+        parent = getattr(super(), "__getattr__", None)        # nn.Module resolves parameters / buffers / submodules here
+        if parent is not None:
+            return parent(name)
+        raise AttributeError("%r object has no attribute %r" % (type(self).__name__, name))
+
+
+class MeanAveragePrecisionBase(LiveParams):
     """reset_states / update_state / result with the reference's public attributes
     (utils/yolov3_utils.py:93-149, utils/yolov2_utils.py:81-128)."""
 
@@ -39,8 +62,12 @@ class MeanAveragePrecisionBase:
         self.anchors = anchors
         self.input_size = input_size
         self.conf_threshold = conf_threshold
-        self._pp = engine.PostProcessor(num_classes, anchors, input_size, conf_threshold, kind=kind, **modes)
+        self._kind, self._modes = kind, modes
         self.reset_states()
+
+    def _make_processor(self):
+        return engine.PostProcessor(self.num_classes, self.anchors, self.input_size, self.conf_threshold,
+                                    kind=self._kind, **self._modes)
 
     def reset_states(self):
         self._true = None          # RowAccumulators, made on the first batch's device

@@ -7,7 +7,7 @@
 from torch import nn
 
 from .. import engine
-from ._accum import MeanAveragePrecisionBase
+from ._accum import LiveParams, MeanAveragePrecisionBase
 from .yolo_utils import nms_v3, mean_average_precision  # noqa: F401  (re-exported like the reference)
 
 
@@ -17,7 +17,7 @@ def decode_predictions(input, num_classes, anchors, input_size):
     return pp.decode([input])
 
 
-class DecodeYoloV3(nn.Module):
+class DecodeYoloV3(LiveParams, nn.Module):
     """Decode YOLOv3 predictions of ONE image to boxes [K,6] (decode + nms_v3)."""
 
     def __init__(self, num_classes, anchors, input_size, conf_threshold=0.5, **modes):
@@ -26,7 +26,11 @@ class DecodeYoloV3(nn.Module):
         self.anchors = anchors
         self.input_size = input_size
         self.conf_threshold = conf_threshold
-        self._pp = engine.PostProcessor(num_classes, anchors, input_size, conf_threshold, kind="v3", **modes)
+        self._modes = modes
+
+    def _make_processor(self):
+        return engine.PostProcessor(self.num_classes, self.anchors, self.input_size, self.conf_threshold, kind="v3",
+                                    **self._modes)
 
     def forward(self, x):
         assert x[0].size(0) == 1

@@ -5,6 +5,7 @@ ypp.dist, torch.distributed.  All arithmetic happens in libypp.so (csrc/*.cu).
 """
 import contextlib
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -39,18 +40,42 @@ def _ptr(t: Optional[torch.Tensor]):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
 
 
-_ws_cache = {}
+def _stream_key(device):
+    """(device ordinal, raw handle of the stream current on it)."""
+    idx = device.index if device.index is not None else _cur_dev()
+    if _raw_stream is not None:
+        return idx, _raw_stream(idx)
+    return idx, torch.cuda.current_stream(idx).cuda_stream
+
+
+class _Scratch:
+    """Scratch buffers of ONE owner (a PostProcessor, or the module-level helpers below), one per
+    (device, stream, tag), grown on demand.  A buffer is only ever handed to work queued on the stream it is
+    keyed on, so everything that touches it is stream-ordered; two streams (or two owners) never share one.
+    A buffer that is replaced goes back to the caching allocator, which is stream-ordered on that same stream.
+    Streams come and go (CUDA graph captures, per-call side streams): beyond `max_live` entries the oldest go."""
+
+    def __init__(self, max_live=16):
+        self._bufs = {}
+        self.max_live = max_live
+
+    def get(self, nbytes: int, device, tag: str = "post") -> torch.Tensor:
+        key = _stream_key(device) + (tag,)
+        buf = self._bufs.get(key)
+        if buf is None or buf.numel() < nbytes:
+            if buf is None and len(self._bufs) >= self.max_live:
+                self._bufs.pop(next(iter(self._bufs)))
+            buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+            self._bufs[key] = buf
+        return buf
+
+
+_module_scratch = _Scratch()
 
 
 def _workspace(nbytes: int, device, tag: str) -> torch.Tensor:
-    """One scratch buffer per (device, tag), grown on demand; safe because every consumer is
-    ordered on the current stream."""
-    key = (device.index if device.index is not None else _cur_dev(), tag)
-    buf = _ws_cache.get(key)
-    if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
-        _ws_cache[key] = buf
-    return buf
+    """Scratch of the module-level entry points (map_match, nms_ultralytics, confusion_update)."""
+    return _module_scratch.get(nbytes, device, tag)
 
 
 def _check_head(t: torch.Tensor, name="head") -> torch.Tensor:
@@ -91,7 +116,11 @@ class RowAccumulator:
     `self.all_pred_boxes_variable = torch.cat([...])` (utils/yolov3_utils.py:139-146) builds, without a host
     read of the count per batch.  The kernels append behind a device cursor (ypp_nms_append /
     ypp_target_rows_append); the host only tracks an upper bound of the rows (worst case per append) and reads
-    the cursor when that bound reaches the capacity - once per `sync_every` appends at most."""
+    the cursor when that bound reaches the capacity - once per `sync_every` appends at most.
+
+    Appends may be queued on side streams (PostProcessor.accumulate with several batches in flight): `last`
+    is then the event behind the most recent append, and everything that reads or moves the rows on the
+    current stream (count, growth, view) waits for it first."""
 
     def __init__(self, device, sync_every=16):
         self.device = torch.device(device)
@@ -101,8 +130,27 @@ class RowAccumulator:
         self.buf = None
         self.bound = 0                                                     # rows <= bound, known without a sync
         self.syncs = 0
+        self.last = None                                                   # torch.cuda.Event or None
+        self._streams = set()                                              # side streams that were told about buf / cur
+
+    def join(self):
+        """The current stream waits for every append queued so far (they complete in order: one event)."""
+        if self.last is not None:
+            torch.cuda.current_stream(self.device).wait_event(self.last)
+            self.last = None
+
+    def used_by(self, stream):
+        """A side stream is about to append: the caching allocator must not hand the buffers to anyone else
+        while work queued on that stream still touches them."""
+        key = (stream.cuda_stream, 0 if self.buf is None else self.buf.data_ptr())
+        if key not in self._streams:
+            self._streams.add(key)
+            self.cur.record_stream(stream)
+            if self.buf is not None:
+                self.buf.record_stream(stream)
 
     def count(self) -> int:
+        self.join()
         self.syncs += 1
         n = int(self.cur[self.k & 1].item())
         self.bound = n
@@ -132,7 +180,31 @@ class RowAccumulator:
     def view(self) -> torch.Tensor:
         if self.buf is None:
             return torch.empty((0, 7), dtype=torch.float32, device=self.device)
-        return self.buf[: self.count()]
+        n = self.count()
+        # reserve() books the worst case of every append, so the kernels never had to drop a row
+        assert n <= self.buf.shape[0], "RowAccumulator: %d rows were appended to a buffer of %d" % (n, self.buf.shape[0])
+        return self.buf[:n]
+
+
+class _Plan:
+    """Parameter blocks of one set of head buffers.  Holds NO tensor: the key (pointer, shape, dtype, device of
+    every head) guarantees the pointers inside `arr` are those of whatever tensors are passed with that key."""
+    __slots__ = ("arr", "B", "n_boxes", "cfg", "nbytes", "dev")
+
+    def __init__(self, arr, B, n_boxes, cfg, nbytes, dev):
+        self.arr, self.B, self.n_boxes, self.cfg, self.nbytes, self.dev = arr, B, n_boxes, cfg, nbytes, dev
+
+
+class _Slot:
+    """One batch in flight of PostProcessor.accumulate: a side stream with its own workspace and count outputs."""
+
+    def __init__(self, dev):
+        self.stream = torch.cuda.Stream(device=dev)
+        self.raw = ctypes.c_void_p(self.stream.cuda_stream)
+        self.ready = torch.cuda.Event()          # recorded on the caller's stream: inputs and accumulator are ready
+        self.done = torch.cuda.Event()           # recorded on the side stream behind the row gather
+        self.ws = None
+        self.sc = None
 
 
 class PostProcessor:
@@ -143,17 +215,28 @@ class PostProcessor:
     Heads are consumed in list order with anchors[A*i : A*i+A] (utils/yolov3_utils.py:76-78).
     Defaults reproduce what the reference computes when it runs on a CUDA device:
     torchvision's CUDA heuristic for the coordinate trick and its fma-contracted union.
+
+    Scratch memory belongs to the processor and is keyed on the stream it is used from, so two processors, or
+    one processor called from two streams, never share a buffer.  pipeline_depth: batches `accumulate` keeps
+    in flight (each on its own side stream and workspace; only the row gathers, which append behind one
+    device cursor, are chained in batch order).  None = 3 for batches of at least 32 768 boxes, else 1;
+    the environment variable YPP_PIPELINE overrides the default.
     """
 
     def __init__(self, num_classes, anchors, input_size, conf_threshold=0.25, iou_threshold=0.45,
                  kind="v3", anchors_per_scale=None, offset_mode="auto_cuda", union_mode="fma",
-                 score_mode="obj", compare_in_double=None, ws_tag="post"):
+                 score_mode="obj", compare_in_double=None, pipeline_depth=None):
         self.num_classes = int(num_classes)
-        self.ws_tag = ws_tag            # scratch buffer name: processors used from different streams need their own
         self.anchors = [list(map(float, a)) for a in anchors]
         self.input_size = input_size
-        self.conf_threshold = float(conf_threshold)
-        self.iou_threshold = float(iou_threshold)
+        self._plans = {}
+        self._scratch = {}
+        self._ws = _Scratch()
+        self._rings = {}
+        self._batches = 0
+        if pipeline_depth is None and os.environ.get("YPP_PIPELINE"):
+            pipeline_depth = int(os.environ["YPP_PIPELINE"])
+        self.pipeline_depth = pipeline_depth
         self.kind = kind
         if anchors_per_scale is None:
             anchors_per_scale = len(self.anchors) if kind == "v2" else 3
@@ -163,13 +246,38 @@ class PostProcessor:
         self.score_mode = _lib.SCORE_MODES[score_mode] if isinstance(score_mode, str) else int(score_mode)
         if compare_in_double is None:
             compare_in_double = self.union_mode == _lib.UNION_SEPARATE   # CPU kernel semantics
-        self.iou_thr_eff = float(lib().ypp_effective_iou_thr(self.iou_threshold, int(bool(compare_in_double))))
-        self._plans = {}
-        self._scratch = {}
+        self._compare_in_double = bool(compare_in_double)
+        self.conf_threshold = conf_threshold
+        self.iou_threshold = iou_threshold
+
+    # the thresholds are plain attributes in the reference (read on every call, utils/yolov3_utils.py:88,125):
+    # assigning one takes effect on the next call here too (the cached parameter blocks are dropped)
+    @property
+    def conf_threshold(self):
+        return self._conf
+
+    @conf_threshold.setter
+    def conf_threshold(self, v):
+        self._conf = float(v)
+        self._plans.clear()
+
+    @property
+    def iou_threshold(self):
+        return self._iou
+
+    @iou_threshold.setter
+    def iou_threshold(self, v):
+        self._iou = float(v)
+        self.iou_thr_eff = float(lib().ypp_effective_iou_thr(self._iou, int(self._compare_in_double)))
+        self._plans.clear()
+
+    def workspace(self, nbytes, device) -> torch.Tensor:
+        """This processor's scratch buffer for the stream current on `device`."""
+        return self._ws.get(nbytes, device)
 
     # -- parameter blocks ------------------------------------------------------------------
     def _cfg(self, B, n_scales):
-        return YppCfg(self.num_classes, int(B), int(n_scales), self.conf_threshold, self.iou_thr_eff,
+        return YppCfg(self.num_classes, int(B), int(n_scales), self._conf, self.iou_thr_eff,
                       self.score_mode, self.offset_mode, self.union_mode)
 
     def _scales(self, heads: Sequence[torch.Tensor]):
@@ -226,38 +334,36 @@ class PostProcessor:
             n_boxes=n_boxes)
 
     def _plan(self, heads):
-        """Parameter blocks for these exact head buffers, cached (the per-call host cost is what
-        bounds the sparse regime): key = (pointer, shape) of every head."""
+        """Parameter blocks for these exact head buffers, cached (the per-call host cost is what bounds the sparse
+        regime): key = (pointer, shape, ...) of every head.  Returns (plan, heads actually read): the second is
+        only there to keep contiguous copies of non-contiguous heads alive until the launches are queued."""
         key = tuple((h.data_ptr(), tuple(h.shape), h.is_contiguous(), h.dtype, h.device.index) for h in heads)
         plan = self._plans.get(key)
-        if plan is None:
-            arr, heads_c, B, n_boxes = self._scales(heads)
-            if any(hc is not h for hc, h in zip(heads_c, heads)):
-                return (arr, heads_c, B, n_boxes, self._cfg(B, len(heads)), None)     # temporaries: do not cache
-            dev = heads[0].device
-            nbytes = lib().ypp_workspace_bytes(B, n_boxes, self.num_classes)
-            plan = (arr, heads_c, B, n_boxes, self._cfg(B, len(heads)), nbytes)
+        if plan is not None:
+            return plan, heads
+        arr, heads_c, B, n_boxes = self._scales(heads)
+        plan = _Plan(arr, B, n_boxes, self._cfg(B, len(heads)), lib().ypp_workspace_bytes(B, n_boxes, self.num_classes),
+                     heads_c[0].device)
+        if all(hc is h for hc, h in zip(heads_c, heads)):        # temporaries are not worth remembering
             if len(self._plans) > 64:
                 self._plans.clear()
             self._plans[key] = plan
-        return plan
+        return plan, heads_c
 
     def __call__(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
-                 out: Optional[PostResult] = None) -> PostResult:
-        arr, heads, B, n_boxes, cfg, nbytes = self._plan(heads)
-        dev = heads[0].device
-        res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
-        L = lib()
-        if nbytes is None:
-            nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
-        ws = _workspace(nbytes, dev, self.ws_tag)
+                 out: Optional[PostResult] = None, ws: Optional[torch.Tensor] = None) -> PostResult:
+        plan, heads = self._plan(heads)
+        dev = plan.dev
         if dev.index is not None and dev.index != _cur_dev():
             with _on(dev):
-                return self.__call__(heads, img_idx_base, row_width, want_keep_idx, res)
-        check(L.ypp_postprocess(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
-                                _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
-                                res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
-                                float(img_idx_base), _stream()))
+                return self.__call__(heads, img_idx_base, row_width, want_keep_idx, out, ws)
+        res = self._outputs(plan.B, plan.n_boxes, dev, row_width, want_keep_idx, out)
+        if ws is None:
+            ws = self._ws.get(plan.nbytes, dev)
+        check(lib().ypp_postprocess(ctypes.byref(plan.cfg), plan.arr, _ptr(ws), ws.numel(), _ptr(res.cand_count),
+                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
+                                    res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
+                                    float(img_idx_base), _stream()))
         return res
 
     def from_features(self, features: Sequence[torch.Tensor], weights: Sequence[torch.Tensor], img_idx_base=0,
@@ -311,8 +417,8 @@ class PostProcessor:
         res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
         cfg = self._cfg(B, n)
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
         with _on(dev):
+            ws = self._ws.get(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev)
             if tuple(stages) == ("decode", "sort", "nms"):
                 check(L.ypp_head_postprocess(ctypes.byref(cfg), arr, src, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                              _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
@@ -330,87 +436,160 @@ class PostProcessor:
                                     float(img_idx_base), _stream()))
         return (res, heads_out) if want_heads else res
 
+    def _depth(self, B, n_boxes):
+        d = self.pipeline_depth
+        if d is None:
+            d = 3 if B * n_boxes >= 32768 else 1
+        return max(1, int(d))
+
+    def _slot(self, dev, depth, B, nbytes):
+        ring = self._rings.get(dev.index)
+        if ring is None or len(ring) != depth:
+            self.join()
+            ring = [_Slot(dev) for _ in range(depth)]
+            self._rings[dev.index] = ring
+        sl = ring[self._batches % depth]
+        if sl.ws is None or sl.ws.numel() < nbytes:
+            sl.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+            sl.ws.record_stream(sl.stream)
+        if sl.sc is None or sl.sc.keep_count.numel() != B:
+            z = torch.empty
+            sl.sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                               z(B, dtype=torch.int32, device=dev), None, 0)
+            sl.sc.keep_count.record_stream(sl.stream)
+            sl.sc.cand_count.record_stream(sl.stream)
+        return sl
+
+    def join(self):
+        """The current stream of every device this processor has batches in flight on waits for them."""
+        for idx, ring in self._rings.items():
+            cur = torch.cuda.current_stream(idx)
+            for sl in ring:
+                cur.wait_stream(sl.stream)
+
     def accumulate(self, acc: RowAccumulator, heads: Sequence[torch.Tensor], weights=None, img_idx_base=0):
         """The chain with the gather appending to `acc` (7-column rows) instead of filling a per-call buffer:
         nothing is read back, so a validation loop queues batch after batch.  weights given: `heads` are the
-        INPUTS of the heads' 1x1 convolutions (from_features)."""
-        plan = None
-        if weights is None:
-            plan = self._plan(heads)
-            _, hc, B, n_boxes, _, _ = plan
-            dev = hc[0].device
-        else:
+        INPUTS of the heads' 1x1 convolutions (from_features).
+
+        With a pipeline depth above 1 (see the class) batch i runs on side stream i mod depth: its decode, sort
+        and suppression overlap the neighbouring batches' (the per-image sort alone leaves most SMs idle), its
+        row gather waits for the previous batch's (the cursor chain) - so rows still land in batch order - and
+        `acc` remembers the event behind it; acc.view() / count() / a later growth wait for that event.  The
+        counts returned belong to this batch and are valid for the current stream after acc.join()."""
+        L = lib()
+        if weights is not None:                       # fused-head entry: current stream, one batch at a time
             B = heads[0].shape[0]
             n_boxes = sum(self.A * f.shape[2] * f.shape[3] for f in heads)
             dev = heads[0].device
-        if acc.device != dev:
-            raise ValueError("accumulator and heads are on different devices")
-        sc = self._scratch.get((B, dev))
-        if sc is None:
-            z = torch.empty
-            sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
-                            z(B, dtype=torch.int32, device=dev), None, n_boxes)
-            self._scratch[(B, dev)] = sc
-        L = lib()
-        if plan is None:
+            if acc.device != dev:
+                raise ValueError("accumulator and heads are on different devices")
+            sc = self._scratch.get((B, dev))
+            if sc is None:
+                z = torch.empty
+                sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                                z(B, dtype=torch.int32, device=dev), None, n_boxes)
+                self._scratch[(B, dev)] = sc
+            acc.join()
             self.from_features(heads, weights, stages=("decode", "sort"), out=sc)
             cfg = self._cfg(B, len(heads))
-            nbytes = L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
-        else:
-            arr, cfg, nbytes = plan[0], plan[4], plan[5] or L.ypp_workspace_bytes(B, n_boxes, self.num_classes)
-        ws = _workspace(nbytes, dev, self.ws_tag)
-        with _on(dev):
-            acc.reserve(B * n_boxes)
-            cin, cout = acc.cursors()
-            if plan is not None:                      # the cached parameter blocks of these head buffers: one call
-                check(L.ypp_postprocess_append(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _ptr(sc.cand_count),
-                                               _ptr(sc.keep_count), _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout,
-                                               float(img_idx_base), _stream()))
-            else:
+            with _on(dev):
+                ws = self._ws.get(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev)
+                acc.reserve(B * n_boxes)
+                cin, cout = acc.cursors()
                 check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),
                                        _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream()))
-        return sc
+            return sc
+        plan, heads = self._plan(heads)
+        dev, B, n_boxes = plan.dev, plan.B, plan.n_boxes
+        if acc.device != dev:
+            raise ValueError("accumulator and heads are on different devices")
+        depth = self._depth(B, n_boxes)
+        with _on(dev):
+            if depth == 1:
+                acc.join()
+                sc = self._scratch.get((B, dev))
+                if sc is None:
+                    z = torch.empty
+                    sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
+                                    z(B, dtype=torch.int32, device=dev), None, n_boxes)
+                    self._scratch[(B, dev)] = sc
+                ws = self._ws.get(plan.nbytes, dev)
+                acc.reserve(B * n_boxes)
+                cin, cout = acc.cursors()
+                check(L.ypp_postprocess_append(ctypes.byref(plan.cfg), plan.arr, _ptr(ws), ws.numel(), _ptr(sc.cand_count),
+                                               _ptr(sc.keep_count), _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout,
+                                               float(img_idx_base), _stream()))
+                return sc
+            sl = self._slot(dev, depth, B, plan.nbytes)
+            self._batches += 1
+            acc.reserve(B * n_boxes)                 # may read the cursor / move the rows: on the current stream, joined
+            cin, cout = acc.cursors()
+            acc.used_by(sl.stream)
+            for h in heads:                          # the allocator must not reuse a head the side stream still reads
+                h.record_stream(sl.stream)
+            cur = torch.cuda.current_stream(dev)
+            sl.ready.record(cur)
+            sl.stream.wait_event(sl.ready)
+            cfgp, wsp, wsn = ctypes.byref(plan.cfg), _ptr(sl.ws), sl.ws.numel()
+            check(L.ypp_run_stages(cfgp, plan.arr, n_boxes, wsp, wsn, _lib.STAGE_DECODE | _lib.STAGE_SORT | _lib.STAGE_SUPPRESS,
+                                   None, None, None, None, 7, 0, None, None, None, 0.0, sl.raw))
+            if acc.last is not None:
+                sl.stream.wait_event(acc.last)       # the previous gather wrote the cursor word this one reads
+            check(L.ypp_run_stages(cfgp, plan.arr, n_boxes, wsp, wsn, _lib.STAGE_ROWS, _ptr(sl.sc.cand_count),
+                                   _ptr(sl.sc.keep_count), None, _ptr(acc.buf), 7, acc.buf.shape[0], None, cin, cout,
+                                   float(img_idx_base), sl.raw))
+            sl.done.record(sl.stream)
+            acc.last = sl.done
+        sl.sc.n_boxes = n_boxes
+        return sl.sc
 
     def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
-                repeat=1, stages=None):
+                repeat=1, stages=None, ws: Optional[torch.Tensor] = None):
         """Capture the chain on these (static) head buffers into a CUDA graph.  Returns
         (graph, PostResult); graph.replay() re-runs it with whatever the buffers then hold.
         `repeat` > 1 captures that many back-to-back invocations (timing loops); `stages`
-        restricts the capture to some of ("decode", "sort", "nms")."""
+        restricts the capture to some of ("decode", "sort", "nms").  The graph bakes in the address of its
+        workspace: a private one is allocated here (or `ws` is used: graphs that are only ever replayed on one
+        stream may share one) and lives as long as the result (`res.ws`)."""
         heads = [_check_head(h) for h in heads]
-        if stages is None:
-            res = self(heads, img_idx_base, row_width, want_keep_idx)          # warm-up, allocations
-        else:
-            res = self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=("decode", "sort", "nms"))
+        arr, _, B, n_boxes = self._scales(heads)
+        nbytes = lib().ypp_workspace_bytes(B, n_boxes, self.num_classes)
+        if ws is None:
+            ws = torch.empty(int(nbytes), dtype=torch.uint8, device=heads[0].device)
+        elif ws.numel() < nbytes:
+            raise ValueError("graphed: workspace of %d bytes, %d needed" % (ws.numel(), nbytes))
+        res = self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=("decode", "sort", "nms"), ws=ws)   # warm-up, allocations
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             for _ in range(repeat):
                 if stages is None:
-                    self(heads, img_idx_base, row_width, want_keep_idx, out=res)
+                    self(heads, img_idx_base, row_width, want_keep_idx, out=res, ws=ws)
                 else:
-                    self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=stages, out=res)
+                    self.staged(heads, img_idx_base, row_width, want_keep_idx, stages=stages, out=res, ws=ws)
+        res.ws = ws
         return g, res
 
     def staged(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
-               stages=("decode", "sort", "nms"), out: Optional[PostResult] = None) -> PostResult:
-        """Same chain through the three separate C-ABI stages (used to time / profile D1 alone)."""
+               stages=("decode", "sort", "nms"), out: Optional[PostResult] = None,
+               ws: Optional[torch.Tensor] = None) -> PostResult:
+        """Same chain through the separate C-ABI stages (used to time / profile D1 alone); stages from
+        ("decode", "sort", "nms" = "suppress" + "rows")."""
         arr, heads, B, n_boxes = self._scales(heads)
         dev = heads[0].device
         res = self._outputs(B, n_boxes, dev, row_width, want_keep_idx, out)
         cfg = self._cfg(B, len(heads))
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev, self.ws_tag)
+        mask = 0
+        for st in stages:
+            mask |= _lib.STAGES[st]
         with _on(dev):
-            if "decode" in stages:
-                check(L.ypp_decode_compact(ctypes.byref(cfg), arr, _ptr(ws), ws.numel(), _stream()))
-            if "sort" in stages:
-                check(L.ypp_sort_segments(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _stream()))
-            if "nms" in stages:
-                check(L.ypp_nms(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(res.cand_count),
-                                _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
-                                res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),
-                                float(img_idx_base), _stream()))
+            if ws is None:
+                ws = self._ws.get(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev)
+            check(L.ypp_run_stages(ctypes.byref(cfg), arr, n_boxes, _ptr(ws), ws.numel(), mask, _ptr(res.cand_count),
+                                   _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), res.det_rows.shape[1],
+                                   res.det_rows.shape[0], _ptr(res.det_total), None, None, float(img_idx_base), _stream()))
         return res
 
     def nms_rows(self, rows: torch.Tensor, img_idx_base=0, row_width=6, want_keep_idx=False) -> PostResult:
@@ -432,8 +611,8 @@ class PostProcessor:
         res = self._outputs(B, N, dev, row_width, want_keep_idx, None)
         cfg = self._cfg(B, 1)
         L = lib()
-        ws = _workspace(L.ypp_workspace_bytes(B, N, self.num_classes), dev, self.ws_tag)
         with _on(dev):
+            ws = self._ws.get(L.ypp_workspace_bytes(B, N, self.num_classes), dev)
             check(L.ypp_nms_rows(ctypes.byref(cfg), _ptr(rows), N, _ptr(ws), ws.numel(), _ptr(res.cand_count),
                                  _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows),
                                  res.det_rows.shape[1], res.det_rows.shape[0], _ptr(res.det_total),

@@ -63,7 +63,7 @@ def test_overflow_drops_rows_but_counts_them(cuda):
     cur = torch.tensor([3, 0], dtype=torch.int64, device=cuda)         # 3 rows "already there"
     L = _lib.lib()
     cfg = pp._cfg(4, 3)
-    ws = engine._workspace(L.ypp_workspace_bytes(4, sc.n_boxes, 20), cuda, pp.ws_tag)
+    ws = pp.workspace(L.ypp_workspace_bytes(4, sc.n_boxes, 20), cuda)
     _lib.check(L.ypp_nms_append(ctypes.byref(cfg), sc.n_boxes, ws.data_ptr(), ws.numel(), None, sc.keep_count.data_ptr(),
                                 guard.data_ptr(), 7, cap, cur.data_ptr(), cur.data_ptr() + 8, 0.0,
                                 torch.cuda.current_stream().cuda_stream))

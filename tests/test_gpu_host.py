@@ -1,0 +1,137 @@
+"""GPU: the host layer's ownership rules - scratch memory per (processor, stream), cached parameter blocks that
+hold no tensors, several batches in flight in the accumulate path, thresholds that stay live attributes."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _heads(cuda, B, g, mu=0.0, grids=(52, 26, 13)):
+    from ypp import synth
+    return [h.to(cuda) for h in synth.make_heads(B, 20, list(grids), g=g, mu_obj=mu)]
+
+
+def test_one_processor_on_two_streams_does_not_share_scratch(cuda):
+    """Two dense batches through ONE processor from two streams at the same time: each stream has its own
+    workspace, so both results equal the ones computed one after the other (a shared buffer - what a
+    (device, tag) cache gave - mixes the two images' candidates)."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    a, b = _heads(cuda, 16, 900), _heads(cuda, 16, 901)
+    want = [pp(h, want_keep_idx=True) for h in (a, b)]
+    want = [(r.rows().clone(), r.keep_count.clone()) for r in want]
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    torch.cuda.synchronize()
+    for rep in range(8):
+        outs = []
+        for st, h in ((s1, a), (s2, b)):
+            with torch.cuda.stream(st):
+                outs.append(pp(h, want_keep_idx=True))
+        torch.cuda.synchronize()
+        for (rows, kc), r in zip(want, outs):
+            assert torch.equal(r.keep_count, kc)
+            assert torch.equal(r.det_rows[: rows.shape[0]], rows)
+    with torch.cuda.stream(s1):
+        w1 = pp.workspace(1024, cuda)
+    with torch.cuda.stream(s2):
+        w2 = pp.workspace(1024, cuda)
+    assert w1.data_ptr() != w2.data_ptr()
+    other = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    with torch.cuda.stream(s1):
+        assert other.workspace(1024, cuda).data_ptr() != w1.data_ptr()
+
+
+def test_fresh_head_tensors_are_not_retained(cuda):
+    """A validation loop hands over fresh head tensors every batch: the cached parameter blocks must not keep them
+    alive (80 batches of 3 heads stayed resident before)."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    acc = engine.RowAccumulator(cuda)
+    base = _heads(cuda, 8, 910, mu=-5.0)
+    pp.accumulate(acc, [h.clone() for h in base])
+    pp(base)
+    torch.cuda.synchronize()
+    m0 = torch.cuda.memory_allocated()
+    per_batch = sum(h.numel() * 4 for h in base)
+    for i in range(80):
+        fresh = [h.clone() + 0.0 for h in base]
+        pp.accumulate(acc, fresh, img_idx_base=8 * i)
+        pp(fresh)
+        del fresh
+    acc.view()
+    torch.cuda.synchronize()
+    grown = torch.cuda.memory_allocated() - m0
+    assert grown < 4 * per_batch, "memory grew by %.1f MB over 80 fresh batches" % (grown / 1e6)
+    assert all(not isinstance(v, torch.Tensor) for pl in pp._plans.values() for v in vars(type(pl)).keys())
+    for pl in pp._plans.values():
+        for name in pl.__slots__:
+            assert not isinstance(getattr(pl, name), (torch.Tensor, list, tuple))
+
+
+@pytest.mark.parametrize("depth", [1, 2, 3, 5])
+def test_batches_in_flight_append_in_batch_order(cuda, depth):
+    """accumulate with `depth` batches in flight on side streams: rows, order and counts equal the batches
+    processed one by one; growth of the accumulator in the middle included (sync_every=1 forces it)."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25, pipeline_depth=depth)
+    seq = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25, pipeline_depth=1)
+    batches = [_heads(cuda, 4, 920 + i, mu=(0.0 if i % 3 == 0 else -3.0)) for i in range(9)]
+    want = torch.cat([seq(h, img_idx_base=4 * i).rows().clone() for i, h in enumerate(batches)])
+    for sync_every in (1, 16):
+        acc = engine.RowAccumulator(cuda, sync_every)
+        counts = []
+        for i, h in enumerate(batches):
+            sc = pp.accumulate(acc, [x.clone() for x in h], img_idx_base=4 * i)     # fresh tensors, dropped at once
+            counts.append(sc)
+        got = acc.view()
+        assert got.shape == want.shape
+        assert torch.equal(got, want)
+        assert int(counts[-1].keep_count.sum()) == int(seq(batches[-1]).det_total)
+
+
+def test_thresholds_are_live_attributes(cuda):
+    """The reference reads self.conf_threshold on every call (utils/yolov3_utils.py:88,125); assigning it after
+    construction must change the next call here too."""
+    from ypp import engine, synth
+    from ypp.compat.yolov3_utils import DecodeYoloV3, MeanAveragePrecision
+    h = _heads(cuda, 1, 930, mu=-2.0)
+    dec = DecodeYoloV3(20, synth.YOLOV3_ANCHORS, 416, 0.5)
+    n_hi = dec(h).shape[0]
+    dec.conf_threshold = 0.25
+    got = dec(h)
+    want = DecodeYoloV3(20, synth.YOLOV3_ANCHORS, 416, 0.25)(h)
+    assert got.shape[0] > n_hi and torch.equal(got, want)
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.5)
+    a = int(pp(h).det_total)
+    pp.conf_threshold = 0.25
+    assert int(pp(h).det_total) == want.shape[0] and a == n_hi
+    pp.iou_threshold = 0.9
+    assert int(pp(h).det_total) >= want.shape[0]
+    m = MeanAveragePrecision(20, synth.YOLOV3_ANCHORS, 416, 0.5)
+    annot = synth.make_annots(1, 20, g=0).to(cuda)
+    m.update_state(annot, h)
+    k0 = m.all_pred_boxes_variable.shape[0]
+    m.reset_states()
+    m.conf_threshold = 0.25
+    m.update_state(annot, h)
+    assert m.all_pred_boxes_variable.shape[0] == want.shape[0] and k0 == n_hi
+
+
+def test_graph_keeps_its_own_workspace(cuda):
+    """A captured chain bakes in the address of its workspace: a later, larger request through the same processor
+    must not free it under the graph."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    small = _heads(cuda, 2, 940)
+    g, res = pp.graphed(small, want_keep_idx=True)
+    want = pp(small, want_keep_idx=True)
+    want_rows, want_kc = want.rows().clone(), want.keep_count.clone()
+    big = _heads(cuda, 32, 941)
+    pp(big)                                         # grows the processor's own scratch
+    junk = [torch.full((int(res.ws.numel()) // 4,), float("nan"), device=cuda) for _ in range(4)]   # would land on a freed buffer
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(res.keep_count, want_kc)
+    assert torch.equal(res.det_rows[: want_rows.shape[0]], want_rows)
+    del junk

@@ -32,7 +32,7 @@ for g in range(g0, g0 + 4):
     import numpy as np
     from ypp._lib import lib
     B, N, nc = w["batch"], synth.boxes_per_image(w["grids"], w["A"]), w["nc"]
-    ws = engine._workspace(lib().ypp_workspace_bytes(B, N, nc), dev, "post").cpu().numpy()
+    ws = pp.workspace(lib().ypp_workspace_bytes(B, N, nc), dev).cpu().numpy()
     off = [0]
     def take(nbytes):
         o = off[0]

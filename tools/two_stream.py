@@ -12,7 +12,7 @@ dev = torch.device("cuda:0")
 ring = [[h.to(dev) for h in synth.make_heads(w["batch"], w["nc"], w["grids"], A=w["A"], g=i)] for i in range(12)]
 for ns in (1, 2, 3, 4, 6):
     pps = [engine.PostProcessor(w["nc"], synth.workload_anchors(w), w["input_size"], w["conf"], kind=w["kind"],
-                                anchors_per_scale=w["A"], ws_tag="post%d" % k) for k in range(ns)]
+                                anchors_per_scale=w["A"]) for k in range(ns)]
     streams = [torch.cuda.Stream() for _ in range(ns)]
     graphs = [pps[i % ns].graphed(ring[i]) for i in range(12)]
     torch.cuda.synchronize()

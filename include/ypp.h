@@ -270,6 +270,17 @@ int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, co
 /* box_iou, utils/metrics.py:233-255: xyxy [N,4] x [M,4] -> [N,M]. */
 int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_NM, void* stream);
 
+/* bbox_iou, utils/metrics.py:192-230 (the Ultralytics flavour: eps on the union, no abs; the mAP matching uses the
+ * one of utils/yolo_utils.py, inside ypp_map_match): box1 [n1,4] against box2 [n2,4] element by element with
+ * n1 == n2 or either equal to 1 (broadcast), out [max(n1,n2)] (the reference returns [n,1]).
+ * xywh != 0: rows are cx,cy,w,h, else x1,y1,x2,y2.  mode: */
+#define YPP_IOU 0
+#define YPP_GIOU 1
+#define YPP_DIOU 2
+#define YPP_CIOU 3      /* atan through CUDA's atanf: within an ulp of torch's on any device */
+int ypp_bbox_iou(const float* box1, int n1, const float* box2, int n2, int xywh, int mode, double eps, float* out,
+                 void* stream);
+
 /* ConfusionMatrix.process_batch, utils/metrics.py:122-160, for n_img images in one launch (the
  * reference is called once per image):
  *   det [K,6] x1,y1,x2,y2,conf,cls of all images, det_off [n_img+1] row offsets (det_off[n_img] = K)

@@ -442,3 +442,123 @@ def head_conv1x1(feature, weight):
     head = np.einsum("bkhw,ck->bchw", x, w)
     bound = np.einsum("bkhw,ck->bchw", np.abs(x), np.abs(w))
     return head, bound
+
+
+# ---------------------------------------------------------------- utils/metrics.py: the AP side (compute_ap, ap_per_class, bbox_iou)
+def best_class_scores(prediction, conf_thres=0.25):
+    """The scoring lines of the vendored NMS alone, utils/general.py:645,669,679-680, for ONE image [n,5+nc]:
+    obj > conf -> conf_j = cls_j * obj -> (conf, j) = first maximum over j -> conf > conf_thres.
+    Returns (box numbers, conf, j): what YPP_SCORE_OBJ_TIMES_CLS must compute before NMS."""
+    x = _f32(prediction)
+    t = np.float32(conf_thres)
+    idx, conf, cls = [], [], []
+    for r in range(x.shape[0]):
+        if not (x[r, 4] > t):
+            continue
+        best, bj = None, 0
+        for j in range(x.shape[1] - 5):
+            v = np.float32(x[r, 5 + j] * x[r, 4])
+            if best is None or v > best:
+                best, bj = v, j
+        if best is not None and best > t:
+            idx.append(r); conf.append(best); cls.append(bj)
+    return np.array(idx, np.int64), np.array(conf, np.float32), np.array(cls, np.int64)
+
+
+def compute_ap(recall, precision):
+    """utils/metrics.py:86-111, float64, method 'interp': sentinels (0,1) / (1,0), right-to-left running maximum of
+    the precision, trapezoid of the envelope sampled at 101 recall points.  Plain loops, no numpy reductions
+    besides np.interp (whose definition is numpy's)."""
+    mrec = [0.0] + [float(v) for v in recall] + [1.0]
+    mpre = [1.0] + [float(v) for v in precision] + [0.0]
+    for i in range(len(mpre) - 2, -1, -1):               # np.flip(np.maximum.accumulate(np.flip(mpre))); NaN propagates
+        if mpre[i] == mpre[i] and not (mpre[i] >= mpre[i + 1]):
+            mpre[i] = mpre[i + 1]
+    mrec, mpre = np.array(mrec, np.float64), np.array(mpre, np.float64)
+    x = np.linspace(0, 1, 101)
+    y = np.interp(x, mrec, mpre)
+    ap = float(np.add.reduce(np.diff(x) * (y[1:] + y[:-1]) / 2.0))      # np.trapz(y, x)
+    return ap, mpre, mrec
+
+
+def ap_per_class(tp, conf, pred_cls, target_cls):
+    """utils/metrics.py:21-83 without the plots: -> (p, r, ap, f1, unique_classes.astype(int32))."""
+    tp = np.asarray(tp)
+    conf = np.asarray(conf)
+    pred_cls = np.asarray(pred_cls)
+    target_cls = np.asarray(target_cls)
+    order = np.argsort(-conf)                                                    # :37 (numpy's default sort, as there)
+    tp, conf, pred_cls = tp[order], conf[order], pred_cls[order]
+    classes = np.unique(target_cls)
+    nc = classes.shape[0]
+    px = np.linspace(0, 1, 1000)
+    ap = np.zeros((nc, tp.shape[1]))
+    p = np.zeros((nc, 1000))
+    r = np.zeros((nc, 1000))
+    for ci in range(nc):
+        c = classes[ci]
+        sel = pred_cls == c
+        n_l = int((target_cls == c).sum())
+        n_p = int(sel.sum())
+        if n_p == 0 or n_l == 0:
+            continue
+        fpc = (1 - tp[sel]).cumsum(0)
+        tpc = tp[sel].cumsum(0)
+        recall = tpc / (n_l + 1e-16)
+        r[ci] = np.interp(-px, -conf[sel], recall[:, 0], left=0)
+        precision = tpc / (tpc + fpc)
+        p[ci] = np.interp(-px, -conf[sel], precision[:, 0], left=1)
+        for j in range(tp.shape[1]):
+            ap[ci, j] = compute_ap(recall[:, j], precision[:, j])[0]
+    f1 = 2 * p * r / (p + r + 1e-16)
+    i = f1.mean(0).argmax()
+    return p[:, i], r[:, i], ap, f1[:, i], classes.astype("int32")
+
+
+def bbox_iou_metrics(box1, box2, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7):
+    """utils/metrics.py:192-230 (NOT utils/yolo_utils.py's bbox_iou: no abs, eps 1e-7, xywh flag): box1 [1|n,4]
+    against box2 [n,4] -> [n,1], one fp32 rounding per torch operation, in the reference's operand order."""
+    f = np.float32
+    a, b = _f32(box1).reshape(-1, 4), _f32(box2).reshape(-1, 4)
+    n = max(a.shape[0], b.shape[0])
+    e = f(eps)
+    out = np.empty((n, 1), np.float32)
+    with np.errstate(all="ignore"):
+        for k in range(n):
+            p, q = a[k if a.shape[0] > 1 else 0], b[k if b.shape[0] > 1 else 0]
+            if xywh:
+                w1, h1, w2, h2 = p[2], p[3], q[2], q[3]
+                ax1, ax2, ay1, ay2 = f(p[0] - f(w1 / f(2))), f(p[0] + f(w1 / f(2))), f(p[1] - f(h1 / f(2))), f(p[1] + f(h1 / f(2)))
+                bx1, bx2, by1, by2 = f(q[0] - f(w2 / f(2))), f(q[0] + f(w2 / f(2))), f(q[1] - f(h2 / f(2))), f(q[1] + f(h2 / f(2)))
+            else:
+                ax1, ay1, ax2, ay2 = p
+                bx1, by1, bx2, by2 = q
+                w1, h1 = f(ax2 - ax1), f(f(ay2 - ay1) + e)
+                w2, h2 = f(bx2 - bx1), f(f(by2 - by1) + e)
+            iw = max(f(min(ax2, bx2) - max(ax1, bx1)), f(0))
+            ih = max(f(min(ay2, by2) - max(ay1, by1)), f(0))
+            inter = f(iw * ih)
+            union = f(f(f(f(w1 * h1) + f(w2 * h2)) - inter) + e)
+            iou = f(inter / union)
+            res = iou
+            if CIoU or DIoU or GIoU:
+                cw = f(max(ax2, bx2) - min(ax1, bx1))
+                ch = f(max(ay2, by2) - min(ay1, by1))
+                if CIoU or DIoU:
+                    c2 = f(f(f(cw * cw) + f(ch * ch)) + e)
+                    dx = f(f(f(bx1 + bx2) - ax1) - ax2)
+                    dy = f(f(f(by1 + by2) - ay1) - ay2)
+                    rho2 = f(f(f(dx * dx) + f(dy * dy)) / f(4))
+                    if CIoU:
+                        import math
+                        da = f(f(np.arctan(f(w2 / h2))) - f(np.arctan(f(w1 / h1))))
+                        v = f(f(4 / math.pi ** 2) * f(da * da))
+                        alpha = f(v / f(f(v - iou) + f(1 + eps)))
+                        res = f(iou - f(f(rho2 / c2) + f(v * alpha)))
+                    else:
+                        res = f(iou - f(rho2 / c2))
+                else:
+                    c_area = f(f(cw * ch) + e)
+                    res = f(iou - f(f(c_area - union) / c_area))
+            out[k, 0] = res
+    return out

@@ -446,6 +446,17 @@ int ypp_box_iou(const float* a_N4, int N, const float* b_M4, int M, float* out_N
     return ypp_launch_box_iou(a_N4, N, b_M4, M, out_NM, (cudaStream_t)stream);
 }
 
+int ypp_bbox_iou(const float* box1, int n1, const float* box2, int n2, int xywh, int mode, double eps, float* out, void* stream)
+{
+    if (n1 < 0 || n2 < 0 || mode < 0 || mode > 3) { ypp_set_error("bbox_iou: bad size or mode"); return YPP_E_BADARG; }
+    if (n1 == 0 || n2 == 0) return YPP_OK;
+    if (n1 != n2 && n1 != 1 && n2 != 1) { ypp_set_error("bbox_iou: %d and %d boxes do not broadcast", n1, n2); return YPP_E_BADARG; }
+    if (!box1 || !box2 || !out) { ypp_set_error("bbox_iou: null pointer"); return YPP_E_BADARG; }
+    if ((((uintptr_t)box1) | ((uintptr_t)box2)) & 15u) { ypp_set_error("bbox_iou: inputs must be 16-byte aligned"); return YPP_E_BADARG; }
+    // eps and 1 + eps are Python floats in the reference: rounded to fp32 once when they meet an fp32 tensor
+    return ypp_launch_bbox_iou(box1, n1, box2, n2, xywh ? 1 : 0, mode, (float)eps, (float)(1.0 + eps), out, (cudaStream_t)stream);
+}
+
 size_t ypp_map_workspace_bytes(int64_t G, int64_t K, int nc) { return ypp_map_ws_bytes(G, K, nc); }
 
 int ypp_map_match(const float* gt_G7, int64_t G, const float* det_K7, int64_t K, int nc, float iou_thr, void* ws,

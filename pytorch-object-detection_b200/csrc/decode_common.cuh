@@ -50,6 +50,20 @@ __device__ __noinline__ int cls_resolve(const float* cls_base, int stride, int n
     return best;
 }
 
+// YPP_SCORE_OBJ_TIMES_CLS: the class is the first maximum of the PRODUCTS conf_j = sigmoid(cls_j) * sigmoid(obj)
+// (utils/general.py:669 `x[:, 5:] *= x[:, 4:5]`, :679 `conf, j = x[:, 5:].max(1)`).  The fp32 product is monotone in
+// sigmoid(cls_j), so its maximum P belongs to the largest sigmoid, but a slightly smaller sigmoid at a LOWER index
+// may round to the same product and then wins the arg-max.  Only logits inside `band` of the largest can do that.
+__device__ __noinline__ int cls_resolve_product(const float* cls_base, int stride, int nc, float m1, float band, float sobj,
+                                                float P, int fallback, int q, int hwm)
+{
+    for (int c = 0; c < nc; ++c) {
+        const float v = cls_base[(size_t)c * stride + ((q + c * hwm) & 3)];
+        if (v >= m1 - band && __fmul_rn(ypp_sigmoid(v), sobj) == P) return c;
+    }
+    return fallback;
+}
+
 template <class Load>
 __device__ __forceinline__ void class_sweep(Load ld, int nc, ClsTrack& tr)      // ld(c) = logit of class c
 {
@@ -89,9 +103,15 @@ __device__ __forceinline__ Decoded decode_cell(const YppDecodeParams& p, const Y
         const float tol = cls_tol(tr.m1);
         if (!(tr.m1 - tr.m2 > tol)) ci = cls_resolve(cls_base, cls_stride, p.nc, tr.m1, tol, cls_q, cls_hwm);
     }
-    d.cls = ci;
     d.score = sobj;
-    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) d.score = __fmul_rn(sobj, ypp_sigmoid(tr.m1));
+    if (p.score_mode == YPP_SCORE_OBJ_TIMES_CLS) {
+        d.score = __fmul_rn(ypp_sigmoid(tr.m1), sobj);
+        // a sigmoid within 2^-21 relative of the largest is the most that can still round to the same product
+        const float band = 8.0f * cls_tol(tr.m1);
+        if (p.nc > 1 && !(tr.m1 - tr.m2 > band))
+            ci = cls_resolve_product(cls_base, cls_stride, p.nc, tr.m1, band, sobj, d.score, ci, cls_q, cls_hwm);
+    }
+    d.cls = ci;
     return d;
 }
 

@@ -82,6 +82,59 @@ ypp_box_iou_kernel(const float4* __restrict__ a, int N, const float4* __restrict
     out[(size_t)i * M + j] = __fdiv_rn(inter, __fsub_rn(__fadd_rn(s1, s2), inter));
 }
 
+// ------------------------------------------------------------------ bbox_iou of utils/metrics.py:192-230
+// The Ultralytics flavour (not the one of utils/yolo_utils.py that the mAP matching uses: no abs, eps 1e-7 on the
+// union, an xywh flag, and the GIoU / DIoU / CIoU returns): box1 [1|n,4] against box2 [n,4], element by element,
+// one fp32 rounding per torch operation in the reference's operand order.  mode: 0 IoU, 1 GIoU, 2 DIoU, 3 CIoU.
+__global__ void __launch_bounds__(256)
+ypp_bbox_iou_kernel(const float4* __restrict__ a, int na, const float4* __restrict__ b, int nb, int n, int xywh, int mode,
+                    float eps, float one_eps, float* __restrict__ out)
+{
+    const int k = blockIdx.x * 256 + threadIdx.x;
+    if (k >= n) return;
+    const float4 p = __ldg(a + (na > 1 ? k : 0)), q = __ldg(b + (nb > 1 ? k : 0));
+    float ax1, ay1, ax2, ay2, bx1, by1, bx2, by2, w1, h1, w2, h2;
+    if (xywh) {
+        w1 = p.z; h1 = p.w; w2 = q.z; h2 = q.w;
+        const float w1h = __fmul_rn(w1, 0.5f), h1h = __fmul_rn(h1, 0.5f), w2h = __fmul_rn(w2, 0.5f), h2h = __fmul_rn(h2, 0.5f);   // x / 2, exact
+        ax1 = __fsub_rn(p.x, w1h); ax2 = __fadd_rn(p.x, w1h); ay1 = __fsub_rn(p.y, h1h); ay2 = __fadd_rn(p.y, h1h);
+        bx1 = __fsub_rn(q.x, w2h); bx2 = __fadd_rn(q.x, w2h); by1 = __fsub_rn(q.y, h2h); by2 = __fadd_rn(q.y, h2h);
+    } else {
+        ax1 = p.x; ay1 = p.y; ax2 = p.z; ay2 = p.w;
+        bx1 = q.x; by1 = q.y; bx2 = q.z; by2 = q.w;
+        w1 = __fsub_rn(ax2, ax1); h1 = __fadd_rn(__fsub_rn(ay2, ay1), eps);
+        w2 = __fsub_rn(bx2, bx1); h2 = __fadd_rn(__fsub_rn(by2, by1), eps);
+    }
+    const float iw = fmaxf(__fsub_rn(fminf(ax2, bx2), fmaxf(ax1, bx1)), 0.0f);
+    const float ih = fmaxf(__fsub_rn(fminf(ay2, by2), fmaxf(ay1, by1)), 0.0f);
+    const float inter = __fmul_rn(iw, ih);
+    const float uni = __fadd_rn(__fsub_rn(__fadd_rn(__fmul_rn(w1, h1), __fmul_rn(w2, h2)), inter), eps);
+    const float iou = __fdiv_rn(inter, uni);
+    float res = iou;
+    if (mode != 0) {
+        const float cw = __fsub_rn(fmaxf(ax2, bx2), fminf(ax1, bx1));
+        const float ch = __fsub_rn(fmaxf(ay2, by2), fminf(ay1, by1));
+        if (mode == 1) {
+            const float ca = __fadd_rn(__fmul_rn(cw, ch), eps);
+            res = __fsub_rn(iou, __fdiv_rn(__fsub_rn(ca, uni), ca));
+        } else {
+            const float c2 = __fadd_rn(__fadd_rn(__fmul_rn(cw, cw), __fmul_rn(ch, ch)), eps);
+            const float dx = __fsub_rn(__fsub_rn(__fadd_rn(bx1, bx2), ax1), ax2);
+            const float dy = __fsub_rn(__fsub_rn(__fadd_rn(by1, by2), ay1), ay2);
+            const float rho2 = __fmul_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), 0.25f);
+            if (mode == 2) {
+                res = __fsub_rn(iou, __fdiv_rn(rho2, c2));
+            } else {
+                const float da = __fsub_rn(atanf(__fdiv_rn(w2, h2)), atanf(__fdiv_rn(w1, h1)));
+                const float v = __fmul_rn(0.40528473456935109f, __fmul_rn(da, da));            // 4 / pi^2
+                const float alpha = __fdiv_rn(v, __fadd_rn(__fsub_rn(v, iou), one_eps));
+                res = __fsub_rn(iou, __fadd_rn(__fdiv_rn(rho2, c2), __fmul_rn(v, alpha)));
+            }
+        }
+    }
+    out[k] = res;
+}
+
 // ------------------------------------------------------------------ stable LSD radix sort
 #define RS_THREADS 256
 #define RS_ITEMS 8
@@ -521,6 +574,15 @@ int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out,
     ypp_box_iou_kernel<<<grid, 256, 0, st>>>((const float4*)a, N, (const float4*)b, M, out);
     ypp_count_launch(1);
     return ypp_check_launch("box_iou");
+}
+
+int ypp_launch_bbox_iou(const float* a, int na, const float* b, int nb, int xywh, int mode, float eps, float one_eps,
+                        float* out, cudaStream_t st)
+{
+    const int n = na > nb ? na : nb;
+    ypp_bbox_iou_kernel<<<(n + 255) / 256, 256, 0, st>>>((const float4*)a, na, (const float4*)b, nb, n, xywh, mode, eps, one_eps, out);
+    ypp_count_launch(1);
+    return ypp_check_launch("bbox_iou");
 }
 
 size_t ypp_map_ws_bytes(long long G, long long K, int nc)

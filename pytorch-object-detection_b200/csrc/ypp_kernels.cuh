@@ -86,6 +86,8 @@ int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, f
                            float* out, int* gt_count, long long capacity, const long long* cursor_in,
                            long long* cursor_out, cudaStream_t st);
 int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);
+int ypp_launch_bbox_iou(const float* a, int na, const float* b, int nb, int xywh, int mode, float eps, float one_eps,
+                        float* out, cudaStream_t st);
 size_t ypp_map_ws_bytes(long long G, long long K, int nc);
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,

@@ -57,7 +57,7 @@ WRITER_MODES = {"pred_file": 0, "coco": 1}
 
 EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "ypp_decode_compact",
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
-           "ypp_target_rows", "ypp_box_iou", "ypp_map_workspace_bytes", "ypp_map_match",
+           "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
            "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
@@ -120,6 +120,7 @@ def lib():
     L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_run_stages.argtypes = [cfgp, scp, ci, vp, ctypes.c_size_t, ci, vp, vp, vp, vp, ci, i64, vp, vp, vp, cf, vp]
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
+    L.ypp_bbox_iou.argtypes = [vp, ci, vp, ci, ci, ci, ctypes.c_double, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]
     L.ypp_ultra_rows.argtypes = [ci, ci, ci]
     L.ypp_ultra_rows.restype = i64
@@ -134,10 +135,10 @@ def lib():
     L.ypp_launch_count.argtypes = [ci]
     L.ypp_launch_count.restype = i64
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
-                 "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_map_match",
+                 "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_match",
                  "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update",
                  "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_run_stages", "ypp_nms_append",
-                 "ypp_postprocess_append", "ypp_target_rows_append"):
+                 "ypp_postprocess_append", "ypp_target_rows_append", "ypp_bbox_iou"):
         getattr(L, name).restype = ci
     _lib = L
     return L

@@ -666,6 +666,20 @@ def box_iou(box1: torch.Tensor, box2: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def bbox_iou(box1: torch.Tensor, box2: torch.Tensor, xywh=True, GIoU=False, DIoU=False, CIoU=False, eps=1e-7) -> torch.Tensor:
+    """utils/metrics.py:192-230: box1 [1|n,4] against box2 [n,4] -> [n,1]."""
+    if not (box1.is_cuda and box2.is_cuda):
+        raise ValueError("bbox_iou needs CUDA tensors (ypp has no CPU path)")
+    a = box1.to(torch.float32).reshape(-1, 4).contiguous()
+    b = box2.to(torch.float32).reshape(-1, 4).contiguous()
+    n = max(a.shape[0], b.shape[0]) if a.shape[0] and b.shape[0] else 0
+    out = torch.empty((n, 1), dtype=torch.float32, device=a.device)
+    mode = 3 if CIoU else 2 if DIoU else 1 if GIoU else 0
+    with _on(a.device):
+        check(lib().ypp_bbox_iou(_ptr(a), a.shape[0], _ptr(b), b.shape[0], int(bool(xywh)), mode, float(eps), _ptr(out), _stream()))
+    return out
+
+
 def map_match(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, iou_threshold=0.5,
               want_tp=True):
     """mean_average_precision / metrics_per_class on the GPU.

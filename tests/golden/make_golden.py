@@ -37,6 +37,7 @@ from utils.yolov3_utils import DecodeYoloV3, MeanAveragePrecision as RefMAPv3   
 from utils.yolov2_utils import decode_predictions as ref_decode_v2      # noqa: E402
 from utils.yolov2_utils import DecodeYoloV2, MeanAveragePrecision as RefMAPv2   # noqa: E402
 from utils.metrics import box_iou as ref_box_iou      # noqa: E402
+import utils.metrics as ref_metrics                   # noqa: E402
 
 from oracle import oracle as O                        # noqa: E402
 from ypp import synth                                 # noqa: E402
@@ -520,6 +521,160 @@ def case_confusion():
                         matrix=cm.matrix, nc=nc, conf=0.3, iou_thres=0.4)
 
 
+# ------------------------------------------------------------------ utils/metrics.py: AP side + bbox_iou
+
+def case_metrics_ap():
+    """ap_per_class (:21-83), compute_ap (:86-111) and bbox_iou (:192-230) of utils/metrics.py run as they are."""
+    rng = np.random.RandomState(61)
+    out = {}
+    for tag, n, T, ncp, nct, m in (("t1", 900, 1, 7, 6, 260), ("t10", 700, 10, 5, 5, 300), ("few", 12, 1, 3, 4, 9)):
+        conf = rng.uniform(0, 1, n)
+        conf[::11] = 0.5                                  # tied confidences
+        tp = rng.uniform(0, 1, (n, T)) < np.linspace(0.7, 0.2, T)[None]
+        pred_cls = rng.randint(0, ncp, n).astype(np.float64)
+        target_cls = rng.randint(0, nct, m).astype(np.float64)
+        ref = ref_metrics.ap_per_class(tp, conf, pred_cls, target_cls, names={})
+        got = O.ap_per_class(tp, conf, pred_cls, target_cls)
+        check("metrics:ap_per_class:" + tag, all(np.array_equal(a, b) for a, b in zip(ref, got)), "mAP %.4f" % ref[2].mean())
+        for k, v in zip(("tp", "conf", "pred_cls", "target_cls"), (tp, conf, pred_cls, target_cls)):
+            out["%s_%s" % (tag, k)] = v
+        for k, v in zip(("p", "r", "ap", "f1", "classes"), ref):
+            out["%s_%s" % (tag, k)] = v
+    rec = np.sort(rng.uniform(0, 1, 64))
+    pre = rng.uniform(0, 1, 64)
+    ap, mpre, mrec = ref_metrics.compute_ap(rec, pre)
+    oap, ompre, omrec = O.compute_ap(rec, pre)
+    check("metrics:compute_ap", ap == oap and np.array_equal(mpre, ompre) and np.array_equal(mrec, omrec), "ap %.6f" % ap)
+    out.update(ca_recall=rec, ca_precision=pre, ca_ap=np.float64(ap), ca_mpre=mpre, ca_mrec=mrec)
+    # bbox_iou: xywh and xyxy, n-to-n and 1-to-n, the four returns
+    b1 = np.concatenate([rng.uniform(0, 416, (240, 2)), rng.uniform(1, 200, (240, 2))], 1).astype(np.float32)
+    b2 = np.concatenate([rng.uniform(0, 416, (240, 2)), rng.uniform(1, 200, (240, 2))], 1).astype(np.float32)
+    b2[:12] = b1[:12]                                    # identical pairs
+    b2[12:24, :2] = b1[12:24, :2] + 1000.0               # disjoint pairs
+    b1[24, 2:] = 0.0                                     # a zero-area box
+    out["bi_box1"], out["bi_box2"] = b1, b2
+    for xywh in (True, False):
+        A, B = b1.copy(), b2.copy()
+        if not xywh:
+            A[:, 2:] += A[:, :2]
+            B[:, 2:] += B[:, :2]
+        for mode, kw in (("iou", {}), ("giou", {"GIoU": True}), ("diou", {"DIoU": True}), ("ciou", {"CIoU": True})):
+            for bc, a_in in (("nn", A), ("1n", A[:1])):
+                with np.errstate(all="ignore"):
+                    ref = ref_metrics.bbox_iou(torch.tensor(a_in), torch.tensor(B), xywh=xywh, **kw).numpy()
+                    got = O.bbox_iou_metrics(a_in, B, xywh=xywh, **kw)
+                ok = np.array_equal(ref, got, equal_nan=True) if mode != "ciou" else np.allclose(ref, got, rtol=0, atol=1e-6, equal_nan=True)
+                check("metrics:bbox_iou:%s:%s:%s" % ("xywh" if xywh else "xyxy", mode, bc), ok)
+                out["bi_%s_%s_%s" % ("xywh" if xywh else "xyxy", mode, bc)] = ref
+    np.savez_compressed(os.path.join(HERE, "metrics_ap.npz"), **out)
+
+
+# ------------------------------------------------------------------ objectness x class scores (YPP_SCORE_OBJ_TIMES_CLS)
+
+def decoded_prediction(heads, nc, anchors, input_size, A=3):
+    """[B, n, 5+nc] rows cx,cy,w,h,obj,cls_0.. the way a Detect layer would emit them: the boxes and the objectness
+    are the reference decode's own (utils/yolov3_utils.py:12-59), the class columns torch.sigmoid of the class
+    logits in the same box order (:45-46,51: view -> permute -> sigmoid)."""
+    rows = torch.cat([ref_decode_v3(h, nc, anchors[A * i: A * i + A], input_size) for i, h in enumerate(heads)], dim=1)
+    cls = []
+    for h in heads:
+        B, _, H, W = h.shape
+        t = h.view(B, A, 5 + nc, H, W).permute(0, 1, 3, 4, 2)[..., 5:]
+        cls.append(torch.sigmoid(t).reshape(B, A * H * W, nc))
+    return torch.cat([rows[..., :5], torch.cat(cls, dim=1)], dim=2).contiguous()
+
+
+def case_objcls():
+    """The scoring of the vendored NMS (utils/general.py:645,669,679-680) on decoded heads: run the reference function
+    with iou_thres = 1 (nothing is ever suppressed: IoU <= 1) and no max_det cap, so its output IS the scored
+    candidate list; pins oracle.best_class_scores and tests/util.ultra_best_class (the torch-op restatement the GPU
+    test runs on the device)."""
+    from utils.general import non_max_suppression as ref_nms
+    sys.path.insert(0, os.path.dirname(HERE))
+    import util as T
+    nc, conf = 20, 0.25
+    heads = synth.make_heads(2, nc, [52, 26, 13], g=70, mu_obj=-1.5)
+    # class logits that tie after the sigmoid (saturation) and products that collide after the rounding
+    heads[0][0, 5:25, 0, 0] = 20.0
+    heads[0][0, 4, 0, 0] = 2.0
+    # 208 cells whose two best class probabilities sit an ulp or two apart, the larger at the HIGHER index: where their
+    # products with the objectness round to the same float, the first maximum of the products is the lower index
+    gen = torch.Generator("cpu").manual_seed(71)
+    v = torch.rand(8, 26, generator=gen) * 3 - 1
+    delta = 2.0 ** -23 * (1 + torch.exp(v)) * (0.3 + 0.9 * torch.rand(8, 26, generator=gen))
+    heads[1][1, 5:25, :8, :] = -3.0
+    heads[1][1, 5 + 7, :8, :] = v
+    heads[1][1, 5 + 2, :8, :] = v - delta
+    heads[1][1, 4, :8, :] = torch.rand(8, 26, generator=gen) * 2
+    pred = decoded_prediction(heads, nc, synth.YOLOV3_ANCHORS, 416)
+    ref = ref_nms(pred.clone(), conf_thres=conf, iou_thres=1.0, max_det=1000000)
+    store = {"g": 70, "mu_obj": np.float32(-1.5), "nc": nc, "conf": np.float32(conf),
+             "head_crc": np.array([crc(h.numpy()) for h in heads], np.uint64)}
+    ok_o, ok_t = True, True
+    for b in range(2):
+        idx, sc, cl = O.best_class_scores(pred[b].numpy(), conf)
+        r = ref[b].numpy()
+        order = np.lexsort((idx, -sc.astype(np.float64)))         # the reference sorts by conf (stable on CPU)
+        ok_o &= len(r) == len(idx) and np.array_equal(r[:, 4], sc[order]) and np.array_equal(r[:, 5], cl[order].astype(np.float32))
+        ti, ts, tc = T.ultra_best_class(pred[b], conf)
+        ok_t &= np.array_equal(ti.numpy(), idx) and np.array_equal(ts.numpy(), sc) and np.array_equal(tc.numpy(), cl)
+        store["idx_%d" % b], store["conf_%d" % b], store["cls_%d" % b] = idx, sc, cl
+    check("objcls:oracle.best_class_scores == reference scoring", ok_o, "cand %s" % [len(store["idx_%d" % b]) for b in range(2)])
+    check("objcls:tests/util.ultra_best_class == oracle", ok_t)
+    am = pred[1][store["idx_1"]][:, 5:].argmax(1).numpy()
+    n_coll = int((am != store["cls_1"]).sum())
+    check("objcls:fixture holds colliding products", n_coll >= 10, "%d boxes whose class is not argmax(sigmoid(cls))" % n_coll)
+    store["n_collisions"] = n_coll
+    np.savez_compressed(os.path.join(HERE, "objcls.npz"), **store)
+
+
+# ------------------------------------------------------------------ heads of the random-init eval-mode reference model
+
+def case_model_tie():
+    """SURVEY 8(d), third input regime: the heads of the reference's own YoloV3 (models/detector/yolov3.py:71-91, darknet19
+    features, random init, eval mode) on torch.rand images, seed 0.  Every head value is ~1e-5 .. 1e-9, so every score
+    is 0.5 to within a few ulps (exactly 0.5 on the coarse scales): the ordering is decided by ties -> box index."""
+    for name in ("torchinfo", "timm", "pytorch_lightning"):
+        if name not in sys.modules:
+            try:
+                __import__(name)
+            except Exception:
+                sys.modules[name] = types.ModuleType(name)
+    if not hasattr(sys.modules["torchinfo"], "summary"):
+        sys.modules["torchinfo"].summary = lambda *a, **k: None
+    from utils.module_select import get_model
+    from models.detector.yolov3 import YoloV3
+    torch.manual_seed(0)
+    backbone = get_model("darknet19")(pretrained="", features_only=True, out_indices=[3, 4, 5])
+    model = YoloV3(backbone, 20, 9).eval()
+    x = torch.rand(2, 3, 224, 224)
+    with torch.no_grad():
+        heads = [h.contiguous() for h in model(x)]
+    nc, conf, S = 20, 0.25, 224
+    rows = torch.cat([ref_decode_v3(h, nc, synth.YOLOV3_ANCHORS[3 * i: 3 * i + 3], S) for i, h in enumerate(heads)], dim=1)
+    rows_np = rows.numpy()
+    orows = O.decode_multi_scale([h.numpy() for h in heads], nc, synth.YOLOV3_ANCHORS, S, 3)
+    rel = np.abs(orows[..., :5] - rows_np[..., :5]) / np.maximum(np.abs(rows_np[..., :5]), 1e-30)
+    check("model_tie:decode", rel.max() <= 1e-5, "max rel %.2e, scores == 0.5: %.1f%%, distinct scores %d" % (
+        rel.max(), 100 * float((rows_np[..., 4] == 0.5).mean()), len(np.unique(rows_np[..., 4]))))
+    keeps, counts = [], []
+    ok = True
+    for b in range(2):
+        k, _ = ref_nms_indices(rows[b], conf)
+        om, um = cpu_modes(int((rows_np[b, :, 4] > conf).sum()))
+        ok_, _ = O.nms_v3_indices(rows_np[b], conf, 0.45, offset_mode=om, union_mode=um)
+        ref = k if om == O.OFFSET_TRICK else canon(k, rows_np[b])
+        ok &= np.array_equal(ok_, ref)
+        keeps.append(ref); counts.append(len(ref))
+    check("model_tie:nms", ok, "kept %s of %d" % (counts, rows_np.shape[1]))
+    keep_arr = np.full((2, max(counts)), -1, np.int32)
+    for b, k in enumerate(keeps):
+        keep_arr[b, :len(k)] = k
+    np.savez_compressed(os.path.join(HERE, "model_tie.npz"), heads0=heads[0].numpy(), heads1=heads[1].numpy(),
+                        heads2=heads[2].numpy(), rows=rows_np, keep=keep_arr, keep_count=np.array(counts, np.int32),
+                        nc=nc, conf=np.float32(conf), input_size=S)
+
+
 if __name__ == "__main__":
     O.build(force=True)
     if len(sys.argv) > 1:                      # regenerate only the named cases, e.g. `make_golden.py writers`
@@ -536,6 +691,8 @@ if __name__ == "__main__":
     case_heads("c2_yolov3_sparse_b4", "v3", 20, [52, 26, 13], 3, 4, 416, 0.25, -5.0, g=3, store_rows_stride=16)
     # C3 shape (single class), 1 image dense
     case_heads("c3_person_dense_b1", "v3", 1, [52, 26, 13], 3, 1, 416, 0.25, 0.0, g=4, store_rows_stride=16)
+    # BASELINE config 3 as written: the canonical 2-scale YOLOv4-tiny head (26/13), single class, 2 images dense
+    case_heads("c3_person2s_dense_b2", "v3", 1, [26, 13], 3, 2, 416, 0.25, 0.0, g=6, store_rows_stride=4)
     # C4 shape, 1 image, conf .001
     case_heads("c4_coco608_b1", "v3", 80, [76, 38, 19], 3, 1, 608, 0.001, 0.0, g=5, store_rows_stride=32)
     case_wrappers()
@@ -545,5 +702,8 @@ if __name__ == "__main__":
     case_ultralytics()
     case_yolov1()
     case_confusion()
+    case_metrics_ap()
+    case_objcls()
+    case_model_tie()
     print("FAILED: %s" % FAIL if FAIL else "all golden cases agree with the oracle")
     sys.exit(1 if FAIL else 0)

@@ -168,3 +168,77 @@ def test_confusion_matrix(oracle):
     for i in range(len(do) - 1):
         oracle.confusion_process_batch(m, g["det"][do[i]: do[i + 1]], g["lab"][lo[i]: lo[i + 1]], nc, float(g["conf"]), float(g["iou_thres"]))
     assert np.array_equal(m, g["matrix"])
+
+
+def test_metrics_ap_side_against_reference(oracle):
+    """utils/metrics.py: ap_per_class (:21-83), compute_ap (:86-111), bbox_iou (:192-230) - the oracle's plain-loop
+    restatements AND the product's host implementations (ypp.compat.metrics: float64 numpy by design)
+    against the reference's stored outputs."""
+    import importlib
+    g = util.load("metrics_ap")
+    M = importlib.import_module("ypp.compat.metrics")
+    for tag in ("t1", "t10", "few"):
+        args = [g["%s_%s" % (tag, k)] for k in ("tp", "conf", "pred_cls", "target_cls")]
+        want = [g["%s_%s" % (tag, k)] for k in ("p", "r", "ap", "f1", "classes")]
+        for impl in (oracle.ap_per_class, M.ap_per_class):
+            got = impl(*args)
+            for a, b in zip(got, want):
+                assert np.array_equal(np.asarray(a), b), (tag, impl.__module__)
+            assert got[4].dtype == np.int32
+    for impl in (oracle.compute_ap, M.compute_ap):
+        ap, mpre, mrec = impl(g["ca_recall"], g["ca_precision"])
+        assert ap == float(g["ca_ap"]) and np.array_equal(mpre, g["ca_mpre"]) and np.array_equal(mrec, g["ca_mrec"])
+    b1, b2 = g["bi_box1"], g["bi_box2"]
+    for xywh in (True, False):
+        A, B = b1.copy(), b2.copy()
+        if not xywh:
+            A[:, 2:] += A[:, :2]
+            B[:, 2:] += B[:, :2]
+        for mode, kw in (("iou", {}), ("giou", {"GIoU": True}), ("diou", {"DIoU": True}), ("ciou", {"CIoU": True})):
+            for bc, a_in in (("nn", A), ("1n", A[:1])):
+                want = g["bi_%s_%s_%s" % ("xywh" if xywh else "xyxy", mode, bc)]
+                got = oracle.bbox_iou_metrics(a_in, B, xywh=xywh, **kw)
+                if mode == "ciou":
+                    assert np.allclose(got, want, rtol=0, atol=1e-6, equal_nan=True)      # atan differs by an ulp between libms
+                else:
+                    assert np.array_equal(got, want, equal_nan=True), (xywh, mode, bc)
+
+
+def test_objectness_times_class_scoring(oracle):
+    """YPP_SCORE_OBJ_TIMES_CLS semantics = the scoring lines of the vendored NMS (utils/general.py:645,669,679-680):
+    oracle.best_class_scores and the torch-op restatement the GPU test uses, against what the reference function
+    itself returned for the decoded fixture heads (iou_thres = 1: its output is the scored candidate list)."""
+    import torch
+    g, heads = util.objcls_heads()
+    from ypp import synth
+    pred = util.torch_prediction(heads, int(g["nc"]), synth.YOLOV3_ANCHORS, 416)
+    assert int(g["n_collisions"]) >= 10
+    for b in range(2):
+        idx, sc, cl = oracle.best_class_scores(pred[b].numpy(), float(g["conf"]))
+        ti, ts, tc = util.ultra_best_class(pred[b], float(g["conf"]))
+        assert np.array_equal(ti.numpy(), idx) and np.array_equal(ts.numpy(), sc) and np.array_equal(tc.numpy(), cl)
+        # against what the reference function returned when the fixture was made (its own decode fed it; here the
+        # decode is restated, and a vectorised CPU sigmoid may differ by an ulp with the memory layout or the machine):
+        # same candidates up to the threshold's edge, scores to 1e-6, classes equal outside the 208 crafted cells
+        # (whose winner depends on the last bit by construction)
+        assert len(set(idx.tolist()) ^ set(g["idx_%d" % b].tolist())) <= 2
+        common, ia, ib = np.intersect1d(idx, g["idx_%d" % b], return_indices=True)
+        assert util.rel_err(sc[ia], g["conf_%d" % b][ib]).max() <= 1e-6
+        crafted = (common >= 8112) & (common < 8112 + 208) if b == 1 else np.zeros(len(common), bool)
+        assert int(((cl[ia] != g["cls_%d" % b][ib]) & ~crafted).sum()) <= 2
+        if b == 1:
+            assert set(cl[ia][crafted].tolist()) <= {2, 7} and set(g["cls_1"][ib][crafted].tolist()) == {2, 7}
+
+
+def test_random_init_model_heads_tie_regime(oracle):
+    """Heads of the random-init eval-mode reference model: scores 0.5 +- a few ulps, order decided by ties."""
+    g = util.load("model_tie")
+    from ypp import synth
+    heads = [g["heads%d" % i] for i in range(3)]
+    rows = oracle.decode_multi_scale(heads, int(g["nc"]), synth.YOLOV3_ANCHORS, int(g["input_size"]), 3)
+    assert util.rel_err(rows[..., :5], g["rows"][..., :5]).max() <= 1e-5
+    assert (rows[..., 4] == 0.5).mean() > 0.1
+    for b in range(2):
+        keep, _ = oracle.nms_v3_indices(g["rows"][b], float(g["conf"]), 0.45, offset_mode=oracle.OFFSET_AUTO_CPU,
+                                        union_mode=oracle.UNION_SEPARATE)
+        assert np.array_equal(util.canon(keep, g["rows"][b]), util.canon(g["keep"][b, : int(g["keep_count"][b])], g["rows"][b]))

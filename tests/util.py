@@ -5,7 +5,8 @@ import zlib
 import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-HEAD_CASES = ["c1_yolov2_dense", "c2_yolov3_dense_b2", "c2_yolov3_sparse_b4", "c3_person_dense_b1", "c4_coco608_b1"]
+HEAD_CASES = ["c1_yolov2_dense", "c2_yolov3_dense_b2", "c2_yolov3_sparse_b4", "c3_person_dense_b1", "c3_person2s_dense_b2",
+              "c4_coco608_b1"]
 
 
 def crc(a):
@@ -45,3 +46,55 @@ def rel_err(a, b):
     with np.errstate(invalid="ignore", divide="ignore"):
         fin = np.isfinite(b)
         return np.where(fin, np.abs(a - b) / np.maximum(np.abs(b), 1e-30), 0.0)
+
+
+def ultra_best_class(pred, conf_thres):
+    """The scoring lines of the vendored Ultralytics NMS (utils/general.py:645,669,679-680) in torch ops, for ONE image
+    [n, 5+nc] on any device: obj > conf -> conf_j = cls_j * obj -> (conf, j) = max over j (first maximum) -> conf > conf.
+    Returns (box numbers, conf, j).  Pinned to the reference function by tests/golden/make_golden.py:case_objcls."""
+    import torch
+    sel = torch.nonzero(pred[:, 4] > conf_thres)[:, 0]
+    x = pred[sel].clone()
+    x[:, 5:] *= x[:, 4:5]
+    conf, j = x[:, 5:].max(1)
+    m = conf > conf_thres
+    return sel[m], conf[m], j[m]
+
+
+def torch_prediction(heads, nc, anchors, input_size, A=3):
+    """decode_predictions (utils/yolov3_utils.py:27-59) restated in plain torch ops on whatever device the heads are
+    on, with the class PROBABILITIES kept: [B, n, 5+nc] rows cx,cy,w,h,sigmoid(obj),sigmoid(cls_0).. in the reference's
+    box order (scale, anchor, y, x) - what the vendored non_max_suppression expects as `prediction`."""
+    import torch
+    out = []
+    for i, h in enumerate(heads):
+        B, _, H, W = h.shape
+        p = h.view(B, A, 5 + nc, H, W).permute(0, 1, 3, 4, 2)
+        stride = input_size / H
+        an = torch.tensor([[a / stride, b / stride] for a, b in anchors[A * i: A * i + A]], device=h.device)
+        gx = torch.arange(W, device=h.device).view(1, 1, 1, W).float().expand(B, A, H, W)
+        gy = torch.arange(H, device=h.device).view(1, 1, H, 1).float().expand(B, A, H, W)
+        xy = torch.stack([torch.sigmoid(p[..., 0]) + gx, torch.sigmoid(p[..., 1]) + gy], -1) * stride
+        wh = torch.exp(p[..., 2:4]) * an.view(1, A, 1, 1, 2) * stride
+        out.append(torch.cat([xy, wh, torch.sigmoid(p[..., 4:5]), torch.sigmoid(p[..., 5:])], -1).reshape(B, -1, 5 + nc))
+    return torch.cat(out, 1)
+
+
+def objcls_heads():
+    """The heads of tests/golden/objcls.npz (seeded + the edits of make_golden.py:case_objcls), crc-checked."""
+    import torch
+    from ypp import synth
+    g = load("objcls")
+    nc = int(g["nc"])
+    heads = synth.make_heads(2, nc, [52, 26, 13], g=int(g["g"]), mu_obj=float(g["mu_obj"]))
+    heads[0][0, 5:25, 0, 0] = 20.0
+    heads[0][0, 4, 0, 0] = 2.0
+    gen = torch.Generator("cpu").manual_seed(71)
+    v = torch.rand(8, 26, generator=gen) * 3 - 1
+    delta = 2.0 ** -23 * (1 + torch.exp(v)) * (0.3 + 0.9 * torch.rand(8, 26, generator=gen))
+    heads[1][1, 5:25, :8, :] = -3.0
+    heads[1][1, 5 + 7, :8, :] = v
+    heads[1][1, 5 + 2, :8, :] = v - delta
+    heads[1][1, 4, :8, :] = torch.rand(8, 26, generator=gen) * 2
+    assert [crc(h.numpy()) for h in heads] == [int(x) for x in g["head_crc"]], "regenerated objcls heads differ from the fixture"
+    return g, heads

@@ -303,6 +303,36 @@ int ypp_map_match(const float* gt_G7, int64_t G, const float* det_K7, int64_t K,
                   float iou_thr, void* ws, size_t ws_bytes,
                   unsigned char* tp, float* per_class, float* map, void* stream);
 
+/* The same matching split for an image-sharded evaluation (the reference never gathers, its metric
+ * state is rank-local: module/yolov3_detector.py:45-47).  An image's detections and ground truths live on ONE
+ * rank, and the greedy rule of utils/yolo_utils.py:404-430 never looks across images, so
+ *   M1  ypp_map_flags          on every rank, over its own rows: the TP flag of every detection (no sort of the
+ *                              detections: "first detection to choose a ground truth" is a 64-bit atomic minimum
+ *                              of (score descending, row order));
+ *   --  all-gather             of the (score, cls, tp) triples - 12 bytes per detection instead of the 28-byte row,
+ *                              and no ground-truth rows at all, only their per-class counts;
+ *   M2  ypp_map_ap_from_flags  on the rank that owns classes [c_lo, c_hi): select them, stable sort by score, AP;
+ *   --  all-gather             of the per-class results, then ypp_map_mean.
+ * The result is bit-identical to ypp_map_match over the gathered rows when the segments are concatenated in the
+ * order one process would have seen the images (ties in score keep that order).
+ *   tp [K] out (optional): 1 TP, 0 FP, 255 class without ground truth ON THIS RANK (pass the global counts through
+ *                          ypp_map_ap_from_flags for the real decision; the triples carry the plain flag)
+ *   triples [K,3] out (optional): score, cls, tp (0/1) per detection, in row order
+ *   gt_per_class [nc] out (optional): ground truths of every class among gt_G7 (device int64) */
+int ypp_map_flags(const float* gt_G7, int64_t G, const float* det_K7, int64_t K, int nc, float iou_thr,
+                  void* ws, size_t ws_bytes, unsigned char* tp, float* triples, int64_t* gt_per_class, void* stream);
+
+/* triples: n_seg segments of seg_stride rows each (the padded all-gather buffer as it arrives); seg_count [n_seg]
+ * device int64 = valid rows of every segment, or NULL = all.  gt_per_class [nc] device int64 (summed over the ranks).
+ * per_class [nc,4]: rows c_lo .. c_hi-1 are written (AP, TP, FP, FN).  Workspace: ypp_map_workspace_bytes(0,
+ * n_seg * seg_stride, nc). */
+int ypp_map_ap_from_flags(const float* triples, int64_t n_seg, int64_t seg_stride, const int64_t* seg_count,
+                          const int64_t* gt_per_class, int nc, int c_lo, int c_hi, void* ws, size_t ws_bytes,
+                          float* per_class, void* stream);
+
+/* mean of column 0 of per_class [nc,4] over all nc classes, fp32 in class order (torch.mean, utils/yolo_utils.py:456) */
+int ypp_map_mean(const float* per_class_nc4, int nc, float* map, void* stream);
+
 /* ---- misc ---------------------------------------------------------------------------- */
 
 const char* ypp_last_error(void);

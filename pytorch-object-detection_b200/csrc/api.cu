@@ -468,6 +468,37 @@ int ypp_map_match(const float* gt_G7, int64_t G, const float* det_K7, int64_t K,
     return ypp_launch_map(gt_G7, G, det_K7, K, nc, iou_thr, ws, ws_bytes, tp, per_class, map, (cudaStream_t)stream);
 }
 
+int ypp_map_flags(const float* gt_G7, int64_t G, const float* det_K7, int64_t K, int nc, float iou_thr, void* ws,
+                  size_t ws_bytes, unsigned char* tp, float* triples, int64_t* gt_per_class, void* stream)
+{
+    if (G < 0 || K < 0 || nc <= 0 || !ws) { ypp_set_error("map_flags: bad argument"); return YPP_E_BADARG; }
+    if ((G > 0 && !gt_G7) || (K > 0 && !det_K7)) { ypp_set_error("map_flags: null rows"); return YPP_E_BADARG; }
+    if (nc > 65535 || K >= (1LL << 31) || G >= (1LL << 31)) { ypp_set_error("map_flags: size out of range"); return YPP_E_UNSUPPORTED; }
+    return ypp_launch_map_flags(gt_G7, G, det_K7, K, nc, iou_thr, ws, ws_bytes, tp, triples, (long long*)gt_per_class,
+                                (cudaStream_t)stream);
+}
+
+int ypp_map_ap_from_flags(const float* triples, int64_t n_seg, int64_t seg_stride, const int64_t* seg_count,
+                          const int64_t* gt_per_class, int nc, int c_lo, int c_hi, void* ws, size_t ws_bytes,
+                          float* per_class, void* stream)
+{
+    if (n_seg < 0 || seg_stride < 0 || nc <= 0 || c_lo < 0 || c_hi > nc || c_lo > c_hi || !ws || !gt_per_class || !per_class) {
+        ypp_set_error("map_ap_from_flags: bad argument"); return YPP_E_BADARG;
+    }
+    const int64_t n = n_seg * seg_stride;
+    if (n > 0 && !triples) { ypp_set_error("map_ap_from_flags: null rows"); return YPP_E_BADARG; }
+    if (nc > 65535 || n >= (1LL << 31)) { ypp_set_error("map_ap_from_flags: size out of range"); return YPP_E_UNSUPPORTED; }
+    if (c_lo == c_hi) return YPP_OK;
+    return ypp_launch_map_ap_flags(triples, n, seg_stride > 0 ? seg_stride : 1, (const long long*)seg_count,
+                                   (const long long*)gt_per_class, nc, c_lo, c_hi, ws, ws_bytes, per_class, (cudaStream_t)stream);
+}
+
+int ypp_map_mean(const float* per_class_nc4, int nc, float* map, void* stream)
+{
+    if (!per_class_nc4 || !map || nc <= 0) { ypp_set_error("map_mean: bad argument"); return YPP_E_BADARG; }
+    return ypp_launch_map_mean(per_class_nc4, nc, map, (cudaStream_t)stream);
+}
+
 const char* ypp_last_error(void) { return g_err; }
 int ypp_version(void) { return 100; }
 int64_t ypp_launch_count(int reset)

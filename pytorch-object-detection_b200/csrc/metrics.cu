@@ -141,9 +141,11 @@ ypp_bbox_iou_kernel(const float4* __restrict__ a, int na, const float4* __restri
 #define RS_TILE (RS_THREADS * RS_ITEMS)
 
 __global__ void __launch_bounds__(RS_THREADS)
-rs_hist_kernel(const u64* __restrict__ keys, long long n, int shift, int* __restrict__ counts, int nblocks)
+rs_hist_kernel(const u64* __restrict__ keys, long long n, const long long* __restrict__ n_dev, int shift,
+               int* __restrict__ counts, int nblocks)
 {
     __shared__ int h[256];
+    if (n_dev) n = min(n, *n_dev);               // the launch is sized for the bound n; the count lives on the device
     h[threadIdx.x] = 0;
     __syncthreads();
     const long long base = (long long)blockIdx.x * RS_TILE;
@@ -184,11 +186,13 @@ rs_scan_kernel(int* __restrict__ counts, long long total)
 
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter_kernel(const u64* __restrict__ kin, const u32* __restrict__ vin, u64* __restrict__ kout, u32* __restrict__ vout,
-                  long long n, int shift, const int* __restrict__ offsets, int nblocks)
+                  long long n, const long long* __restrict__ n_dev, int shift, const int* __restrict__ offsets, int nblocks)
 {
     __shared__ int wc[RS_THREADS / 32][256];
     __shared__ int dbase[256];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n_dev) n = min(n, *n_dev);
+    if ((long long)blockIdx.x * RS_TILE >= n) return;
     dbase[tid] = offsets[(size_t)tid * nblocks + blockIdx.x];
     const long long base = (long long)blockIdx.x * RS_TILE;
     for (int it = 0; it < RS_ITEMS; ++it) {
@@ -221,15 +225,15 @@ rs_scatter_kernel(const u64* __restrict__ kin, const u32* __restrict__ vin, u64*
 struct RsBuffers { u64* k[2]; u32* v[2]; int* counts; };
 
 // sorts (k[0], v[0]) over bits [0, nbits); returns which buffer holds the result
-int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st)
+int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st, const long long* n_dev = nullptr)
 {
     int cur = 0;
     if (n <= 0) return cur;
     const int nblocks = (int)((n + RS_TILE - 1) / RS_TILE);
     for (int shift = 0; shift < nbits; shift += 8) {
-        rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], n, shift, rb.counts, nblocks);
+        rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], n, n_dev, shift, rb.counts, nblocks);
         rs_scan_kernel<<<1, 1024, 0, st>>>(rb.counts, 256LL * nblocks);
-        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], rb.v[cur], rb.k[cur ^ 1], rb.v[cur ^ 1], n, shift,
+        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], rb.v[cur], rb.k[cur ^ 1], rb.v[cur ^ 1], n, n_dev, shift,
                                                           rb.counts, nblocks);
         ypp_count_launch(3);
         cur ^= 1;
@@ -316,34 +320,46 @@ __global__ void map_best_kernel(const float* __restrict__ det, long long K, cons
     if (bg >= 0) atomicMin(first_rank + bg, (int)p);
 }
 
-// one CTA per class: TP flags, cumulative precision/recall, envelope, AP
+// one CTA per class: TP flags, cumulative precision/recall, envelope, AP.
+// kFlags = false: the detections were matched here (best_g / first_rank); the class's ground truths are counted in
+//                 the sorted ground-truth keys.
+// kFlags = true:  every detection arrives with its TP flag (bit 0 of its sort value: matched where its image lives)
+//                 and the class's ground-truth count comes from gt_per_class; K is read from *n_dev; classes
+//                 c_lo + blockIdx.x.
+// term[] (K floats) receives, at the class's own ranks, first the rank of its t-th true positive and then that
+// true positive's contribution to the AP sum.
 #define AP_THREADS 1024
+template <bool kFlags>
 __global__ void __launch_bounds__(AP_THREADS)
-map_ap_kernel(long long K, long long G, int nc, const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
+map_ap_kernel(long long K, const long long* __restrict__ n_dev, long long G, int nc, int c_lo,
+              const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
               const u64* __restrict__ gkeys, const int* __restrict__ best_g, const int* __restrict__ first_rank,
-              float* __restrict__ prec, float* __restrict__ contrib, unsigned char* __restrict__ tp_out,
-              float* __restrict__ per_class)
+              const long long* __restrict__ gt_per_class,
+              float* __restrict__ prec, float* __restrict__ term, float* __restrict__ class_ap,
+              unsigned char* __restrict__ tp_out, float* __restrict__ per_class)
 {
     __shared__ int warp_i[32];
     __shared__ float warp_f[32];
-    __shared__ long long s_lo, s_hi, g_lo, g_hi;
+    __shared__ long long s_lo, s_hi, s_ng;
     __shared__ int carry_i;
     __shared__ float carry_f;
-    const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = c_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (n_dev) K = min(K, *n_dev);
     if (tid == 0) {
         s_lo = lower_bound_u64(dkeys, K, (u64)c << 32);
         s_hi = lower_bound_u64(dkeys, K, (u64)(c + 1) << 32);
-        g_lo = lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
-        g_hi = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS);
+        if (kFlags) s_ng = gt_per_class[c];
+        else s_ng = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS) - lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
         carry_i = 0;
     }
     __syncthreads();
     const long long lo = s_lo, hi = s_hi;
-    const long long ng = g_hi - g_lo;
+    const long long ng = s_ng;
     float* pc = per_class ? per_class + 4 * (size_t)c : nullptr;
     if (ng == 0) {                                           // class skipped, AP 0 (:379-381)
         if (tp_out) for (long long p = lo + tid; p < hi; p += AP_THREADS) tp_out[dvals[p]] = 255;
         if (pc && tid < 4) pc[tid] = 0.0f;
+        if (tid == 0) class_ap[c] = 0.0f;
         return;
     }
     const float rec_den = (float)((double)ng + 1e-6);         // python float64 (G + eps) -> fp32
@@ -351,7 +367,10 @@ map_ap_kernel(long long K, long long G, int nc, const u64* __restrict__ dkeys, c
     for (long long p0 = lo; p0 < hi; p0 += AP_THREADS) {
         const long long p = p0 + tid;
         int t = 0;
-        if (p < hi) { const int bg = best_g[p]; t = (bg >= 0 && first_rank[bg] == (int)p) ? 1 : 0; }
+        if (p < hi) {
+            if (kFlags) t = (int)(dvals[p] & 1u);
+            else { const int bg = best_g[p]; t = (bg >= 0 && first_rank[bg] == (int)p) ? 1 : 0; }
+        }
         int inc = t;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
@@ -363,11 +382,9 @@ map_ap_kernel(long long K, long long G, int nc, const u64* __restrict__ dkeys, c
         if (p < hi) {
             const int tpc = cbase + before + inc;
             const float ftp = (float)tpc, ffp = (float)((int)(p - lo + 1) - tpc);
-            const float pr = __fdiv_rn(ftp, __fadd_rn(__fadd_rn(ftp, ffp), 1e-6f));      // :435
-            // positive tpc marks a TP rank (recall change point); sign carries the flag
-            prec[p] = pr;
-            if (tp_out) tp_out[dvals[p]] = (unsigned char)t;
-            if (t) contrib[g_lo + tpc - 1] = __uint_as_float((u32)(p - lo));             // rank of the tpc-th TP (int bits)
+            prec[p] = __fdiv_rn(ftp, __fadd_rn(__fadd_rn(ftp, ffp), 1e-6f));                 // :435
+            if (!kFlags && tp_out) tp_out[dvals[p]] = (unsigned char)t;
+            if (t) term[lo + tpc - 1] = __uint_as_float((u32)(p - lo));                      // rank of the tpc-th TP (int bits)
         }
         __syncthreads();
         if (tid == 0) carry_i = cbase + tot;
@@ -394,39 +411,162 @@ map_ap_kernel(long long K, long long G, int nc, const u64* __restrict__ dkeys, c
         if (tid == 0) carry_f = tot;
         __syncthreads();
     }
-    // AP = sum over recall change points, accumulated sequentially in fp32 like the reference (:445-452)
+    // AP = sum over the recall change points (every true positive) of (recall step) x (envelope there), :445-452.
+    // The terms are independent: every thread computes some (same roundings as the reference's one-by-one
+    // evaluation); only the fp32 ADDITIONS stay sequential, in rank order, so the sum rounds as the reference's.
+    for (int t = 1 + tid; t <= n_tp; t += AP_THREADS) {
+        const long long p = lo + (long long)__float_as_uint(term[lo + t - 1]);
+        const float r1 = __fdiv_rn((float)t, rec_den), r0 = __fdiv_rn((float)(t - 1), rec_den);
+        term[lo + t - 1] = __fmul_rn(__fsub_rn(r1, r0), prec[p]);
+    }
+    __syncthreads();
     if (tid == 0) {
         float ap = 0.0f;
-        for (int t = 1; t <= n_tp; ++t) {
-            const long long p = lo + (long long)__float_as_uint(contrib[g_lo + t - 1]);
-            const float r1 = __fdiv_rn((float)t, rec_den), r0 = __fdiv_rn((float)(t - 1), rec_den);
-            ap = __fadd_rn(ap, __fmul_rn(__fsub_rn(r1, r0), prec[p]));
+        int t = 0;
+        for (; t + 8 <= n_tp; t += 8) {
+            float v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = term[lo + t + q];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) ap = __fadd_rn(ap, v[q]);
         }
+        for (; t < n_tp; ++t) ap = __fadd_rn(ap, term[lo + t]);
         if (pc) { pc[0] = ap; pc[1] = (float)n_tp; pc[2] = (float)((int)len - n_tp); pc[3] = (float)((int)ng - n_tp); }
-        contrib[g_lo] = ap;       // per-class AP parked for the mean kernel (slot is free again)
+        class_ap[c] = ap;
     }
 }
 
-__global__ void map_mean_kernel(int nc, long long G, const u64* __restrict__ gkeys, const float* __restrict__ contrib,
-                                float* __restrict__ map_out)
+// mean over ALL nc classes (torch.mean of the stacked per-class APs, :456), fp32, in class order
+__global__ void map_mean_kernel(int nc, const float* __restrict__ class_ap, int stride, float* __restrict__ map_out)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     float s = 0.0f;
-    for (int c = 0; c < nc; ++c) {
-        const long long g_lo = lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
-        const long long g_hi = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS);
-        if (g_hi > g_lo) s = __fadd_rn(s, contrib[g_lo]);
+    for (int c = 0; c < nc; ++c) s = __fadd_rn(s, class_ap[(size_t)c * stride]);
+    *map_out = __fdiv_rn(s, (float)nc);
+}
+
+// ---- matching alone (M1), without sorting the detections ------------------------------------------------
+// A detection's best ground truth g*(d) depends on d and its image's ground truths only; d is a true positive iff
+// IoU > thr and d is the first in (score descending, row order) among the detections that chose g*(d).  "First" is
+// a 64-bit minimum: claim[g] = min over those detections of (~enc(score)) << 32 | d.  No sort of the detections, so a
+// rank of an image-sharded evaluation can flag ITS detections against ITS ground truths in two short kernels.
+__global__ void map_claim_kernel(const float* __restrict__ det, long long K, const float* __restrict__ gt, long long G, int nc,
+                                 const u64* __restrict__ gkeys, const u32* __restrict__ gvals, float iou_thr,
+                                 int* __restrict__ best_g, u64* __restrict__ claim)
+{
+    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= K) return;
+    const float* dr = det + (size_t)d * 7;
+    const u32 cls = map_cls(dr[6], nc);
+    const u32 img = (u32)dr[0] & ((1u << MAP_IMG_BITS) - 1u);
+    const u64 gk = ((u64)cls << MAP_IMG_BITS) | img;
+    long long s = lower_bound_u64(gkeys, G, gk);
+    float best = 0.0f;
+    int bg = -1;
+    for (; s < G && gkeys[s] == gk; ++s) {
+        const float iou = map_iou(dr + 1, gt + (size_t)gvals[s] * 7 + 1);
+        if (iou > best) { best = iou; bg = (int)s; }
     }
-    *map_out = __fdiv_rn(s, (float)nc);                       // torch.mean over all nc classes (:456)
+    if (!(best > iou_thr) || cls >= (u32)nc) bg = -1;
+    best_g[d] = bg;
+    if (bg >= 0) atomicMin(claim + bg, ((u64)(~ypp_enc(dr[5])) << 32) | (u64)(u32)d);
+}
+
+__global__ void map_flags_kernel(const float* __restrict__ det, long long K, int nc, const int* __restrict__ best_g,
+                                 const u64* __restrict__ claim, const long long* __restrict__ gt_per_class,
+                                 unsigned char* __restrict__ tp_out, float* __restrict__ triples)
+{
+    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= K) return;
+    const float score = det[d * 7 + 5], cf = det[d * 7 + 6];
+    const u32 cls = map_cls(cf, nc);
+    const int bg = best_g[d];
+    const bool tp = bg >= 0 && claim[bg] == (((u64)(~ypp_enc(score)) << 32) | (u64)(u32)d);
+    const bool counted = cls < (u32)nc && gt_per_class[cls] > 0;
+    if (tp_out) tp_out[d] = counted ? (tp ? 1 : 0) : 255;
+    if (triples) { triples[d * 3] = score; triples[d * 3 + 1] = cf; triples[d * 3 + 2] = tp ? 1.0f : 0.0f; }
+}
+
+__global__ void map_gt_count_kernel(const float* __restrict__ gt, long long G, int nc, unsigned long long* __restrict__ per_class)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    const u32 cls = map_cls(gt[g * 7 + 6], nc);
+    if (cls < (u32)nc) atomicAdd(per_class + cls, 1ull);
+}
+
+// ---- AP from flagged detections gathered from every rank (M2), for the classes [c_lo, c_hi) ----------------------
+// Input: n_seg segments of seg_stride triples (score, cls, tp) each, of which the first seg_count[s] are valid
+// (the padded all-gather buffer as it is).  Selection in input order (block counts -> scan -> scatter), so the
+// stable sort keeps ties in segment-then-row order: the order one process would have seen.
+#define SEL_THREADS 256
+#define SEL_ITEMS 8
+#define SEL_TILE (SEL_THREADS * SEL_ITEMS)
+__device__ __forceinline__ bool sel_take(const float* __restrict__ tr, long long i, long long seg_stride,
+                                         const long long* __restrict__ seg_count, int nc, int c_lo, int c_hi, u32& cls)
+{
+    const long long sgm = i / seg_stride, r = i - sgm * seg_stride;
+    if (seg_count && r >= seg_count[sgm]) return false;
+    cls = map_cls(tr[i * 3 + 1], nc);
+    return cls >= (u32)c_lo && cls < (u32)c_hi;
+}
+
+__global__ void __launch_bounds__(SEL_THREADS)
+map_select_count_kernel(const float* __restrict__ tr, long long n, long long seg_stride, const long long* __restrict__ seg_count,
+                        int nc, int c_lo, int c_hi, int* __restrict__ block_count)
+{
+    __shared__ int wsum[SEL_THREADS / 32];
+    const long long base = (long long)blockIdx.x * SEL_TILE;
+    int cnt = 0;
+    for (int it = 0; it < SEL_ITEMS; ++it) {
+        const long long i = base + (long long)it * SEL_THREADS + threadIdx.x;
+        u32 cls;
+        if (i < n && sel_take(tr, i, seg_stride, seg_count, nc, c_lo, c_hi, cls)) ++cnt;
+    }
+    cnt = __reduce_add_sync(YPP_FULL_MASK, cnt);
+    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; ++w) t += wsum[w]; block_count[blockIdx.x] = t; }
+}
+
+// block_count holds the exclusive offsets now (rs_scan_kernel); the last block also publishes the total
+__global__ void __launch_bounds__(SEL_THREADS)
+map_select_scatter_kernel(const float* __restrict__ tr, long long n, long long seg_stride, const long long* __restrict__ seg_count,
+                          int nc, int c_lo, int c_hi, const int* __restrict__ block_off, u64* __restrict__ keys,
+                          u32* __restrict__ vals, long long* __restrict__ n_sel)
+{
+    __shared__ int wsum[SEL_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long base = (long long)blockIdx.x * SEL_TILE;
+    int run = block_off[blockIdx.x];
+    for (int it = 0; it < SEL_ITEMS; ++it) {
+        const long long i = base + (long long)it * SEL_THREADS + tid;
+        u32 cls = 0;
+        const bool take = i < n && sel_take(tr, i, seg_stride, seg_count, nc, c_lo, c_hi, cls);
+        const u32 m = __ballot_sync(YPP_FULL_MASK, take);
+        if (lane == 0) wsum[warp] = __popc(m);
+        __syncthreads();
+        int before = 0, tot = 0;
+        for (int w = 0; w < SEL_THREADS / 32; ++w) { const int t = wsum[w]; if (w < warp) before += t; tot += t; }
+        if (take) {
+            const int dst = run + before + __popc(m & ((1u << lane) - 1u));
+            keys[dst] = ((u64)cls << 32) | (u64)(~ypp_enc(tr[i * 3]));
+            vals[dst] = tr[i * 3 + 2] != 0.0f ? 1u : 0u;
+        }
+        run += tot;
+        __syncthreads();
+    }
+    if (blockIdx.x == gridDim.x - 1 && tid == 0) *n_sel = run;
 }
 
 struct MapWs {
     RsBuffers det, gt;
-    int* best_g; float* prec; int* first_rank; float* contrib;
+    int* best_g; float* prec; int* first_rank; float* term; float* class_ap;
+    u64* claim; unsigned long long* gt_per_class; int* sel_blocks; long long* n_sel;
     size_t total;
 };
 
-MapWs make_map_ws(void* base, long long G, long long K)
+MapWs make_map_ws(void* base, long long G, long long K, int nc)
 {
     MapWs w;
     char* p = (char*)base;
@@ -443,7 +583,12 @@ MapWs make_map_ws(void* base, long long G, long long K)
     w.best_g = (int*)take(4 * Kp);
     w.prec = (float*)take(4 * Kp);
     w.first_rank = (int*)take(4 * Gp);
-    w.contrib = (float*)take(4 * Gp);
+    w.term = (float*)take(4 * Kp);
+    w.class_ap = (float*)take(4 * (size_t)(nc > 0 ? nc : 1));
+    w.claim = (u64*)take(8 * Gp);
+    w.gt_per_class = (unsigned long long*)take(8 * (size_t)(nc > 0 ? nc : 1));
+    w.sel_blocks = (int*)take(4 * ((size_t)((Kp + SEL_TILE - 1) / SEL_TILE) + 1));
+    w.n_sel = (long long*)take(8);
     w.total = off;
     return w;
 }
@@ -587,15 +732,14 @@ int ypp_launch_bbox_iou(const float* a, int na, const float* b, int nb, int xywh
 
 size_t ypp_map_ws_bytes(long long G, long long K, int nc)
 {
-    (void)nc;
-    return make_map_ws(nullptr, G, K).total;
+    return make_map_ws(nullptr, G, K, nc).total;
 }
 
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
                    cudaStream_t st)
 {
-    MapWs w = make_map_ws(ws, G, K);
+    MapWs w = make_map_ws(ws, G, K, nc);
     if (ws_bytes < w.total) { ypp_set_error("map_match: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
     const int cbits = bits_for(nc + 1);
     int gcur = 0, dcur = 0;
@@ -612,11 +756,66 @@ int ypp_launch_map(const float* gt, long long G, const float* det, long long K, 
                                                                      w.gt.k[gcur], w.gt.v[gcur], iou_thr, w.best_g, w.first_rank);
         ypp_count_launch(1);
     }
-    map_ap_kernel<<<nc, AP_THREADS, 0, st>>>(K, G, nc, w.det.k[dcur], w.det.v[dcur], w.gt.k[gcur], w.best_g, w.first_rank,
-                                             w.prec, w.contrib, tp, per_class);
-    map_mean_kernel<<<1, 32, 0, st>>>(nc, G, w.gt.k[gcur], w.contrib, map);
+    map_ap_kernel<false><<<nc, AP_THREADS, 0, st>>>(K, nullptr, G, nc, 0, w.det.k[dcur], w.det.v[dcur], w.gt.k[gcur], w.best_g,
+                                                    w.first_rank, nullptr, w.prec, w.term, w.class_ap, tp, per_class);
+    map_mean_kernel<<<1, 32, 0, st>>>(nc, w.class_ap, 1, map);
     ypp_count_launch(2);
     return ypp_check_launch("map_match");
+}
+
+int ypp_launch_map_flags(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr, void* ws,
+                         size_t ws_bytes, unsigned char* tp, float* triples, long long* gt_per_class, cudaStream_t st)
+{
+    MapWs w = make_map_ws(ws, G, K, nc);
+    if (ws_bytes < w.total) { ypp_set_error("map_flags: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
+    unsigned long long* gpc = gt_per_class ? (unsigned long long*)gt_per_class : w.gt_per_class;
+    cudaMemsetAsync(gpc, 0, 8 * (size_t)nc, st);
+    int gcur = 0;
+    if (G > 0) {
+        cudaMemsetAsync(w.claim, 0xff, 8 * (size_t)G, st);
+        map_gt_keys_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, w.gt.k[0], w.gt.v[0], w.first_rank);
+        map_gt_count_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, gpc);
+        ypp_count_launch(2);
+        gcur = rs_sort(w.gt, G, MAP_IMG_BITS + bits_for(nc + 1), st);
+    }
+    if (K > 0) {
+        map_claim_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, gt, G, nc, w.gt.k[gcur], w.gt.v[gcur], iou_thr,
+                                                                      w.best_g, w.claim);
+        map_flags_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, nc, w.best_g, w.claim, (const long long*)gpc, tp, triples);
+        ypp_count_launch(2);
+    }
+    return ypp_check_launch("map_flags");
+}
+
+int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_stride, const long long* seg_count,
+                            const long long* gt_per_class, int nc, int c_lo, int c_hi, void* ws, size_t ws_bytes,
+                            float* per_class, cudaStream_t st)
+{
+    MapWs w = make_map_ws(ws, 0, n, nc);
+    if (ws_bytes < w.total) { ypp_set_error("map_ap_from_flags: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
+    if (n > 0) {
+        const int nb = (int)((n + SEL_TILE - 1) / SEL_TILE);
+        map_select_count_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks);
+        rs_scan_kernel<<<1, 1024, 0, st>>>(w.sel_blocks, nb);
+        // the scan is exclusive: the last block adds its own count to publish the total
+        map_select_scatter_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks,
+                                                              w.det.k[0], w.det.v[0], w.n_sel);
+        ypp_count_launch(3);
+    } else {
+        cudaMemsetAsync(w.n_sel, 0, 8, st);
+    }
+    const int dcur = rs_sort(w.det, n, 32 + bits_for(nc + 1), st, w.n_sel);
+    map_ap_kernel<true><<<c_hi - c_lo, AP_THREADS, 0, st>>>(n, w.n_sel, 0, nc, c_lo, w.det.k[dcur], w.det.v[dcur], nullptr, nullptr,
+                                                            nullptr, gt_per_class, w.prec, w.term, w.class_ap, nullptr, per_class);
+    ypp_count_launch(1);
+    return ypp_check_launch("map_ap_from_flags");
+}
+
+int ypp_launch_map_mean(const float* per_class, int nc, float* map, cudaStream_t st)
+{
+    map_mean_kernel<<<1, 32, 0, st>>>(nc, per_class, 4, map);
+    ypp_count_launch(1);
+    return ypp_check_launch("map_mean");
 }
 
 int ypp_launch_detection_ints(const float* rows, long long K, int row_width, int mode, const float* scale_xy, int n_img,

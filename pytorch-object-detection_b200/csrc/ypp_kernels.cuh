@@ -93,6 +93,13 @@ int ypp_launch_map(const float* gt, long long G, const float* det, long long K, 
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
                    cudaStream_t st);
 
+int ypp_launch_map_flags(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr, void* ws,
+                         size_t ws_bytes, unsigned char* tp, float* triples, long long* gt_per_class, cudaStream_t st);
+int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_stride, const long long* seg_count,
+                            const long long* gt_per_class, int nc, int c_lo, int c_hi, void* ws, size_t ws_bytes,
+                            float* per_class, cudaStream_t st);
+int ypp_launch_map_mean(const float* per_class, int nc, float* map, cudaStream_t st);
+
 // ---- programmatic dependent launch (PDL) --------------------------------------------------
 // The chain D1 -> S1 -> N1 -> N1b -> G is five short kernels; with the attribute below the next kernel's
 // CTAs are scheduled while the previous one drains and park in ypp_grid_wait() (griddepcontrol.wait:

@@ -57,7 +57,7 @@ WRITER_MODES = {"pred_file": 0, "coco": 1}
 
 EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "ypp_decode_compact",
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
-           "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match",
+           "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match", "ypp_map_flags", "ypp_map_ap_from_flags", "ypp_map_mean",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
            "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
@@ -130,6 +130,9 @@ def lib():
     L.ypp_map_workspace_bytes.argtypes = [i64, i64, ci]
     L.ypp_map_workspace_bytes.restype = ctypes.c_size_t
     L.ypp_map_match.argtypes = [vp, i64, vp, i64, ci, cf, vp, ctypes.c_size_t, vp, vp, vp, vp]
+    L.ypp_map_flags.argtypes = [vp, i64, vp, i64, ci, cf, vp, ctypes.c_size_t, vp, vp, vp, vp]
+    L.ypp_map_ap_from_flags.argtypes = [vp, i64, i64, vp, vp, ci, ci, ci, vp, ctypes.c_size_t, vp, vp]
+    L.ypp_map_mean.argtypes = [vp, ci, vp, vp]
     L.ypp_last_error.restype = ctypes.c_char_p
     L.ypp_version.restype = ci
     L.ypp_launch_count.argtypes = [ci]
@@ -138,7 +141,8 @@ def lib():
                  "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_match",
                  "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update",
                  "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_run_stages", "ypp_nms_append",
-                 "ypp_postprocess_append", "ypp_target_rows_append", "ypp_bbox_iou"):
+                 "ypp_postprocess_append", "ypp_target_rows_append", "ypp_bbox_iou", "ypp_map_flags",
+                 "ypp_map_ap_from_flags", "ypp_map_mean"):
         getattr(L, name).restype = ci
     _lib = L
     return L

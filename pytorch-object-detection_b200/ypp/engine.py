@@ -701,6 +701,62 @@ def map_match(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, i
     return m, pc, (tp[:K] if tp is not None else None)
 
 
+def map_flags(true_boxes: torch.Tensor, pred_boxes: torch.Tensor, num_classes, iou_threshold=0.5, want_tp=False):
+    """M1 alone (ypp_map_flags): the TP flag of every detection against the ground truths given, no AP.
+    Returns (triples float32 [K,3] = score, cls, tp; gt_per_class int64 [nc]; tp uint8 [K] or None)."""
+    gt = true_boxes.reshape(-1, 7).to(torch.float32).contiguous()
+    det = pred_boxes.reshape(-1, 7).to(torch.float32).contiguous()
+    if not (gt.is_cuda and det.is_cuda):
+        raise ValueError("map_flags needs CUDA tensors")
+    dev = det.device
+    G, K, nc = gt.shape[0], det.shape[0], int(num_classes)
+    L = lib()
+    triples = torch.empty((K, 3), dtype=torch.float32, device=dev)
+    gpc = torch.empty(nc, dtype=torch.int64, device=dev)
+    tp = torch.empty(max(K, 1), dtype=torch.uint8, device=dev) if want_tp else None
+    with _on(dev):
+        ws = _workspace(L.ypp_map_workspace_bytes(G, K, nc), dev, "map")
+        check(L.ypp_map_flags(_ptr(gt), G, _ptr(det), K, nc, float(iou_threshold), _ptr(ws), ws.numel(), _ptr(tp),
+                              _ptr(triples), _ptr(gpc), _stream()))
+    return triples, gpc, (tp[:K] if tp is not None else None)
+
+
+def map_ap_from_flags(triples: torch.Tensor, gt_per_class: torch.Tensor, num_classes, c_lo=0, c_hi=None,
+                      seg_count: Optional[torch.Tensor] = None, per_class: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """M2 (ypp_map_ap_from_flags) for the classes [c_lo, c_hi): triples [n,3] or the padded all-gather buffer
+    [n_seg, seg_stride, 3] with seg_count int64 [n_seg] valid rows each; gt_per_class int64 [nc] (global counts).
+    Returns per_class float32 [nc,4] with the rows of the owned classes filled in (AP, TP, FP, FN)."""
+    nc = int(num_classes)
+    c_hi = nc if c_hi is None else int(c_hi)
+    if not triples.is_cuda or triples.dtype != torch.float32 or triples.shape[-1] != 3:
+        raise ValueError("triples must be a float32 CUDA tensor [..., 3]")
+    t = triples.contiguous()
+    if t.dim() == 2:
+        n_seg, stride = 1, t.shape[0]
+    else:
+        n_seg, stride = t.shape[0], t.shape[1]
+    dev = t.device
+    gpc = gt_per_class.to(device=dev, dtype=torch.int64).contiguous()
+    sc = None if seg_count is None else seg_count.to(device=dev, dtype=torch.int64).contiguous()
+    if per_class is None:
+        per_class = torch.zeros((nc, 4), dtype=torch.float32, device=dev)
+    L = lib()
+    with _on(dev):
+        ws = _workspace(L.ypp_map_workspace_bytes(0, n_seg * stride, nc), dev, "map")
+        check(L.ypp_map_ap_from_flags(_ptr(t), n_seg, stride, _ptr(sc), _ptr(gpc), nc, int(c_lo), c_hi, _ptr(ws), ws.numel(),
+                                      _ptr(per_class), _stream()))
+    return per_class
+
+
+def map_mean(per_class: torch.Tensor) -> torch.Tensor:
+    """mean AP over all classes of per_class [nc,4], fp32 in class order -> float32 [1]."""
+    pc = per_class.to(torch.float32).contiguous()
+    m = torch.empty(1, dtype=torch.float32, device=pc.device)
+    with _on(pc.device):
+        check(lib().ypp_map_mean(_ptr(pc), pc.shape[0], _ptr(m), _stream()))
+    return m
+
+
 def detection_ints(rows: torch.Tensor, mode="pred_file", scale_xy: Optional[torch.Tensor] = None, img_idx_base=0) -> torch.Tensor:
     """Integer box columns of the reference's detection writers for rows [K,6|7] -> int32 [K,4].
     pred_file: xmin,ymin,xmax,ymax (make_pred_file_yolov3.py:73-86); coco: xmin,ymin,w,h after scaling by

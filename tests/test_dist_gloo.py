@@ -38,7 +38,25 @@ def _worker(rank, world, port, q):
     empty = gather_rows(torch.zeros((0, 7)))
     uneven = gather_rows(torch.full((rank * 3, 7), float(rank)))
     m = float(O.mean_average_precision(all_gt.numpy(), all_det.numpy(), nc))
-    q.put((rank, counts, all_det.numpy(), all_gt.numpy(), empty.shape[0], uneven.numpy(), m))
+    # "flags" mode: flag locally (the oracle stands in for ypp_map_flags), exchange (score, cls, tp) + per-class ground-truth
+    # counts, AP of this rank's block of classes (numpy stands in for ypp_map_ap_from_flags), gather the per-class rows
+    from ypp.dist import map_from_flags, class_range
+    _, ltp, _ = O.mean_average_precision(my_gt.numpy(), my_det.numpy(), nc, 0.5, True)
+    triples = torch.tensor(np.stack([my_det[:, 5].numpy(), my_det[:, 6].numpy(), (ltp == 1).astype(np.float32)], 1))
+    gpc = torch.tensor(np.bincount(my_gt[:, 6].numpy().astype(np.int64), minlength=nc)[:nc])
+
+    def ap_fn(recv, gpc_all, nc_, lo_, hi_, seg_count=None):
+        return torch.tensor(util.ap_from_flags_numpy(recv.numpy(), gpc_all.numpy(), nc_, lo_, hi_, seg_count.numpy()))
+
+    def mean_fn(pc):
+        s_ = np.float32(0)
+        for v in pc[:, 0].numpy():
+            s_ = np.float32(s_ + v)
+        return torch.tensor([np.float32(s_ / np.float32(pc.shape[0]))])
+
+    fm, fpc = map_from_flags(triples, gpc, nc, ap_fn=ap_fn, mean_fn=mean_fn)
+    q.put((rank, counts, all_det.numpy(), all_gt.numpy(), empty.shape[0], uneven.numpy(), m, float(fm[0]), fpc.numpy(),
+           class_range(nc, rank, world)))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -67,7 +85,11 @@ def test_gather_rows_and_sharded_map_world2():
         assert p.exitcode == 0
     g = util.load("map_cases")
     det, gt = g["syn_det"], g["syn_gt"]
-    for rank, counts, all_det, all_gt, n_empty, uneven, m in out:
+    for rank, counts, all_det, all_gt, n_empty, uneven, m, fm, fpc, crange in out:
+        # flags mode: every rank ends with the single-process per-class table and mAP
+        assert abs(fm - float(g["syn_map"])) <= 1e-6
+        assert np.allclose(fpc[:, 0], g["syn_per_class"][:, 0], atol=1e-6) and np.array_equal(fpc[:, 1:], g["syn_per_class"][:, 1:])
+        assert crange == ((0, 3), (3, 6))[rank]
         assert sum(counts) == len(det)
         # image-major fixture: rank-after-rank concatenation restores the original order
         assert np.array_equal(all_det, det) and np.array_equal(all_gt, gt)

@@ -151,3 +151,144 @@ def test_random_init_model_heads(oracle, cuda, offset_mode, union_mode):
             ref = set(g["keep"][b, : int(g["keep_count"][b])].tolist())
             got = set(res.keep_idx[b, :k].cpu().numpy().tolist())
             assert len(ref ^ got) <= max(4, len(ref) // 50), len(ref ^ got)
+
+
+# ------------------------------------------------------------------ the matching split for image-sharded evaluation
+
+def _random_eval_set(seed, n_img, nc, tie_scores=False):
+    """Image-major detections jittered around their image's ground truths (TPs, duplicates, wrong classes, misses)."""
+    rng = np.random.RandomState(seed)
+    gts, dets = [], []
+    for i in range(n_img):
+        ng = rng.randint(0, 7)
+        gt = np.concatenate([np.full((ng, 1), i), rng.uniform(50, 360, (ng, 2)), rng.uniform(20, 150, (ng, 2)),
+                             np.ones((ng, 1)), rng.randint(0, nc - 1, (ng, 1))], 1)          # the last class never has ground truth
+        gts.append(gt)
+        for _ in range(rng.randint(0, 25)):
+            if ng and rng.rand() < .75:
+                s = gt[rng.randint(ng)]
+                box = s[1:5] * rng.uniform(.85, 1.2, 4)
+                c = s[6] if rng.rand() < .9 else rng.randint(nc)
+            else:
+                box = np.concatenate([rng.uniform(0, 416, 2), rng.uniform(10, 150, 2)])
+                c = rng.randint(nc)
+            sc = np.round(rng.uniform(.25, 1), 2) if tie_scores else rng.uniform(.25, 1)
+            dets.append(np.concatenate([[i], box, [sc], [c]]))
+    return np.concatenate(gts).astype(np.float32), np.array(dets, dtype=np.float32)
+
+
+@pytest.mark.parametrize("tie_scores", [False, True])
+def test_flags_then_ap_equals_whole_matching(oracle, cuda, tie_scores):
+    """ypp_map_flags on shards + ypp_map_ap_from_flags on the concatenated (padded) triples == ypp_map_match on the whole
+    set, bit for bit (flags, per-class table, mAP) - also with scores tied in crowds, where the order of equal scores
+    (image order) decides the precision curve."""
+    from ypp import engine
+    nc, n_img = 12, 600
+    gt, det = _random_eval_set(5 + tie_scores, n_img, nc, tie_scores)
+    G, D = torch.tensor(gt).to(cuda), torch.tensor(det).to(cuda)
+    m, pc, tp = engine.map_match(G, D, nc)
+    _, otp, _ = oracle.mean_average_precision(gt, det, nc, 0.5, True)
+    assert np.array_equal(tp.cpu().numpy(), otp)
+    # one shard: the flags alone
+    tr, gpc, ftp = engine.map_flags(G, D, nc, want_tp=True)
+    assert torch.equal(ftp, tp)
+    assert torch.equal(tr[:, 2] == 1, tp == 1) and torch.equal(tr[:, 0], D[:, 5]) and torch.equal(tr[:, 1], D[:, 6])
+    assert np.array_equal(gpc.cpu().numpy(), np.bincount(gt[:, 6].astype(np.int64), minlength=nc)[:nc])
+    pc1 = engine.map_ap_from_flags(tr, gpc, nc)
+    assert torch.equal(pc1, pc) and torch.equal(engine.map_mean(pc1), m)
+    # three uneven image shards, flagged separately, padded to the longest like the all-gather buffer
+    cuts = [0, 170, 171, n_img]
+    shards, gsum = [], torch.zeros(nc, dtype=torch.int64, device=cuda)
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        g_s = G[(G[:, 0] >= a) & (G[:, 0] < b)]
+        d_s = D[(D[:, 0] >= a) & (D[:, 0] < b)]
+        t_s, gpc_s, _ = engine.map_flags(g_s, d_s, nc)
+        shards.append(t_s)
+        gsum += gpc_s
+    kmax = max(s.shape[0] for s in shards)
+    recv = torch.full((3, kmax, 3), float("nan"), device=cuda)
+    for r, s in enumerate(shards):
+        recv[r, : s.shape[0]] = s
+    counts = torch.tensor([s.shape[0] for s in shards], dtype=torch.int64, device=cuda)
+    assert torch.equal(gsum, gpc)
+    # class-sharded M2: three owners, each fills its rows
+    table = torch.zeros((nc, 4), device=cuda)
+    for lo, hi in ((0, 4), (4, 8), (8, 12)):
+        engine.map_ap_from_flags(recv, gsum, nc, lo, hi, seg_count=counts, per_class=table)
+    assert torch.equal(table, pc), "per-class table differs in %d entries" % int((table != pc).sum())
+    assert torch.equal(engine.map_mean(table), m)
+    # and against the numpy restatement
+    want = util.ap_from_flags_numpy(recv.cpu().numpy(), gsum.cpu().numpy(), nc, seg_count=counts.cpu().numpy())
+    assert np.array_equal(table.cpu().numpy()[:, 1:], want[:, 1:]) and np.allclose(table.cpu().numpy()[:, 0], want[:, 0], atol=1e-6)
+    # empty inputs
+    z3 = torch.zeros((0, 3), device=cuda)
+    assert float(engine.map_mean(engine.map_ap_from_flags(z3, gpc, nc))) == 0.0
+    t0, g0, _ = engine.map_flags(torch.zeros((0, 7), device=cuda), D, nc)
+    assert int(g0.sum()) == 0 and float(t0[:, 2].sum()) == 0.0
+
+
+def _nccl_worker(rank, world, port, q):
+    import os
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path[:0] = [root, os.path.join(root, "pytorch-object-detection_b200"), os.path.join(root, "tests")]
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from ypp import synth
+    from ypp.dist import ShardedMeanAveragePrecision
+    nc, B, n_batches = 20, 8, 6                                   # 48 images per rank
+    n_total = world * n_batches * B
+    m = ShardedMeanAveragePrecision(nc, synth.YOLOV3_ANCHORS, 416, 0.25, n_total)
+    m.warm()
+    for i in range(n_batches):
+        g = rank * n_batches + i
+        heads = [h.to(dev) for h in synth.make_heads(B, nc, [52, 26, 13], g=600 + g, mu_obj=-4.0)]
+        m.update_state(synth.make_annots(B, nc, g=g).to(dev), heads)
+    mf, pcf = m.per_class("flags")
+    mr, pcr = m.per_class("rows")
+    gt_all, det_all = m.gathered()
+    q.put((rank, float(mf[0]), pcf.cpu().numpy(), float(mr[0]), pcr.cpu().numpy(), gt_all.cpu().numpy(), det_all.cpu().numpy()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_map_over_nccl_equals_single_process(cuda):
+    """Two ranks over NCCL (needs a 2-GPU box): ShardedMeanAveragePrecision in both modes against ONE process that
+    sees all the images - gathered rows identical, per-class table and mAP bit-identical."""
+    import socket
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from ypp import synth
+    from ypp.compat.yolov3_utils import MeanAveragePrecision
+    from ypp.compat.yolo_utils import metrics_per_class
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out = sorted([q.get(timeout=300) for _ in procs], key=lambda t: t[0])
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    nc, B = 20, 8
+    single = MeanAveragePrecision(nc, synth.YOLOV3_ANCHORS, 416, 0.25)
+    for g in range(12):
+        heads = [h.to(cuda) for h in synth.make_heads(B, nc, [52, 26, 13], g=600 + g, mu_obj=-4.0)]
+        single.update_state(synth.make_annots(B, nc, g=g).to(cuda), heads)
+    want_m = float(single.result())
+    want_pc = metrics_per_class(single.all_true_boxes_variable, single.all_pred_boxes_variable, nc).cpu().numpy()
+    want_det = single.all_pred_boxes_variable.cpu().numpy()
+    want_gt = single.all_true_boxes_variable.cpu().numpy()
+    assert want_det.shape[0] > 500
+    for rank, mf, pcf, mr, pcr, gt_all, det_all in out:
+        assert np.array_equal(det_all, want_det) and np.array_equal(gt_all, want_gt)
+        assert np.array_equal(pcr, want_pc) and mr == want_m
+        assert np.array_equal(pcf, want_pc) and mf == want_m

@@ -98,3 +98,35 @@ def objcls_heads():
     heads[1][1, 4, :8, :] = torch.rand(8, 26, generator=gen) * 2
     assert [crc(h.numpy()) for h in heads] == [int(x) for x in g["head_crc"]], "regenerated objcls heads differ from the fixture"
     return g, heads
+
+
+def ap_from_flags_numpy(triples, gt_per_class, nc, c_lo=0, c_hi=None, seg_count=None):
+    """What ypp_map_ap_from_flags computes, in numpy with one fp32 rounding per operation (utils/yolo_utils.py:432-452
+    on detections that already carry their TP flag): triples [n,3] or [n_seg, stride, 3] (score, cls, tp), valid rows
+    per segment in seg_count; stable order by score descending inside a class -> per_class [nc,4]."""
+    f = np.float32
+    t = np.asarray(triples, dtype=np.float32)
+    if t.ndim == 2:
+        t = t[None]
+    segs = [t[s, : (int(seg_count[s]) if seg_count is not None else t.shape[1])] for s in range(t.shape[0])]
+    rows = np.concatenate(segs, 0) if segs else np.zeros((0, 3), np.float32)
+    c_hi = nc if c_hi is None else c_hi
+    out = np.zeros((nc, 4), np.float32)
+    for c in range(c_lo, c_hi):
+        ng = int(gt_per_class[c])
+        if ng == 0:
+            continue
+        r = rows[rows[:, 1] == c]
+        r = r[np.argsort(-r[:, 0].astype(np.float64), kind="stable")]
+        tp = (r[:, 2] != 0).astype(np.int64)
+        tpc = np.cumsum(tp)
+        fpc = np.cumsum(1 - tp)
+        prec = (tpc.astype(f) / ((tpc.astype(f) + fpc.astype(f)).astype(f) + f(1e-6)).astype(f)).astype(f)
+        env = np.maximum.accumulate(prec[::-1])[::-1] if len(prec) else prec
+        rec_den = f(np.float64(ng) + 1e-6)
+        ap = f(0)
+        for k, p in enumerate(np.nonzero(tp)[0], start=1):
+            ap = f(ap + f(f(f(k) / rec_den - f(k - 1) / rec_den) * env[p]))
+        n_tp = int(tp.sum())
+        out[c] = [ap, n_tp, len(r) - n_tp, ng - n_tp]
+    return out

@@ -13,7 +13,7 @@ communication.  Two ways through the epoch end, same result bit for bit:
 
 The reference never gathers (its metric state is rank-local, module/yolov3_detector.py:45-47); parity for this
 module is judged against the single-process result over all images.  Works with backend "nccl" (CUDA tensors,
-NVLink/NVSwitch) and "gloo" (CPU tensors: the tests run the plumbing there and plug the CPU oracle in for the
+NVLink/NVSwitch) and "gloo" (CPU tensors: the tests run the plumbing there with CPU stand-ins for the
 kernels).
 """
 from typing import Callable, Optional, Tuple

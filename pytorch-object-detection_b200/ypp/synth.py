@@ -65,3 +65,48 @@ def head_bytes_per_image(nc, grids, A=3):
 
 def boxes_per_image(grids, A=3):
     return sum(A * H * H for H in grids)
+
+
+def plant_annots(heads, annots, nc, anchors, input_size, A=3, g=0, p_detect=0.85, p_dup=0.5, p_wrong=0.1,
+                 jitter=0.06, obj_logit=2.5):
+    """Write detections DERIVED FROM the ground truth into (sparse-regime) heads, in place: for every valid row of
+    annots [B,T,5] (cx,cy,w,h normalised, class) one cell of a random scale / anchor gets the logits that decode to
+    that box (jittered), a confident objectness and its class (a wrong one with probability p_wrong); with
+    probability p_dup a second anchor of the same cell gets a weaker copy (a duplicate: false positive after the
+    first claims the ground truth).  The evaluation of such heads has an mAP of order 0.5 instead of the ~1e-7 of
+    random boxes against random ground truth, so a matcher that returns nothing cannot pass for a correct one."""
+    import math
+    rng = torch.Generator("cpu").manual_seed(9000 + g)
+    B, T, _ = annots.shape
+    u = torch.rand((B, T, 8), generator=rng)
+    n = torch.randn((B, T, 8), generator=rng)
+    for b in range(B):
+        for t in range(T):
+            row = annots[b, t]
+            if float(row.sum()) <= 0 or u[b, t, 0] > p_detect:
+                continue
+            si = int(u[b, t, 1] * len(heads)) % len(heads)
+            H = heads[si].shape[2]
+            stride = input_size / H
+            a0 = int(u[b, t, 2] * A) % A
+            cls = int(row[4]) if u[b, t, 3] > p_wrong else int(u[b, t, 4] * nc) % nc
+            cx, cy = float(row[0]) * input_size / stride, float(row[1]) * input_size / stride
+            gx, gy = min(int(cx), H - 1), min(int(cy), H - 1)
+            for k, a in enumerate((a0, (a0 + 1) % A)):
+                if k == 1 and u[b, t, 5] > p_dup:
+                    break
+                aw, ah = anchors[A * si + a]
+                fx = min(max(cx - gx + jitter * float(n[b, t, 2 * k]), 0.03), 0.97)
+                fy = min(max(cy - gy + jitter * float(n[b, t, 2 * k + 1]), 0.03), 0.97)
+                w = float(row[2]) * input_size * math.exp(jitter * float(n[b, t, 4 + k]))
+                h = float(row[3]) * input_size * math.exp(jitter * float(n[b, t, 6 + k]))
+                base = a * (5 + nc)
+                hd = heads[si]
+                hd[b, base + 0, gy, gx] = math.log(fx / (1 - fx))
+                hd[b, base + 1, gy, gx] = math.log(fy / (1 - fy))
+                hd[b, base + 2, gy, gx] = math.log(max(w, 1e-3) / aw)
+                hd[b, base + 3, gy, gx] = math.log(max(h, 1e-3) / ah)
+                hd[b, base + 4, gy, gx] = obj_logit - 1.2 * k + 0.8 * float(u[b, t, 6 + k])
+                hd[b, base + 5: base + 5 + nc, gy, gx] = -3.0
+                hd[b, base + 5 + cls, gy, gx] = 4.0
+    return heads

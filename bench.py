@@ -35,6 +35,7 @@ def parse_args():
     ap.add_argument("--regime", default="dense", choices=["dense", "sparse"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the sparse-regime and mAP epoch extras")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip the reference-path-on-this-GPU comparison")
     ap.add_argument("--ring", type=int, default=6, help="distinct input batches cycled through (> L2 in total)")
     ap.add_argument("--in-flight", type=int, default=3,
                     help="steps in flight: each on its own stream with its own workspace and outputs (must divide --ring)")
@@ -187,24 +188,38 @@ def run_reference(args):
 
 def _bind_to_gpu_numa_node(gpu_index):
     """Run this rank (and first-touch its pinned host buffers) on the CPUs NVML reports as local to its GPU,
-    so that with several ranks per box the H2D copies of the e2e path do not cross sockets."""
+    so that with several ranks per box the H2D copies of the e2e path do not cross sockets.  Returns what
+    happened, for the JSON line (affinity is an optimisation, but whether it took place explains the e2e curve)."""
+    info = {"bound": False, "cpus_before": len(os.sched_getaffinity(0))}
     try:
         import pynvml
+    except Exception as e:                          # nvidia-ml-py not importable
+        info["why"] = "pynvml import failed: %s" % type(e).__name__
+        return info
+    try:
         pynvml.nvmlInit()
         try:                                        # NVML ignores CUDA_VISIBLE_DEVICES: go through the PCI address
             import torch
             pr = torch.cuda.get_device_properties(gpu_index)
             h = pynvml.nvmlDeviceGetHandleByPciBusId("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id))
+            info["handle"] = "pci"
         except Exception:
             h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            info["handle"] = "index"
         n = (os.cpu_count() + 63) // 64
         words = pynvml.nvmlDeviceGetCpuAffinity(h, n)
         cpus = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (wd >> b) & 1}
+        info["gpu_local_cpus"] = len(cpus)
         cpus &= os.sched_getaffinity(0)
         if cpus:
             os.sched_setaffinity(0, cpus)
-    except Exception:
-        pass                                        # affinity is an optimisation only
+            info["bound"] = True
+            info["cpus_after"] = len(cpus)
+        else:
+            info["why"] = "no GPU-local CPU inside this process's affinity mask"
+    except Exception as e:
+        info["why"] = "%s: %s" % (type(e).__name__, str(e)[:80])
+    return info
 
 
 
@@ -221,7 +236,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    _bind_to_gpu_numa_node(local)
+    numa = _bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     if not os.path.exists(_lib.LIB_PATH):       # a snapshot taken before __graft_entry__.build(): compile, never fall back
@@ -261,10 +276,8 @@ def run_ours(args):
     NS = max(1, args.in_flight)
     if args.ring % NS != 0:
         raise SystemExit("bench.py: --in-flight must divide --ring")
-    pps = [pp] + [engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A,
-                                       ws_tag="post%d" % k) for k in range(1, NS)]
     engine.launch_count(True)
-    graphs = [pps[i % NS].graphed(hs) for i, hs in enumerate(ring)]
+    graphs = [pp.graphed(hs) for hs in ring]              # every captured chain owns its workspace and outputs
     launches_per_step = engine.launch_count(True) // (2 * len(ring))      # warm-up call + captured call
     res = graphs[0][1]
     streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
@@ -282,25 +295,50 @@ def run_ours(args):
 
     run_steps(W)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed_windows(fn, est_ms, min_total_ms=120.0, lo=5, hi=400):
+        """fn() = one window of exactly K steps.  Repeated until >= min_total_ms of device time are covered (a single
+        window of 40 steps is 3 ms: its run-to-run noise is as large as the effects being reported); every window is
+        bracketed by the barrier + synchronize and timed with CUDA events, max over ranks.  Returns the list of ms."""
+        reps = int(min(hi, max(lo, -(-min_total_ms // max(est_ms, 1e-3)))))
+        out = []
+        for _ in range(reps):
+            barrier()
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            out.append(e0.elapsed_time(e1))
+        if world > 1:
+            t = torch.tensor(out, dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            out = t.tolist()
+        return out
+
+    def spread(xs):
+        xs = sorted(xs)
+        return {"median": xs[len(xs) // 2], "min": xs[0], "max": xs[-1], "p10": xs[len(xs) // 10], "p90": xs[(9 * len(xs)) // 10],
+                "windows": len(xs)}
+
     # one step at a time on one stream (the latency of a step), before the clocks are sampled
+    def one_at_a_time():
+        for i in range(K):
+            graphs[i % args.ring][0].replay()
+
+    one_at_a_time()
     torch.cuda.synchronize()
-    e0.record()
-    for i in range(K):
-        graphs[i % args.ring][0].replay()
-    e1.record()
-    torch.cuda.synchronize()
-    ms_single = e0.elapsed_time(e1) / K
+    e0.record(); one_at_a_time(); e1.record(); torch.cuda.synchronize()
+    single_windows = timed_windows(one_at_a_time, e0.elapsed_time(e1))
+    ms_single = spread(single_windows)["median"] / K
     sampler = ClockSampler(local) if rank == 0 else None
-    barrier()
+    e0.record(); run_steps(K); e1.record(); torch.cuda.synchronize()
+    est = e0.elapsed_time(e1)
     if sampler:
         sampler.start()
-    e0.record()
-    run_steps(K)
-    e1.record()
-    torch.cuda.synchronize()
+    windows = timed_windows(lambda: run_steps(K), est)
     launches = launches_per_step * K
-    barrier()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    win = spread(windows)
+    ms_total = win["median"]
     # keep the GPU busy a little longer so that the 200 ms sampler sees clocks under load
     t_end = time.time() + 1.0
     while time.time() < t_end:
@@ -325,13 +363,15 @@ def run_ours(args):
     for i in range(3):
         g_d1.replay()
     torch.cuda.synchronize()
-    d1_ms = 1e9
-    for rep in range(5):
+    d1_list = []
+    for rep in range(120):                          # 120 x 48 launches x ~19 us = ~110 ms of device time
         e0.record()
         g_d1.replay()
         e1.record()
         torch.cuda.synchronize()
-        d1_ms = min(d1_ms, e0.elapsed_time(e1) / (REPS * len(ring)))
+        d1_list.append(e0.elapsed_time(e1) / (REPS * len(ring)))
+    d1_sp = spread(d1_list)
+    d1_ms = d1_sp["median"]
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json, burst copy)"
@@ -346,12 +386,21 @@ def run_ours(args):
             traffic = json.load(open(tpath)).get(args.workload + ":" + args.regime)
         except Exception:
             traffic = None
+    dram_bytes = None
+    if isinstance(traffic, dict):
+        dram_bytes = traffic.get("dram_bytes_per_launch")
+    elif isinstance(traffic, (int, float)):
+        dram_bytes = float(traffic)
     roofline = {"kernel": "ypp_decode_compact_kernel (D1)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": d1_ms,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": dram_bytes, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": d1_ms, "ms_per_launch_spread": d1_sp,
+                "frac_on_dram_bytes": (dram_bytes / (d1_ms * 1e-3) / 1e9 / peak) if dram_bytes else None,
+                "traffic_source": "profiles/d1_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum of one launch)"
+                                  if dram_bytes else None,
                 "bytes_per_image": "4*sum_s A(5+nc)HW + 28*n_cand = %d + 28*%.0f" % (head_bytes, cand_per_img),
-                "how": "CUDA events around a graph of %d back-to-back D1 launches over the %d-batch ring (inputs > L2)"
-                       % (REPS * len(ring), len(ring))}
+                "how": "CUDA events around a graph of %d back-to-back D1 launches over the %d-batch ring (inputs > L2), median of 120 replays; "
+                       "frac = algorithmic bytes / time / peak (SURVEY 8(d)); frac_on_dram_bytes = the bytes ncu saw reach HBM / the same time / peak "
+                       "(most of the 28-byte record writes are still in L2 when the kernel ends)" % (REPS * len(ring), len(ring))}
 
     # ---- stage split: each stage captured 8 times into a CUDA graph on the same (decoded, sorted) state and replayed,
     # so the figures are device time without host gaps (repeating S1 or N1+G on the same state costs the same work)
@@ -414,22 +463,43 @@ def run_ours(args):
             d2h_bytes += 4 * (B + 1) + 28 * tot
 
     e2e_loop(W)
-    barrier()
-    e0.record()
-    e2e_loop(K)
-    e1.record()
+    e2e_est = None
+    e0.record(); e2e_loop(K); e1.record(); torch.cuda.synchronize()
+    e2e_est = e0.elapsed_time(e1)
+    e2e_windows = timed_windows(lambda: e2e_loop(K), e2e_est, min_total_ms=150.0, lo=3, hi=20)
+    e2e_sp = spread(e2e_windows)
+    e2e_ms = e2e_sp["median"]
+    # the ceiling of that number: this rank's H2D copies alone (same pinned buffers, same copy stream), every rank at once
+    def h2d_only(n):
+        with torch.cuda.stream(copy_stream):
+            for i in range(n):
+                for hd, hp in zip(dbuf[i & 1], pinned[i & 1]):
+                    hd.copy_(hp, non_blocking=True)
+        main.wait_stream(copy_stream)
+    h2d_only(2)
     torch.cuda.synchronize()
     barrier()
-    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+    e0.record(); h2d_only(8); e1.record(); torch.cuda.synchronize()
+    h2d_ms = e0.elapsed_time(e1) / 8
+    h2d_gbs = B * head_bytes / (h2d_ms * 1e-3) / 1e9
+    per_rank = [{"rank": rank, "h2d_gb_per_s": h2d_gbs, "numa": numa}]
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, per_rank[0])
+        per_rank = gathered
     e2e = {"value": world * B * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": B * head_bytes,
-           "d2h_bytes_per_step": d2h_bytes // K, "ms_per_step": e2e_ms / K,
+           "d2h_bytes_per_step": d2h_bytes // K, "ms_per_step": e2e_ms / K, "window_ms": e2e_sp,
+           "h2d_only_ms_per_step": h2d_ms, "h2d_gb_per_s_this_rank": h2d_gbs,
+           "h2d_bound_images_per_s": world * B / (max(r["h2d_gb_per_s"] and B * head_bytes / (r["h2d_gb_per_s"] * 1e9) for r in per_rank)),
+           "per_rank": per_rank,
            "how": "pinned host heads -> H2D on a copy stream (double buffered) -> ypp_postprocess -> "
-                  "D2H of keep counts + kept rows [K,7]; all inside the timed region"}
+                  "D2H of keep counts + kept rows [K,7]; all inside the timed region; h2d_only = the same copies with nothing "
+                  "else running, all ranks at once: the ceiling the host links put on e2e at this N"}
 
     extras = {}
     if not args.no_extras:
         extras = run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks,
-                            ring_dense=ring[0])
+                            ring_dense=ring[0], ring_all=ring)
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -441,7 +511,11 @@ def run_ours(args):
                 "dtype": "f32", "data": "synthetic", "config": workload_config(args, w, world),
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
                 "cpu_baseline": cpu, "stage_ms": stage_ms,
+                "timing": {"what": "the K-step window repeated; value / ms_per_step are the MEDIAN window (max over ranks per window)",
+                           "window_ms": win, "total_timed_ms": sum(windows),
+                           "value_spread": {"best": world * B * K / (win["min"] * 1e-3), "worst": world * B * K / (win["max"] * 1e-3)}},
                 "single_stream": {"ms_per_step": ms_single, "value": world * B / (ms_single * 1e-3), "unit": UNIT,
+                                  "window_ms": spread(single_windows),
                                   "what": "the same K steps one at a time on one stream: the latency of a step"},
                 "per_image": {"candidates": cand_per_img, "kept": kept_per_img}}
         line.update(extras)
@@ -451,21 +525,25 @@ def run_ours(args):
     return 0
 
 
-def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks, ring_dense=None):
+def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, pp, barrier, max_over_ranks, ring_dense=None, ring_all=None):
     """Reported beside the headline: the sparse (deployment-like) regime, and the mAP epoch end
     (all-gather of detections over NCCL + GPU TP/FP matching) on sparse-regime detections."""
-    from ypp.dist import gather_rows
     B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
     out = {}
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     n_ring = args.ring
+    if rank == 0 and not args.no_ref_cuda:
+        cases = [(args.workload, "dense"), (args.workload, "sparse")]
+        if args.workload != "yolov4tiny_416_person_b256" and world == 1:
+            cases.append(("yolov4tiny_416_person_b256", "dense"))          # one class: the O(n^2) stress of the mask kernel
+        out["ref_cuda"] = [ref_cuda_compare(torch, engine, synth, dev, nm, rg) for nm, rg in cases]
+    if world > 1:
+        dist.barrier()
     sparse = [[h.to(dev) for h in synth.make_heads(B, nc, grids, A=A, g=500 + rank * 64 + i, mu_obj=-5.0)]
               for i in range(n_ring)]
     # same protocol as the headline: NS steps in flight, each stream with its own processor (workspace) and outputs
     NS = max(1, args.in_flight)
-    pps = [pp] + [engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A,
-                                       ws_tag="post%d" % k) for k in range(1, NS)]
-    sg = [pps[i % NS].graphed(hs) for i, hs in enumerate(sparse)]
+    sg = [pp.graphed(hs) for hs in sparse]
     res = sg[0][1]
     streams = [torch.cuda.Stream(device=dev) for _ in range(NS)]
     main = torch.cuda.current_stream()
@@ -496,51 +574,35 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
     out["sparse_regime"] = {"value": world * B * args.steps / (ms * 1e-3), "unit": UNIT,
                             "candidates_per_image": float(res.cand_count.float().mean().item()),
                             "ms_per_step": ms / args.steps, "steps_in_flight": NS, "single_stream_ms_per_step": ms_one}
-    # mAP epoch: n_batches of B images per rank, detections accumulated on device, then gather + match
-    n_batches = 32                      # C5 shape: 2048 images per rank in batches of 64
-    # the accumulation is MeanAveragePrecision.update_state's: the gather and the GT ingest append behind device
-    # cursors (ypp_nms_append / ypp_target_rows_append), the host reads nothing back between batches
-    annots = [synth.make_annots(B, nc, g=rank * n_batches + i).to(dev) for i in range(n_batches)]
-
-    def accumulate():
-        acc_d, acc_g = engine.RowAccumulator(dev), engine.RowAccumulator(dev, 1024)
-        for i in range(n_batches):
-            base = (rank * n_batches + i) * B
-            pp.accumulate(acc_d, sparse[i % n_ring], img_idx_base=base)
-            engine.target_rows_append(acc_g, annots[i], w["input_size"], base)
-        return acc_d, acc_g
-
-    accumulate()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    acc_d, acc_g = accumulate()
-    torch.cuda.synchronize()
-    ms_acc = (time.perf_counter() - t0) * 1e3 / n_batches
-    det_local, gt_local = acc_d.view().clone(), acc_g.view().clone()
-    del acc_d, acc_g
-    ms_gathers = []
-    for _ in range(3):                  # the first call also pays NCCL's one-time set-up for this collective
-        barrier()
-        e0.record()
-        det_all = gather_rows(det_local)
-        gt_all = gather_rows(gt_local)
-        e1.record()
-        torch.cuda.synchronize()
-        ms_gathers.append(max_over_ranks(e0.elapsed_time(e1)))
-    ms_gather = ms_gathers[-1]
-    engine.map_match(gt_all, det_all, nc)
-    torch.cuda.synchronize()
-    e0.record()
-    m, pc, _ = engine.map_match(gt_all, det_all, nc)
-    e1.record()
-    torch.cuda.synchronize()
-    ms_match = max_over_ranks(e0.elapsed_time(e1))
-    out["map_epoch"] = {"images": world * n_batches * B, "detections": int(det_all.shape[0]),
-                        "ground_truths": int(gt_all.shape[0]), "accumulate_ms_per_batch": ms_acc,
-                        "allgather_ms": ms_gather, "allgather_first_call_ms": ms_gathers[0], "match_ms": ms_match,
-                        "mAP": float(m.item()), "detections_per_s": det_all.shape[0] / (ms_match * 1e-3)}
+    out["map_epoch"] = map_epoch_extra(args, torch, dist, engine, synth, dev, rank, world, w, anchors, barrier, max_over_ranks)
+    # the drop-in accumulator on DENSE batches (MeanAveragePrecision.update_state, heads resident): what a caller of
+    # ypp.compat gets per batch, one batch at a time vs several in flight inside the product (PostProcessor.accumulate)
+    if w["kind"] == "v3" and ring_all is not None:
+        from ypp.compat.yolov3_utils import MeanAveragePrecision as MAPv3
+        ann = [synth.make_annots(B, nc, g=900 + i).to(dev) for i in range(len(ring_all))]
+        vl = {}
+        for depth in (1, 2, 3, 4):
+            mm = MAPv3(nc, anchors, w["input_size"], w["conf"], anchors_per_scale=A, pipeline_depth=depth)
+            best = None
+            for rep in range(3):
+                mm.reset_states()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for i in range(48):
+                    mm.update_state(ann[i % len(ann)], ring_all[i % len(ring_all)])
+                n_rows = mm.all_pred_boxes_variable.shape[0]
+                torch.cuda.synchronize()
+                dt = (time.perf_counter() - t0) * 1e3 / 48
+                best = dt if best is None else min(best, dt)
+            vl["depth_%d_ms_per_batch" % depth] = best
+            vl["rows"] = int(n_rows)
+            del mm
+        vl["default_depth"] = 3
+        vl["images_per_s_default"] = B / (vl["depth_3_ms_per_batch"] * 1e-3)
+        vl["what"] = "48 dense batches through ypp.compat.yolov3_utils.MeanAveragePrecision.update_state, wall clock incl. the final row count read; best of 3"
+        out["val_loop_dense"] = vl
     # detection writers: integer box columns of one dense step's kept rows
-    rows = pp(ring_dense).rows() if ring_dense is not None else det_local
+    rows = pp(ring_dense).rows()
     scale = torch.tensor([[500 / w["input_size"], 375 / w["input_size"]]] * B, dtype=torch.float64).float().to(dev)
     engine.detection_ints(rows, "coco", scale_xy=scale)
     torch.cuda.synchronize()
@@ -662,6 +724,245 @@ def fused_head_extra(torch, engine, dev, w, anchors, cins=(256, 512, 1024)):
             "cudnn_plus_unfused_images_per_s": B / (t_unf * 1e-3), "candidates_per_image": cand,
             "allow_tf32": bool(torch.backends.cudnn.allow_tf32),
             "what": "input of the heads' 1x1 convs [B,H,W,Cin] fp32 resident in HBM -> kept rows; CUDA-graph timed"}
+
+
+# ------------------------------------------------------------------------------------ C5: the evaluation epoch
+
+def epoch_data(synth, w, rank, n_distinct):
+    """n_distinct (heads, annots) pairs of rank `rank`: sparse-regime heads with detections derived from that batch's
+    ground truth planted in (synth.plant_annots), so the epoch's mAP is of order 0.7 and says something."""
+    B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
+    anchors = synth.workload_anchors(w)
+    pairs = []
+    for i in range(n_distinct):
+        g = 7000 + rank * 64 + i
+        heads = synth.make_heads(B, nc, grids, A=A, g=g, mu_obj=-5.0)
+        an = synth.make_annots(B, nc, g=g)
+        if w["kind"] == "v3":
+            synth.plant_annots(heads, an, nc, anchors, w["input_size"], A=A, g=g)
+        pairs.append((heads, an))
+    return pairs
+
+
+def map_epoch_extra(args, torch, dist, engine, synth, dev, rank, world, w, anchors, barrier, max_over_ranks):
+    """BASELINE config 5: every rank accumulates n_batches x B images through the drop-in accumulator
+    (ShardedMeanAveragePrecision.update_state = MeanAveragePrecision.update_state with global image ids; batches in
+    flight inside the product), then the epoch end in both exchange modes:
+      rows   all-gather of [K,7] detections + [G,7] ground truths (NCCL), whole matching on every rank (north star);
+      flags  local TP flags, all-gather of (score, cls, tp) + per-class ground-truth counts, class-sharded AP.
+    Wall clock between barriers (the host drives the loop), max over ranks; second epoch reported (the first warms
+    NCCL and the allocator).  Rank 0 then recomputes everything in ONE process over all ranks' images and compares."""
+    from ypp.dist import ShardedMeanAveragePrecision
+    from ypp.compat.yolov3_utils import MeanAveragePrecision as MAPv3
+    from ypp.compat.yolov2_utils import MeanAveragePrecision as MAPv2
+    B, nc = w["batch"], w["nc"]
+    n_batches, n_distinct = 32, min(args.ring, 6)
+    n_total = world * n_batches * B
+    pairs = [([h.to(dev) for h in hs], an.to(dev)) for hs, an in epoch_data(synth, w, rank, n_distinct)]
+    m = ShardedMeanAveragePrecision(nc, anchors, w["input_size"], w["conf"], n_total, kind=w["kind"],
+                                    anchors_per_scale=w["A"])
+    m.warm()
+
+    def feed(metric):
+        for i in range(n_batches):
+            hs, an = pairs[i % n_distinct]
+            metric.update_state(an, hs if w["kind"] == "v3" else hs[0])
+
+    def epoch(mode):
+        """-> (ms accumulate, ms epoch end, mAP, per_class) with the accumulation queued behind nothing."""
+        m.reset_states()
+        barrier()
+        t0 = time.perf_counter()
+        feed(m)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        mp, pc = m.per_class(mode)
+        val = float(mp[0].item())                 # the read of the result ends the epoch
+        t2 = time.perf_counter()
+        return 1e3 * (t1 - t0), 1e3 * (t2 - t1), val, pc
+
+    res = {}
+    for mode in ("flags", "rows"):
+        epoch(mode)
+        acc_ms, end_ms, val, pc = epoch(mode)
+        acc_ms, end_ms = max_over_ranks(acc_ms), max_over_ranks(end_ms)
+        res[mode] = {"accumulate_ms": acc_ms, "epoch_end_ms": end_ms, "epoch_ms": acc_ms + end_ms, "mAP": val,
+                     "images_per_s": n_total / ((acc_ms + end_ms) * 1e-3), "per_class": pc}
+    gt_l, det_l = m.local_rows()
+    # the same epoch on one GPU, in this run: this rank's own images, no exchange
+    Single = MAPv3 if w["kind"] == "v3" else MAPv2
+    one = Single(nc, anchors, w["input_size"], w["conf"], anchors_per_scale=w["A"]) if w["kind"] == "v3" else \
+        Single(nc, anchors, w["input_size"], w["conf"])
+    one_ms = None
+    for _ in range(2):
+        one.reset_states()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        feed(one)
+        float(one.result().item())
+        one_ms = 1e3 * (time.perf_counter() - t0)
+    one_ms = max_over_ranks(one_ms)
+    out = {"images": n_total, "images_per_rank": n_batches * B, "detections_per_rank": int(det_l.shape[0]),
+           "ground_truths_per_rank": int(gt_l.shape[0]),
+           "flags": {k: v for k, v in res["flags"].items() if k != "per_class"},
+           "rows": {k: v for k, v in res["rows"].items() if k != "per_class"},
+           "one_gpu_epoch_ms": one_ms, "one_gpu_images_per_s": n_batches * B / (one_ms * 1e-3),
+           "epoch_efficiency_flags": one_ms / res["flags"]["epoch_ms"], "epoch_efficiency_rows": one_ms / res["rows"]["epoch_ms"],
+           "mAP": res["flags"]["mAP"],
+           "what": "n_batches=%d x B=%d images per rank; detections derived from the ground truth; epoch = update_state loop + result(), "
+                   "wall clock between barriers, max over ranks; efficiency = the same epoch on one GPU (this run) / the N-GPU epoch" % (n_batches, B)}
+    # ---- hardware parity: ONE process over every rank's images (rank 0 regenerates the other ranks' data)
+    same_modes = bool(torch.equal(res["flags"]["per_class"], res["rows"]["per_class"])) and res["flags"]["mAP"] == res["rows"]["mAP"]
+    gt_all, det_all = m.gathered()
+    if rank == 0:
+        ref = Single(nc, anchors, w["input_size"], w["conf"], anchors_per_scale=w["A"]) if w["kind"] == "v3" else \
+            Single(nc, anchors, w["input_size"], w["conf"])
+        ref.reset_states()
+        for r in range(world):
+            pr = pairs if r == 0 else [([h.to(dev) for h in hs], an.to(dev)) for hs, an in epoch_data(synth, w, r, n_distinct)]
+            for i in range(n_batches):
+                hs, an = pr[i % n_distinct]
+                ref.update_state(an, hs if w["kind"] == "v3" else hs[0])
+            del pr
+        r_gt, r_det = ref.all_true_boxes_variable, ref.all_pred_boxes_variable
+        r_map, r_pc, r_tp = engine.map_match(r_gt, r_det, nc, want_tp=True)
+        _, _, g_tp = engine.map_match(gt_all, det_all, nc, want_tp=True)
+        checks = {"gathered_detections_equal": bool(det_all.shape == r_det.shape and torch.equal(det_all, r_det)),
+                  "gathered_ground_truths_equal": bool(gt_all.shape == r_gt.shape and torch.equal(gt_all, r_gt)),
+                  "tp_flags_equal": bool(g_tp.shape == r_tp.shape and torch.equal(g_tp, r_tp)),
+                  "per_class_rows_mode_equal": bool(torch.equal(res["rows"]["per_class"], r_pc)),
+                  "per_class_flags_mode_equal": bool(torch.equal(res["flags"]["per_class"], r_pc)),
+                  "mAP_abs_diff": abs(res["flags"]["mAP"] - float(r_map[0].item())), "modes_agree": same_modes}
+        ok = all(v for k, v in checks.items() if k != "mAP_abs_diff") and checks["mAP_abs_diff"] <= 1e-6
+        out["parity"] = "ok" if ok else "FAILED"
+        out["parity_checks"] = checks
+        out["single_process_mAP"] = float(r_map[0].item())
+        out["true_positives"] = int((r_tp == 1).sum().item())
+    barrier()
+    return out
+
+
+# ------------------------------------------------------------------------------------ the shipped sm_100 kernels to beat
+
+def _ref_decode_eager(torch, inp, num_classes, anchors, input_size):
+    """decode_predictions of the reference (utils/yolov3_utils.py:27-59) as the same sequence of eager torch ops on
+    the heads' own device: view -> permute -> contiguous copy, materialised anchor / grid tensors, sigmoid / exp,
+    *= stride, argmax of the class sigmoids, cat.  (The reference itself cannot travel to this box; this is its op
+    list, so the launches and the HBM traffic are the reference's.)"""
+    B, _, H, W = inp.shape
+    A = len(anchors)
+    sh, sw = input_size / H, input_size / W
+    dev = inp.device
+    pred = inp.view(B, A, -1, H, W).permute(0, 1, 3, 4, 2).contiguous()
+    stride = torch.tensor([sw, sh] * 2, dtype=torch.float32, device=dev)
+    sa = torch.tensor([[aw / sw, ah / sh] for aw, ah in anchors], dtype=torch.float32, device=dev).unsqueeze(0)
+    sa = sa.repeat(B, 1, 1).repeat(1, 1, H * W).view(B, A, H, W, 2)
+    gx = torch.arange(0, W, device=dev).repeat(H, 1).repeat(B * A, 1, 1).view(B, A, H, W, 1).float()
+    gy = torch.arange(0, W, device=dev).repeat(H, 1).t().repeat(B * A, 1, 1).view(B, A, H, W, 1).float()
+    pxy = torch.sigmoid(pred[..., 0:2]) + torch.cat([gx, gy], dim=-1)
+    pwh = torch.exp(pred[..., 2:4]) * sa
+    pbox = torch.cat([pxy, pwh], dim=-1).view(B, -1, 4)
+    pbox *= stride
+    pconf = torch.sigmoid(pred[..., 4:5]).view(B, -1, 1)
+    pcls = torch.argmax(torch.sigmoid(pred[..., 5:]).view(B, -1, num_classes), dim=-1, keepdim=True)
+    return torch.cat((pbox, pconf, pcls), -1)
+
+
+def _ref_nms_v3_eager(torch, tv, boxes, conf, iou):
+    """nms_v3 (utils/yolo_utils.py:334-348) on one image's rows, on their device."""
+    boxes = boxes[torch.where(boxes[..., 4] > conf)[0]]
+    if boxes.shape[0] == 0:
+        return boxes
+    x1 = (boxes[..., 0] - (boxes[..., 2] / 2)).unsqueeze(dim=-1)
+    y1 = (boxes[..., 1] - (boxes[..., 3] / 2)).unsqueeze(dim=-1)
+    x2 = (boxes[..., 0] + (boxes[..., 2] / 2)).unsqueeze(dim=-1)
+    y2 = (boxes[..., 1] + (boxes[..., 3] / 2)).unsqueeze(dim=-1)
+    keep = tv.ops.batched_nms(torch.cat([x1, y1, x2, y2], dim=-1), boxes[..., 4], boxes[..., 5], iou)
+    return boxes[keep]
+
+
+def ref_cuda_compare(torch, engine, synth, dev, name, regime, reps=7):
+    """SURVEY 2a K6/K7, BASELINE.md 4: the reference's own path on THIS GPU - eager decode + per-image nms_v3 ->
+    torchvision.ops.batched_nms (its shipped sm_100 nms_kernel_impl<float> + gather_keep_from_mask) - against our chain
+    on the same resident heads; and batched_nms ALONE on our compacted candidates (candidate selection and the xyxy
+    conversion done beforehand, outside the timed region) against our S1 + N1 + N1b + G on the same candidates.
+    CUDA events, 3 warm-ups, median of `reps`; the per-image Python loop and its host syncs are part of the reference."""
+    try:
+        import torchvision as tv
+    except Exception as e:
+        return {"unavailable": "torchvision: %s" % type(e).__name__}
+    w = synth.WORKLOADS[name]
+    anchors = synth.workload_anchors(w)
+    B, nc, grids, A = w["batch"], w["nc"], w["grids"], w["A"]
+    heads = [h.to(dev) for h in synth.make_heads(B, nc, grids, A=A, g=4000, mu_obj=0.0 if regime == "dense" else -5.0)]
+    pp = engine.PostProcessor(nc, anchors, w["input_size"], w["conf"], kind=w["kind"], anchors_per_scale=A)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def med(fn, n=reps, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(n):
+            e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    kept_ref = [0]
+
+    def ref_chain():
+        if w["kind"] == "v2":
+            rows = _ref_decode_eager(torch, heads[0], nc, anchors, w["input_size"])
+        else:
+            rows = torch.cat([_ref_decode_eager(torch, h, nc, anchors[A * i: A * i + A], w["input_size"]) for i, h in enumerate(heads)], dim=1)
+        k = 0
+        for b in range(B):
+            k += _ref_nms_v3_eager(torch, tv, rows[b], w["conf"], 0.45).shape[0]
+        kept_ref[0] = k
+        return rows
+
+    def ref_decode_only():
+        if w["kind"] == "v2":
+            return _ref_decode_eager(torch, heads[0], nc, anchors, w["input_size"])
+        return torch.cat([_ref_decode_eager(torch, h, nc, anchors[A * i: A * i + A], w["input_size"]) for i, h in enumerate(heads)], dim=1)
+
+    g_all, res = pp.graphed(heads)
+    ours_ms = med(g_all.replay, n=25)
+    ours_eager_ms = med(lambda: pp(heads, out=res), n=25)
+    ref_ms = med(ref_chain)
+    ref_dec_ms = med(ref_decode_only)
+    kept_ours = int(res.keep_count.sum().item())
+    # batched_nms alone on OUR candidates
+    rows = pp.decode(heads)
+    cands = []
+    for b in range(B):
+        c = rows[b][rows[b][:, 4] > w["conf"]]
+        xyxy = torch.stack([c[:, 0] - c[:, 2] / 2, c[:, 1] - c[:, 3] / 2, c[:, 0] + c[:, 2] / 2, c[:, 1] + c[:, 3] / 2], 1).contiguous()
+        cands.append((xyxy, c[:, 4].contiguous(), c[:, 5].contiguous()))
+
+    def tv_nms_only():
+        for xyxy, sc, cl in cands:
+            if xyxy.shape[0]:
+                tv.ops.batched_nms(xyxy, sc, cl, 0.45)
+
+    tv_ms = med(tv_nms_only)
+    pp.staged(heads, stages=("decode",), out=res, ws=res.ws)
+    g_sn = torch.cuda.CUDAGraph()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g_sn):
+        pp.staged(heads, stages=("sort", "nms"), out=res, ws=res.ws)
+    ours_sn_ms = med(g_sn.replay, n=25)
+    n_cand = float(res.cand_count.float().mean().item())
+    return {"workload": name, "regime": regime, "batch": B, "candidates_per_image": n_cand,
+            "kept_total_ours": kept_ours, "kept_total_reference_path": kept_ref[0],
+            "ours_chain_ms": ours_ms, "ours_chain_eager_launch_ms": ours_eager_ms,
+            "ref_cuda_chain_ms": ref_ms, "ref_cuda_decode_ms": ref_dec_ms,
+            "ours_images_per_s": B / (ours_ms * 1e-3), "ref_cuda_images_per_s": B / (ref_ms * 1e-3),
+            "chain_speedup": ref_ms / ours_ms,
+            "tv_batched_nms_only_ms": tv_ms, "ours_sort_nms_rows_ms": ours_sn_ms, "nms_speedup": tv_ms / ours_sn_ms,
+            "what": "ref_cuda = eager decode_predictions + per-image nms_v3 -> torchvision.ops.batched_nms on this GPU (heads resident); "
+                    "tv_batched_nms_only = %d batched_nms calls on our compacted candidates; ours = CUDA-graph replay of the same work" % B}
 
 
 if __name__ == "__main__":

@@ -151,6 +151,21 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
                     float* det_rows, int row_width, int64_t det_capacity, int* det_total,
                     float img_idx_base, void* stream);
 
+/* ypp_postprocess for callers that cannot provide scratch memory (code under CUDA graph capture set-up, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The chain's workspace is a device array built into the library - YPP_STATIC_WS_BYTES (4 MiB) on every
+ * GPU that loads libypp.so, held until the process exits - so the call allocates nothing: no cudaMalloc / cudaFree, no
+ * allocating library routine.  Inputs and outputs are the caller's, with the meaning they have in ypp_postprocess.
+ * Limit: ypp_workspace_bytes(cfg->B, n_boxes, cfg->nc) <= YPP_STATIC_WS_BYTES, else YPP_E_WORKSPACE with the sizes in
+ * ypp_last_error() (one YOLOv3-416 image - 10 647 boxes, 80 classes - needs 0.58 MB; four of them, six with 20
+ * classes, or one 608-pixel image of 22 743 boxes fit; a batch of 8 does not).  Nothing in the workspace has to start at zero (every kernel of the chain initialises what it
+ * reads), so the array simply keeps the last call's contents.  ALL calls on a device share the one array: calls that
+ * overlap on the GPU (two streams, two host threads) race - serialise them on one stream or with events. */
+#define YPP_STATIC_WS_BYTES (4 << 20)
+int ypp_postprocess_static(const ypp_cfg* cfg, const ypp_scale* scales, int* cand_count, int* keep_count, int* keep_idx,
+                           float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
+                           void* stream);
+
 /* Any contiguous part of the chain as ONE call: stages is a mask of YPP_STAGE_* (DECODE = D1, SORT = S1,
  * SUPPRESS = N1 (+ the long-segment kernel), ROWS = the row gather G).  The state between stages lives in
  * the workspace, so a chain may be cut anywhere and continued by a later call on the same workspace (on any

@@ -284,6 +284,54 @@ int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, voi
                         (const long long*)cursor_in, (long long*)cursor_out, (stages & YPP_STAGE_ROWS) != 0);
 }
 
+// ---- ypp_postprocess without caller scratch --------------------------------------------------------------
+// The chain's whole workspace in a file-scope device array (YPP_STATIC_WS_BYTES; every GPU that loads the library
+// holds it until exit).  In HOST code `g_static_ws` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) unsigned char g_static_ws[YPP_STATIC_WS_BYTES];
+
+static void* static_ws_ptr(int* rc)
+{
+    static void* ptr_d[YPP_MAX_DEVICES];              // per device ordinal; a racing first call stores the same value twice
+    int dev = 0;
+    *rc = YPP_OK;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= YPP_MAX_DEVICES) {
+        ypp_set_error("postprocess_static: device ordinal %d out of range", dev); *rc = YPP_E_UNSUPPORTED; return nullptr;
+    }
+    if (!ptr_d[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_ws);
+        if (e != cudaSuccess || !p) {
+            ypp_set_error("postprocess_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); *rc = YPP_E_CUDA; return nullptr;
+        }
+        ptr_d[dev] = p;
+    }
+    return ptr_d[dev];
+}
+
+int ypp_postprocess_static(const ypp_cfg* cfg, const ypp_scale* scales, int* cand_count, int* keep_count, int* keep_idx,
+                           float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
+                           void* stream)
+{
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, false, &p);
+    if (rc) return rc;
+    const size_t need = ypp_make_ws(nullptr, cfg->B, p.N, cfg->nc).total_bytes;
+    if (need > (size_t)YPP_STATIC_WS_BYTES) {
+        ypp_set_error("postprocess_static: B=%d x %d boxes x %d classes needs %zu bytes of scratch, the built-in array holds %d "
+                      "(use ypp_postprocess with a caller workspace)", cfg->B, p.N, cfg->nc, need, YPP_STATIC_WS_BYTES);
+        return YPP_E_WORKSPACE;
+    }
+    void* ws = static_ws_ptr(&rc);
+    if (rc) return rc;
+    rc = bind_ws(cfg->B, p.N, cfg->nc, ws, YPP_STATIC_WS_BYTES, &p.ws);
+    if (rc) return rc;
+    rc = ypp_launch_decode_compact(p, cfg->B, (cudaStream_t)stream);
+    if (rc) return rc;
+    return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
+                        img_idx_base, nullptr, true, true, (cudaStream_t)stream);
+}
+
 // the heads' 1x1 convolutions fused with D1: one tcgen05 kernel over every scale writes the slot records
 static int head_decode_all(const ypp_cfg* cfg, const ypp_scale* scales, const ypp_head_src* src, void* ws, size_t ws_bytes,
                            YppDecodeParams* p, cudaStream_t st)

@@ -13,6 +13,7 @@ LIB_PATH = os.environ.get("YPP_LIB") or os.path.join(_PKG, "libypp.so")   # YPP_
 SOURCES = ["api.cu", "decode.cu", "head.cu", "organise.cu", "nms.cu", "metrics.cu"]
 
 YPP_MAX_SCALES = 4
+YPP_STATIC_WS_BYTES = 4 << 20
 YPP_MAX_ANCHORS = 8
 
 SCORE_OBJ, SCORE_OBJ_TIMES_CLS = 0, 1
@@ -59,7 +60,7 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match", "ypp_map_flags", "ypp_map_ap_from_flags", "ypp_map_mean",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
-           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_postprocess_static", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -119,6 +120,8 @@ def lib():
     L.ypp_postprocess_append.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
     L.ypp_run_stages.argtypes = [cfgp, scp, ci, vp, ctypes.c_size_t, ci, vp, vp, vp, vp, ci, i64, vp, vp, vp, cf, vp]
+    L.ypp_postprocess_static.argtypes = [cfgp, scp, vp, vp, vp, vp, ci, i64, vp, cf, vp]
+    L.ypp_postprocess_static.restype = ci
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
     L.ypp_bbox_iou.argtypes = [vp, ci, vp, ci, ci, ci, ctypes.c_double, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]

@@ -127,6 +127,16 @@ int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes,
             float* det_rows, int row_width, int64_t det_capacity, int* det_total,
             float img_idx_base, void* stream);
 
+/* Optional companion of every append-mode call: the kernel that advances the device cursor also stores
+ * (new cursor value << 24) | (seq & 0xffffff) - ONE 8-byte word - into pinned host memory (cudaHostAlloc / cudaMallocHost
+ * memory is device-accessible under unified addressing).  The host then knows, without a copy, an event or a wait, how
+ * many rows the accumulator held after append number `seq`, and sizes its buffer from that plus the worst case of the
+ * appends issued since (utils/yolov3_utils.py:139-146 reads the count through torch.cat on every batch).  NULL = none. */
+typedef struct {
+    int64_t* host_word;   /* pinned host memory, 8-byte aligned */
+    uint32_t seq;         /* the caller's number for this append (only the low 24 bits travel) */
+} ypp_probe;
+
 /* ypp_nms in append mode: the accumulation `self.all_pred_boxes_variable = torch.cat([self.all_pred_boxes_variable,
  * pred_boxes])` of MeanAveragePrecision.update_state (utils/yolov3_utils.py:139-144) done by the gather itself,
  * with no host read of the row count between batches.  det_rows is the whole accumulator ([det_capacity,
@@ -137,12 +147,13 @@ int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes,
  * case (B * n_boxes rows per call) between two reads of the cursor. */
 int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count,
                    float* det_rows, int row_width, int64_t det_capacity, const int64_t* cursor_in,
-                   int64_t* cursor_out, float img_idx_base, void* stream);
+                   int64_t* cursor_out, float img_idx_base, void* stream, const ypp_probe* probe);
 
 /* ypp_postprocess with the gather in append mode (one call per batch of a validation loop). */
 int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
                            int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
-                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream);
+                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream,
+                           const ypp_probe* probe);
 
 /* The three stages above, back to back, from the heads (DecodeYoloV3/V2.forward and the body
  * of MeanAveragePrecision.update_state: utils/yolov3_utils.py:73-90,108-146). */
@@ -182,7 +193,7 @@ int ypp_postprocess_static(const ypp_cfg* cfg, const ypp_scale* scales, int* can
 int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, void* ws, size_t ws_bytes, int stages,
                    int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width,
                    int64_t det_capacity, int* det_total, const int64_t* cursor_in, int64_t* cursor_out,
-                   float img_idx_base, void* stream);
+                   float img_idx_base, void* stream, const ypp_probe* probe);
 
 /* ---- the head's 1x1 convolution fused with the decode ---------------------------
  * Every detector ends each scale in nn.Conv2d(Cin, A*(5+nc), 1, 1, bias=False)
@@ -264,7 +275,7 @@ int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, floa
  * out_G7 is the whole accumulator [capacity,7]; rows go after the *cursor rows already there and *cursor
  * (device int64, in/out - the kernel is one block) is advanced.  A call adds at most B*T rows. */
 int ypp_target_rows_append(const float* annot_BT5, int B, int T, float input_size, float img_idx_base,
-                           float* out_G7, int64_t capacity, int64_t* cursor, void* stream);
+                           float* out_G7, int64_t capacity, int64_t* cursor, void* stream, const ypp_probe* probe);
 
 /* ---- detection writers --------------------------------------------------
  * The integer box columns the reference's detection writers put on disk, for K rows
@@ -347,6 +358,38 @@ int ypp_map_ap_from_flags(const float* triples, int64_t n_seg, int64_t seg_strid
 
 /* mean of column 0 of per_class [nc,4] over all nc classes, fp32 in class order (torch.mean, utils/yolo_utils.py:456) */
 int ypp_map_mean(const float* per_class_nc4, int nc, float* map, void* stream);
+
+/* ---- several batches in flight (the validation loop of module/yolov3_detector.py:33-47) --------------------------
+ * MeanAveragePrecision.update_state (utils/yolov3_utils.py:108-146) is called batch after batch, and a batch's
+ * chain leaves most of the GPU idle for a third of its time (the per-image sort is one CTA per image).  A pipeline
+ * owns `depth` side streams (and two events each; no device memory): ypp_pipeline_submit runs batch i on stream
+ * i mod depth - it starts behind whatever the caller's stream has queued, its decode / sort / suppression overlap
+ * the neighbouring batches', and only its row gather waits for the previous batch's, because both append behind one
+ * device cursor (ypp_postprocess_append's contract: two different cursor words, alternate).  One call per batch
+ * replaces ~10 runtime calls from the host language.  The caller provides a workspace PER SLOT
+ * (ypp_pipeline_next_slot says which the next submit uses) and keeps inputs, workspaces and the accumulator alive
+ * until the batch has completed.  probe (optional, see ypp_probe): the gather reports the cursor to pinned host
+ * memory, so the host sizes its buffers from the newest completed count without ever blocking.
+ * Not thread-safe: one pipeline per host thread.  Created on, and bound to, the current device. */
+#define YPP_PIPELINE_MAX_DEPTH 8
+typedef struct ypp_pipeline ypp_pipeline;
+int ypp_pipeline_create(int depth, ypp_pipeline** out);
+int ypp_pipeline_destroy(ypp_pipeline* p);
+int ypp_pipeline_next_slot(const ypp_pipeline* p);
+void* ypp_pipeline_stream(const ypp_pipeline* p, int slot);      /* cudaStream_t of a slot (allocator bookkeeping) */
+int ypp_pipeline_submit(ypp_pipeline* p, const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,
+                        int* cand_count, int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
+                        const int64_t* cursor_in, int64_t* cursor_out, const ypp_probe* probe, float img_idx_base,
+                        void* caller_stream, int64_t* ticket);
+int ypp_pipeline_query(const ypp_pipeline* p, int64_t ticket);          /* 1 = that batch has completed */
+int ypp_pipeline_wait_ticket(const ypp_pipeline* p, int64_t ticket);    /* the HOST waits for that batch only */
+int ypp_pipeline_join(const ypp_pipeline* p, void* stream);             /* `stream` waits on the device for all batches */
+
+/* Stream-ordered copy of a few bytes (<= 4096) of device memory - an append cursor, a count - into PINNED host memory,
+ * without waiting for it.  The accumulation of MeanAveragePrecision.update_state (utils/yolov3_utils.py:139-146) needs
+ * the row count on the host only to size its buffer; with a probe behind every append and an event behind the probe
+ * the host reads the newest COMPLETED count and never blocks on the device.  Never synchronises. */
+int ypp_peek_async(const void* device_src, void* host_dst, size_t bytes, void* stream);
 
 /* ---- misc ---------------------------------------------------------------------------- */
 

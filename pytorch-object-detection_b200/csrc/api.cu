@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <new>
 
 static thread_local char g_err[512] = "";
 static thread_local long long g_launches = 0;
@@ -96,7 +97,8 @@ int bind_ws(int B, int N, int nc, void* ws, size_t ws_bytes, YppWs* out)
 int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int* keep_count, int* keep_idx,
                  float* det_rows, int row_width, int64_t det_capacity, int* det_total, float img_idx_base,
                  const float* src_rows, bool do_sort, bool do_nms, cudaStream_t st,
-                 const long long* cursor_in = nullptr, long long* cursor_out = nullptr, bool do_rows = true)
+                 const long long* cursor_in = nullptr, long long* cursor_out = nullptr, bool do_rows = true,
+                 const ypp_probe* probe = nullptr)
 {
     int rc = YPP_OK;
     if (do_sort) {
@@ -123,6 +125,7 @@ int run_sort_nms(const ypp_cfg* cfg, int N, const YppWs& w, int* cand_count, int
         g.det_rows = det_rows; g.row_width = row_width; g.det_capacity = det_capacity; g.det_total = det_total;
         g.img_idx_base = img_idx_base; g.src_rows = src_rows;
         g.cursor_in = cursor_in; g.cursor_out = cursor_out;
+        if (probe && probe->host_word && cursor_out) { g.host_probe = (long long*)probe->host_word; g.probe_seq = probe->seq; }
         rc = ypp_launch_gather(g, st);
     }
     return rc;
@@ -200,7 +203,7 @@ int ypp_nms(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* can
 
 int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, int* cand_count, int* keep_count,
                    float* det_rows, int row_width, int64_t det_capacity, const int64_t* cursor_in, int64_t* cursor_out,
-                   float img_idx_base, void* stream)
+                   float img_idx_base, void* stream, const ypp_probe* probe)
 {
     int rc = check_cfg(cfg);
     if (rc) return rc;
@@ -212,7 +215,7 @@ int ypp_nms_append(const ypp_cfg* cfg, int n_boxes, void* ws, size_t ws_bytes, i
     if (rc) return rc;
     return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr,
                         img_idx_base, nullptr, false, true, (cudaStream_t)stream, (const long long*)cursor_in,
-                        (long long*)cursor_out);
+                        (long long*)cursor_out, true, probe);
 }
 
 int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
@@ -232,7 +235,8 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
 
 int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes, int* cand_count,
                            int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
-                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream)
+                           const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream,
+                           const ypp_probe* probe)
 {
     YppDecodeParams p;
     int rc = build_decode_params(cfg, scales, false, &p);
@@ -246,12 +250,13 @@ int ypp_postprocess_append(const ypp_cfg* cfg, const ypp_scale* scales, void* ws
     if (rc) return rc;
     return run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr,
                         img_idx_base, nullptr, true, true, (cudaStream_t)stream, (const long long*)cursor_in,
-                        (long long*)cursor_out);
+                        (long long*)cursor_out, true, probe);
 }
 
 int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, void* ws, size_t ws_bytes, int stages,
                    int* cand_count, int* keep_count, int* keep_idx, float* det_rows, int row_width, int64_t det_capacity,
-                   int* det_total, const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream)
+                   int* det_total, const int64_t* cursor_in, int64_t* cursor_out, float img_idx_base, void* stream,
+                   const ypp_probe* probe)
 {
     if (stages <= 0 || stages > 15) { ypp_set_error("run_stages: stages=%d is not a mask of YPP_STAGE_*", stages); return YPP_E_BADARG; }
     if ((cursor_in == nullptr) != (cursor_out == nullptr) || (cursor_in && (const int64_t*)cursor_out == cursor_in)) {
@@ -281,7 +286,7 @@ int ypp_run_stages(const ypp_cfg* cfg, const ypp_scale* scales, int n_boxes, voi
     }
     return run_sort_nms(cfg, n_boxes, w, cand_count, keep_count, keep_idx, det_rows, row_width, det_capacity, det_total,
                         img_idx_base, nullptr, (stages & YPP_STAGE_SORT) != 0, (stages & YPP_STAGE_SUPPRESS) != 0, st,
-                        (const long long*)cursor_in, (long long*)cursor_out, (stages & YPP_STAGE_ROWS) != 0);
+                        (const long long*)cursor_in, (long long*)cursor_out, (stages & YPP_STAGE_ROWS) != 0, probe);
 }
 
 // ---- ypp_postprocess without caller scratch --------------------------------------------------------------
@@ -446,15 +451,16 @@ int ypp_target_rows(const float* annot_BT5, int B, int T, float input_size, floa
 {
     if (!annot_BT5 || !out_G7 || !gt_count || B <= 0 || T <= 0) { ypp_set_error("target_rows: bad argument"); return YPP_E_BADARG; }
     return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, gt_count, (long long)B * T, nullptr,
-                                  nullptr, (cudaStream_t)stream);
+                                  nullptr, nullptr, 0u, (cudaStream_t)stream);
 }
 
 int ypp_target_rows_append(const float* annot_BT5, int B, int T, float input_size, float img_idx_base, float* out_G7,
-                           int64_t capacity, int64_t* cursor, void* stream)
+                           int64_t capacity, int64_t* cursor, void* stream, const ypp_probe* probe)
 {
     if (!annot_BT5 || !out_G7 || !cursor || B <= 0 || T <= 0 || capacity < 0) { ypp_set_error("target_rows_append: bad argument"); return YPP_E_BADARG; }
     return ypp_launch_target_rows(annot_BT5, B, T, input_size, img_idx_base, out_G7, nullptr, capacity, (const long long*)cursor,
-                                  (long long*)cursor, (cudaStream_t)stream);
+                                  (long long*)cursor, probe ? (long long*)probe->host_word : nullptr, probe ? probe->seq : 0u,
+                                  (cudaStream_t)stream);
 }
 
 int ypp_detection_ints(const float* rows, int64_t K, int row_width, int mode, const float* scale_xy, int n_img,
@@ -545,6 +551,122 @@ int ypp_map_mean(const float* per_class_nc4, int nc, float* map, void* stream)
 {
     if (!per_class_nc4 || !map || nc <= 0) { ypp_set_error("map_mean: bad argument"); return YPP_E_BADARG; }
     return ypp_launch_map_mean(per_class_nc4, nc, map, (cudaStream_t)stream);
+}
+
+// ---- batches in flight: the stream choreography of a validation loop, in one call per batch ----------------------
+struct ypp_pipeline {
+    int depth, device;
+    cudaStream_t stream[YPP_PIPELINE_MAX_DEPTH];
+    cudaEvent_t ready[YPP_PIPELINE_MAX_DEPTH], done[YPP_PIPELINE_MAX_DEPTH];
+    long long submitted;                      // tickets 0 .. submitted-1 exist; ticket t ran in slot t % depth
+};
+
+int ypp_pipeline_create(int depth, ypp_pipeline** out)
+{
+    if (!out || depth < 1 || depth > YPP_PIPELINE_MAX_DEPTH) { ypp_set_error("pipeline_create: depth must be 1..%d", YPP_PIPELINE_MAX_DEPTH); return YPP_E_BADARG; }
+    ypp_pipeline* p = new (std::nothrow) ypp_pipeline();
+    if (!p) { ypp_set_error("pipeline_create: out of host memory"); return YPP_E_CUDA; }
+    p->depth = depth; p->submitted = 0;
+    cudaError_t e = cudaGetDevice(&p->device);
+    for (int i = 0; i < depth && e == cudaSuccess; ++i) {
+        e = cudaStreamCreateWithFlags(&p->stream[i], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ready[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->done[i], cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) { ypp_set_error("pipeline_create: %s", cudaGetErrorString(e)); delete p; return YPP_E_CUDA; }
+    *out = p;
+    return YPP_OK;
+}
+
+int ypp_pipeline_destroy(ypp_pipeline* p)
+{
+    if (!p) return YPP_OK;
+    for (int i = 0; i < p->depth; ++i) {      // destruction of a busy stream / event is deferred by the runtime
+        cudaStreamDestroy(p->stream[i]); cudaEventDestroy(p->ready[i]); cudaEventDestroy(p->done[i]);
+    }
+    delete p;
+    return YPP_OK;
+}
+
+int ypp_pipeline_next_slot(const ypp_pipeline* p) { return p ? (int)(p->submitted % p->depth) : -1; }
+
+void* ypp_pipeline_stream(const ypp_pipeline* p, int slot) { return (p && slot >= 0 && slot < p->depth) ? (void*)p->stream[slot] : nullptr; }
+
+int ypp_pipeline_submit(ypp_pipeline* pl, const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_t ws_bytes,
+                        int* cand_count, int* keep_count, float* det_rows, int row_width, int64_t det_capacity,
+                        const int64_t* cursor_in, int64_t* cursor_out, const ypp_probe* probe, float img_idx_base,
+                        void* caller_stream, int64_t* ticket)
+{
+    if (!pl) { ypp_set_error("pipeline_submit: null pipeline"); return YPP_E_BADARG; }
+    YppDecodeParams p;
+    int rc = build_decode_params(cfg, scales, false, &p);
+    if (rc) return rc;
+    if (!det_rows || !cursor_in || !cursor_out || cursor_in == cursor_out) {
+        ypp_set_error("pipeline_submit: det_rows and two different cursor words are required"); return YPP_E_BADARG;
+    }
+    if (row_width != 6 && row_width != 7) { ypp_set_error("row_width must be 6 or 7"); return YPP_E_BADARG; }
+    rc = bind_ws(cfg->B, p.N, cfg->nc, ws, ws_bytes, &p.ws);
+    if (rc) return rc;
+    const int slot = (int)(pl->submitted % pl->depth);
+    cudaStream_t st = pl->stream[slot];
+    // the side stream starts behind everything the caller's stream has queued: the heads, the accumulator's state
+    cudaError_t e = cudaEventRecord(pl->ready[slot], (cudaStream_t)caller_stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(st, pl->ready[slot], 0);
+    if (e != cudaSuccess) { ypp_set_error("pipeline_submit: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    rc = ypp_launch_decode_compact(p, cfg->B, st);
+    if (rc) return rc;
+    rc = run_sort_nms(cfg, p.N, p.ws, nullptr, nullptr, nullptr, nullptr, row_width, 0, nullptr, 0.f, nullptr, true, true, st,
+                      nullptr, nullptr, false);
+    if (rc) return rc;
+    // the rows go behind the previous batch's rows: its gather wrote the cursor word this one reads
+    if (pl->submitted > 0 && pl->depth > 1) {
+        e = cudaStreamWaitEvent(st, pl->done[(int)((pl->submitted - 1) % pl->depth)], 0);
+        if (e != cudaSuccess) { ypp_set_error("pipeline_submit: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    }
+    rc = run_sort_nms(cfg, p.N, p.ws, cand_count, keep_count, nullptr, det_rows, row_width, det_capacity, nullptr, img_idx_base,
+                      nullptr, false, false, st, (const long long*)cursor_in, (long long*)cursor_out, true, probe);
+    if (rc) return rc;
+    e = cudaEventRecord(pl->done[slot], st);
+    if (e != cudaSuccess) { ypp_set_error("pipeline_submit: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    if (ticket) *ticket = pl->submitted;
+    pl->submitted += 1;
+    return YPP_OK;
+}
+
+// 1: batch `ticket` has completed (rows, counts and cursor probe included); 0: not known to have
+int ypp_pipeline_query(const ypp_pipeline* p, int64_t ticket)
+{
+    if (!p || ticket < 0 || ticket >= p->submitted) return 0;
+    // the slot's event belongs to the newest ticket of the slot; that one completes after `ticket` (same stream)
+    return cudaEventQuery(p->done[(int)(ticket % p->depth)]) == cudaSuccess ? 1 : 0;
+}
+
+// the HOST waits for batch `ticket` (newer batches stay in flight)
+int ypp_pipeline_wait_ticket(const ypp_pipeline* p, int64_t ticket)
+{
+    if (!p || ticket < 0 || ticket >= p->submitted) { ypp_set_error("pipeline_wait_ticket: no such ticket"); return YPP_E_BADARG; }
+    // a reused slot's event belongs to a newer batch on the same stream: waiting for that one covers `ticket` too
+    const cudaError_t e = cudaEventSynchronize(p->done[(int)(ticket % p->depth)]);
+    if (e != cudaSuccess) { ypp_set_error("pipeline_wait_ticket: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    return YPP_OK;
+}
+
+// `stream` waits ON THE DEVICE for every batch submitted so far (batches complete in order: the last one's event)
+int ypp_pipeline_join(const ypp_pipeline* p, void* stream)
+{
+    if (!p) { ypp_set_error("pipeline_join: null pipeline"); return YPP_E_BADARG; }
+    if (p->submitted == 0) return YPP_OK;
+    const cudaError_t e = cudaStreamWaitEvent((cudaStream_t)stream, p->done[(int)((p->submitted - 1) % p->depth)], 0);
+    if (e != cudaSuccess) { ypp_set_error("pipeline_join: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    return YPP_OK;
+}
+
+int ypp_peek_async(const void* device_src, void* host_dst, size_t bytes, void* stream)
+{
+    if (!device_src || !host_dst || bytes == 0 || bytes > 4096) { ypp_set_error("peek_async: bad argument"); return YPP_E_BADARG; }
+    const cudaError_t e = cudaMemcpyAsync(host_dst, device_src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+    if (e != cudaSuccess) { ypp_set_error("peek_async: %s", cudaGetErrorString(e)); return YPP_E_CUDA; }
+    return YPP_OK;
 }
 
 const char* ypp_last_error(void) { return g_err; }

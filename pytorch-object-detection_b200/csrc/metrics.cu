@@ -21,7 +21,7 @@ namespace {
 __global__ void __launch_bounds__(1024)
 ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float input_size, float img_base,
                        float* __restrict__ out, int* __restrict__ gt_count, long long capacity,
-                       const long long* cursor_in, long long* cursor_out)
+                       const long long* cursor_in, long long* cursor_out, long long* host_probe, unsigned probe_seq)
 {
     __shared__ int warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -63,6 +63,7 @@ ypp_target_rows_kernel(const float* __restrict__ annot, int B, int T, float inpu
     if (tid == 0) {
         if (gt_count) *gt_count = running;
         if (cursor_out) *cursor_out = base + running;       // one block: may be the word cursor_in points at
+        if (host_probe) *(volatile long long*)host_probe = ((base + running) << 24) | (long long)(probe_seq & 0xffffffu);
     }
 }
 
@@ -701,14 +702,14 @@ ypp_confusion_kernel(const float* __restrict__ det, const int* __restrict__ det_
 
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
                            float* out, int* gt_count, long long capacity, const long long* cursor_in,
-                           long long* cursor_out, cudaStream_t st)
+                           long long* cursor_out, long long* host_probe, unsigned probe_seq, cudaStream_t st)
 {
     if (cursor_in)      // append mode: the buffers are the accumulator's own, nothing of the kernel before is read
         ypp_launch_chain(0, ypp_target_rows_kernel, dim3(1), dim3(1024), 0, st, annot, B, T, input_size, img_base, out, gt_count,
-                         capacity, cursor_in, cursor_out);
+                         capacity, cursor_in, cursor_out, host_probe, probe_seq);
     else
         ypp_target_rows_kernel<<<1, 1024, 0, st>>>(annot, B, T, input_size, img_base, out, gt_count, capacity, cursor_in,
-                                                   cursor_out);
+                                                   cursor_out, host_probe, probe_seq);
     ypp_count_launch(1);
     return ypp_check_launch("target_rows");
 }

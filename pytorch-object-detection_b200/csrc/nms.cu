@@ -1009,6 +1009,8 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         const long long rows = img_rows + min(p.ws.keep_count[b], cap);
         if (p.det_total) *p.det_total = (int)rows;
         if (p.cursor_out) *p.cursor_out = base + rows;               // never the word cursor_in points at
+        // the host's view of the cursor: one 8-byte store into pinned memory, count and sequence number together
+        if (p.host_probe) *(volatile long long*)p.host_probe = ((base + rows) << 24) | (long long)(p.probe_seq & 0xffffffu);
     }
     if (r_begin >= n || pre_rows >= cap) return;
     const u64* keys = p.ws.skeys + (size_t)b * N;

@@ -63,6 +63,8 @@ struct YppGatherParams {
     int xyxy_out;            // rows carry x1,y1,x2,y2 instead of cx,cy,w,h
     const long long* cursor_in;   // optional: rows already in det_rows; this call's rows go after them
     long long* cursor_out;        // optional: *cursor_in + rows of this call (a different word than cursor_in)
+    long long* host_probe;        // optional, pinned host memory (device-accessible): receives (*cursor_out << 24) | probe_seq
+    unsigned probe_seq;
 };
 
 int ypp_launch_decode_compact(const YppDecodeParams& p, int B, cudaStream_t st);
@@ -84,7 +86,7 @@ int ypp_launch_confusion(const float* det, const int* det_off, const float* lab,
                          float conf, float thr, int* bestg, float* bestiou, unsigned long long* matrix, cudaStream_t st);
 int ypp_launch_target_rows(const float* annot, int B, int T, float input_size, float img_base,
                            float* out, int* gt_count, long long capacity, const long long* cursor_in,
-                           long long* cursor_out, cudaStream_t st);
+                           long long* cursor_out, long long* host_probe, unsigned probe_seq, cudaStream_t st);
 int ypp_launch_box_iou(const float* a, int N, const float* b, int M, float* out, cudaStream_t st);
 int ypp_launch_bbox_iou(const float* a, int na, const float* b, int nb, int xywh, int mode, float eps, float one_eps,
                         float* out, cudaStream_t st);

@@ -49,6 +49,10 @@ class YppUltraCfg(ctypes.Structure):
                 ("union_mode", ctypes.c_int)]
 
 
+class YppProbe(ctypes.Structure):
+    _fields_ = [("host_word", ctypes.c_void_p), ("seq", ctypes.c_uint32)]
+
+
 class YppHeadSrc(ctypes.Structure):
     _fields_ = [("feature", ctypes.c_void_p), ("weight", ctypes.c_void_p), ("cin", ctypes.c_int),
                 ("head_out", ctypes.c_void_p)]
@@ -60,7 +64,8 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_rows_compact", "ypp_sort_segments", "ypp_nms", "ypp_postprocess", "ypp_nms_rows",
            "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match", "ypp_map_flags", "ypp_map_ap_from_flags", "ypp_map_mean",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
-           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_postprocess_static", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_postprocess_static", "ypp_peek_async", "ypp_pipeline_create", "ypp_pipeline_destroy", "ypp_pipeline_next_slot", "ypp_pipeline_stream",
+           "ypp_pipeline_submit", "ypp_pipeline_query", "ypp_pipeline_wait_ticket", "ypp_pipeline_join", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -100,7 +105,7 @@ def lib():
             "Build it with `python -c \"import __graft_entry__ as g; g.build()\"`." % LIB_PATH)
     L = ctypes.CDLL(LIB_PATH)
     vp, ci, cf, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_int64
-    cfgp, scp = ctypes.POINTER(YppCfg), ctypes.POINTER(YppScale)
+    cfgp, scp, prp = ctypes.POINTER(YppCfg), ctypes.POINTER(YppScale), ctypes.POINTER(YppProbe)
     L.ypp_workspace_bytes.argtypes = [ci, ci, ci]
     L.ypp_workspace_bytes.restype = ctypes.c_size_t
     L.ypp_effective_iou_thr.argtypes = [ctypes.c_double, ci]
@@ -116,12 +121,26 @@ def lib():
     L.ypp_head_postprocess.argtypes = [cfgp, scp, hsp, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_nms_rows.argtypes = [cfgp, vp, ci, vp, ctypes.c_size_t, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_target_rows.argtypes = [vp, ci, ci, cf, cf, vp, vp, vp]
-    L.ypp_target_rows_append.argtypes = [vp, ci, ci, cf, cf, vp, i64, vp, vp]
-    L.ypp_postprocess_append.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
-    L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp]
-    L.ypp_run_stages.argtypes = [cfgp, scp, ci, vp, ctypes.c_size_t, ci, vp, vp, vp, vp, ci, i64, vp, vp, vp, cf, vp]
+    L.ypp_target_rows_append.argtypes = [vp, ci, ci, cf, cf, vp, i64, vp, vp, prp]
+    L.ypp_postprocess_append.argtypes = [cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp, prp]
+    L.ypp_nms_append.argtypes = [cfgp, ci, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, cf, vp, prp]
+    L.ypp_run_stages.argtypes = [cfgp, scp, ci, vp, ctypes.c_size_t, ci, vp, vp, vp, vp, ci, i64, vp, vp, vp, cf, vp, prp]
     L.ypp_postprocess_static.argtypes = [cfgp, scp, vp, vp, vp, vp, ci, i64, vp, cf, vp]
     L.ypp_postprocess_static.restype = ci
+    L.ypp_pipeline_create.argtypes = [ci, ctypes.POINTER(vp)]
+    L.ypp_pipeline_destroy.argtypes = [vp]
+    L.ypp_pipeline_next_slot.argtypes = [vp]
+    L.ypp_pipeline_stream.argtypes = [vp, ci]
+    L.ypp_pipeline_stream.restype = vp
+    L.ypp_pipeline_submit.argtypes = [vp, cfgp, scp, vp, ctypes.c_size_t, vp, vp, vp, ci, i64, vp, vp, prp, cf, vp, ctypes.POINTER(i64)]
+    L.ypp_pipeline_query.argtypes = [vp, i64]
+    L.ypp_pipeline_wait_ticket.argtypes = [vp, i64]
+    L.ypp_pipeline_join.argtypes = [vp, vp]
+    for name in ("ypp_pipeline_create", "ypp_pipeline_destroy", "ypp_pipeline_next_slot", "ypp_pipeline_submit", "ypp_pipeline_query",
+                 "ypp_pipeline_wait_ticket", "ypp_pipeline_join"):
+        getattr(L, name).restype = ci
+    L.ypp_peek_async.argtypes = [vp, vp, ctypes.c_size_t, vp]
+    L.ypp_peek_async.restype = ci
     L.ypp_box_iou.argtypes = [vp, ci, vp, ci, vp, vp]
     L.ypp_bbox_iou.argtypes = [vp, ci, vp, ci, ci, ci, ctypes.c_double, vp, vp]
     L.ypp_detection_ints.argtypes = [vp, i64, ci, ci, vp, ci, cf, vp, vp]

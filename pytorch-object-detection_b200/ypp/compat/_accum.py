@@ -70,6 +70,11 @@ class MeanAveragePrecisionBase(LiveParams):
                                     kind=self._kind, **self._modes)
 
     def reset_states(self):
+        # validation epochs repeat: the next epoch's accumulators start at the size this one ended with (an upper
+        # bound known without reading the device), so they are allocated once instead of doubling their way up
+        prev = self.__dict__.get("_pred"), self.__dict__.get("_true")
+        hints = self.__dict__.get("_hints", (0, 0))
+        self._hints = tuple(max(h, min(a.bound, a.buf.shape[0]) if a is not None and a.buf is not None else 0) for h, a in zip(hints, prev))
         self._true = None          # RowAccumulators, made on the first batch's device
         self._pred = None
         self.img_idx = 0
@@ -90,8 +95,8 @@ class MeanAveragePrecisionBase(LiveParams):
     def _update(self, y_true, heads, weights=None):
         dev = heads[0].device
         if self._pred is None:
-            self._pred = engine.RowAccumulator(dev, self.sync_every)
-            self._true = engine.RowAccumulator(dev, 64 * self.sync_every)
+            self._pred = engine.RowAccumulator(dev, self.sync_every, self._hints[0])
+            self._true = engine.RowAccumulator(dev, 64 * self.sync_every, self._hints[1])
         # both appends happen on the device behind the accumulators' cursors: no host read per batch
         self._pp.accumulate(self._pred, heads, weights, img_idx_base=self.img_idx)
         engine.target_rows_append(self._true, y_true.to(dev, non_blocking=True), self.input_size, self.img_idx)

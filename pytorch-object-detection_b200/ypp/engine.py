@@ -113,31 +113,49 @@ class PostResult:
 
 class RowAccumulator:
     """[n, 7] rows growing on the device with the row count kept ON the device: what
-    `self.all_pred_boxes_variable = torch.cat([...])` (utils/yolov3_utils.py:139-146) builds, without a host
-    read of the count per batch.  The kernels append behind a device cursor (ypp_nms_append /
-    ypp_target_rows_append); the host only tracks an upper bound of the rows (worst case per append) and reads
-    the cursor when that bound reaches the capacity - once per `sync_every` appends at most.
+    `self.all_pred_boxes_variable = torch.cat([...])` (utils/yolov3_utils.py:139-146) builds, without the host ever
+    waiting for the device inside the loop.  The kernels append behind a device cursor (ypp_nms_append /
+    ypp_target_rows_append).  The host needs the count only to size the buffer, and an upper bound does for that:
+      - the kernel that advances the cursor also stores (count << 24 | append number) into ONE pinned host word
+        (ypp_probe): no copy, no event, nothing between two chains on the stream;
+      - bound = the newest count that has arrived + the worst case of the appends issued after that one;
+      - when the bound does not fit, the buffer grows by copying `bound` rows on the device (rows past the real count
+        are garbage nobody reads) - a wait on the GPU for the appends in flight, none on the host.  Only if the host
+        has run more than STALE appends ahead of the device does it first wait for the append STALE back (newer
+        batches stay queued, nothing drains): a bound that stale would grow the buffer for rows that never come.
+    `sync_every` sizes the growth steps (worst cases booked per step).  Only count() / view() read the cursor itself.
 
-    Appends may be queued on side streams (PostProcessor.accumulate with several batches in flight): `last`
-    is then the event behind the most recent append, and everything that reads or moves the rows on the
-    current stream (count, growth, view) waits for it first."""
+    Appends may be queued on side streams (PostProcessor.accumulate with several batches in flight): everything
+    that reads or moves the rows on the current stream (count, growth, view) first waits, on the device, for them."""
 
-    def __init__(self, device, sync_every=16):
+    STALE = 6
+    RING = 64
+    _SEQ = 0xFFFFFF
+
+    def __init__(self, device, sync_every=16, capacity_hint=0):
         self.device = torch.device(device)
         self.sync_every = max(1, int(sync_every))
+        self.capacity_hint = int(capacity_hint)     # rows the previous epoch ended with: the first allocation covers them
         self.cur = torch.zeros(2, dtype=torch.int64, device=self.device)   # two words: see ypp_nms_append
         self.k = 0                                                         # appends so far: the live word is k & 1
         self.buf = None
         self.bound = 0                                                     # rows <= bound, known without a sync
-        self.syncs = 0
-        self.last = None                                                   # torch.cuda.Event or None
+        self.syncs = 0                                                     # host reads of the cursor (count / view)
+        self._ring = None                                                  # the pipeline the newest append went through
         self._streams = set()                                              # side streams that were told about buf / cur
+        self._host = torch.zeros(1, dtype=torch.int64).pin_memory()        # the probe word
+        self._host_np = self._host.numpy()
+        self._probe = _lib.YppProbe(self._host.data_ptr(), 0)
+        self._probe_ref = ctypes.byref(self._probe)
+        self._seq = 0                                                      # appends issued (probe sequence numbers start at 1)
+        self._booked = 0                                                   # sum of the worst cases of every append so far
+        self._booked_at = [0] * self.RING                                  # ... as it was when append seq was issued
 
     def join(self):
-        """The current stream waits for every append queued so far (they complete in order: one event)."""
-        if self.last is not None:
-            torch.cuda.current_stream(self.device).wait_event(self.last)
-            self.last = None
+        """The current stream waits (on the device) for every append queued on side streams so far."""
+        if self._ring is not None:
+            self._ring.join(_stream())
+            self._ring = None
 
     def used_by(self, stream):
         """A side stream is about to append: the caching allocator must not hand the buffers to anyone else
@@ -149,6 +167,39 @@ class RowAccumulator:
             if self.buf is not None:
                 self.buf.record_stream(stream)
 
+    def next_probe(self, ring=None):
+        """The ypp_probe* for the append about to be issued (after reserve()); ring: the pipeline it goes through."""
+        self._seq += 1
+        self._booked_at[self._seq % self.RING] = self._booked
+        self._probe.seq = self._seq & self._SEQ
+        if ring is not None:
+            self._ring = ring
+        return self._probe_ref
+
+    def _arrived(self):
+        """(append number, rows after it) of the newest append whose probe word has arrived; (0, 0) before the first."""
+        v = int(self._host_np[0])
+        low = v & self._SEQ
+        seq = self._seq - ((self._seq - low) & self._SEQ)      # undo the 24-bit wrap
+        return seq, v >> 24
+
+    def _refresh(self):
+        seq, n = self._arrived()
+        if seq > 0 and self._seq - seq < self.RING:
+            b = n + (self._booked - self._booked_at[seq % self.RING])
+            if b < self.bound:
+                self.bound = b
+
+    def _wait_for(self, seq, timeout_s=30.0):
+        """The host waits until append `seq` has reported (the device is busy with it or with earlier work)."""
+        import time
+        t0 = time.perf_counter()
+        spins = 0
+        while self._arrived()[0] < seq:
+            spins += 1
+            if spins & 1023 == 0 and time.perf_counter() - t0 > timeout_s:
+                raise _lib.YppError("RowAccumulator: append %d did not report within %.0f s (device error?)" % (seq, timeout_s))
+
     def count(self) -> int:
         self.join()
         self.syncs += 1
@@ -157,16 +208,25 @@ class RowAccumulator:
         return n
 
     def reserve(self, worst: int):
-        """Room for `worst` more rows; reads the cursor only when the bound says they might not fit."""
+        """Room for `worst` more rows.  Never drains the device."""
         cap = 0 if self.buf is None else self.buf.shape[0]
         if self.bound + worst > cap:
-            n = self.count() if self.buf is not None else 0
-            if n + worst > cap:
-                nb = torch.empty((max(n + worst * self.sync_every, 2 * cap, 1024), 7), dtype=torch.float32, device=self.device)
-                if n:
+            self._refresh()
+            if self.bound + worst > cap and self._seq > self.STALE:
+                self._wait_for(self._seq - self.STALE)
+                self._refresh()
+            if self.bound + worst > cap:
+                want = max(self.bound + worst * self.sync_every, 2 * cap, 1024)
+                if self.buf is None and self.capacity_hint:
+                    want = max(want, self.capacity_hint + self.capacity_hint // 8 + worst * self.STALE)
+                nb = torch.empty((want, 7), dtype=torch.float32, device=self.device)
+                if self.buf is not None and self.bound:
+                    self.join()                                    # the appends in flight wrote (and sized) the old buffer
+                    n = min(self.bound, cap)
                     nb[:n] = self.buf[:n]
                 self.buf = nb
         self.bound += worst
+        self._booked += worst
 
     def cursors(self, in_place=False):
         """(pointer to the live word, pointer to the word the next append writes)."""
@@ -195,16 +255,56 @@ class _Plan:
         self.arr, self.B, self.n_boxes, self.cfg, self.nbytes, self.dev = arr, B, n_boxes, cfg, nbytes, dev
 
 
-class _Slot:
-    """One batch in flight of PostProcessor.accumulate: a side stream with its own workspace and count outputs."""
+_pipeline_pool = {}      # (device index, depth) -> [(handle, streams)] not in use
 
-    def __init__(self, dev):
-        self.stream = torch.cuda.Stream(device=dev)
-        self.raw = ctypes.c_void_p(self.stream.cuda_stream)
-        self.ready = torch.cuda.Event()          # recorded on the caller's stream: inputs and accumulator are ready
-        self.done = torch.cuda.Event()           # recorded on the side stream behind the row gather
-        self.ws = None
-        self.sc = None
+
+class _Ring:
+    """The batches in flight of one PostProcessor on one device: a ypp_pipeline (side streams + events, owned by the
+    library) and, per slot, the workspace and count outputs this side owns.  The caching allocator remembers every
+    stream a tensor was record_stream()ed on and touches it when the tensor is freed, so a pipeline's streams must
+    outlive every tensor they have seen: pipelines are never destroyed, a ring that goes away hands its pipeline back
+    to a per-(device, depth) pool and the next ring takes it over (their batches simply queue behind)."""
+
+    def __init__(self, dev, depth):
+        self.dev, self.depth = dev, depth
+        self.key = (dev.index if dev.index is not None else _cur_dev(), depth)
+        free = _pipeline_pool.setdefault(self.key, [])
+        if free:
+            self.handle, self.streams = free.pop()
+        else:
+            h = ctypes.c_void_p()
+            with _on(dev):
+                check(lib().ypp_pipeline_create(depth, ctypes.byref(h)))
+            L = lib()
+            self.handle = h
+            self.streams = [torch.cuda.ExternalStream(L.ypp_pipeline_stream(h, i), device=dev) for i in range(depth)]
+        self.ws = [None] * depth
+        self.sc = [None] * depth
+
+    def __del__(self):
+        try:
+            _pipeline_pool[self.key].append((self.handle, self.streams))
+        except Exception:
+            pass
+
+    def slot(self, B, nbytes):
+        i = lib().ypp_pipeline_next_slot(self.handle)
+        st = self.streams[i]
+        if self.ws[i] is None or self.ws[i].numel() < nbytes:
+            self.ws[i] = torch.empty(int(nbytes), dtype=torch.uint8, device=self.dev)
+            self.ws[i].record_stream(st)
+        sc = self.sc[i]
+        if sc is None or sc.keep_count.numel() != B:
+            z = torch.empty
+            sc = PostResult(z((0, 7), device=self.dev), z(1, dtype=torch.int32, device=self.dev), z(B, dtype=torch.int32, device=self.dev),
+                            z(B, dtype=torch.int32, device=self.dev), None, 0)
+            sc.keep_count.record_stream(st)
+            sc.cand_count.record_stream(st)
+            self.sc[i] = sc
+        return i, st, self.ws[i], sc
+
+    def join(self, raw_stream):
+        check(lib().ypp_pipeline_join(self.handle, raw_stream))
 
 
 class PostProcessor:
@@ -442,30 +542,21 @@ class PostProcessor:
             d = 3 if B * n_boxes >= 32768 else 1
         return max(1, int(d))
 
-    def _slot(self, dev, depth, B, nbytes):
+    def _ring(self, dev, depth):
         ring = self._rings.get(dev.index)
-        if ring is None or len(ring) != depth:
-            self.join()
-            ring = [_Slot(dev) for _ in range(depth)]
+        if ring is None or ring.depth != depth:
+            if ring is not None:
+                with _on(dev):
+                    ring.join(_stream())
+            ring = _Ring(dev, depth)
             self._rings[dev.index] = ring
-        sl = ring[self._batches % depth]
-        if sl.ws is None or sl.ws.numel() < nbytes:
-            sl.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
-            sl.ws.record_stream(sl.stream)
-        if sl.sc is None or sl.sc.keep_count.numel() != B:
-            z = torch.empty
-            sl.sc = PostResult(z((0, 7), device=dev), z(1, dtype=torch.int32, device=dev), z(B, dtype=torch.int32, device=dev),
-                               z(B, dtype=torch.int32, device=dev), None, 0)
-            sl.sc.keep_count.record_stream(sl.stream)
-            sl.sc.cand_count.record_stream(sl.stream)
-        return sl
+        return ring
 
     def join(self):
-        """The current stream of every device this processor has batches in flight on waits for them."""
+        """The current stream of every device this processor has batches in flight on waits for them (on the device)."""
         for idx, ring in self._rings.items():
-            cur = torch.cuda.current_stream(idx)
-            for sl in ring:
-                cur.wait_stream(sl.stream)
+            with _on(ring.dev):
+                ring.join(_stream())
 
     def accumulate(self, acc: RowAccumulator, heads: Sequence[torch.Tensor], weights=None, img_idx_base=0):
         """The chain with the gather appending to `acc` (7-column rows) instead of filling a per-call buffer:
@@ -498,7 +589,7 @@ class PostProcessor:
                 acc.reserve(B * n_boxes)
                 cin, cout = acc.cursors()
                 check(L.ypp_nms_append(ctypes.byref(cfg), n_boxes, _ptr(ws), ws.numel(), _ptr(sc.cand_count), _ptr(sc.keep_count),
-                                       _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream()))
+                                       _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, float(img_idx_base), _stream(), acc.next_probe()))
             return sc
         plan, heads = self._plan(heads)
         dev, B, n_boxes = plan.dev, plan.B, plan.n_boxes
@@ -519,30 +610,20 @@ class PostProcessor:
                 cin, cout = acc.cursors()
                 check(L.ypp_postprocess_append(ctypes.byref(plan.cfg), plan.arr, _ptr(ws), ws.numel(), _ptr(sc.cand_count),
                                                _ptr(sc.keep_count), _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout,
-                                               float(img_idx_base), _stream()))
+                                               float(img_idx_base), _stream(), acc.next_probe()))
                 return sc
-            sl = self._slot(dev, depth, B, plan.nbytes)
-            self._batches += 1
-            acc.reserve(B * n_boxes)                 # may read the cursor / move the rows: on the current stream, joined
+            ring = self._ring(dev, depth)
+            i, st, ws, sc = ring.slot(B, plan.nbytes)
+            acc.reserve(B * n_boxes)                 # may move the rows: on the current stream, behind the batches in flight
             cin, cout = acc.cursors()
-            acc.used_by(sl.stream)
+            acc.used_by(st)
             for h in heads:                          # the allocator must not reuse a head the side stream still reads
-                h.record_stream(sl.stream)
-            cur = torch.cuda.current_stream(dev)
-            sl.ready.record(cur)
-            sl.stream.wait_event(sl.ready)
-            cfgp, wsp, wsn = ctypes.byref(plan.cfg), _ptr(sl.ws), sl.ws.numel()
-            check(L.ypp_run_stages(cfgp, plan.arr, n_boxes, wsp, wsn, _lib.STAGE_DECODE | _lib.STAGE_SORT | _lib.STAGE_SUPPRESS,
-                                   None, None, None, None, 7, 0, None, None, None, 0.0, sl.raw))
-            if acc.last is not None:
-                sl.stream.wait_event(acc.last)       # the previous gather wrote the cursor word this one reads
-            check(L.ypp_run_stages(cfgp, plan.arr, n_boxes, wsp, wsn, _lib.STAGE_ROWS, _ptr(sl.sc.cand_count),
-                                   _ptr(sl.sc.keep_count), None, _ptr(acc.buf), 7, acc.buf.shape[0], None, cin, cout,
-                                   float(img_idx_base), sl.raw))
-            sl.done.record(sl.stream)
-            acc.last = sl.done
-        sl.sc.n_boxes = n_boxes
-        return sl.sc
+                h.record_stream(st)
+            check(L.ypp_pipeline_submit(ring.handle, ctypes.byref(plan.cfg), plan.arr, _ptr(ws), ws.numel(), _ptr(sc.cand_count),
+                                        _ptr(sc.keep_count), _ptr(acc.buf), 7, acc.buf.shape[0], cin, cout, acc.next_probe(ring),
+                                        float(img_idx_base), _stream(), None))
+        sc.n_boxes = n_boxes
+        return sc
 
     def graphed(self, heads: Sequence[torch.Tensor], img_idx_base=0, row_width=7, want_keep_idx=False,
                 repeat=1, stages=None, ws: Optional[torch.Tensor] = None):
@@ -589,7 +670,7 @@ class PostProcessor:
                 ws = self._ws.get(L.ypp_workspace_bytes(B, n_boxes, self.num_classes), dev)
             check(L.ypp_run_stages(ctypes.byref(cfg), arr, n_boxes, _ptr(ws), ws.numel(), mask, _ptr(res.cand_count),
                                    _ptr(res.keep_count), _ptr(res.keep_idx), _ptr(res.det_rows), res.det_rows.shape[1],
-                                   res.det_rows.shape[0], _ptr(res.det_total), None, None, float(img_idx_base), _stream()))
+                                   res.det_rows.shape[0], _ptr(res.det_total), None, None, float(img_idx_base), _stream(), None))
         return res
 
     def nms_rows(self, rows: torch.Tensor, img_idx_base=0, row_width=6, want_keep_idx=False) -> PostResult:
@@ -645,13 +726,15 @@ def target_rows_append(acc: RowAccumulator, annot: torch.Tensor, input_size, img
         raise ValueError("annot must be [B, max_num_annots, 5]")
     if not annot.is_cuda or annot.device != acc.device:
         raise ValueError("annot must be a CUDA tensor on the accumulator's device")
-    annot = annot.to(torch.float32).contiguous()
+    if annot.dtype != torch.float32 or not annot.is_contiguous():
+        annot = annot.to(torch.float32).contiguous()
     B, T, _ = annot.shape
     with _on(annot.device):
+        acc.join()
         acc.reserve(B * T)
         cin, _ = acc.cursors(in_place=True)
         check(lib().ypp_target_rows_append(_ptr(annot), B, T, float(input_size), float(img_idx_base), _ptr(acc.buf),
-                                           acc.buf.shape[0], cin, _stream()))
+                                           acc.buf.shape[0], cin, _stream(), acc.next_probe()))
 
 
 def box_iou(box1: torch.Tensor, box2: torch.Tensor) -> torch.Tensor:

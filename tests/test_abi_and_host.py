@@ -127,17 +127,17 @@ def test_append_entry_points_check_their_arguments_before_any_launch():
     L = _lib.lib()
     cfg = _lib.YppCfg(20, 2, 1, 0.25, 0.45, 0, 3, 1)
     c = ctypes.byref(cfg)
-    assert L.ypp_nms_append(c, 507, None, 0, None, None, None, 7, 0, 64, 72, 0.0, None) == -1       # no det_rows
-    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 64, 0.0, None) == -1       # one word twice
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, None, 7, 0, 64, 72, 0.0, None, None) == -1       # no det_rows
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 64, 0.0, None, None) == -1       # one word twice
     assert b"cursor" in L.ypp_last_error()
-    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 72, 0.0, None) == -3       # YPP_E_WORKSPACE
+    assert L.ypp_nms_append(c, 507, None, 0, None, None, 1024, 7, 0, 64, 72, 0.0, None, None) == -3       # YPP_E_WORKSPACE
     sc = (_lib.YppScale * 1)()
     sc[0].head, sc[0].A, sc[0].H, sc[0].W = 4096, 3, 13, 13
     sc[0].stride_w = sc[0].stride_h = 32.0
-    assert L.ypp_postprocess_append(c, sc, None, 0, None, None, 1024, 7, 0, 64, 64, 0.0, None) == -1   # one word twice
-    assert L.ypp_postprocess_append(c, sc, None, 0, None, None, 1024, 7, 0, 64, 72, 0.0, None) == -3   # YPP_E_WORKSPACE
-    assert L.ypp_target_rows_append(1024, 2, 8, 416.0, 0.0, 2048, 16, None, None) == -1             # no cursor
-    assert L.ypp_target_rows_append(1024, 0, 8, 416.0, 0.0, 2048, 16, 64, None) == -1               # B = 0
+    assert L.ypp_postprocess_append(c, sc, None, 0, None, None, 1024, 7, 0, 64, 64, 0.0, None, None) == -1   # one word twice
+    assert L.ypp_postprocess_append(c, sc, None, 0, None, None, 1024, 7, 0, 64, 72, 0.0, None, None) == -3   # YPP_E_WORKSPACE
+    assert L.ypp_target_rows_append(1024, 2, 8, 416.0, 0.0, 2048, 16, None, None, None) == -1             # no cursor
+    assert L.ypp_target_rows_append(1024, 0, 8, 416.0, 0.0, 2048, 16, 64, None, None) == -1               # B = 0
 
 
 def test_oracle_head_conv_is_the_reference_layer(oracle):

@@ -62,12 +62,15 @@ def test_overflow_drops_rows_but_counts_them(cuda):
     guard = torch.full((cap + 64, 7), -7.0, device=cuda)
     cur = torch.tensor([3, 0], dtype=torch.int64, device=cuda)         # 3 rows "already there"
     L = _lib.lib()
+    word = torch.zeros(1, dtype=torch.int64).pin_memory()
+    probe = _lib.YppProbe(word.data_ptr(), 77)
     cfg = pp._cfg(4, 3)
     ws = pp.workspace(L.ypp_workspace_bytes(4, sc.n_boxes, 20), cuda)
     _lib.check(L.ypp_nms_append(ctypes.byref(cfg), sc.n_boxes, ws.data_ptr(), ws.numel(), None, sc.keep_count.data_ptr(),
                                 guard.data_ptr(), 7, cap, cur.data_ptr(), cur.data_ptr() + 8, 0.0,
-                                torch.cuda.current_stream().cuda_stream))
+                                torch.cuda.current_stream().cuda_stream, ctypes.byref(probe)))
     assert cur.tolist() == [3, 3 + n]
+    assert int(word[0]) == ((3 + n) << 24) | 77        # the kernel reported the cursor and the append number to pinned memory
     assert torch.equal(guard[3:cap], full[: cap - 3])
     assert bool((guard[:3] == -7).all()) and bool((guard[cap:] == -7).all())
 

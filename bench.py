@@ -238,7 +238,9 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     numa = _bind_to_gpu_numa_node(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a rank that dies or disagrees must not cost ten minutes of eight GPUs: collectives give up after two
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
     if not os.path.exists(_lib.LIB_PATH):       # a snapshot taken before __graft_entry__.build(): compile, never fall back
         if local == 0:
             _lib.build()
@@ -300,6 +302,7 @@ def run_ours(args):
         """fn() = one window of exactly K steps.  Repeated until >= min_total_ms of device time are covered (a single
         window of 40 steps is 3 ms: its run-to-run noise is as large as the effects being reported); every window is
         bracketed by the barrier + synchronize and timed with CUDA events, max over ranks.  Returns the list of ms."""
+        est_ms = max_over_ranks(est_ms)             # every rank must run the SAME number of windows (each holds a barrier)
         reps = int(min(hi, max(lo, -(-min_total_ms // max(est_ms, 1e-3)))))
         out = []
         for _ in range(reps):

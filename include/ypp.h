@@ -321,7 +321,9 @@ int ypp_confusion_update(const float* det_K6, const int* det_off, const float* l
 size_t ypp_map_workspace_bytes(int64_t G, int64_t K, int nc);
 
 /* mean_average_precision / metrics_per_class, utils/yolo_utils.py:351-456,458-574.
- *   gt [G,7], det [K,7] rows img,cx,cy,w,h,score,cls (any order)
+ *   gt [G,7], det [K,7] rows img,cx,cy,w,h,score,cls.  Detections in any order.  Ground truths in any order too, but
+ *   rows sorted by image (what the accumulators above produce, one process or gathered rank after rank) are found by
+ *   binary search; any other order is detected on the device and handled by a scan of all G rows per detection
  *   tp [K] out (optional): 1 TP, 0 FP, 255 class without ground truth
  *   per_class [nc,4] out (optional): AP, TP, FP, FN
  *   map [1] out: mean AP over all nc classes */

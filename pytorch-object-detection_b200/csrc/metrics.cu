@@ -158,30 +158,40 @@ rs_hist_kernel(const u64* __restrict__ keys, long long n, const long long* __res
     counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// exclusive scan over the digit-major [256][nblocks] table, one CTA
+// exclusive scan over the digit-major [256][nblocks] table, one CTA: warp w owns a contiguous 1/32 of the table and
+// walks it 32 entries at a time (coalesced; the loads do not depend on the running carry, only the shuffles do), after
+// one reduction pass has told it where its part starts (the chunked version - a block scan with three barriers per
+// 1024 entries - took 44 us on 27 k entries, 220 us per sort)
 __global__ void __launch_bounds__(1024)
 rs_scan_kernel(int* __restrict__ counts, long long total)
 {
     __shared__ int warp_tot[32];
-    __shared__ int carry;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) carry = 0;
+    const long long S = ((total + 31) / 32 + 31) / 32 * 32;                 // entries per warp, a multiple of 32
+    const long long a = min(total, (long long)warp * S), b = min(total, a + S);
+    int sum = 0;
+#pragma unroll 8
+    for (long long i = a + lane; i < b; i += 32) sum += counts[i];
+    sum = __reduce_add_sync(YPP_FULL_MASK, sum);
+    if (lane == 0) warp_tot[warp] = sum;
     __syncthreads();
-    for (long long i0 = 0; i0 < total; i0 += 1024) {
-        const long long i = i0 + tid;
-        const int v = i < total ? counts[i] : 0;
-        int inc = v;
+    int carry = 0;
+    for (int w = 0; w < warp; ++w) carry += warp_tot[w];
+    // 1024 entries per round: all 32 loads of a lane are issued before the first shuffle (one L2 round trip per round,
+    // not per 32 entries)
+    for (long long base = a; base < b; base += 1024) {
+        int v[32];
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
-        if (lane == 31) warp_tot[warp] = inc;
-        __syncthreads();
-        int before = 0, tot = 0;
-        for (int w = 0; w < 32; ++w) { const int t = warp_tot[w]; if (w < warp) before += t; tot += t; }
-        const int c = carry;
-        if (i < total) counts[i] = c + before + inc - v;
-        __syncthreads();
-        if (tid == 0) carry = c + tot;
-        __syncthreads();
+        for (int k = 0; k < 32; ++k) { const long long i = base + k * 32 + lane; v[k] = i < b ? counts[i] : 0; }
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+            const long long i = base + k * 32 + lane;
+            int inc = v[k];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
+            if (i < b) counts[i] = carry + inc - v[k];
+            carry += __shfl_sync(YPP_FULL_MASK, inc, 31);
+        }
     }
 }
 
@@ -243,42 +253,11 @@ int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st, const 
 }
 
 // ------------------------------------------------------------------ matching
-#define MAP_IMG_BITS 24
 
 // class ids that are not integers in [0, nc) can never equal a loop class c (:370-375): marker nc
 __device__ __forceinline__ u32 map_cls(float cf, int nc)
 {
     return (cf >= 0.0f && cf < (float)nc && (float)(int)cf == cf) ? (u32)cf : (u32)nc;
-}
-
-__global__ void map_gt_keys_kernel(const float* __restrict__ gt, long long G, int nc, u64* __restrict__ keys, u32* __restrict__ vals,
-                                   int* __restrict__ first_rank)
-{
-    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= G) return;
-    const u32 img = (u32)gt[g * 7 + 0] & ((1u << MAP_IMG_BITS) - 1u);
-    const u32 cls = map_cls(gt[g * 7 + 6], nc);
-    keys[g] = ((u64)cls << MAP_IMG_BITS) | img;
-    vals[g] = (u32)g;
-    first_rank[g] = INT_MAX;
-}
-
-__global__ void map_det_keys_kernel(const float* __restrict__ det, long long K, int nc, u64* __restrict__ keys, u32* __restrict__ vals,
-                                    unsigned char* __restrict__ tp_out)
-{
-    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= K) return;
-    const u32 cls = map_cls(det[d * 7 + 6], nc);
-    keys[d] = ((u64)cls << 32) | (u64)(~ypp_enc(det[d * 7 + 5]));
-    vals[d] = (u32)d;
-    if (tp_out) tp_out[d] = 255;
-}
-
-__device__ __forceinline__ long long lower_bound_u64(const u64* a, long long n, u64 key)
-{
-    long long lo = 0, hi = n;
-    while (lo < hi) { const long long mid = (lo + hi) >> 1; if (a[mid] < key) lo = mid + 1; else hi = mid; }
-    return lo;
 }
 
 // bbox_iou IoU branch on cxcywh (abs areas, eps on the union): utils/yolo_utils.py:103-123
@@ -297,47 +276,35 @@ __device__ __forceinline__ float map_iou(const float* a, const float* b)
     return __fdiv_rn(inter, uni);
 }
 
-__global__ void map_best_kernel(const float* __restrict__ det, long long K, const float* __restrict__ gt, long long G,
-                                const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
-                                const u64* __restrict__ gkeys, const u32* __restrict__ gvals,
-                                float iou_thr, int* __restrict__ best_g, int* __restrict__ first_rank)
+// lower bound by a whole warp: 32 probes per round instead of one (a lone thread's binary search over 200 k keys is 18
+// dependent global loads, ~20 us at the head of every class's CTA); every lane returns the same answer
+__device__ __forceinline__ long long warp_lower_bound_u64(const u64* __restrict__ a, long long n, u64 key)
 {
-    const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= K) return;
-    const u32 d = dvals[p];
-    const float* dr = det + (size_t)d * 7;
-    const u32 cls = (u32)(dkeys[p] >> 32);
-    const u32 img = (u32)dr[0] & ((1u << MAP_IMG_BITS) - 1u);
-    const u64 gk = ((u64)cls << MAP_IMG_BITS) | img;
-    long long s = lower_bound_u64(gkeys, G, gk);
-    float best = 0.0f;
-    int bg = -1;
-    for (; s < G && gkeys[s] == gk; ++s) {
-        const float iou = map_iou(dr + 1, gt + (size_t)gvals[s] * 7 + 1);
-        if (iou > best) { best = iou; bg = (int)s; }          // strict >, first max wins (:415-417)
+    const int lane = threadIdx.x & 31;
+    long long lo = 0, hi = n;                                  // the answer lies in [lo, hi]
+    while (hi > lo) {
+        const long long step = (hi - lo + 31) / 32;
+        const long long p = lo + lane * step;
+        const bool less = p < hi && a[p] < key;                // a prefix of the lanes
+        const int c = __popc(__ballot_sync(YPP_FULL_MASK, less));
+        if (c == 0) { hi = lo; break; }
+        const long long last = lo + (long long)(c - 1) * step;  // a[last] < key <= a[last + step] (or the end)
+        hi = min(hi, last + step);
+        lo = last + 1;
     }
-    if (!(best > iou_thr)) bg = -1;                            // :419
-    best_g[p] = bg;
-    if (bg >= 0) atomicMin(first_rank + bg, (int)p);
+    return lo;
 }
 
-// one CTA per class: TP flags, cumulative precision/recall, envelope, AP.
-// kFlags = false: the detections were matched here (best_g / first_rank); the class's ground truths are counted in
-//                 the sorted ground-truth keys.
-// kFlags = true:  every detection arrives with its TP flag (bit 0 of its sort value: matched where its image lives)
-//                 and the class's ground-truth count comes from gt_per_class; K is read from *n_dev; classes
-//                 c_lo + blockIdx.x.
+// one CTA per class: cumulative precision/recall over the class's detections (sorted by score, every one with its TP
+// flag in bit 0 of its sort value: matched where its image lives), envelope, AP.  The class's ground-truth count comes
+// from gt_per_class; K is read from *n_dev when given; classes c_lo + blockIdx.x.
 // term[] (K floats) receives, at the class's own ranks, first the rank of its t-th true positive and then that
 // true positive's contribution to the AP sum.
 #define AP_THREADS 1024
-template <bool kFlags>
 __global__ void __launch_bounds__(AP_THREADS)
-map_ap_kernel(long long K, const long long* __restrict__ n_dev, long long G, int nc, int c_lo,
-              const u64* __restrict__ dkeys, const u32* __restrict__ dvals,
-              const u64* __restrict__ gkeys, const int* __restrict__ best_g, const int* __restrict__ first_rank,
-              const long long* __restrict__ gt_per_class,
-              float* __restrict__ prec, float* __restrict__ term, float* __restrict__ class_ap,
-              unsigned char* __restrict__ tp_out, float* __restrict__ per_class)
+map_ap_kernel(long long K, const long long* __restrict__ n_dev, int nc, int c_lo,
+              const u64* __restrict__ dkeys, const u32* __restrict__ dvals, const long long* __restrict__ gt_per_class,
+              float* __restrict__ prec, float* __restrict__ term, float* __restrict__ class_ap, float* __restrict__ per_class)
 {
     __shared__ int warp_i[32];
     __shared__ float warp_f[32];
@@ -346,92 +313,102 @@ map_ap_kernel(long long K, const long long* __restrict__ n_dev, long long G, int
     __shared__ float carry_f;
     const int c = c_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (n_dev) K = min(K, *n_dev);
-    if (tid == 0) {
-        s_lo = lower_bound_u64(dkeys, K, (u64)c << 32);
-        s_hi = lower_bound_u64(dkeys, K, (u64)(c + 1) << 32);
-        if (kFlags) s_ng = gt_per_class[c];
-        else s_ng = lower_bound_u64(gkeys, G, (u64)(c + 1) << MAP_IMG_BITS) - lower_bound_u64(gkeys, G, (u64)c << MAP_IMG_BITS);
-        carry_i = 0;
+    if (warp == 0) {
+        const long long a = warp_lower_bound_u64(dkeys, K, (u64)c << 32);
+        const long long b = warp_lower_bound_u64(dkeys, K, (u64)(c + 1) << 32);
+        if (lane == 0) { s_lo = a; s_hi = b; s_ng = gt_per_class[c]; carry_i = 0; }
     }
     __syncthreads();
     const long long lo = s_lo, hi = s_hi;
     const long long ng = s_ng;
     float* pc = per_class ? per_class + 4 * (size_t)c : nullptr;
     if (ng == 0) {                                           // class skipped, AP 0 (:379-381)
-        if (tp_out) for (long long p = lo + tid; p < hi; p += AP_THREADS) tp_out[dvals[p]] = 255;
         if (pc && tid < 4) pc[tid] = 0.0f;
         if (tid == 0) class_ap[c] = 0.0f;
         return;
     }
     const float rec_den = (float)((double)ng + 1e-6);         // python float64 (G + eps) -> fp32
-    // forward: cumulative TP -> precision at every rank
-    for (long long p0 = lo; p0 < hi; p0 += AP_THREADS) {
-        const long long p = p0 + tid;
-        int t = 0;
-        if (p < hi) {
-            if (kFlags) t = (int)(dvals[p] & 1u);
-            else { const int bg = best_g[p]; t = (bg >= 0 && first_rank[bg] == (int)p) ? 1 : 0; }
-        }
-        int inc = t;
+    constexpr int IT = 4, CH = AP_THREADS * IT;              // ranks per thread and per round
+    // forward: cumulative TP -> precision at every rank (thread = IT consecutive ranks)
+    for (long long p0 = lo; p0 < hi; p0 += CH) {
+        const long long pb = p0 + (long long)tid * IT;
+        int t[IT], tsum = 0;
+#pragma unroll
+        for (int q = 0; q < IT; ++q) { t[q] = (pb + q < hi) ? (int)(dvals[pb + q] & 1u) : 0; tsum += t[q]; }
+        int inc = tsum;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
         if (lane == 31) warp_i[warp] = inc;
         __syncthreads();
-        int before = 0, tot = 0;
-        for (int w = 0; w < 32; ++w) { const int v = warp_i[w]; if (w < warp) before += v; tot += v; }
+        const int wv = warp_i[lane];
+        int winc = wv;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, winc, d); if (lane >= d) winc += o; }
+        const int tot = __shfl_sync(YPP_FULL_MASK, winc, 31);
+        const int before = __shfl_sync(YPP_FULL_MASK, winc - wv, warp);
         const int cbase = carry_i;
-        if (p < hi) {
-            const int tpc = cbase + before + inc;
-            const float ftp = (float)tpc, ffp = (float)((int)(p - lo + 1) - tpc);
-            prec[p] = __fdiv_rn(ftp, __fadd_rn(__fadd_rn(ftp, ffp), 1e-6f));                 // :435
-            if (!kFlags && tp_out) tp_out[dvals[p]] = (unsigned char)t;
-            if (t) term[lo + tpc - 1] = __uint_as_float((u32)(p - lo));                      // rank of the tpc-th TP (int bits)
+        int tpc = cbase + before + inc - tsum;
+#pragma unroll
+        for (int q = 0; q < IT; ++q) {
+            const long long p = pb + q;
+            if (p < hi) {
+                tpc += t[q];
+                const float ftp = (float)tpc, ffp = (float)((int)(p - lo + 1) - tpc);
+                prec[p] = __fdiv_rn(ftp, __fadd_rn(__fadd_rn(ftp, ffp), 1e-6f));             // :435
+                if (t[q]) term[lo + tpc - 1] = __uint_as_float((u32)(p - lo));               // rank of the tpc-th TP (int bits)
+            }
         }
         __syncthreads();
         if (tid == 0) carry_i = cbase + tot;
         __syncthreads();
     }
     const int n_tp = carry_i;
-    // backward: precision envelope = running max from the right (:442-443)
+    // backward: precision envelope = running max from the right (:442-443); thread 0 owns the right-most IT ranks
     if (tid == 0) carry_f = -INFINITY;
     __syncthreads();
     const long long len = hi - lo;
-    const long long nchunks = (len + AP_THREADS - 1) / AP_THREADS;
-    for (long long ch = nchunks - 1; ch >= 0; --ch) {
-        const long long p = lo + ch * AP_THREADS + (AP_THREADS - 1 - tid);   // thread 0 = right-most
-        float v = p < hi ? prec[p] : -INFINITY;
-        float inc = v;
+    for (long long r0 = 0; r0 < len; r0 += CH) {
+        const long long pr = hi - 1 - r0 - (long long)tid * IT;      // my right-most rank; I walk pr, pr-1, ..
+        float v[IT], m = -INFINITY;
+#pragma unroll
+        for (int q = 0; q < IT; ++q) { v[q] = (pr - q >= lo) ? prec[pr - q] : -INFINITY; m = fmaxf(m, v[q]); }
+        float inc = m;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const float o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc = fmaxf(inc, o); }
         if (lane == 31) warp_f[warp] = inc;
         __syncthreads();
         float before = carry_f, tot = carry_f;
         for (int w = 0; w < 32; ++w) { const float x = warp_f[w]; if (w < warp) before = fmaxf(before, x); tot = fmaxf(tot, x); }
-        if (p < hi) prec[p] = fmaxf(before, inc);
+        float run = fmaxf(before, __shfl_up_sync(YPP_FULL_MASK, inc, 1));     // everything to my right
+        if (lane == 0) run = before;
+#pragma unroll
+        for (int q = 0; q < IT; ++q) {
+            if (pr - q >= lo) { run = fmaxf(run, v[q]); prec[pr - q] = run; }
+        }
         __syncthreads();
         if (tid == 0) carry_f = tot;
         __syncthreads();
     }
     // AP = sum over the recall change points (every true positive) of (recall step) x (envelope there), :445-452.
     // The terms are independent: every thread computes some (same roundings as the reference's one-by-one
-    // evaluation); only the fp32 ADDITIONS stay sequential, in rank order, so the sum rounds as the reference's.
-    for (int t = 1 + tid; t <= n_tp; t += AP_THREADS) {
-        const long long p = lo + (long long)__float_as_uint(term[lo + t - 1]);
-        const float r1 = __fdiv_rn((float)t, rec_den), r0 = __fdiv_rn((float)(t - 1), rec_den);
-        term[lo + t - 1] = __fmul_rn(__fsub_rn(r1, r0), prec[p]);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        float ap = 0.0f;
-        int t = 0;
-        for (; t + 8 <= n_tp; t += 8) {
-            float v[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) v[q] = term[lo + t + q];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) ap = __fadd_rn(ap, v[q]);
+    // evaluation); only the fp32 ADDITIONS stay sequential, in rank order, so the sum rounds as the reference's:
+    // the terms are staged in shared memory CH at a time and one thread adds them up.
+    __shared__ float stage[CH];
+    float ap = 0.0f;
+    for (int t0 = 0; t0 < n_tp; t0 += CH) {
+        for (int t = t0 + tid; t < min(n_tp, t0 + CH); t += AP_THREADS) {
+            const long long p = lo + (long long)__float_as_uint(term[lo + t]);
+            const float r1 = __fdiv_rn((float)(t + 1), rec_den), r0 = __fdiv_rn((float)t, rec_den);
+            stage[t - t0] = __fmul_rn(__fsub_rn(r1, r0), prec[p]);
         }
-        for (; t < n_tp; ++t) ap = __fadd_rn(ap, term[lo + t]);
+        __syncthreads();
+        if (tid == 0) {
+            const int n = min(CH, n_tp - t0);
+            for (int k = 0; k < n; ++k) ap = __fadd_rn(ap, stage[k]);
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
         if (pc) { pc[0] = ap; pc[1] = (float)n_tp; pc[2] = (float)((int)len - n_tp); pc[3] = (float)((int)ng - n_tp); }
         class_ap[c] = ap;
     }
@@ -446,29 +423,53 @@ __global__ void map_mean_kernel(int nc, const float* __restrict__ class_ap, int 
     *map_out = __fdiv_rn(s, (float)nc);
 }
 
-// ---- matching alone (M1), without sorting the detections ------------------------------------------------
-// A detection's best ground truth g*(d) depends on d and its image's ground truths only; d is a true positive iff
-// IoU > thr and d is the first in (score descending, row order) among the detections that chose g*(d).  "First" is
-// a 64-bit minimum: claim[g] = min over those detections of (~enc(score)) << 32 | d.  No sort of the detections, so a
-// rank of an image-sharded evaluation can flag ITS detections against ITS ground truths in two short kernels.
+// ---- matching (M1): no sort at all ----------------------------------------------------------------------------
+// A detection's best ground truth g*(d) depends on d and its image's ground truths only (same image id - float
+// equality, utils/yolo_utils.py:407 -, same class, strict >, first maximum in row order wins, :412-417); d is a true
+// positive iff IoU > thr and d is the first in (score descending, row order) among the detections that chose g*(d)
+// (:419-430).  "First" is a 64-bit minimum: claim[g] = min over those detections of (~enc(score)) << 32 | d.
+// The ground truths of a validation run arrive in image order (the accumulators append them batch after batch), so
+// the rows of an image are found by a binary search on the image column and the ground truths are never sorted.
+// Any other row order is still handled - `unsorted` is raised on the device by the prepare kernel and every
+// detection then scans all G rows: correct, O(K G).
+__global__ void map_gt_prepare_kernel(const float* __restrict__ gt, long long G, int nc, u64* __restrict__ claim,
+                                      unsigned long long* __restrict__ per_class, int* __restrict__ unsorted)
+{
+    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    claim[g] = ~0ull;
+    const u32 cls = map_cls(gt[g * 7 + 6], nc);
+    if (cls < (u32)nc) atomicAdd(per_class + cls, 1ull);
+    if (g > 0 && !(gt[g * 7] >= gt[(g - 1) * 7])) *unsorted = 1;        // every writer writes the same value
+}
+
 __global__ void map_claim_kernel(const float* __restrict__ det, long long K, const float* __restrict__ gt, long long G, int nc,
-                                 const u64* __restrict__ gkeys, const u32* __restrict__ gvals, float iou_thr,
-                                 int* __restrict__ best_g, u64* __restrict__ claim)
+                                 const int* __restrict__ unsorted, float iou_thr, int* __restrict__ best_g, u64* __restrict__ claim)
 {
     const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (d >= K) return;
     const float* dr = det + (size_t)d * 7;
     const u32 cls = map_cls(dr[6], nc);
-    const u32 img = (u32)dr[0] & ((1u << MAP_IMG_BITS) - 1u);
-    const u64 gk = ((u64)cls << MAP_IMG_BITS) | img;
-    long long s = lower_bound_u64(gkeys, G, gk);
+    const float img = dr[0];
+    const bool sorted = *unsorted == 0;
+    long long s = 0;
+    if (sorted) {                                             // first row whose image id is not below mine
+        long long hi = G;
+        while (s < hi) { const long long mid = (s + hi) >> 1; if (gt[mid * 7] < img) s = mid + 1; else hi = mid; }
+    }
     float best = 0.0f;
     int bg = -1;
-    for (; s < G && gkeys[s] == gk; ++s) {
-        const float iou = map_iou(dr + 1, gt + (size_t)gvals[s] * 7 + 1);
-        if (iou > best) { best = iou; bg = (int)s; }
+    if (cls < (u32)nc) {
+        for (; s < G; ++s) {
+            const float* gr = gt + (size_t)s * 7;
+            const float gi = gr[0];
+            if (gi != img) { if (sorted) break; continue; }
+            if (map_cls(gr[6], nc) != cls) continue;
+            const float iou = map_iou(dr + 1, gr + 1);
+            if (iou > best) { best = iou; bg = (int)s; }
+        }
     }
-    if (!(best > iou_thr) || cls >= (u32)nc) bg = -1;
+    if (!(best > iou_thr)) bg = -1;
     best_g[d] = bg;
     if (bg >= 0) atomicMin(claim + bg, ((u64)(~ypp_enc(dr[5])) << 32) | (u64)(u32)d);
 }
@@ -488,12 +489,13 @@ __global__ void map_flags_kernel(const float* __restrict__ det, long long K, int
     if (triples) { triples[d * 3] = score; triples[d * 3 + 1] = cf; triples[d * 3 + 2] = tp ? 1.0f : 0.0f; }
 }
 
-__global__ void map_gt_count_kernel(const float* __restrict__ gt, long long G, int nc, unsigned long long* __restrict__ per_class)
+// sort keys of ALL the triples of one buffer (the single-process case: nothing to select)
+__global__ void map_triple_keys_kernel(const float* __restrict__ tr, long long K, int nc, u64* __restrict__ keys, u32* __restrict__ vals)
 {
-    const long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= G) return;
-    const u32 cls = map_cls(gt[g * 7 + 6], nc);
-    if (cls < (u32)nc) atomicAdd(per_class + cls, 1ull);
+    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= K) return;
+    keys[d] = ((u64)map_cls(tr[d * 3 + 1], nc) << 32) | (u64)(~ypp_enc(tr[d * 3]));
+    vals[d] = tr[d * 3 + 2] != 0.0f ? 1u : 0u;
 }
 
 // ---- AP from flagged detections gathered from every rank (M2), for the classes [c_lo, c_hi) ----------------------
@@ -561,9 +563,9 @@ map_select_scatter_kernel(const float* __restrict__ tr, long long n, long long s
 }
 
 struct MapWs {
-    RsBuffers det, gt;
-    int* best_g; float* prec; int* first_rank; float* term; float* class_ap;
-    u64* claim; unsigned long long* gt_per_class; int* sel_blocks; long long* n_sel;
+    RsBuffers det;
+    int* best_g; float* prec; float* term; float* class_ap; float* triples;
+    u64* claim; unsigned long long* gt_per_class; int* sel_blocks; long long* n_sel; int* unsorted;
     size_t total;
 };
 
@@ -574,20 +576,18 @@ MapWs make_map_ws(void* base, long long G, long long K, int nc)
     size_t off = 0;
     auto take = [&](size_t bytes) { char* r = p + off; off += ypp_align_up(bytes ? bytes : 8, 256); return r; };
     const long long Kp = K > 0 ? K : 1, Gp = G > 0 ? G : 1;
-    const size_t nbk = (size_t)((Kp + RS_TILE - 1) / RS_TILE), nbg = (size_t)((Gp + RS_TILE - 1) / RS_TILE);
+    const size_t nbk = (size_t)((Kp + RS_TILE - 1) / RS_TILE);
     w.det.k[0] = (u64*)take(8 * Kp); w.det.k[1] = (u64*)take(8 * Kp);
     w.det.v[0] = (u32*)take(4 * Kp); w.det.v[1] = (u32*)take(4 * Kp);
     w.det.counts = (int*)take(4 * 256 * nbk);
-    w.gt.k[0] = (u64*)take(8 * Gp); w.gt.k[1] = (u64*)take(8 * Gp);
-    w.gt.v[0] = (u32*)take(4 * Gp); w.gt.v[1] = (u32*)take(4 * Gp);
-    w.gt.counts = (int*)take(4 * 256 * nbg);
     w.best_g = (int*)take(4 * Kp);
     w.prec = (float*)take(4 * Kp);
-    w.first_rank = (int*)take(4 * Gp);
     w.term = (float*)take(4 * Kp);
+    w.triples = (float*)take(12 * Kp);
     w.class_ap = (float*)take(4 * (size_t)(nc > 0 ? nc : 1));
     w.claim = (u64*)take(8 * Gp);
-    w.gt_per_class = (unsigned long long*)take(8 * (size_t)(nc > 0 ? nc : 1));
+    w.gt_per_class = (unsigned long long*)take(8 * (size_t)(nc > 0 ? nc : 1) + 8);     // + the `unsorted` word: one memset
+    w.unsorted = (int*)(w.gt_per_class + (nc > 0 ? nc : 1));
     w.sel_blocks = (int*)take(4 * ((size_t)((Kp + SEL_TILE - 1) / SEL_TILE) + 1));
     w.n_sel = (long long*)take(8);
     w.total = off;
@@ -736,29 +736,40 @@ size_t ypp_map_ws_bytes(long long G, long long K, int nc)
     return make_map_ws(nullptr, G, K, nc).total;
 }
 
+// M1: per-class ground-truth counts, claims, flags.  gpc_out: caller's [nc] int64 or NULL (then the workspace's).
+static int launch_m1(const MapWs& w, const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
+                     unsigned char* tp, float* triples, unsigned long long* gpc, cudaStream_t st)
+{
+    if (gpc == w.gt_per_class) cudaMemsetAsync(w.gt_per_class, 0, 8 * (size_t)nc + 8, st);
+    else { cudaMemsetAsync(gpc, 0, 8 * (size_t)nc, st); cudaMemsetAsync(w.unsorted, 0, 4, st); }
+    if (G > 0) {
+        map_gt_prepare_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, w.claim, gpc, w.unsorted);
+        ypp_count_launch(1);
+    }
+    if (K > 0) {
+        map_claim_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, gt, G, nc, w.unsorted, iou_thr, w.best_g, w.claim);
+        map_flags_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, nc, w.best_g, w.claim, (const long long*)gpc, tp, triples);
+        ypp_count_launch(2);
+    }
+    return YPP_OK;
+}
+
+// mean_average_precision in one process = M1, then M2 over every class of the one buffer
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
                    cudaStream_t st)
 {
     MapWs w = make_map_ws(ws, G, K, nc);
     if (ws_bytes < w.total) { ypp_set_error("map_match: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
-    const int cbits = bits_for(nc + 1);
-    int gcur = 0, dcur = 0;
-    if (G > 0) {
-        map_gt_keys_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, w.gt.k[0], w.gt.v[0], w.first_rank);
-        ypp_count_launch(1);
-        gcur = rs_sort(w.gt, G, MAP_IMG_BITS + cbits, st);
-    }
+    launch_m1(w, gt, G, det, K, nc, iou_thr, tp, w.triples, w.gt_per_class, st);
+    int dcur = 0;
     if (K > 0) {
-        map_det_keys_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, nc, w.det.k[0], w.det.v[0], tp);
+        map_triple_keys_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(w.triples, K, nc, w.det.k[0], w.det.v[0]);
         ypp_count_launch(1);
-        dcur = rs_sort(w.det, K, 32 + cbits, st);
-        map_best_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, gt, G, w.det.k[dcur], w.det.v[dcur],
-                                                                     w.gt.k[gcur], w.gt.v[gcur], iou_thr, w.best_g, w.first_rank);
-        ypp_count_launch(1);
+        dcur = rs_sort(w.det, K, 32 + bits_for(nc + 1), st);
     }
-    map_ap_kernel<false><<<nc, AP_THREADS, 0, st>>>(K, nullptr, G, nc, 0, w.det.k[dcur], w.det.v[dcur], w.gt.k[gcur], w.best_g,
-                                                    w.first_rank, nullptr, w.prec, w.term, w.class_ap, tp, per_class);
+    map_ap_kernel<<<nc, AP_THREADS, 0, st>>>(K, nullptr, nc, 0, w.det.k[dcur], w.det.v[dcur], (const long long*)w.gt_per_class,
+                                             w.prec, w.term, w.class_ap, per_class);
     map_mean_kernel<<<1, 32, 0, st>>>(nc, w.class_ap, 1, map);
     ypp_count_launch(2);
     return ypp_check_launch("map_match");
@@ -769,22 +780,7 @@ int ypp_launch_map_flags(const float* gt, long long G, const float* det, long lo
 {
     MapWs w = make_map_ws(ws, G, K, nc);
     if (ws_bytes < w.total) { ypp_set_error("map_flags: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
-    unsigned long long* gpc = gt_per_class ? (unsigned long long*)gt_per_class : w.gt_per_class;
-    cudaMemsetAsync(gpc, 0, 8 * (size_t)nc, st);
-    int gcur = 0;
-    if (G > 0) {
-        cudaMemsetAsync(w.claim, 0xff, 8 * (size_t)G, st);
-        map_gt_keys_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, w.gt.k[0], w.gt.v[0], w.first_rank);
-        map_gt_count_kernel<<<(unsigned)((G + 255) / 256), 256, 0, st>>>(gt, G, nc, gpc);
-        ypp_count_launch(2);
-        gcur = rs_sort(w.gt, G, MAP_IMG_BITS + bits_for(nc + 1), st);
-    }
-    if (K > 0) {
-        map_claim_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, gt, G, nc, w.gt.k[gcur], w.gt.v[gcur], iou_thr,
-                                                                      w.best_g, w.claim);
-        map_flags_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(det, K, nc, w.best_g, w.claim, (const long long*)gpc, tp, triples);
-        ypp_count_launch(2);
-    }
+    launch_m1(w, gt, G, det, K, nc, iou_thr, tp, triples, gt_per_class ? (unsigned long long*)gt_per_class : w.gt_per_class, st);
     return ypp_check_launch("map_flags");
 }
 
@@ -806,8 +802,8 @@ int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_str
         cudaMemsetAsync(w.n_sel, 0, 8, st);
     }
     const int dcur = rs_sort(w.det, n, 32 + bits_for(nc + 1), st, w.n_sel);
-    map_ap_kernel<true><<<c_hi - c_lo, AP_THREADS, 0, st>>>(n, w.n_sel, 0, nc, c_lo, w.det.k[dcur], w.det.v[dcur], nullptr, nullptr,
-                                                            nullptr, gt_per_class, w.prec, w.term, w.class_ap, nullptr, per_class);
+    map_ap_kernel<<<c_hi - c_lo, AP_THREADS, 0, st>>>(n, w.n_sel, nc, c_lo, w.det.k[dcur], w.det.v[dcur], gt_per_class,
+                                                      w.prec, w.term, w.class_ap, per_class);
     ypp_count_launch(1);
     return ypp_check_launch("map_ap_from_flags");
 }

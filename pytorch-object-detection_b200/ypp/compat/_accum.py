@@ -106,4 +106,5 @@ class MeanAveragePrecisionBase(LiveParams):
         from .yolo_utils import mean_average_precision
         if self._pred is None:
             raise RuntimeError("result() before any update_state()")
-        return mean_average_precision(self._true.view(), self._pred.view(), self.num_classes)
+        true, pred = engine.views(self._true, self._pred)                  # one host read for both counts
+        return mean_average_precision(true, pred, self.num_classes)

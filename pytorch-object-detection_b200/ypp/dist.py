@@ -158,8 +158,8 @@ class ShardedMeanAveragePrecision:
         self._acc._update(y_true, list(y_preds) if isinstance(y_preds, (list, tuple)) else [y_preds])
 
     def local_rows(self):
-        gt = self._acc._true.view() if self._acc._true is not None else self._empty()
-        det = self._acc._pred.view() if self._acc._pred is not None else self._empty()
+        from . import engine
+        gt, det = engine.views(self._acc._true, self._acc._pred)           # one host read for both counts
         return gt, det
 
     def gathered(self):

@@ -246,6 +246,26 @@ class RowAccumulator:
         return self.buf[:n]
 
 
+def views(*accs):
+    """view() of several accumulators with ONE host read of their cursors (each .item() is a device synchronisation)."""
+    live = [a for a in accs if a is not None and a.buf is not None]
+    for a in live:
+        a.join()
+    counts = torch.stack([a.cur[a.k & 1] for a in live]).tolist() if live else []
+    out, it = [], iter(counts)
+    for a in accs:
+        if a is None or a.buf is None:
+            dev = a.device if a is not None else torch.device("cuda", _cur_dev())
+            out.append(torch.empty((0, 7), dtype=torch.float32, device=dev))
+            continue
+        n = int(next(it))
+        a.syncs += 1
+        a.bound = n
+        assert n <= a.buf.shape[0], "RowAccumulator: %d rows were appended to a buffer of %d" % (n, a.buf.shape[0])
+        out.append(a.buf[:n])
+    return out
+
+
 class _Plan:
     """Parameter blocks of one set of head buffers.  Holds NO tensor: the key (pointer, shape, dtype, device of
     every head) guarantees the pointers inside `arr` are those of whatever tensors are passed with that key."""

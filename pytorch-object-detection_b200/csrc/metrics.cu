@@ -163,15 +163,21 @@ rs_hist_kernel(const u64* __restrict__ keys, long long n, const long long* __res
 // one reduction pass has told it where its part starts (the chunked version - a block scan with three barriers per
 // 1024 entries - took 44 us on 27 k entries, 220 us per sort)
 __global__ void __launch_bounds__(1024)
-rs_scan_kernel(int* __restrict__ counts, long long total)
+rs_scan_kernel(int* __restrict__ counts, int nblocks, long long n, const long long* __restrict__ n_dev)
 {
     __shared__ int warp_tot[32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // the launch is sized for the bound n; with the count on the device only the blocks that hold keys have columns
+    // worth scanning (the others' counts are never read by their scatter blocks either)
+    if (n_dev) n = min(n, *n_dev);
+    const int nb = n_dev ? (int)((n + RS_TILE - 1) / RS_TILE) : nblocks;
+    const long long total = 256LL * nb;
+    auto at = [&](long long e) -> int& { return counts[(e / nb) * nblocks + (e % nb)]; };   // logical entry e = digit * nb + block
     const long long S = ((total + 31) / 32 + 31) / 32 * 32;                 // entries per warp, a multiple of 32
     const long long a = min(total, (long long)warp * S), b = min(total, a + S);
     int sum = 0;
 #pragma unroll 8
-    for (long long i = a + lane; i < b; i += 32) sum += counts[i];
+    for (long long i = a + lane; i < b; i += 32) sum += at(i);
     sum = __reduce_add_sync(YPP_FULL_MASK, sum);
     if (lane == 0) warp_tot[warp] = sum;
     __syncthreads();
@@ -182,14 +188,14 @@ rs_scan_kernel(int* __restrict__ counts, long long total)
     for (long long base = a; base < b; base += 1024) {
         int v[32];
 #pragma unroll
-        for (int k = 0; k < 32; ++k) { const long long i = base + k * 32 + lane; v[k] = i < b ? counts[i] : 0; }
+        for (int k = 0; k < 32; ++k) { const long long i = base + k * 32 + lane; v[k] = i < b ? at(i) : 0; }
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
             const long long i = base + k * 32 + lane;
             int inc = v[k];
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
-            if (i < b) counts[i] = carry + inc - v[k];
+            if (i < b) at(i) = carry + inc - v[k];
             carry += __shfl_sync(YPP_FULL_MASK, inc, 31);
         }
     }
@@ -243,7 +249,7 @@ int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st, const 
     const int nblocks = (int)((n + RS_TILE - 1) / RS_TILE);
     for (int shift = 0; shift < nbits; shift += 8) {
         rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], n, n_dev, shift, rb.counts, nblocks);
-        rs_scan_kernel<<<1, 1024, 0, st>>>(rb.counts, 256LL * nblocks);
+        rs_scan_kernel<<<1, 1024, 0, st>>>(rb.counts, nblocks, n, n_dev);
         rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], rb.v[cur], rb.k[cur ^ 1], rb.v[cur ^ 1], n, n_dev, shift,
                                                           rb.counts, nblocks);
         ypp_count_launch(3);
@@ -532,7 +538,34 @@ map_select_count_kernel(const float* __restrict__ tr, long long n, long long seg
     if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; ++w) t += wsum[w]; block_count[blockIdx.x] = t; }
 }
 
-// block_count holds the exclusive offsets now (rs_scan_kernel); the last block also publishes the total
+// exclusive scan of the per-block counts of the selection, one CTA
+__global__ void __launch_bounds__(1024)
+block_offsets_kernel(int* __restrict__ counts, int n)
+{
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += 1024) {
+        const int i = i0 + tid;
+        const int v = i < n ? counts[i] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        int before = 0, tot = 0;
+        for (int w = 0; w < 32; ++w) { const int t = warp_tot[w]; if (w < warp) before += t; tot += t; }
+        const int c = carry;
+        if (i < n) counts[i] = c + before + inc - v;
+        __syncthreads();
+        if (tid == 0) carry = c + tot;
+        __syncthreads();
+    }
+}
+
+// block_count holds the exclusive offsets now (block_offsets_kernel); the last block also publishes the total
 __global__ void __launch_bounds__(SEL_THREADS)
 map_select_scatter_kernel(const float* __restrict__ tr, long long n, long long seg_stride, const long long* __restrict__ seg_count,
                           int nc, int c_lo, int c_hi, const int* __restrict__ block_off, u64* __restrict__ keys,
@@ -793,7 +826,7 @@ int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_str
     if (n > 0) {
         const int nb = (int)((n + SEL_TILE - 1) / SEL_TILE);
         map_select_count_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks);
-        rs_scan_kernel<<<1, 1024, 0, st>>>(w.sel_blocks, nb);
+        block_offsets_kernel<<<1, 1024, 0, st>>>(w.sel_blocks, nb);
         // the scan is exclusive: the last block adds its own count to publish the total
         map_select_scatter_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks,
                                                               w.det.k[0], w.det.v[0], w.n_sel);

@@ -465,8 +465,11 @@ __device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size
 // memory, every warp resolves the greedy order redundantly (ballot fix-point: a row is kept once
 // every earlier row that could suppress it is known dead, dead once one of them is known kept),
 // and then broadcasts ITS kept rows against all later columns (lane = column mod 32).
+#ifndef YPP_NMSQ_MIN_BLOCKS
+#define YPP_NMSQ_MIN_BLOCKS 9       /* resident CTAs per SM the register allocation is capped for */
+#endif
 template <bool kFast, bool kFma>
-__global__ void __launch_bounds__(YPP_NMSQ_THREADS, 9)
+__global__ void __launch_bounds__(YPP_NMSQ_THREADS, YPP_NMSQ_MIN_BLOCKS)
 ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
 {
     __shared__ SegSmem sm;
@@ -743,8 +746,9 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
 #define YPP_BSP_MIN_EDGES 2048          /* the edge list takes whatever shared memory the boxes leave; at least this */
 #define YPP_BSP_FIXED (4 * YPP_BSP_BINS + 2 * (YPP_BSP_BINS + 2) + 64)
 
+#define YPP_BSP_SIDE 32                 /* the bins are a YPP_BSP_SIDE x YPP_BSP_SIDE grid over (x1, y1), x-major */
 struct BigSparseHdr {
-    u32 xlo, xhi, amax, cmax;
+    u32 xlo, xhi, ylo, yhi, amax, cmax;
     int nedges, odd;
     int wtot[YPP_NMS_BIG_THREADS / 32];
 };
@@ -756,6 +760,8 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
 {
     constexpr int T = YPP_NMS_BIG_THREADS;
     static_assert(T == YPP_BSP_BINS, "the bin scan gives every thread one bin");
+    static_assert(YPP_BSP_SIDE * YPP_BSP_SIDE == YPP_BSP_BINS, "square grid of bins");
+    constexpr int SD = YPP_BSP_SIDE;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (len > 65535) return false;                                                          // uniform
     const long long spare = (long long)smem_bytes - (long long)len * 21 - YPP_BSP_FIXED;
@@ -770,29 +776,33 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
     unsigned char* pend = state + len;
     unsigned char* kill = pend + len;
     u32* edges = reinterpret_cast<u32*>(smem + (((size_t)(kill + len - smem) + 15) & ~(size_t)15));
-    if (tid == 0) { H.xlo = 0xffffffffu; H.xhi = 0u; H.amax = 0u; H.cmax = 0u; H.nedges = 0; H.odd = 0; }
+    if (tid == 0) { H.xlo = 0xffffffffu; H.xhi = 0u; H.ylo = 0xffffffffu; H.yhi = 0u; H.amax = 0u; H.cmax = 0u; H.nedges = 0; H.odd = 0; }
     for (int i = tid; i < YPP_BSP_BINS; i += T) hist[i] = 0;
     __syncthreads();
     // ---- pass 1: ordinary? x1 range, largest |area| and |coordinate|
     {
         bool odd = false;
-        u32 xlo = 0xffffffffu, xhi = 0u, amax_bits = 0u, cmax_bits = 0u;
+        u32 xlo = 0xffffffffu, xhi = 0u, ylo = 0xffffffffu, yhi = 0u, amax_bits = 0u, cmax_bits = 0u;
         for (int i = tid; i < len; i += T) {
             const float4 q = seg[i];
             const float bw = __fsub_rn(q.z, q.x), bh = __fsub_rn(q.w, q.y);
             odd |= !(bw > 0.0f && bh > 0.0f && bw < INFINITY && bh < INFINITY && fabsf(q.x) < INFINITY && fabsf(q.y) < INFINITY);
-            const u32 e = ypp_enc(q.x);
+            const u32 e = ypp_enc(q.x), ey = ypp_enc(q.y);
             xlo = min(xlo, e); xhi = max(xhi, e);
+            ylo = min(ylo, ey); yhi = max(yhi, ey);
             amax_bits = max(amax_bits, __float_as_uint(fabsf(__fmul_rn(bw, bh))));
             cmax_bits = max(max(cmax_bits, __float_as_uint(fabsf(q.x))), max(__float_as_uint(fabsf(q.y)),
                             max(__float_as_uint(fabsf(q.z)), __float_as_uint(fabsf(q.w)))));
         }
         xlo = __reduce_min_sync(YPP_FULL_MASK, xlo);
         xhi = __reduce_max_sync(YPP_FULL_MASK, xhi);
+        ylo = __reduce_min_sync(YPP_FULL_MASK, ylo);
+        yhi = __reduce_max_sync(YPP_FULL_MASK, yhi);
         amax_bits = __reduce_max_sync(YPP_FULL_MASK, amax_bits);
         cmax_bits = __reduce_max_sync(YPP_FULL_MASK, cmax_bits);
         if (lane == 0) {
-            atomicMin(&H.xlo, xlo); atomicMax(&H.xhi, xhi); atomicMax(&H.amax, amax_bits); atomicMax(&H.cmax, cmax_bits);
+            atomicMin(&H.xlo, xlo); atomicMax(&H.xhi, xhi); atomicMin(&H.ylo, ylo); atomicMax(&H.yhi, yhi);
+            atomicMax(&H.amax, amax_bits); atomicMax(&H.cmax, cmax_bits);
         }
         if (__syncthreads_or(odd)) return false;
     }
@@ -801,10 +811,12 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
     if (cexp < 67 || cexp > 187 || !(Bseg < INFINITY)) return false;                     // uniform
     const float scale = __uint_as_float((u32)(252 - cexp) << 23);
     const float c1k = __fmul_rn(__fadd_rn(1.0f, thr), __uint_as_float((u32)(cexp + 2) << 23));
-    const float xmin = ypp_dec(H.xlo), xmax = ypp_dec(H.xhi);
-    const float inv = __fdiv_rn((float)YPP_BSP_BINS, __fsub_rn(xmax, xmin));
+    const float xmin = ypp_dec(H.xlo), xmax = ypp_dec(H.xhi), ymin = ypp_dec(H.ylo), ymax = ypp_dec(H.yhi);
+    const float inv = __fdiv_rn((float)SD, __fsub_rn(xmax, xmin));           // inf when every x1 is the same: one column
+    const float invy = __fdiv_rn((float)SD, __fsub_rn(ymax, ymin));
+    auto bin_of = [&](const float4 q) { return sp_bin<SD>(q.x, xmin, inv) * SD + sp_bin<SD>(q.y, ymin, invy); };
     // ---- pass 2: histogram, scan (one bin per thread), pass 3: scatter
-    for (int i = tid; i < len; i += T) atomicAdd(&hist[sp_bin<YPP_BSP_BINS>(seg[i].x, xmin, inv)], 1u);
+    for (int i = tid; i < len; i += T) atomicAdd(&hist[bin_of(seg[i])], 1u);
     __syncthreads();
     {
         const int h = (int)hist[tid];
@@ -825,37 +837,55 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
     __syncthreads();
     for (int i = tid; i < len; i += T) {
         const float4 q = seg[i];
-        const int pos = (int)atomicAdd(&hist[sp_bin<YPP_BSP_BINS>(q.x, xmin, inv)], 1u);
+        const int pos = (int)atomicAdd(&hist[bin_of(q)], 1u);
         box[pos] = q;
         rk[pos] = (unsigned short)i;
         state[i] = 0; pend[i] = 0; kill[i] = 0;
     }
     __syncthreads();
-    // ---- sweep: a warp per box, lanes over its range
+    // ---- sweep: a warp per box, lanes over its windows.  Box p (bin column xb_p) meets the boxes AFTER it in the
+    // (x-major) order that lie in columns xb_p .. column of xe and, inside every column, in the rows of its y window:
+    //   x:  xe = x1 + (1 - 0.9 thr) w_p                       (as in nms_sparse: beyond it IoU <= 0.9 thr)
+    //   y:  y1_c <= y1_p + (1 - 0.9 thr) h_p                  (y1_c >= y1_p: IoU <= overlap_y / h_p <= 1 - dy / h_p)
+    //       y1_c >= y1_p - (1 - 0.9 thr) / (0.9 thr) h_p      (y1_c <  y1_p: IoU <= 1 - dy / h_c, and IoU > 0.9 thr
+    //                                                          needs h_c <= h_p / (0.9 thr))
+    // every step rounded outwards, windows widened to whole bins: a pair outside has IoU <= 0.9 thr in exact
+    // arithmetic, which no rounding of the fp32 quotient lifts above thr.  Both windows follow from IoU > 0.9 thr alone,
+    // so a real edge lies in the window of BOTH its boxes and is met from the side that comes first in the order.
     {
         const float ct = __fsub_ru(1.0f, __fmul_rd(0.9f, thr));
+        const float cdown = __fdiv_ru(ct, __fmul_rd(0.9f, thr));
         const float nthr = -thr;
         for (int pr = warp; pr < len; pr += T / 32) {
             if (*(volatile int*)&H.nedges >= ecap) break;
             const float4 a = box[pr];
+            const float hp = __fsub_ru(a.w, a.y);
             const float xe = __fadd_ru(a.x, __fmul_ru(ct, __fsub_ru(a.z, a.x)));
-            const int cend = bstart[sp_bin_end<YPP_BSP_BINS>(xe, xmin, inv) + 1];
+            const float yu = __fadd_ru(a.y, __fmul_ru(ct, hp));
+            const float yd = __fsub_rd(a.y, __fmul_ru(cdown, hp));
+            const int xb0 = sp_bin<SD>(a.x, xmin, inv), xb1 = sp_bin_end<SD>(xe, xmin, inv);
+            const int yb0 = sp_bin<SD>(yd, ymin, invy), yb1 = sp_bin_end<SD>(yu, ymin, invy);
             const float ta = __fmul_rn(nthr, fabsf(ypp_area(a)));
             const int ra = rk[pr];
-            for (int c = pr + 1 + lane; c < cend; c += 32) {
-                const float4 bq = box[c];
-                const float D = __fadd_rn(pair_g(a, ta, bq, c1k, scale), __fmul_rn(nthr, fabsf(ypp_area(bq))));
-                if (D < -Bseg) continue;
-                const int rb = rk[c];
-                bool dead = D > Bseg;
-                if (!dead) {
-                    const bool a_first = ra < rb;
-                    const float4 hi = a_first ? a : bq, lo = a_first ? bq : a;
-                    dead = pair_exact(hi, ypp_area(hi), lo, thr, kFma ? 1 : 0);
-                }
-                if (dead) {
-                    const int e = atomicAdd(&H.nedges, 1);
-                    if (e < ecap) edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
+            for (int xb = xb0; xb <= xb1; ++xb) {
+                int c0 = bstart[xb * SD + yb0];
+                const int c1 = bstart[xb * SD + yb1 + 1];
+                if (xb == xb0) c0 = max(c0, pr + 1);                 // my own column: only what comes after me
+                for (int c = c0 + lane; c < c1; c += 32) {
+                    const float4 bq = box[c];
+                    const float D = __fadd_rn(pair_g(a, ta, bq, c1k, scale), __fmul_rn(nthr, fabsf(ypp_area(bq))));
+                    if (D < -Bseg) continue;
+                    const int rb = rk[c];
+                    bool dead = D > Bseg;
+                    if (!dead) {
+                        const bool a_first = ra < rb;
+                        const float4 hi = a_first ? a : bq, lo = a_first ? bq : a;
+                        dead = pair_exact(hi, ypp_area(hi), lo, thr, kFma ? 1 : 0);
+                    }
+                    if (dead) {
+                        const int e = atomicAdd(&H.nedges, 1);
+                        if (e < ecap) edges[e] = ((u32)min(ra, rb) << 16) | (u32)max(ra, rb);
+                    }
                 }
             }
         }

@@ -159,7 +159,7 @@ def run_reference(args):
     O.set_num_threads(cores)
     w = synth.WORKLOADS[args.workload]
     anchors = synth.workload_anchors(w)
-    sample = max(16, cores)
+    sample = w["batch"]                         # one step = one batch of the workload, as on the GPU arm
     mu = 0.0 if args.regime == "dense" else -5.0
     ring = [[h.numpy() for h in synth.make_heads(sample, w["nc"], w["grids"], A=w["A"], g=2000 + i, mu_obj=mu)]
             for i in range(2)]

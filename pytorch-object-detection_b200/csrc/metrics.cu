@@ -136,128 +136,6 @@ ypp_bbox_iou_kernel(const float4* __restrict__ a, int na, const float4* __restri
     out[k] = res;
 }
 
-// ------------------------------------------------------------------ stable LSD radix sort
-#define RS_THREADS 256
-#define RS_ITEMS 8
-#define RS_TILE (RS_THREADS * RS_ITEMS)
-
-__global__ void __launch_bounds__(RS_THREADS)
-rs_hist_kernel(const u64* __restrict__ keys, long long n, const long long* __restrict__ n_dev, int shift,
-               int* __restrict__ counts, int nblocks)
-{
-    __shared__ int h[256];
-    if (n_dev) n = min(n, *n_dev);               // the launch is sized for the bound n; the count lives on the device
-    h[threadIdx.x] = 0;
-    __syncthreads();
-    const long long base = (long long)blockIdx.x * RS_TILE;
-    for (int it = 0; it < RS_ITEMS; ++it) {
-        const long long i = base + it * RS_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&h[(int)((keys[i] >> shift) & 255ull)], 1);
-    }
-    __syncthreads();
-    counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
-}
-
-// exclusive scan over the digit-major [256][nblocks] table, one CTA: warp w owns a contiguous 1/32 of the table and
-// walks it 32 entries at a time (coalesced; the loads do not depend on the running carry, only the shuffles do), after
-// one reduction pass has told it where its part starts (the chunked version - a block scan with three barriers per
-// 1024 entries - took 44 us on 27 k entries, 220 us per sort)
-__global__ void __launch_bounds__(1024)
-rs_scan_kernel(int* __restrict__ counts, int nblocks, long long n, const long long* __restrict__ n_dev)
-{
-    __shared__ int warp_tot[32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // the launch is sized for the bound n; with the count on the device only the blocks that hold keys have columns
-    // worth scanning (the others' counts are never read by their scatter blocks either)
-    if (n_dev) n = min(n, *n_dev);
-    const int nb = n_dev ? (int)((n + RS_TILE - 1) / RS_TILE) : nblocks;
-    const long long total = 256LL * nb;
-    auto at = [&](long long e) -> int& { return counts[(e / nb) * nblocks + (e % nb)]; };   // logical entry e = digit * nb + block
-    const long long S = ((total + 31) / 32 + 31) / 32 * 32;                 // entries per warp, a multiple of 32
-    const long long a = min(total, (long long)warp * S), b = min(total, a + S);
-    int sum = 0;
-#pragma unroll 8
-    for (long long i = a + lane; i < b; i += 32) sum += at(i);
-    sum = __reduce_add_sync(YPP_FULL_MASK, sum);
-    if (lane == 0) warp_tot[warp] = sum;
-    __syncthreads();
-    int carry = 0;
-    for (int w = 0; w < warp; ++w) carry += warp_tot[w];
-    // 1024 entries per round: all 32 loads of a lane are issued before the first shuffle (one L2 round trip per round,
-    // not per 32 entries)
-    for (long long base = a; base < b; base += 1024) {
-        int v[32];
-#pragma unroll
-        for (int k = 0; k < 32; ++k) { const long long i = base + k * 32 + lane; v[k] = i < b ? at(i) : 0; }
-#pragma unroll
-        for (int k = 0; k < 32; ++k) {
-            const long long i = base + k * 32 + lane;
-            int inc = v[k];
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
-            if (i < b) at(i) = carry + inc - v[k];
-            carry += __shfl_sync(YPP_FULL_MASK, inc, 31);
-        }
-    }
-}
-
-__global__ void __launch_bounds__(RS_THREADS)
-rs_scatter_kernel(const u64* __restrict__ kin, const u32* __restrict__ vin, u64* __restrict__ kout, u32* __restrict__ vout,
-                  long long n, const long long* __restrict__ n_dev, int shift, const int* __restrict__ offsets, int nblocks)
-{
-    __shared__ int wc[RS_THREADS / 32][256];
-    __shared__ int dbase[256];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (n_dev) n = min(n, *n_dev);
-    if ((long long)blockIdx.x * RS_TILE >= n) return;
-    dbase[tid] = offsets[(size_t)tid * nblocks + blockIdx.x];
-    const long long base = (long long)blockIdx.x * RS_TILE;
-    for (int it = 0; it < RS_ITEMS; ++it) {
-        for (int w = 0; w < RS_THREADS / 32; ++w) wc[w][tid] = 0;
-        __syncthreads();
-        const long long i = base + it * RS_THREADS + tid;
-        const bool ok = i < n;
-        u64 k = 0;
-        int d = -1 - lane;
-        if (ok) { k = kin[i]; d = (int)((k >> shift) & 255ull); }
-        const unsigned peers = __match_any_sync(YPP_FULL_MASK, d);
-        const int rank = __popc(peers & ((1u << lane) - 1u));
-        if (ok && rank == 0) wc[warp][d] = __popc(peers);
-        __syncthreads();
-        {   // thread tid owns digit tid: turn per-warp counts into destinations
-            int run = dbase[tid];
-            for (int w = 0; w < RS_THREADS / 32; ++w) { const int t = wc[w][tid]; wc[w][tid] = run; run += t; }
-            dbase[tid] = run;
-        }
-        __syncthreads();
-        if (ok) {
-            const int dst = wc[warp][d] + rank;
-            kout[dst] = k;
-            vout[dst] = vin[i];
-        }
-        __syncthreads();
-    }
-}
-
-struct RsBuffers { u64* k[2]; u32* v[2]; int* counts; };
-
-// sorts (k[0], v[0]) over bits [0, nbits); returns which buffer holds the result
-int rs_sort(const RsBuffers& rb, long long n, int nbits, cudaStream_t st, const long long* n_dev = nullptr)
-{
-    int cur = 0;
-    if (n <= 0) return cur;
-    const int nblocks = (int)((n + RS_TILE - 1) / RS_TILE);
-    for (int shift = 0; shift < nbits; shift += 8) {
-        rs_hist_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], n, n_dev, shift, rb.counts, nblocks);
-        rs_scan_kernel<<<1, 1024, 0, st>>>(rb.counts, nblocks, n, n_dev);
-        rs_scatter_kernel<<<nblocks, RS_THREADS, 0, st>>>(rb.k[cur], rb.v[cur], rb.k[cur ^ 1], rb.v[cur ^ 1], n, n_dev, shift,
-                                                          rb.counts, nblocks);
-        ypp_count_launch(3);
-        cur ^= 1;
-    }
-    return cur;
-}
-
 // ------------------------------------------------------------------ matching
 
 // class ids that are not integers in [0, nc) can never equal a loop class c (:370-375): marker nc
@@ -282,48 +160,99 @@ __device__ __forceinline__ float map_iou(const float* a, const float* b)
     return __fdiv_rn(inter, uni);
 }
 
-// lower bound by a whole warp: 32 probes per round instead of one (a lone thread's binary search over 200 k keys is 18
-// dependent global loads, ~20 us at the head of every class's CTA); every lane returns the same answer
-__device__ __forceinline__ long long warp_lower_bound_u64(const u64* __restrict__ a, long long n, u64 key)
+// lanes of the warp that hold the same 8-bit digit (eight ballots; lanes with ok == false belong to no group)
+__device__ __forceinline__ u32 same_digit_lanes(int v, bool ok)
 {
-    const int lane = threadIdx.x & 31;
-    long long lo = 0, hi = n;                                  // the answer lies in [lo, hi]
-    while (hi > lo) {
-        const long long step = (hi - lo + 31) / 32;
-        const long long p = lo + lane * step;
-        const bool less = p < hi && a[p] < key;                // a prefix of the lanes
-        const int c = __popc(__ballot_sync(YPP_FULL_MASK, less));
-        if (c == 0) { hi = lo; break; }
-        const long long last = lo + (long long)(c - 1) * step;  // a[last] < key <= a[last + step] (or the end)
-        hi = min(hi, last + step);
-        lo = last + 1;
+    u32 peers = __ballot_sync(YPP_FULL_MASK, ok);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const bool bit = (v >> i) & 1;
+        const u32 bal = __ballot_sync(YPP_FULL_MASK, bit);
+        peers &= bit ? bal : ~bal;
     }
-    return lo;
+    return peers;
 }
 
-// one CTA per class: cumulative precision/recall over the class's detections (sorted by score, every one with its TP
-// flag in bit 0 of its sort value: matched where its image lives), envelope, AP.  The class's ground-truth count comes
-// from gt_per_class; K is read from *n_dev when given; classes c_lo + blockIdx.x.
-// term[] (K floats) receives, at the class's own ranks, first the rank of its t-th true positive and then that
-// true positive's contribution to the AP sum.
+// One stable LSD pass (8 bits at `shift`) over items [0, len) of a class, by the whole CTA: warp w owns the contiguous
+// ranks [w L, (w+1) L) and walks them 32 at a time, so "warp, then step, then lane" is the input order; counters per
+// (digit, warp) make the scatter stable.  tab: 256 x 33 ints of shared memory.
 #define AP_THREADS 1024
+#define AP_TAB_PITCH 33
+__device__ void cta_radix_pass(const u64* __restrict__ src, u64* __restrict__ dst, long long len, long long L, int shift,
+                               int* tab, int* warp_tot)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 256 * AP_TAB_PITCH; i += AP_THREADS) tab[i] = 0;
+    __syncthreads();
+    const long long r_begin = min(len, (long long)warp * L), r_end = min(len, r_begin + L);
+    for (long long r = r_begin + lane; r < r_end; r += 32)
+        atomicAdd(&tab[(int)((src[r] >> shift) & 255ull) * AP_TAB_PITCH + warp], 1);       // only this warp touches column `warp`
+    __syncthreads();
+    {   // exclusive scan in (digit, warp) order: thread t owns the 8 entries digit = t / 4, warps 8 (t % 4) ..
+        const int d = tid >> 2, w0 = (tid & 3) * 8;
+        int v[8], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { v[k] = tab[d * AP_TAB_PITCH + w0 + k]; sum += v[k]; }
+        int inc = sum;
+#pragma unroll
+        for (int q = 1; q < 32; q <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, q); if (lane >= q) inc += o; }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        int run = inc - sum;
+        for (int w = 0; w < warp; ++w) run += warp_tot[w];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { tab[d * AP_TAB_PITCH + w0 + k] = run; run += v[k]; }
+    }
+    __syncthreads();
+    for (long long r0 = r_begin; r0 < r_end; r0 += 32) {
+        const long long r = r0 + lane;
+        const bool ok = r < r_end;
+        u64 k = 0;
+        int d = 0;
+        if (ok) { k = src[r]; d = (int)((k >> shift) & 255ull); }
+        const u32 peers = same_digit_lanes(d, ok);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        int base = 0;
+        if (ok) base = tab[d * AP_TAB_PITCH + warp];
+        __syncwarp();
+        if (ok) {
+            if (rank == 0) tab[d * AP_TAB_PITCH + warp] = base + __popc(peers);
+            dst[base + rank] = k;
+        }
+        __syncwarp();
+    }
+    __syncthreads();                                   // the block's global writes are visible to the block after it
+}
+
+// one CTA per class c_lo + blockIdx.x.  Its items (u64: (~enc(score)) << 1 | tp, in input order) lie at
+// [table[class row, block 0], start of the next class) of `items`; they are sorted here by the 32 score bits (four stable
+// passes, ending in `items` again), then: cumulative precision/recall, envelope, AP.  The class's ground-truth count comes
+// from gt_per_class.  term[] / prec[] (one float per item) are scratch at the class's own positions.
 __global__ void __launch_bounds__(AP_THREADS)
-map_ap_kernel(long long K, const long long* __restrict__ n_dev, int nc, int c_lo,
-              const u64* __restrict__ dkeys, const u32* __restrict__ dvals, const long long* __restrict__ gt_per_class,
+map_ap_kernel(const int* __restrict__ table, int nblocks, int nc, int c_lo, int c_hi,
+              u64* __restrict__ items, u64* __restrict__ items2, const long long* __restrict__ gt_per_class,
               float* __restrict__ prec, float* __restrict__ term, float* __restrict__ class_ap, float* __restrict__ per_class)
 {
+    __shared__ int tab[256 * AP_TAB_PITCH];
     __shared__ int warp_i[32];
     __shared__ float warp_f[32];
-    __shared__ long long s_lo, s_hi, s_ng;
     __shared__ int carry_i;
     __shared__ float carry_f;
     const int c = c_lo + blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (n_dev) K = min(K, *n_dev);
-    if (warp == 0) {
-        const long long a = warp_lower_bound_u64(dkeys, K, (u64)c << 32);
-        const long long b = warp_lower_bound_u64(dkeys, K, (u64)(c + 1) << 32);
-        if (lane == 0) { s_lo = a; s_hi = b; s_ng = gt_per_class[c]; carry_i = 0; }
+    const long long s_lo = table[(size_t)(c - c_lo) * nblocks], s_hi = table[(size_t)(c - c_lo + 1) * nblocks];   // the table has one entry more: the total
+    const long long s_ng = gt_per_class[c];
+    if (tid == 0) carry_i = 0;
+    if (s_ng != 0 && s_hi > s_lo) {
+        const long long len = s_hi - s_lo;
+        const long long L = ((len + 31) / 32 + 31) / 32 * 32;
+        u64* a = items + s_lo;
+        u64* b = items2 + s_lo;
+        for (int pass = 0; pass < 4; ++pass) {
+            cta_radix_pass(a, b, len, L, 1 + 8 * pass, tab, warp_i);
+            u64* t = a; a = b; b = t;
+        }
     }
+    const u64* __restrict__ sorted = items;            // four passes: back where they started
     __syncthreads();
     const long long lo = s_lo, hi = s_hi;
     const long long ng = s_ng;
@@ -340,7 +269,7 @@ map_ap_kernel(long long K, const long long* __restrict__ n_dev, int nc, int c_lo
         const long long pb = p0 + (long long)tid * IT;
         int t[IT], tsum = 0;
 #pragma unroll
-        for (int q = 0; q < IT; ++q) { t[q] = (pb + q < hi) ? (int)(dvals[pb + q] & 1u) : 0; tsum += t[q]; }
+        for (int q = 0; q < IT; ++q) { t[q] = (pb + q < hi) ? (int)(sorted[pb + q] & 1ull) : 0; tsum += t[q]; }
         int inc = tsum;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d); if (lane >= d) inc += o; }
@@ -399,7 +328,8 @@ map_ap_kernel(long long K, const long long* __restrict__ n_dev, int nc, int c_lo
     // The terms are independent: every thread computes some (same roundings as the reference's one-by-one
     // evaluation); only the fp32 ADDITIONS stay sequential, in rank order, so the sum rounds as the reference's:
     // the terms are staged in shared memory CH at a time and one thread adds them up.
-    __shared__ float stage[CH];
+    static_assert(CH * sizeof(float) <= sizeof(tab), "the staged terms reuse the radix table");
+    float* stage = reinterpret_cast<float*>(tab);                  // the sort is long over
     float ap = 0.0f;
     for (int t0 = 0; t0 < n_tp; t0 += CH) {
         for (int t = t0 + tid; t < min(n_tp, t0 + CH); t += AP_THREADS) {
@@ -495,22 +425,18 @@ __global__ void map_flags_kernel(const float* __restrict__ det, long long K, int
     if (triples) { triples[d * 3] = score; triples[d * 3 + 1] = cf; triples[d * 3 + 2] = tp ? 1.0f : 0.0f; }
 }
 
-// sort keys of ALL the triples of one buffer (the single-process case: nothing to select)
-__global__ void map_triple_keys_kernel(const float* __restrict__ tr, long long K, int nc, u64* __restrict__ keys, u32* __restrict__ vals)
-{
-    const long long d = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= K) return;
-    keys[d] = ((u64)map_cls(tr[d * 3 + 1], nc) << 32) | (u64)(~ypp_enc(tr[d * 3]));
-    vals[d] = tr[d * 3 + 2] != 0.0f ? 1u : 0u;
-}
-
 // ---- AP from flagged detections gathered from every rank (M2), for the classes [c_lo, c_hi) ----------------------
 // Input: n_seg segments of seg_stride triples (score, cls, tp) each, of which the first seg_count[s] are valid
-// (the padded all-gather buffer as it is).  Selection in input order (block counts -> scan -> scatter), so the
-// stable sort keeps ties in segment-then-row order: the order one process would have seen.
+// (the padded all-gather buffer as it is).  Three steps, four launches:
+//   select   the triples of my classes, GROUPED BY CLASS and in input order inside a class (per-(class, block) counts ->
+//            one scan in class-major order -> scatter): item = (~enc(score)) << 1 | tp, one u64 each;
+//   sort+AP  one CTA per class: stable LSD radix sort of its own items by the 32 score bits (ties keep the input order:
+//            segment after segment, row after row - the order one process would have seen), then the precision /
+//            recall scans and the AP, all in the same kernel.
 #define SEL_THREADS 256
 #define SEL_ITEMS 8
 #define SEL_TILE (SEL_THREADS * SEL_ITEMS)
+#define SEL_MAX_CLASSES 128            /* classes per call the shared-memory counters hold; more: the call is split */
 __device__ __forceinline__ bool sel_take(const float* __restrict__ tr, long long i, long long seg_stride,
                                          const long long* __restrict__ seg_count, int nc, int c_lo, int c_hi, u32& cls)
 {
@@ -520,22 +446,23 @@ __device__ __forceinline__ bool sel_take(const float* __restrict__ tr, long long
     return cls >= (u32)c_lo && cls < (u32)c_hi;
 }
 
+// table[(c - c_lo) * nblocks + block] = items of class c in this block's tile
 __global__ void __launch_bounds__(SEL_THREADS)
 map_select_count_kernel(const float* __restrict__ tr, long long n, long long seg_stride, const long long* __restrict__ seg_count,
-                        int nc, int c_lo, int c_hi, int* __restrict__ block_count)
+                        int nc, int c_lo, int c_hi, int* __restrict__ table, int nblocks)
 {
-    __shared__ int wsum[SEL_THREADS / 32];
+    __shared__ int cnt[SEL_MAX_CLASSES];
+    const int ncls = c_hi - c_lo;
+    for (int c = threadIdx.x; c < ncls; c += SEL_THREADS) cnt[c] = 0;
+    __syncthreads();
     const long long base = (long long)blockIdx.x * SEL_TILE;
-    int cnt = 0;
     for (int it = 0; it < SEL_ITEMS; ++it) {
         const long long i = base + (long long)it * SEL_THREADS + threadIdx.x;
         u32 cls;
-        if (i < n && sel_take(tr, i, seg_stride, seg_count, nc, c_lo, c_hi, cls)) ++cnt;
+        if (i < n && sel_take(tr, i, seg_stride, seg_count, nc, c_lo, c_hi, cls)) atomicAdd(&cnt[cls - c_lo], 1);
     }
-    cnt = __reduce_add_sync(YPP_FULL_MASK, cnt);
-    if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = cnt;
     __syncthreads();
-    if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < SEL_THREADS / 32; ++w) t += wsum[w]; block_count[blockIdx.x] = t; }
+    for (int c = threadIdx.x; c < ncls; c += SEL_THREADS) table[(size_t)c * nblocks + blockIdx.x] = cnt[c];
 }
 
 // exclusive scan of the per-block counts of the selection, one CTA
@@ -565,40 +492,46 @@ block_offsets_kernel(int* __restrict__ counts, int n)
     }
 }
 
-// block_count holds the exclusive offsets now (block_offsets_kernel); the last block also publishes the total
+// the table holds exclusive offsets now (block_offsets_kernel over the class-major table): entry (c, block) is where
+// this block's items of class c go.  Stable inside the block: 256 items at a time, rank among the lanes of the same
+// class by MATCH.ANY, per-(warp, class) counts turned into offsets by the thread that owns the class.
 __global__ void __launch_bounds__(SEL_THREADS)
 map_select_scatter_kernel(const float* __restrict__ tr, long long n, long long seg_stride, const long long* __restrict__ seg_count,
-                          int nc, int c_lo, int c_hi, const int* __restrict__ block_off, u64* __restrict__ keys,
-                          u32* __restrict__ vals, long long* __restrict__ n_sel)
+                          int nc, int c_lo, int c_hi, const int* __restrict__ table, int nblocks, u64* __restrict__ items)
 {
-    __shared__ int wsum[SEL_THREADS / 32];
+    __shared__ int run[SEL_MAX_CLASSES];
+    __shared__ int wc[SEL_THREADS / 32][SEL_MAX_CLASSES];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ncls = c_hi - c_lo;
+    for (int c = tid; c < ncls; c += SEL_THREADS) run[c] = table[(size_t)c * nblocks + blockIdx.x];
     const long long base = (long long)blockIdx.x * SEL_TILE;
-    int run = block_off[blockIdx.x];
     for (int it = 0; it < SEL_ITEMS; ++it) {
+        for (int c = tid; c < ncls; c += SEL_THREADS)
+            for (int w = 0; w < SEL_THREADS / 32; ++w) wc[w][c] = 0;
+        __syncthreads();
         const long long i = base + (long long)it * SEL_THREADS + tid;
         u32 cls = 0;
         const bool take = i < n && sel_take(tr, i, seg_stride, seg_count, nc, c_lo, c_hi, cls);
-        const u32 m = __ballot_sync(YPP_FULL_MASK, take);
-        if (lane == 0) wsum[warp] = __popc(m);
+        const int key = take ? (int)(cls - c_lo) : -1 - lane;                 // lanes without an item match nobody
+        const unsigned peers = __match_any_sync(YPP_FULL_MASK, key);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        if (take && rank == 0) wc[warp][key] = __popc(peers);
         __syncthreads();
-        int before = 0, tot = 0;
-        for (int w = 0; w < SEL_THREADS / 32; ++w) { const int t = wsum[w]; if (w < warp) before += t; tot += t; }
-        if (take) {
-            const int dst = run + before + __popc(m & ((1u << lane) - 1u));
-            keys[dst] = ((u64)cls << 32) | (u64)(~ypp_enc(tr[i * 3]));
-            vals[dst] = tr[i * 3 + 2] != 0.0f ? 1u : 0u;
+        for (int c = tid; c < ncls; c += SEL_THREADS) {                       // per-warp counts -> destinations, in warp order
+            int r = run[c];
+            for (int w = 0; w < SEL_THREADS / 32; ++w) { const int t = wc[w][c]; wc[w][c] = r; r += t; }
+            run[c] = r;
         }
-        run += tot;
+        __syncthreads();
+        if (take) items[wc[warp][key] + rank] = ((u64)(~ypp_enc(tr[i * 3])) << 1) | (tr[i * 3 + 2] != 0.0f ? 1ull : 0ull);
         __syncthreads();
     }
-    if (blockIdx.x == gridDim.x - 1 && tid == 0) *n_sel = run;
 }
 
 struct MapWs {
-    RsBuffers det;
+    u64* items[2];
     int* best_g; float* prec; float* term; float* class_ap; float* triples;
-    u64* claim; unsigned long long* gt_per_class; int* sel_blocks; long long* n_sel; int* unsorted;
+    u64* claim; unsigned long long* gt_per_class; int* table; int* unsorted;
     size_t total;
 };
 
@@ -609,10 +542,9 @@ MapWs make_map_ws(void* base, long long G, long long K, int nc)
     size_t off = 0;
     auto take = [&](size_t bytes) { char* r = p + off; off += ypp_align_up(bytes ? bytes : 8, 256); return r; };
     const long long Kp = K > 0 ? K : 1, Gp = G > 0 ? G : 1;
-    const size_t nbk = (size_t)((Kp + RS_TILE - 1) / RS_TILE);
-    w.det.k[0] = (u64*)take(8 * Kp); w.det.k[1] = (u64*)take(8 * Kp);
-    w.det.v[0] = (u32*)take(4 * Kp); w.det.v[1] = (u32*)take(4 * Kp);
-    w.det.counts = (int*)take(4 * 256 * nbk);
+    const size_t nb = (size_t)((Kp + SEL_TILE - 1) / SEL_TILE);
+    const size_t ncl = (size_t)(nc < SEL_MAX_CLASSES ? (nc > 0 ? nc : 1) : SEL_MAX_CLASSES);
+    w.items[0] = (u64*)take(8 * Kp); w.items[1] = (u64*)take(8 * Kp);
     w.best_g = (int*)take(4 * Kp);
     w.prec = (float*)take(4 * Kp);
     w.term = (float*)take(4 * Kp);
@@ -621,13 +553,11 @@ MapWs make_map_ws(void* base, long long G, long long K, int nc)
     w.claim = (u64*)take(8 * Gp);
     w.gt_per_class = (unsigned long long*)take(8 * (size_t)(nc > 0 ? nc : 1) + 8);     // + the `unsorted` word: one memset
     w.unsorted = (int*)(w.gt_per_class + (nc > 0 ? nc : 1));
-    w.sel_blocks = (int*)take(4 * ((size_t)((Kp + SEL_TILE - 1) / SEL_TILE) + 1));
-    w.n_sel = (long long*)take(8);
+    w.table = (int*)take(4 * (ncl * nb + 1));
     w.total = off;
     return w;
 }
 
-int bits_for(int n) { int b = 1; while ((1 << b) < n) ++b; return b; }
 
 // ---- detection writers: the integer columns of the pred-file / COCO rows -------------------
 // make_pred_file_yolov3.py:73-86, yolo2coco_pred_file_yolov3.py:83-100.  The reference works on
@@ -787,6 +717,27 @@ static int launch_m1(const MapWs& w, const float* gt, long long G, const float* 
     return YPP_OK;
 }
 
+// M2 for the classes [c_lo, c_hi) of n triples: select grouped by class -> per-class sort + AP (<= SEL_MAX_CLASSES per round)
+static void launch_m2(const MapWs& w, const float* triples, long long n, long long seg_stride, const long long* seg_count,
+                      const long long* gpc, int nc, int c_lo, int c_hi, float* per_class, cudaStream_t st)
+{
+    const int nb = (int)((max(n, 1LL) + SEL_TILE - 1) / SEL_TILE);
+    for (int c0 = c_lo; c0 < c_hi; c0 += SEL_MAX_CLASSES) {
+        const int c1 = min(c_hi, c0 + SEL_MAX_CLASSES), ncls = c1 - c0;
+        if (n > 0) {
+            cudaMemsetAsync(w.table + (size_t)ncls * nb, 0, 4, st);           // the extra entry: after the scan it holds the total
+            map_select_count_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c0, c1, w.table, nb);
+            block_offsets_kernel<<<1, 1024, 0, st>>>(w.table, ncls * nb + 1);
+            map_select_scatter_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c0, c1, w.table, nb, w.items[0]);
+            ypp_count_launch(3);
+        } else {
+            cudaMemsetAsync(w.table, 0, 4 * ((size_t)ncls * nb + 1), st);
+        }
+        map_ap_kernel<<<ncls, AP_THREADS, 0, st>>>(w.table, nb, nc, c0, c1, w.items[0], w.items[1], gpc, w.prec, w.term, w.class_ap, per_class);
+        ypp_count_launch(1);
+    }
+}
+
 // mean_average_precision in one process = M1, then M2 over every class of the one buffer
 int ypp_launch_map(const float* gt, long long G, const float* det, long long K, int nc, float iou_thr,
                    void* ws, size_t ws_bytes, unsigned char* tp, float* per_class, float* map,
@@ -795,16 +746,9 @@ int ypp_launch_map(const float* gt, long long G, const float* det, long long K, 
     MapWs w = make_map_ws(ws, G, K, nc);
     if (ws_bytes < w.total) { ypp_set_error("map_match: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
     launch_m1(w, gt, G, det, K, nc, iou_thr, tp, w.triples, w.gt_per_class, st);
-    int dcur = 0;
-    if (K > 0) {
-        map_triple_keys_kernel<<<(unsigned)((K + 255) / 256), 256, 0, st>>>(w.triples, K, nc, w.det.k[0], w.det.v[0]);
-        ypp_count_launch(1);
-        dcur = rs_sort(w.det, K, 32 + bits_for(nc + 1), st);
-    }
-    map_ap_kernel<<<nc, AP_THREADS, 0, st>>>(K, nullptr, nc, 0, w.det.k[dcur], w.det.v[dcur], (const long long*)w.gt_per_class,
-                                             w.prec, w.term, w.class_ap, per_class);
+    launch_m2(w, w.triples, K, K > 0 ? K : 1, nullptr, (const long long*)w.gt_per_class, nc, 0, nc, per_class, st);
     map_mean_kernel<<<1, 32, 0, st>>>(nc, w.class_ap, 1, map);
-    ypp_count_launch(2);
+    ypp_count_launch(1);
     return ypp_check_launch("map_match");
 }
 
@@ -823,21 +767,7 @@ int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_str
 {
     MapWs w = make_map_ws(ws, 0, n, nc);
     if (ws_bytes < w.total) { ypp_set_error("map_ap_from_flags: workspace %zu < %zu", ws_bytes, w.total); return YPP_E_WORKSPACE; }
-    if (n > 0) {
-        const int nb = (int)((n + SEL_TILE - 1) / SEL_TILE);
-        map_select_count_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks);
-        block_offsets_kernel<<<1, 1024, 0, st>>>(w.sel_blocks, nb);
-        // the scan is exclusive: the last block adds its own count to publish the total
-        map_select_scatter_kernel<<<nb, SEL_THREADS, 0, st>>>(triples, n, seg_stride, seg_count, nc, c_lo, c_hi, w.sel_blocks,
-                                                              w.det.k[0], w.det.v[0], w.n_sel);
-        ypp_count_launch(3);
-    } else {
-        cudaMemsetAsync(w.n_sel, 0, 8, st);
-    }
-    const int dcur = rs_sort(w.det, n, 32 + bits_for(nc + 1), st, w.n_sel);
-    map_ap_kernel<<<c_hi - c_lo, AP_THREADS, 0, st>>>(n, w.n_sel, nc, c_lo, w.det.k[dcur], w.det.v[dcur], gt_per_class,
-                                                      w.prec, w.term, w.class_ap, per_class);
-    ypp_count_launch(1);
+    launch_m2(w, triples, n, seg_stride, seg_count, gt_per_class, nc, c_lo, c_hi, per_class, st);
     return ypp_check_launch("map_ap_from_flags");
 }
 

@@ -788,9 +788,13 @@ def map_epoch_extra(args, torch, dist, engine, synth, dev, rank, world, w, ancho
     for mode in ("flags", "rows"):
         epoch(mode)
         acc_ms, end_ms, val, pc = epoch(mode)
+        # the epoch is ONE interval per rank (barrier -> result read), max over ranks; the two parts are maxed separately
+        # for information only (a rank that finishes accumulating early waits inside the first collective: its "end" is
+        # longer by the skew, so max(accumulate) + max(end) counts the skew twice)
+        tot_ms = max_over_ranks(acc_ms + end_ms)
         acc_ms, end_ms = max_over_ranks(acc_ms), max_over_ranks(end_ms)
-        res[mode] = {"accumulate_ms": acc_ms, "epoch_end_ms": end_ms, "epoch_ms": acc_ms + end_ms, "mAP": val,
-                     "images_per_s": n_total / ((acc_ms + end_ms) * 1e-3), "per_class": pc}
+        res[mode] = {"accumulate_ms": acc_ms, "epoch_end_ms": end_ms, "epoch_ms": tot_ms, "mAP": val,
+                     "images_per_s": n_total / (tot_ms * 1e-3), "per_class": pc}
     gt_l, det_l = m.local_rows()
     # the same epoch on one GPU, in this run: this rank's own images, no exchange
     Single = MAPv3 if w["kind"] == "v3" else MAPv2

@@ -204,12 +204,13 @@ __device__ void cta_radix_pass(const u64* __restrict__ src, u64* __restrict__ ds
         for (int k = 0; k < 8; ++k) { tab[d * AP_TAB_PITCH + w0 + k] = run; run += v[k]; }
     }
     __syncthreads();
+    u64 kn = (r_begin + lane < r_end) ? src[r_begin + lane] : 0ull;
     for (long long r0 = r_begin; r0 < r_end; r0 += 32) {
         const long long r = r0 + lane;
         const bool ok = r < r_end;
-        u64 k = 0;
-        int d = 0;
-        if (ok) { k = src[r]; d = (int)((k >> shift) & 255ull); }
+        const u64 k = kn;
+        kn = (r + 32 < r_end) ? src[r + 32] : 0ull;          // the next step's key is in flight during this step's ballots
+        const int d = ok ? (int)((k >> shift) & 255ull) : 0;
         const u32 peers = same_digit_lanes(d, ok);
         const int rank = __popc(peers & ((1u << lane) - 1u));
         int base = 0;

@@ -151,3 +151,28 @@ def test_oracle_head_conv_is_the_reference_layer(oracle):
     exact, bound = oracle.head_conv1x1(x.numpy(), conv.weight.detach().numpy())
     assert exact.shape == y.shape
     assert (np.abs(y - exact) <= 2.0 ** -20 * bound + 1e-7).all()
+
+
+def test_probe_word_arithmetic_survives_the_24_bit_wrap():
+    """RowAccumulator reads (count << 24 | append number mod 2^24) from pinned memory: the append number is
+    reconstructed relative to the number of appends issued, across the wrap."""
+    from ypp.engine import RowAccumulator
+    acc = RowAccumulator.__new__(RowAccumulator)     # the arithmetic only: no device, no pinned memory
+    acc.bound = 10 ** 12
+    for issued, reported in ((5, 3), (2 ** 24 + 7, 2 ** 24 + 2), (2 ** 24 + 3, 2 ** 24 - 4), (3 * 2 ** 24 + 1, 3 * 2 ** 24 + 1)):
+        acc._seq = issued
+        acc._host_np = [(12345 << 24) | (reported & 0xFFFFFF)]
+        assert RowAccumulator._arrived(acc) == (reported, 12345)
+        acc._booked = 1000
+        acc._booked_at = [0] * RowAccumulator.RING
+        acc._booked_at[reported % RowAccumulator.RING] = 400
+        acc.bound = 10 ** 12
+        RowAccumulator._refresh(acc)
+        assert acc.bound == 12345 + 600              # rows after that append + the worst case of the appends since
+    acc._seq = 200
+    acc._host_np = [(1 << 24) | 100]                 # 100 appends behind: older than the ring remembers -> ignored
+    acc.bound = 77
+    RowAccumulator._refresh(acc)
+    assert acc.bound == 77
+    acc._host_np = [0]
+    assert RowAccumulator._arrived(acc)[0] in (0, 200 - (200 & 0xFFFFFF))

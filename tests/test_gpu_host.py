@@ -134,3 +134,59 @@ def test_graph_keeps_its_own_workspace(cuda):
     assert torch.equal(res.keep_count, want_kc)
     assert torch.equal(res.det_rows[: want_rows.shape[0]], want_rows)
     del junk
+
+
+def test_pipeline_c_abi_directly(cuda):
+    """ypp_pipeline_* through ctypes, as a binding in another host language would use it: five batches submitted to a
+    3-deep pipeline (own workspace per slot, two alternating cursor words, a probe word in pinned memory), joined on the
+    caller's stream; rows, counts, cursor, tickets and the probe word against ypp_postprocess_append batch by batch."""
+    import ctypes
+    from ypp import _lib, engine, synth
+    L = _lib.lib()
+    B, nc, N = 4, 20, 10647
+    pp = engine.PostProcessor(nc, synth.YOLOV3_ANCHORS, 416, 0.25)
+    batches = [_heads(cuda, B, 960 + i, mu=(0.0 if i == 2 else -3.0)) for i in range(5)]
+    want = torch.cat([pp(h, img_idx_base=B * i).rows().clone() for i, h in enumerate(batches)])
+    h = ctypes.c_void_p()
+    assert L.ypp_pipeline_create(0, ctypes.byref(h)) == -1 and L.ypp_pipeline_create(9, ctypes.byref(h)) == -1
+    assert L.ypp_pipeline_create(3, ctypes.byref(h)) == 0
+    nbytes = L.ypp_workspace_bytes(B, N, nc)
+    ws = [torch.empty(nbytes, dtype=torch.uint8, device=cuda) for _ in range(3)]
+    keep = [torch.zeros(B, dtype=torch.int32, device=cuda) for _ in range(3)]
+    rows = torch.full((want.shape[0] + 64, 7), -7.0, device=cuda)
+    cur = torch.zeros(2, dtype=torch.int64, device=cuda)
+    word = torch.zeros(1, dtype=torch.int64).pin_memory()
+    probe = _lib.YppProbe(word.data_ptr(), 0)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ticket = ctypes.c_int64(-1)
+    keepalive = []
+    for i, heads in enumerate(batches):
+        slot = L.ypp_pipeline_next_slot(h)
+        assert slot == i % 3 and L.ypp_pipeline_stream(h, slot)
+        arr, hc, _, n_boxes = pp._scales(heads)
+        keepalive.append((arr, hc))
+        cfg = pp._cfg(B, 3)
+        probe.seq = i + 1
+        rc = L.ypp_pipeline_submit(h, ctypes.byref(cfg), arr, ws[slot].data_ptr(), nbytes, None, keep[slot].data_ptr(),
+                                   rows.data_ptr(), 7, rows.shape[0], cur.data_ptr() + 8 * (i & 1), cur.data_ptr() + 8 * ((i + 1) & 1),
+                                   ctypes.byref(probe), float(B * i), st, ctypes.byref(ticket))
+        assert rc == 0, L.ypp_last_error().decode()
+        assert ticket.value == i
+    assert L.ypp_pipeline_query(h, 99) == 0
+    assert L.ypp_pipeline_wait_ticket(h, 2) == 0 and L.ypp_pipeline_query(h, 2) == 1
+    assert L.ypp_pipeline_join(h, st) == 0
+    torch.cuda.synchronize()
+    n = want.shape[0]
+    assert cur[len(batches) & 1].item() == n
+    assert torch.equal(rows[:n], want) and bool((rows[n:] == -7).all())
+    assert int(word[0]) == (n << 24) | len(batches)
+    assert int(keep[(len(batches) - 1) % 3].sum()) == int(pp(batches[-1]).det_total)
+    assert all(L.ypp_pipeline_query(h, t) == 1 for t in range(5))
+    # argument errors: one cursor word twice, missing rows
+    arr, hc, _, _ = pp._scales(batches[0])
+    cfg = pp._cfg(B, 3)
+    assert L.ypp_pipeline_submit(h, ctypes.byref(cfg), arr, ws[0].data_ptr(), nbytes, None, None, rows.data_ptr(), 7, 8, cur.data_ptr(),
+                                 cur.data_ptr(), None, 0.0, st, None) == -1
+    assert L.ypp_pipeline_submit(h, ctypes.byref(cfg), arr, ws[0].data_ptr(), nbytes, None, None, None, 7, 8, cur.data_ptr(),
+                                 cur.data_ptr() + 8, None, 0.0, st, None) == -1
+    assert L.ypp_pipeline_destroy(h) == 0

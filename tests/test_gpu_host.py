@@ -190,3 +190,33 @@ def test_pipeline_c_abi_directly(cuda):
     assert L.ypp_pipeline_submit(h, ctypes.byref(cfg), arr, ws[0].data_ptr(), nbytes, None, None, None, 7, 8, cur.data_ptr(),
                                  cur.data_ptr() + 8, None, 0.0, st, None) == -1
     assert L.ypp_pipeline_destroy(h) == 0
+
+
+def test_batches_in_flight_with_changing_batch_sizes(cuda):
+    """The last batch of an epoch is smaller, and a loader may mix shapes: per-slot count buffers and workspaces are
+    re-made while earlier batches are still in flight; rows and order still equal the one-by-one result."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25, pipeline_depth=3)
+    seq = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25, pipeline_depth=1)
+    shapes = [(4, (52, 26, 13)), (4, (52, 26, 13)), (2, (52, 26, 13)), (6, (26, 13)), (1, (52, 26, 13)), (4, (52, 26, 13)), (3, (13,))]
+    batches, base = [], 0
+    for i, (B, grids) in enumerate(shapes):
+        heads = [h.to(cuda) for h in synth.make_heads(B, 20, list(grids), g=980 + i, mu_obj=-2.5)]
+        anchors = synth.YOLOV3_ANCHORS[:3 * len(grids)] if len(grids) == 3 else synth.YOLOV3_ANCHORS[-3 * len(grids):]
+        batches.append((heads, anchors, base))
+        base += B
+    want = []
+    for heads, anchors, b0 in batches:
+        seq.anchors = [list(map(float, a)) for a in anchors]
+        seq._plans.clear()
+        want.append(seq(heads, img_idx_base=b0).rows().clone())
+    want = torch.cat(want)
+    for rep in range(2):
+        acc = engine.RowAccumulator(cuda, 2)
+        for heads, anchors, b0 in batches:
+            pp.anchors = [list(map(float, a)) for a in anchors]
+            pp._plans.clear()
+            pp.accumulate(acc, [h.clone() for h in heads], img_idx_base=b0)
+        got = acc.view()
+        assert got.shape == want.shape and want.shape[0] > 50
+        assert torch.equal(got, want)

@@ -86,14 +86,13 @@ __device__ __forceinline__ float pair_g(const float4 a, const float ta, const fl
     return __fmaf_rn(c1k, __fmul_rn(w, hs), ta);
 }
 
-// box of global score rank r of image `ibase`: cxcywh -> xyxy exactly as nms_v3 does, plus the
-// coordinate trick's class offset when torchvision would apply it (S1 decided per image)
-__device__ __forceinline__ float4 rank_box(const YppWs& ws, size_t ibase, int r, bool trick, float step)
+// box of one segment position: S1's word for it holds the box index and the class.  cxcywh -> xyxy exactly as nms_v3
+// does, plus the coordinate trick's class offset when torchvision would apply it (S1 decided per image)
+__device__ __forceinline__ float4 pos_box(const YppWs& ws, size_t ibase, u64 g, bool trick, float step)
 {
-    const u64 k = ws.skeys[ibase + r];
-    float4 xy = ypp_xyxy(ws.box[ibase + ypp_key_idx(k)]);
+    float4 xy = ypp_xyxy(ws.box[ibase + ypp_key_idx(g)]);
     if (trick) {
-        const float off = __fmul_rn((float)ypp_key_cls(k), step);    // idxs.to(boxes) * (max_coordinate + 1)
+        const float off = __fmul_rn((float)ypp_key_cls(g), step);    // idxs.to(boxes) * (max_coordinate + 1)
         xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
     }
     return xy;
@@ -295,7 +294,7 @@ __device__ __forceinline__ void sp_pair(SegSmem& sm, const float4 a, const float
 }
 
 template <bool kFma>
-__device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size_t ibase, const int* __restrict__ grank,
+__device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size_t ibase, const u64* __restrict__ gpk,
                                         unsigned char* __restrict__ keepflag, const int len, const int b,
                                         const bool trick, const float step, const float thr)
 {
@@ -312,7 +311,7 @@ __device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size
         const int i = tid + u * YPP_NMSQ_THREADS;
         q[u] = make_float4(0.f, 0.f, 1.f, 1.f);
         if (i < len) {
-            q[u] = rank_box(ws, ibase, grank[i], trick, step);
+            q[u] = pos_box(ws, ibase, gpk[i], trick, step);
             const float bw = __fsub_rn(q[u].z, q[u].x), bh = __fsub_rn(q[u].w, q[u].y);
             const bool ok = bw > 0.0f && bh > 0.0f && bw < INFINITY && bh < INFINITY &&
                             fabsf(q[u].x) < INFINITY && fabsf(q[u].y) < INFINITY;
@@ -454,7 +453,7 @@ __device__ __noinline__ bool nms_sparse(SegSmem& sm, const YppWs& ws, const size
 #endif
     int kept = 0;
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS)
-        if (S.state[i] != 2) { keepflag[grank[i]] = 1; ++kept; }      // ne == 0: every state is still 0
+        if (S.state[i] != 2) { keepflag[ypp_gpk_rank(gpk[i])] = 1; ++kept; }      // ne == 0: every state is still 0
     kept = __reduce_add_sync(YPP_FULL_MASK, kept);
     if (lane == 0 && kept) atomicAdd(ws.keep_count + b, kept);
     return true;
@@ -479,7 +478,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const int s0 = seg_start[c], len = seg_start[c + 1] - s0;
     if (len <= 0 || len > YPP_WARP_SEG) return;
     const size_t ibase = (size_t)b * p.N;
-    const int* __restrict__ grank = p.ws.grank + ibase + s0;
+    const u64* __restrict__ gpk = p.ws.gpk + ibase + s0;
     unsigned char* __restrict__ keepflag = p.ws.keepflag + ibase;
     const float thr = p.iou_thr;
     const int union_fma = p.union_mode;
@@ -487,12 +486,12 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
     const float step = p.ws.img_step[b];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     if (kFast && thr >= 0.0f && len >= p.sparse_min_len) {        // uniform over the CTA
-        if (nms_sparse<kFma>(sm, p.ws, ibase, grank, keepflag, len, b, trick, step, thr)) return;
+        if (nms_sparse<kFma>(sm, p.ws, ibase, gpk, keepflag, len, b, trick, step, thr)) return;
         __syncthreads();
     }
     u32 amax_bits = 0, cmax_bits = 0;   // uint order == float order for non-negative floats; NaN sorts on top
     for (int i = tid; i < len; i += YPP_NMSQ_THREADS) {
-        const float4 q = rank_box(p.ws, ibase, grank[i], trick, step);
+        const float4 q = pos_box(p.ws, ibase, gpk[i], trick, step);
         const float ar = fabsf(ypp_area(q));
         sm.box[i] = q;
         sm.d.tb[i] = __fmul_rn(-thr, ar);
@@ -568,7 +567,7 @@ ypp_nms_seg_kernel(const __grid_constant__ YppNmsParams p)
             undecided = undecided && !(dead_now || keep_now);
         }
         total += __popc(K);
-        if (w == 0 && ((K >> lane) & 1u)) keepflag[grank[j]] = 1;
+        if (w == 0 && ((K >> lane) & 1u)) keepflag[ypp_gpk_rank(gpk[j])] = 1;
         if (T + 1 >= ntiles) break;
         // ---- broadcast my kept rows against the later columns (four column groups per sweep)
         const u32 Kw = K & wmask;
@@ -616,7 +615,7 @@ struct TileSmem {
 // Process one segment.  seg: boxes in score order (global memory), cache: shared staging for
 // the first `cache_cap` boxes, removed: bitmap words (>= (len+31)/32).
 template <int THREADS, bool kFast, bool kFma>
-__device__ void nms_segment(const float4* __restrict__ seg, const int* __restrict__ grank,
+__device__ void nms_segment(const float4* __restrict__ seg, const u64* __restrict__ gpk,
                             unsigned char* __restrict__ keepflag, int len,
                             float4* cache, int cache_cap, u32* removed, TileSmem& ts,
                             float thr, int union_fma)
@@ -690,14 +689,14 @@ __device__ void nms_segment(const float4* __restrict__ seg, const int* __restric
                 const int r = t0 + lane;
                 const float4 bx = r < ncache ? cache[r] : seg[r];
                 ts.kbox[s] = bx; ts.karea[s] = __fmul_rn(nthr, fabsf(ypp_area(bx)));
-                keepflag[grank[r]] = 1;
+                keepflag[ypp_gpk_rank(gpk[r])] = 1;
             }
             if ((khi >> lane) & 1u) {
                 const int s = nlo + __popc(khi & ((1u << lane) - 1u));
                 const int r = t0 + 32 + lane;
                 const float4 bx = r < ncache ? cache[r] : seg[r];
                 ts.kbox[s] = bx; ts.karea[s] = __fmul_rn(nthr, fabsf(ypp_area(bx)));
-                keepflag[grank[r]] = 1;
+                keepflag[ypp_gpk_rank(gpk[r])] = 1;
             }
             if (lane == 0) {
                 const int nk = nlo + __popc(khi);
@@ -754,7 +753,7 @@ struct BigSparseHdr {
 };
 
 template <bool kFma>
-__device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __restrict__ grank,
+__device__ bool nms_big_sparse(const float4* __restrict__ seg, const u64* __restrict__ gpk,
                                unsigned char* __restrict__ keepflag, const int len, unsigned char* smem,
                                const int smem_bytes, BigSparseHdr& H, const float thr, int& kept_total)
 {
@@ -917,7 +916,7 @@ __device__ bool nms_big_sparse(const float4* __restrict__ seg, const int* __rest
     if (!settled) return false;
     int kept = 0;
     for (int i = tid; i < len; i += T)
-        if (state[i] != 2) { keepflag[grank[i]] = 1; ++kept; }
+        if (state[i] != 2) { keepflag[ypp_gpk_rank(gpk[i])] = 1; ++kept; }
     kept = __reduce_add_sync(YPP_FULL_MASK, kept);
     if (lane == 0) H.wtot[warp] = kept;
     __syncthreads();
@@ -955,19 +954,19 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
             const bool trick = (p.ws.imgflag[b] & 2) != 0;
             const float step = p.ws.img_step[b];
             for (int i = threadIdx.x; i < len; i += YPP_NMS_BIG_THREADS)
-                p.ws.sbox[base + s0 + i] = rank_box(p.ws, base, p.ws.grank[base + s0 + i], trick, step);
+                p.ws.sbox[base + s0 + i] = pos_box(p.ws, base, p.ws.gpk[base + s0 + i], trick, step);
             __syncthreads();
         }
         if (kFast && p.iou_thr >= 0.0f && p.sparse_min_len != 0x7fffffff) {
             int kept = 0;
-            if (nms_big_sparse<kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0, p.ws.keepflag + base, len, smem_raw,
+            if (nms_big_sparse<kFma>(p.ws.sbox + base + s0, p.ws.gpk + base + s0, p.ws.keepflag + base, len, smem_raw,
                                      p.big_smem_bytes, bsh, p.iou_thr, kept)) {
                 if (threadIdx.x == 0 && kept) atomicAdd(p.ws.keep_count + b, kept);
                 continue;                                   // uniform over the CTA
             }
             __syncthreads();
         }
-        nms_segment<YPP_NMS_BIG_THREADS, kFast, kFma>(p.ws.sbox + base + s0, p.ws.grank + base + s0,
+        nms_segment<YPP_NMS_BIG_THREADS, kFast, kFma>(p.ws.sbox + base + s0, p.ws.gpk + base + s0,
                                                       p.ws.keepflag + base, len, cache, YPP_BIG_CACHE,
                                                       removed, ts, p.iou_thr, p.union_mode);
         if (threadIdx.x == 0 && ts.total_kept) atomicAdd(p.ws.keep_count + b, ts.total_kept);
@@ -998,8 +997,21 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     ypp_grid_wait();
     const int b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = p.N;
-    const int n = min(p.ws.cand_count[b], N);
     const int r_begin = blockIdx.x * YPP_GATHER_CHUNK;
+    const unsigned char* kf = p.ws.keepflag + (size_t)b * N;
+    const u64* keys = p.ws.skeys + (size_t)b * N;
+    // the chunk's own flags and keys are asked for first, together with the counts: they need nothing the prefix
+    // sums below produce, and the kernel is a chain of dependent load latencies (five before, three now).  Ranks
+    // past the image's candidates read allocated but unwritten words; r < r_end masks them below
+    unsigned char fl[YPP_GATHER_ROUNDS];
+    u64 k[YPP_GATHER_ROUNDS];
+#pragma unroll
+    for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
+        const int r = r_begin + u * YPP_GATHER_THREADS + tid;
+        fl[u] = r < N ? kf[r] : (unsigned char)0;
+        k[u] = r < N ? keys[r] : 0ull;
+    }
+    const int n = min(p.ws.cand_count[b], N);
     const int cap = p.max_det > 0 ? p.max_det : 0x7fffffff;          // rows an image may contribute
     const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && (p.det_total != nullptr || p.cursor_out != nullptr);
     const long long base = p.cursor_in ? *p.cursor_in : 0;          // append mode: rows already in det_rows
@@ -1009,7 +1021,6 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     }
     if (r_begin >= n && !writes_total) return;
     // rows of the images before this one, and kept flags of this image before my chunk
-    const unsigned char* kf = p.ws.keepflag + (size_t)b * N;
     long long img_part = 0;
     for (int i = tid; i < b; i += YPP_GATHER_THREADS) img_part += min(p.ws.keep_count[i], cap);
     int pre_part = 0;
@@ -1043,7 +1054,6 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         if (p.host_probe) *(volatile long long*)p.host_probe = ((base + rows) << 24) | (long long)(p.probe_seq & 0xffffffu);
     }
     if (r_begin >= n || pre_rows >= cap) return;
-    const u64* keys = p.ws.skeys + (size_t)b * N;
     const float4* box = p.ws.box + (size_t)b * N;
     const float img = p.img_idx_base + (float)b;
     const int r_end = min(n, r_begin + YPP_GATHER_CHUNK);
@@ -1054,7 +1064,7 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
 #pragma unroll
     for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
         const int r = r_begin + u * YPP_GATHER_THREADS + tid;
-        f[u] = r < r_end && kf[r];
+        f[u] = r < r_end && fl[u];
     }
 #pragma unroll
     for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
@@ -1062,7 +1072,6 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         if (lane == 0) warp_tot[u][warp] = __popc(m[u]);
     }
     __syncthreads();
-    u64 k[YPP_GATHER_ROUNDS];
     int pos[YPP_GATHER_ROUNDS];
     int running = pre_rows;
 #pragma unroll
@@ -1077,7 +1086,6 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         pos[u] = running + before + __popc(m[u] & ((1u << lane) - 1u));      // position inside the image
         running += total;
         f[u] = f[u] && pos[u] < cap;                                         // max_det: later ranks are dropped
-        k[u] = f[u] ? keys[r_begin + u * YPP_GATHER_THREADS + tid] : 0ull;
     }
     running = min(running, cap);
     float4 bx[YPP_GATHER_ROUNDS];

@@ -256,7 +256,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     const u64* gkeys = p.ws.keys + (size_t)b * N;
     u64* skeys = p.ws.skeys + (size_t)b * N;
     float4* sbox = p.ws.sbox + (size_t)b * N;
-    int* grank = p.ws.grank + (size_t)b * N;
+    u64* gpk = p.ws.gpk + (size_t)b * N;
     int* gseg = p.ws.seg_start + (size_t)b * (nc + 1);
     // the two key buffers of the sort: both in shared memory when they fit, else the first one only (the
     // second in the not-yet-written sbox region), else both global (skeys / sbox)
@@ -607,15 +607,17 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     __syncthreads();
     S1_MARK(6);
-    // ---- 7. stable ranking: segment position -> global rank (N1 gathers the boxes through it)
+    // ---- 7. stable ranking: segment position -> global rank, box index and class in one word (N1 gathers the boxes
+    // through it: one coalesced load, then the box - not rank, then key, then box)
     // two 32-rank chunks (A, then B) per step: B's positions also count A's lanes of the same class,
     // found with the ballots A needs anyway
     const u32 lt = (1u << lane) - 1u;
     for (int r0 = r_begin; r0 < r_end; r0 += 64) {
         const int rA = r0 + lane, rB = rA + 32;
         const bool okA = rA < r_end, okB = rB < r_end;
-        const int cA = okA ? cmap[ypp_key_cls(keys[rA])] : 0;
-        const int cB = okB ? cmap[ypp_key_cls(keys[rB])] : 0;
+        const u64 kA = okA ? keys[rA] : 0ull, kB = okB ? keys[rB] : 0ull;
+        const int cA = okA ? cmap[ypp_key_cls(kA)] : 0;
+        const int cB = okB ? cmap[ypp_key_cls(kB)] : 0;
         u32 pA = __ballot_sync(YPP_FULL_MASK, okA), pB = __ballot_sync(YPP_FULL_MASK, okB);
         u32 xB = pA, xA = pB;        // xB: A lanes of my B class; xA: B lanes of my A class
         for (int i = 0; i < cbits; ++i) {
@@ -631,11 +633,11 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         __syncwarp();
         if (okA) {
             if (rankA == 0) my[cA] = baseA + __popc(pA) + __popc(xA);
-            grank[baseA + rankA] = rA;
+            gpk[baseA + rankA] = ypp_make_gpk(rA, kA);
         }
         if (okB) {
             if (inB == 0 && xB == 0u) my[cB] = baseB + __popc(pB);     // class absent from A: B's leader counts it
-            grank[baseB + __popc(xB) + inB] = rB;
+            gpk[baseB + __popc(xB) + inB] = ypp_make_gpk(rB, kB);
         }
         __syncwarp();
     }

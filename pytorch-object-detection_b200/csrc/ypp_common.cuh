@@ -43,7 +43,7 @@ struct YppWs {
     u64* skeys;           // [B][N] the same keys in stable descending-score order (S1)
     float4* box;          // [B][N] cx,cy,w,h indexed by box index n
     float4* sbox;         // [B][N] x1,y1,x2,y2 (+ class offset) in class-segment order
-    int* grank;           // [B][N] class-order position -> global score rank
+    u64* gpk;             // [B][N] class-order position -> global score rank << 32 | box index << 12 | class (the key's low word)
     unsigned char* keepflag;  // [B][N] by global score rank
     int tiles_max;
     int bigq_per_image;
@@ -78,7 +78,7 @@ static inline YppWs ypp_make_ws(void* base, int B, int N, int nc)
     w.skeys = (u64*)take(sizeof(u64) * (size_t)B * N);
     w.box = (float4*)take(sizeof(float4) * (size_t)B * N);
     w.sbox = (float4*)take(sizeof(float4) * (size_t)B * N);
-    w.grank = (int*)take(sizeof(int) * (size_t)B * N);
+    w.gpk = (u64*)take(sizeof(u64) * (size_t)B * N);
     w.keepflag = (unsigned char*)take((size_t)B * N);
     w.total_bytes = off;
     return w;
@@ -117,6 +117,9 @@ __device__ __forceinline__ u64 ypp_make_key(float score, int idx, int cls)
 __device__ __forceinline__ float ypp_key_score(u64 k) { return ypp_dec(~(u32)(k >> 32)); }
 __device__ __forceinline__ int ypp_key_idx(u64 k) { return (int)(((u32)k >> YPP_KEY_CLS_BITS) & YPP_KEY_IDX_MASK); }
 __device__ __forceinline__ int ypp_key_cls(u64 k) { return (int)((u32)k & YPP_KEY_CLS_MASK); }
+// S1's per-position word: rank in the image's score order on top of the key's low word (index, class)
+__device__ __forceinline__ u64 ypp_make_gpk(int rank, u64 key) { return ((u64)(u32)rank << 32) | (u64)(u32)key; }
+__device__ __forceinline__ int ypp_gpk_rank(u64 g) { return (int)(g >> 32); }
 
 // cxcywh -> xyxy exactly as nms_v3 does (utils/yolo_utils.py:339-343): c -/+ (wh / 2)
 __device__ __forceinline__ float4 ypp_xyxy(float4 c)

@@ -987,11 +987,11 @@ __device__ __forceinline__ int popc_bytes16(const uint4 v)
     return __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w);     // flags are 0/1 bytes
 }
 
-__global__ void __launch_bounds__(YPP_GATHER_THREADS)
+__global__ void __launch_bounds__(YPP_GATHER_THREADS, 4)
 ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
 {
     __shared__ int warp_tot[YPP_GATHER_ROUNDS][YPP_GATHER_THREADS / 32];
-    __shared__ float stage[YPP_GATHER_CHUNK * 7];
+    __shared__ __align__(16) float stage[YPP_GATHER_CHUNK * 7 + 4];
     __shared__ long long red_img[YPP_GATHER_THREADS / 32];
     __shared__ int red_pre[YPP_GATHER_THREADS / 32];
     ypp_grid_wait();
@@ -1011,21 +1011,15 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         fl[u] = r < N ? kf[r] : (unsigned char)0;
         k[u] = r < N ? keys[r] : 0ull;
     }
-    const int n = min(p.ws.cand_count[b], N);
     const int cap = p.max_det > 0 ? p.max_det : 0x7fffffff;          // rows an image may contribute
     const bool writes_total = blockIdx.x == 0 && b == (int)gridDim.y - 1 && (p.det_total != nullptr || p.cursor_out != nullptr);
-    const long long base = p.cursor_in ? *p.cursor_in : 0;          // append mode: rows already in det_rows
-    if (blockIdx.x == 0 && tid == 0) {
-        if (p.cand_count_out) p.cand_count_out[b] = n;
-        if (p.keep_count_out) p.keep_count_out[b] = min(p.ws.keep_count[b], cap);
-    }
-    if (r_begin >= n && !writes_total) return;
-    // rows of the images before this one, and kept flags of this image before my chunk
+    // rows of the images before this one, and kept flags of this image before my chunk - also asked for before the
+    // candidate count is known: a chunk that starts past the count leaves below and its sums are never used
     long long img_part = 0;
     for (int i = tid; i < b; i += YPP_GATHER_THREADS) img_part += min(p.ws.keep_count[i], cap);
     int pre_part = 0;
     {
-        const int pre = min(r_begin, n);
+        const int pre = r_begin;                                  // < N; == min(r_begin, n) for every chunk that stays
         int head = (int)((16 - ((uintptr_t)kf & 15)) & 15);       // b*N need not be a multiple of 16
         if (head > pre) head = pre;
         if (tid < head) pre_part += kf[tid];
@@ -1035,6 +1029,13 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
         const int tail0 = head + (nvec << 4);
         if (tail0 + tid < pre) pre_part += kf[tail0 + tid];
     }
+    const int n = min(p.ws.cand_count[b], N);
+    const long long base = p.cursor_in ? *p.cursor_in : 0;          // append mode: rows already in det_rows
+    if (blockIdx.x == 0 && tid == 0) {
+        if (p.cand_count_out) p.cand_count_out[b] = n;
+        if (p.keep_count_out) p.keep_count_out[b] = min(p.ws.keep_count[b], cap);
+    }
+    if (r_begin >= n && !writes_total) return;
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         img_part += __shfl_xor_sync(YPP_FULL_MASK, img_part, d);
@@ -1105,23 +1106,35 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     }
     if (!want_rows) return;
     // rows of the chunk are contiguous in the output: stage them in shared memory (stride 6 or 7 floats:
-    // conflict-free) and write them out as full lines instead of 7 scattered 4-byte stores per row
+    // conflict-free) and write them out as full lines instead of 7 scattered 4-byte stores per row.  The stage starts
+    // at the same offset inside a 16-byte word as the output does, so the body of the copy moves float4s
     const int width = p.row_width;
+    const long long first = base + img_rows + pre_rows;
+    float* out = p.det_rows + first * width;
+    const int phase = (int)(((uintptr_t)out >> 2) & 3);
 #pragma unroll
     for (int u = 0; u < YPP_GATHER_ROUNDS; ++u) {
         if (!f[u]) continue;
-        float* o = stage + (pos[u] - pre_rows) * width;
+        float* o = stage + phase + (pos[u] - pre_rows) * width;
         if (width == 7) *o++ = img;
         o[0] = bx[u].x; o[1] = bx[u].y; o[2] = bx[u].z; o[3] = bx[u].w;
         o[4] = ypp_key_score(k[u]); o[5] = cls[u];
     }
     __syncthreads();
-    const long long first = base + img_rows + pre_rows;
     long long nrows = running - pre_rows;
     if (first + nrows > p.det_capacity) nrows = p.det_capacity > first ? p.det_capacity - first : 0;
-    float* out = p.det_rows + first * width;
     const int nf = (int)nrows * width;
-    for (int i = tid; i < nf; i += YPP_GATHER_THREADS) out[i] = stage[i];
+    const float* src = stage + phase;
+    const int head = min((4 - phase) & 3, nf);                       // floats before the first aligned word
+    if (tid < head) out[tid] = src[tid];
+    const int nvec = (nf - head) >> 2;
+    {
+        float4* o4 = reinterpret_cast<float4*>(out + head);
+        const float4* s4 = reinterpret_cast<const float4*>(src + head);
+        for (int i = tid; i < nvec; i += YPP_GATHER_THREADS) o4[i] = s4[i];
+    }
+    const int tail0 = head + (nvec << 2);
+    if (tail0 + tid < nf) out[tail0 + tid] = src[tail0 + tid];
 }
 
 template <bool kFast, bool kFma>

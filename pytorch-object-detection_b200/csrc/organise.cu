@@ -266,10 +266,18 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     ypp_grid_wait();
     S1_CTA_BEGIN();
     S1_MARK(0);
-    // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema
-    const int ntiles = min(*p.ws.ntiles, p.ws.tiles_max);
-    const int* tcnt = p.ws.tile_cnt + (size_t)b * p.ws.tiles_max;
+    // ---- 1. tile offsets (exclusive scan of the D1 tile counts) and per-image extrema.  Everything this step reads is
+    // asked for at once, BEFORE the slot count arrives (count -> counts -> first index -> keys used to be four dependent
+    // loads deep): words of slots past the count are allocated but unwritten, and masked once the count is here
+    const int tiles_max = p.ws.tiles_max;
+    const int* tcnt = p.ws.tile_cnt + (size_t)b * tiles_max;
+    const uint4* text = reinterpret_cast<const uint4*>(p.ws.tile_ext) + (size_t)b * tiles_max;
     int* tile_off = table;                                   // [ntiles + 1], dead before the first radix pass
+    int* tile_first_s = table + tiles_max + 1;               // [ntiles] first box index of each slot, likewise
+    int v0 = 0, tf0 = 0;
+    uint4 e0 = make_uint4(0u, 0u, 0u, 0u);
+    if (tid < tiles_max) { v0 = tcnt[tid]; e0 = text[tid]; tf0 = p.ws.tile_first[tid]; }
+    const int ntiles = min(*p.ws.ntiles, tiles_max);
     if (tid == 0) {
         hd->maxc = 0; hd->nminx1 = 0; hd->nminy1 = 0;
         hd->n_low = 0; hd->n_high = 0; hd->flagged = 0; hd->n_edges = 0; hd->n_big = 0;
@@ -277,16 +285,18 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     }
     if (tid < YPP_DET_BINS) { hd->bin_hi[tid] = 0; hd->bin_lo[tid] = 0; }
     {
-        const uint4* text = reinterpret_cast<const uint4*>(p.ws.tile_ext) + (size_t)b * p.ws.tiles_max;
         int run = 0;
         u32 M = 0, NX = 0, NY = 0;
         for (int t0 = 0; t0 < ntiles; t0 += YPP_ORG_THREADS) {
             const int t = t0 + tid;
-            const int v = t < ntiles ? tcnt[t] : 0;
-            if (v > 0) { const uint4 e = text[t]; M = max(M, e.x); NX = max(NX, e.y); NY = max(NY, e.z); }
+            int v = v0, tf = tf0;
+            uint4 e = e0;
+            if (t0 > 0 && t < ntiles) { v = tcnt[t]; e = text[t]; tf = p.ws.tile_first[t]; }
+            if (t >= ntiles) v = 0;
+            if (v > 0) { M = max(M, e.x); NX = max(NX, e.y); NY = max(NY, e.z); }
             int total;
             const int ex = block_exclusive_scan(v, hd->warp_sums, total);   // syncs: the header init above is visible
-            if (t < ntiles) tile_off[t] = run + ex;
+            if (t < ntiles) { tile_off[t] = run + ex; tile_first_s[t] = tf; }
             run += total;
         }
         M = __reduce_max_sync(YPP_FULL_MASK, M);
@@ -321,7 +331,7 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
                 dst[u] = -1;
                 if (t < ntiles) {
                     const int off = tile_off[t], cnt = tile_off[t + 1] - off;
-                    if (lane < cnt) { dst[u] = off + lane; k[u] = gkeys[p.ws.tile_first[t] + lane]; }
+                    if (lane < cnt) { dst[u] = off + lane; k[u] = gkeys[tile_first_s[t] + lane]; }
                 }
             }
 #pragma unroll
@@ -670,7 +680,7 @@ int ypp_org_smem_bytes(int N, int nc, int* keys_in_smem, int* table_ints)
     int tints = YPP_RADIX_MAX * YPP_TABLE_PITCH;
     if (34 * nc + 1 > tints) tints = 34 * nc + 1;
     const int tiles_max = (N / YPP_TILE_BOXES + YPP_MAX_SCALES * YPP_MAX_ANCHORS + 8) * (YPP_TILE_BOXES / 32);
-    if (tiles_max + 1 > tints) tints = tiles_max + 1;
+    if (2 * tiles_max + 1 > tints) tints = 2 * tiles_max + 1;     // tile offsets + first indices
     *table_ints = tints;
     size_t fixed = sizeof(OrgSmemHeader) + sizeof(int) * (size_t)tints;
     fixed = (fixed + 15) / 16 * 16;

@@ -241,6 +241,129 @@ __device__ bool bucket_rank_sort(const u64* src, u64* tmp, u64* dst, int n, int 
     return true;
 }
 
+// ---- images with a handful of candidates (deployment: tens per image at conf 0.25) -----------------------
+// The general path is a dozen block-wide phases whose cost is their latency, not their work: 10 us of S1 and as much
+// again in N1 + N1b for 50 boxes.  Up to YPP_SMALL_MAX candidates the image's CTA does everything here, exactly as
+// torchvision states it and without any of the machinery above:
+//   rank      place of a key = number of smaller keys (unique 64-bit words: that IS the stable score order);
+//   pairs     every (earlier i, later j) through the exact pair test; coordinate trick: ALL pairs on the shifted boxes
+//             (torchvision's single pass over boxes + cls * step - cross-class suppression needs no detector here),
+//             otherwise same-class pairs on the plain boxes (_batched_nms_vanilla);
+//   greedy    fix-point over the bit rows: j is dropped once a kept earlier box suppresses it, kept once every earlier
+//             box that suppresses it is known dropped.
+// It leaves what G reads (sorted keys, keep flags by rank, counts) and NO segments, so N1 / N1b find nothing to do.
+#define YPP_SMALL_MAX 256
+#define YPP_SMALL_WORDS (YPP_SMALL_MAX / 32)
+static_assert(sizeof(OrgSmemHeader) % 16 == 0, "the table behind the header holds float4s in the small path");
+static_assert(YPP_SMALL_MAX * 4 == YPP_ORG_THREADS, "four threads rank one key");
+static_assert((4 * 8 + 16 + 4 * YPP_SMALL_WORDS) * YPP_SMALL_MAX + 64 * YPP_SMALL_WORDS <= 4 * YPP_RADIX_MAX * YPP_TABLE_PITCH,
+              "the small path lives in the radix table");
+
+__device__ void organise_small(const YppOrgParams& p, const int b, const int n, const u64* __restrict__ src, int* table,
+                               const bool trick, const float step)
+{
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int N = p.N, nc = p.nc;
+    float4* sb = reinterpret_cast<float4*>(table);                          // 16-byte aligned: the header's size is a multiple of 16                             // boxes by rank (xyxy, shifted under the trick)
+    u64* uk = reinterpret_cast<u64*>(sb + YPP_SMALL_MAX);                   // keys, box-index order
+    u64* sk = uk + YPP_SMALL_MAX;                                           // keys by rank
+    u32* msk = reinterpret_cast<u32*>(sk + YPP_SMALL_MAX);                  // [j][w]: earlier ranks 32w.. that suppress rank j
+    u32* K = msk + YPP_SMALL_MAX * YPP_SMALL_WORDS;                         // kept ranks
+    u32* D = K + YPP_SMALL_WORDS;                                           // dropped ranks
+    const float4* gbox = p.ws.box + (size_t)b * N;
+    u64* skeys = p.ws.skeys + (size_t)b * N;
+    unsigned char* kf = p.ws.keepflag + (size_t)b * N;                      // zeroed for ranks < n by the caller
+
+    S1_MARK(3);
+    if (tid < n) uk[tid] = src[tid];
+    if (tid < YPP_SMALL_WORDS) { K[tid] = 0u; D[tid] = 0u; }
+    __syncthreads();
+    // ---- rank: four threads per key, each counts a quarter of the others
+    {
+        const int i = tid >> 2, q = tid & 3;
+        const u64 ki = i < n ? uk[i] : 0ull;
+        int r = 0;
+        if (i < n)
+            for (int j = q; j < n; j += 4) r += uk[j] < ki;
+        r += __shfl_xor_sync(YPP_FULL_MASK, r, 1);
+        r += __shfl_xor_sync(YPP_FULL_MASK, r, 2);
+        if (i < n && q == 0) {
+            float4 xy = ypp_xyxy(gbox[ypp_key_idx(ki)]);                     // utils/yolo_utils.py:339-343
+            if (trick) {
+                const float off = __fmul_rn((float)ypp_key_cls(ki), step);  // idxs.to(boxes) * (max_coordinate + 1)
+                xy = make_float4(__fadd_rn(xy.x, off), __fadd_rn(xy.y, off), __fadd_rn(xy.z, off), __fadd_rn(xy.w, off));
+            }
+            sb[r] = xy;
+            sk[r] = ki;
+            skeys[r] = ki;
+        }
+    }
+    __syncthreads();
+    S1_MARK(4);
+    // ---- pairs: thread (j, w) tests rank j against the earlier ranks of word w
+    const int n_in = p.max_cand > 0 ? min(n, p.max_cand) : n;               // ranks past max_cand: never kept, suppress nothing
+    const bool neg_thr = !(p.iou_thr >= 0.0f);
+    for (int t = tid; t < YPP_SMALL_MAX * YPP_SMALL_WORDS; t += YPP_ORG_THREADS) {
+        const int j = t / YPP_SMALL_WORDS, w = t % YPP_SMALL_WORDS;
+        u32 bits = 0u;
+        if (j < n_in && 32 * w < j) {
+            const float4 bj = sb[j];
+            const int cj = ypp_key_cls(sk[j]);
+            const int i_end = min(32 * w + 32, j);
+            for (int i = 32 * w; i < i_end; ++i) {
+                if (!trick && ypp_key_cls(sk[i]) != cj) continue;
+                const float4 bi = sb[i];
+                const float sa = ypp_area(bi);
+                const bool sup = neg_thr ? ypp_suppresses<false>(bi, sa, bj, p.iou_thr, p.union_mode)
+                                         : ypp_suppresses<true>(bi, sa, bj, p.iou_thr, p.union_mode);
+                if (sup) bits |= 1u << (i - 32 * w);
+            }
+        }
+        msk[t] = bits;
+    }
+    __syncthreads();
+    S1_MARK(5);
+    // ---- greedy order as a fix-point; thread j < 256 owns rank j, its bit lives in word `warp`
+    {
+        u32 m[YPP_SMALL_WORDS];
+        const bool mine = tid < n_in;
+#pragma unroll
+        for (int w = 0; w < YPP_SMALL_WORDS; ++w) m[w] = mine ? msk[tid * YPP_SMALL_WORDS + w] : 0u;
+        bool undecided = mine;
+        for (;;) {
+            bool hit = false, wait = false;
+#pragma unroll
+            for (int w = 0; w < YPP_SMALL_WORDS; ++w) {
+                hit |= (m[w] & K[w]) != 0u;
+                wait |= (m[w] & ~D[w]) != 0u;
+            }
+            const bool drop_now = undecided && hit, keep_now = undecided && !wait;      // !wait implies !hit
+            undecided = undecided && !drop_now && !keep_now;
+            __syncthreads();                                                // everyone has read K and D
+            if (warp < YPP_SMALL_WORDS) {
+                const u32 kb = __ballot_sync(YPP_FULL_MASK, keep_now), db = __ballot_sync(YPP_FULL_MASK, drop_now);
+                if (lane == 0) { K[warp] |= kb; D[warp] |= db; }
+            }
+            if (!__syncthreads_or(undecided)) break;
+        }
+    }
+    S1_MARK(6);
+    if (tid < n_in && ((K[warp] >> lane) & 1u)) kf[tid] = 1;
+    if (tid == 0) {
+        int kept = 0;
+#pragma unroll
+        for (int w = 0; w < YPP_SMALL_WORDS; ++w) kept += __popc(K[w]);
+        p.ws.keep_count[b] = kept;
+        p.ws.bigcnt[b] = 0;
+        p.ws.imgflag[b] = (trick ? 2 : 0) | 4;                              // bit 2: the image went this way (diagnostics)
+        p.ws.img_step[b] = step;
+    }
+    int* gseg = p.ws.seg_start + (size_t)b * (nc + 1);
+    for (int c = tid; c <= nc; c += YPP_ORG_THREADS) gseg[c] = 0;
+    S1_MARK(7);
+    S1_MARK(8);
+}
+
 __global__ void __launch_bounds__(YPP_ORG_THREADS, 1)
 ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
 {
@@ -365,6 +488,10 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         trick = true;
         step = p.fixed_step;
         one_segment = !(M <= __fadd_rn(step, -1.0f)) || !(step > 0.0f);
+    }
+    if (n <= p.small_max) {                                  // uniform over the CTA
+        organise_small(p, b, n, bufA, table, trick, step);
+        return;
     }
     DetGeom dg;
     dg.step = step;
@@ -548,37 +675,36 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
     // share no edge stay independent).  Too many candidates or edges -> one class-agnostic segment.
     __syncthreads();                                         // table is free again
     int* cmap = seg + nc + 1;                                // [nc] class -> segment that holds it
-    for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = c;
-    if (trick && nc > 1) {
-        __syncthreads();
-        const int ne = hd->n_edges;
-        if (hd->flagged || ne > YPP_DET_EDGES) {
-            for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = 0;
-            if (tid == 0) hd->flagged = 1;
-        } else if (ne > 0) {
-            if (tid == 0) {                                  // union by smallest class id; a handful of edges
-                for (int e = 0; e < ne; ++e) {
-                    int a = (int)(hd->edges[e] >> 16), c2 = (int)(hd->edges[e] & 0xffffu);
-                    while (cmap[a] != a) a = cmap[a];
-                    while (cmap[c2] != c2) c2 = cmap[c2];
-                    if (a != c2) cmap[max(a, c2)] = min(a, c2);
-                }
-                hd->flagged = 1;
+    const int ne = hd->n_edges;
+    const bool was_flagged = hd->flagged != 0;               // read by every thread before anyone sets it below
+    const bool merge_all = trick && nc > 1 && (was_flagged || ne > YPP_DET_EDGES);
+    for (int c = tid; c < nc; c += YPP_ORG_THREADS) cmap[c] = merge_all ? 0 : c;
+    for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;       // the per-(warp, class) counters of step 6
+    __syncthreads();
+    if (merge_all) {
+        if (tid == 0) hd->flagged = 1;
+    } else if (trick && nc > 1 && ne > 0) {                  // uniform; rare
+        if (tid == 0) {                                      // union by smallest class id; a handful of edges
+            for (int e = 0; e < ne; ++e) {
+                int a = (int)(hd->edges[e] >> 16), c2 = (int)(hd->edges[e] & 0xffffu);
+                while (cmap[a] != a) a = cmap[a];
+                while (cmap[c2] != c2) c2 = cmap[c2];
+                if (a != c2) cmap[max(a, c2)] = min(a, c2);
             }
-            __syncthreads();
-            for (int c0 = 0; c0 < nc; c0 += YPP_ORG_THREADS) {
-                const int c = c0 + tid;
-                int r = c < nc ? c : 0;
-                while (cmap[r] != r) r = cmap[r];
-                __syncthreads();
-                if (c < nc) cmap[c] = r;
-            }
+            hd->flagged = 1;
         }
+        __syncthreads();
+        for (int c0 = 0; c0 < nc; c0 += YPP_ORG_THREADS) {
+            const int c = c0 + tid;
+            int r = c < nc ? c : 0;
+            while (cmap[r] != r) r = cmap[r];
+            __syncthreads();
+            if (c < nc) cmap[c] = r;
+        }
+        __syncthreads();
     }
-    // ---- 6. class counting (warp w owns ranks [w*L, (w+1)*L)), segment starts
-    __syncthreads();
-    for (int i = tid; i < 32 * nc; i += YPP_ORG_THREADS) table[i] = 0;
-    __syncthreads();
+    // ---- 6. class counting (warp w owns ranks [w*L, (w+1)*L)), segment starts.  table[w*nc + c] ends up as the number
+    // of class-c ranks in the warps before w, i.e. warp w's first position RELATIVE to the segment start seg[c]
     const int n_in = p.max_cand > 0 ? min(n, p.max_cand) : n;        // ranks past max_cand join no segment: never kept
     const int r_begin = warp * L, r_end = min(n_in, r_begin + L);
     const int cbits = 32 - __clz(max(nc - 1, 1));            // bits of a class id
@@ -588,10 +714,16 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         if (r < r_end) atomicAdd(&my[cmap[ypp_key_cls(keys[r])]], 1);
     }
     __syncthreads();
-    for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
-        int t = 0;
-        for (int w = 0; w < 32; ++w) t += table[w * nc + c];
-        seg[c] = t;
+    for (int c = warp; c < nc; c += YPP_ORG_THREADS / 32) {  // one warp per class: lane = the warp whose count it holds
+        const int v = table[lane * nc + c];
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(YPP_FULL_MASK, inc, d);
+            if (lane >= d) inc += o;
+        }
+        table[lane * nc + c] = inc - v;
+        if (lane == 31) seg[c] = inc;
     }
     __syncthreads();
     if (warp == 0) {   // exclusive scan of seg[0..nc) -> seg[0..nc]
@@ -609,11 +741,6 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
             run += __shfl_sync(YPP_FULL_MASK, inc, 31);
         }
         if (lane == 0) seg[nc] = run;
-    }
-    __syncthreads();
-    for (int c = tid; c < nc; c += YPP_ORG_THREADS) {
-        int run = seg[c];
-        for (int w = 0; w < 32; ++w) { const int t = table[w * nc + c]; table[w * nc + c] = run; run += t; }
     }
     __syncthreads();
     S1_MARK(6);
@@ -640,14 +767,15 @@ ypp_organise_kernel(const __grid_constant__ YppOrgParams p)
         }
         const int rankA = __popc(pA & lt), inB = __popc(pB & lt);
         const int baseA = okA ? my[cA] : 0, baseB = okB ? my[cB] : 0;
+        const int segA = seg[cA], segB = seg[cB];
         __syncwarp();
         if (okA) {
             if (rankA == 0) my[cA] = baseA + __popc(pA) + __popc(xA);
-            gpk[baseA + rankA] = ypp_make_gpk(rA, kA);
+            gpk[segA + baseA + rankA] = ypp_make_gpk(rA, kA);
         }
         if (okB) {
             if (inB == 0 && xB == 0u) my[cB] = baseB + __popc(pB);     // class absent from A: B's leader counts it
-            gpk[baseB + __popc(xB) + inB] = ypp_make_gpk(rB, kB);
+            gpk[segB + baseB + __popc(xB) + inB] = ypp_make_gpk(rB, kB);
         }
         __syncwarp();
     }
@@ -711,6 +839,9 @@ int ypp_launch_organise(const YppOrgParams& p, cudaStream_t st)
     YppOrgParams q = p;
     q.keys_in_smem = kin;
     q.table_ints = tints;
+    static int small_max = -1;                             // YPP_SMALL: tuning / tests only (0 = every image takes the general path)
+    if (small_max < 0) { const char* e = getenv("YPP_SMALL"); small_max = e ? atoi(e) : YPP_SMALL_MAX; if (small_max > YPP_SMALL_MAX) small_max = YPP_SMALL_MAX; if (small_max < 0) small_max = 0; }
+    q.small_max = small_max;
     static int configured_d[YPP_MAX_DEVICES];              // per device, like the attribute itself
     int dev = 0;
     cudaGetDevice(&dev);

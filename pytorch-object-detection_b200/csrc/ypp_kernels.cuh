@@ -36,6 +36,7 @@ struct YppOrgParams {
     int step_mode;         // 0: class offset step = max coordinate + 1 (torchvision batched_nms); 1: fixed_step, always shifted
     float fixed_step;      //    (Ultralytics: boxes + cls * max_wh, utils/general.py:698-699; 0 = agnostic)
     int max_cand;          // > 0: only the best max_cand candidates of an image enter NMS (max_nms, utils/general.py:694-695)
+    int small_max;         // images with at most this many candidates are finished inside S1 (set by the launcher)
 };
 
 struct YppNmsParams {

@@ -27,6 +27,8 @@ print("rc", rc, "total cycles", v[8] - v[0])
 for i in range(8):
     print("%-12s %8d cycles  %6.2f us @1.965GHz" % (names[i], v[i + 1] - v[i], (v[i + 1] - v[i]) / 1965.0))
 print("longest CTA %.2f us; first CTA start -> last CTA end %.2f us" % (v[9] / 1965.0, (v[11] - v[10]) / 1e3))
-if v[12]:
+if (v[7] - v[3]) < 20000 and v[12] == 0:
+    print('(small-image path: the rows radix sort .. rank above are its rank / pairs / fix-point / outputs phases; marks cost ~1 us each at this scale)')
+elif v[12]:
     print("detector split: pass 1 %.2f, bin scan %.2f, pass 2 %.2f, pair tests %.2f us" % (
         (v[12] - v[2]) / 1965.0, (v[13] - v[12]) / 1965.0, (v[14] - v[13]) / 1965.0, (v[3] - v[14]) / 1965.0))

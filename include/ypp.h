@@ -168,7 +168,7 @@ int ypp_postprocess(const ypp_cfg* cfg, const ypp_scale* scales, void* ws, size_
  * GPU that loads libypp.so, held until the process exits - so the call allocates nothing: no cudaMalloc / cudaFree, no
  * allocating library routine.  Inputs and outputs are the caller's, with the meaning they have in ypp_postprocess.
  * Limit: ypp_workspace_bytes(cfg->B, n_boxes, cfg->nc) <= YPP_STATIC_WS_BYTES, else YPP_E_WORKSPACE with the sizes in
- * ypp_last_error() (one YOLOv3-416 image - 10 647 boxes, 80 classes - needs 0.58 MB; four of them, six with 20
+ * ypp_last_error() (one YOLOv3-416 image - 10 647 boxes, 80 classes - needs 0.63 MB; four of them, six with 20
  * classes, or one 608-pixel image of 22 743 boxes fit; a batch of 8 does not).  Nothing in the workspace has to start at zero (every kernel of the chain initialises what it
  * reads), so the array simply keeps the last call's contents.  ALL calls on a device share the one array: calls that
  * overlap on the GPU (two streams, two host threads) race - serialise them on one stream or with events. */

@@ -5,13 +5,14 @@
 //      image's scores differ + ranking inside the (tiny) buckets; stable LSD radix passes on the
 //      score word when many scores tie;
 //   3. stable counting partition by class -> per (image, class) segments in the same order;
-//   4. emit the segment -> global-rank map and, per image, whether torchvision would take the
-//      coordinate-trick path (_batched_nms_coordinate_trick) and its offset step
-//      max_coordinate + 1; N1 gathers the boxes through the map, converts them to xyxy
-//      (utils/yolo_utils.py:339-343) and applies cls * step;
+//   4. emit, per segment position, one word holding the global rank, the box index and the class
+//      (gpk) and, per image, whether torchvision would take the coordinate-trick path
+//      (_batched_nms_coordinate_trick) and its offset step max_coordinate + 1; N1 reads the word,
+//      then the box, converts it to xyxy (utils/yolo_utils.py:339-343) and applies cls * step;
 //   5. coordinate trick only: detect cross-class suppression edges (possible when a box with
 //      negative x1,y1 is shifted onto the previous class band); the classes such an edge couples
 //      share ONE segment, so the greedy scan sees exactly what torchvision's single pass does.
+// Images with at most YPP_SMALL_MAX candidates skip 2..5: organise_small below finishes them here.
 #include "ypp_kernels.cuh"
 
 #ifdef YPP_PROFILE_S1

@@ -176,17 +176,20 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, u32 bytes, 
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+#ifndef YPP_MBAR_SUSPEND_NS
+#define YPP_MBAR_SUSPEND_NS 20000u      /* upper bound of one suspension; the barrier's completion ends it at once */
+#endif
 __device__ __forceinline__ void mbar_wait(u64* bar, u32 parity)
 {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "YPP_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
         "@p bra YPP_DONE;\n"
         "bra YPP_WAIT;\n"
         "YPP_DONE:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity), "r"(YPP_MBAR_SUSPEND_NS) : "memory");
 }
 
 // tile -> (scale, anchor, first cell, cells)

@@ -395,6 +395,17 @@ int ypp_peek_async(const void* device_src, void* host_dst, size_t bytes, void* s
 
 /* ---- misc ---------------------------------------------------------------------------- */
 
+/* Launch-width hint for the long-segment NMS kernel (segments > 512 boxes; no counterpart in the reference, where
+ * torchvision sizes every launch after reading counts back).  Its CTAs take a whole SM each, so launching it at full
+ * width for batches that hold no long segment costs every batch in flight a few per cent.  enable != 0: the library
+ * pins one word per GPU of its OWN host memory (cudaHostRegister, once per process: nothing is allocated) which that
+ * kernel sets the first time it finds a long segment on the device; until then configurations with many classes
+ * (boxes per image / classes < 1024) launch it 8 CTAs wide, afterwards - for the rest of the process - at full width.
+ * Results never depend on it; the first batch with long segments runs them on 8 CTAs.  A CUDA graph captured before
+ * that keeps the narrow launch.  enable == 0 (the default of the C library): always full width.  The Python layer
+ * turns it on.  Returns YPP_E_CUDA if the host memory cannot be pinned (the library then stays at full width). */
+int ypp_adaptive_launch(int enable);
+
 const char* ypp_last_error(void);
 int ypp_version(void);
 /* kernels launched by this library in the calling thread since the last reset (bench bookkeeping) */

@@ -669,6 +669,8 @@ int ypp_peek_async(const void* device_src, void* host_dst, size_t bytes, void* s
     return YPP_OK;
 }
 
+int ypp_adaptive_launch(int enable) { return ypp_adaptive_launch_set(enable); }
+
 const char* ypp_last_error(void) { return g_err; }
 int ypp_version(void) { return 100; }
 int64_t ypp_launch_count(int reset)

@@ -942,6 +942,8 @@ ypp_nms_big_kernel(const __grid_constant__ YppNmsParams p)
         int any = 0;
         for (int b = threadIdx.x; b < p.B; b += YPP_NMS_BIG_THREADS) any |= p.ws.bigcnt[b];
         if (!__syncthreads_or(any)) return;
+        // long segments exist on this device: the host sizes the next launches for them (ypp_adaptive_launch)
+        if (p.big_seen && blockIdx.x == 0 && threadIdx.x == 0) *(volatile int*)p.big_seen = 1;
     }
     for (int it = blockIdx.x; it < p.B * per; it += gridDim.x) {
         const int b = it / per, k = it - b * per;
@@ -1137,6 +1139,31 @@ ypp_gather_kernel(const __grid_constant__ YppGatherParams p)
     if (tail0 + tid < nf) out[tail0 + tid] = src[tail0 + tid];
 }
 
+// ---- how wide the long-segment kernel is launched (ypp_adaptive_launch) ------------------------------------
+// N1b's CTAs take a whole SM each (1024 threads, up to 222 KB of shared memory).  Launched 148 wide "in case", the
+// kernel that nearly always finds nothing to do still needs every SM fully vacated once per batch - with several
+// batches in flight that is a device-wide hiccup per step (C2: 869 k -> 891 k images/s without it).  When the caller
+// allowed it, the library keeps one page-locked host word per device that N1b sets the first time it finds a long
+// segment; until then many-class configurations launch N1b YPP_BIG_IDLE_CTAS wide (the kernel walks its work list
+// whatever the grid, so results do not depend on this), from then on at full width.  The word is host memory of the
+// library itself, pinned with cudaHostRegister - nothing is allocated - and it is only ever read as a hint.
+#define YPP_BIG_IDLE_CTAS 8
+static int g_big_seen[YPP_MAX_DEVICES][16];                // one cache line per device
+static int* g_big_seen_dev[YPP_MAX_DEVICES];               // the same words as the device sees them
+static int g_adaptive = 0;                                 // 0 off, 1 on, -1 registration failed
+
+// the device-visible address of this device's word (null: feature off), looked up once per device
+static int* big_seen_word(int dev)
+{
+    if (g_adaptive <= 0) return nullptr;
+    if (!g_big_seen_dev[dev]) {
+        void* d = nullptr;
+        if (cudaHostGetDevicePointer(&d, &g_big_seen[dev][0], 0) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        g_big_seen_dev[dev] = (int*)d;
+    }
+    return g_big_seen_dev[dev];
+}
+
 template <bool kFast, bool kFma>
 int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
 {
@@ -1177,6 +1204,9 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
         if (ctas > sms_d[dev]) ctas = sms_d[dev];
         YppNmsParams pb = p;
         pb.big_smem_bytes = smem;
+        pb.big_seen = big_seen_word(dev);
+        // many classes and no long segment seen on this device so far: a narrow launch (see above)
+        if (!big_first && pb.big_seen && !*(volatile int*)&g_big_seen[dev][0] && ctas > YPP_BIG_IDLE_CTAS) ctas = YPP_BIG_IDLE_CTAS;
         ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, pb);
         ypp_count_launch(1);
         rc = ypp_check_launch("nms_big");
@@ -1187,6 +1217,25 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
 }
 
 }  // namespace
+
+int ypp_adaptive_launch_set(int enable)
+{
+    if (!enable) { if (g_adaptive > 0) g_adaptive = 0; return YPP_OK; }
+    if (g_adaptive != 0) { if (g_adaptive < 0) return YPP_E_CUDA; g_adaptive = 1; return YPP_OK; }
+    static bool registered = false;
+    if (!registered) {
+        cudaError_t e = cudaHostRegister(g_big_seen, sizeof(g_big_seen), cudaHostRegisterMapped | cudaHostRegisterPortable);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            g_adaptive = -1;
+            ypp_set_error("adaptive launch: cudaHostRegister: %s", cudaGetErrorString(e));
+            return YPP_E_CUDA;
+        }
+        registered = true;
+    }
+    g_adaptive = 1;
+    return YPP_OK;
+}
 
 #ifdef YPP_SP_STATS
 extern "C" int ypp_debug_sp_stats(unsigned long long* out16, int reset)

@@ -46,6 +46,7 @@ struct YppNmsParams {
     int union_mode;
     int sparse_min_len;    // per-class segments at least this long try the sweep-and-prune path first
     int big_smem_bytes;    // dynamic shared memory of the long-segment kernel (its sweep-and-prune path sizes itself by it)
+    int* big_seen;         // page-locked host word the long-segment kernel sets when it finds work (ypp_adaptive_launch), or null
 };
 
 struct YppGatherParams {
@@ -101,6 +102,7 @@ int ypp_launch_map_flags(const float* gt, long long G, const float* det, long lo
 int ypp_launch_map_ap_flags(const float* triples, long long n, long long seg_stride, const long long* seg_count,
                             const long long* gt_per_class, int nc, int c_lo, int c_hi, void* ws, size_t ws_bytes,
                             float* per_class, cudaStream_t st);
+int ypp_adaptive_launch_set(int enable);      // nms.cu
 int ypp_launch_map_mean(const float* per_class, int nc, float* map, cudaStream_t st);
 
 // ---- programmatic dependent launch (PDL) --------------------------------------------------

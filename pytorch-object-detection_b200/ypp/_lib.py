@@ -65,7 +65,7 @@ EXPORTS = ["ypp_workspace_bytes", "ypp_effective_iou_thr", "ypp_decode_dense", "
            "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_workspace_bytes", "ypp_map_match", "ypp_map_flags", "ypp_map_ap_from_flags", "ypp_map_mean",
            "ypp_detection_ints", "ypp_ultra_rows", "ypp_nms_ultralytics", "ypp_decode_yolov1",
            "ypp_confusion_update", "ypp_head_decode_compact", "ypp_head_postprocess", "ypp_nms_append", "ypp_postprocess_append", "ypp_run_stages", "ypp_postprocess_static", "ypp_peek_async", "ypp_pipeline_create", "ypp_pipeline_destroy", "ypp_pipeline_next_slot", "ypp_pipeline_stream",
-           "ypp_pipeline_submit", "ypp_pipeline_query", "ypp_pipeline_wait_ticket", "ypp_pipeline_join", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count"]
+           "ypp_pipeline_submit", "ypp_pipeline_query", "ypp_pipeline_wait_ticket", "ypp_pipeline_join", "ypp_target_rows_append", "ypp_last_error", "ypp_version", "ypp_launch_count", "ypp_adaptive_launch"]
 
 
 def build(force=False, verbose=False, defines=(), out=None):
@@ -159,6 +159,7 @@ def lib():
     L.ypp_version.restype = ci
     L.ypp_launch_count.argtypes = [ci]
     L.ypp_launch_count.restype = i64
+    L.ypp_adaptive_launch.argtypes = [ci]
     for name in ("ypp_decode_dense", "ypp_decode_compact", "ypp_rows_compact", "ypp_sort_segments", "ypp_nms",
                  "ypp_postprocess", "ypp_nms_rows", "ypp_target_rows", "ypp_box_iou", "ypp_bbox_iou", "ypp_map_match",
                  "ypp_detection_ints", "ypp_nms_ultralytics", "ypp_decode_yolov1", "ypp_confusion_update",

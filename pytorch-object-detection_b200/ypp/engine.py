@@ -12,7 +12,23 @@ from typing import List, Optional, Sequence
 import torch
 
 from . import _lib
-from ._lib import YppCfg, YppScale, check, lib
+from ._lib import YppCfg, YppScale, check
+from ._lib import lib as _load_lib
+
+_hinted = False
+
+
+def lib():
+    """The loaded library; the first call on a machine with a GPU also turns on ypp_adaptive_launch (include/ypp.h: the
+    long-segment kernel is launched narrow until the device has seen a long segment; a hint, results never depend on
+    it; YPP_ADAPTIVE=0 leaves it off)."""
+    global _hinted
+    L = _load_lib()
+    if not _hinted:
+        _hinted = True
+        if torch.cuda.is_available() and os.environ.get("YPP_ADAPTIVE", "1") != "0":
+            L.ypp_adaptive_launch(1)            # a failure only means full-width launches, as before
+    return L
 
 
 # the per-call host cost is what bounds small batches: the current device and stream come from the two C getters

@@ -147,5 +147,54 @@ def test_small_path_against_the_oracle(cuda):
             assert kc[b] == len(k) and np.array_equal(ki[b, : kc[b]], k), (kind, nc, b)
 
 
+_ADAPTIVE = r"""
+import sys
+sys.path[:0] = [%r, %r]
+import numpy as np, torch
+from oracle import oracle as O
+from ypp import engine, synth, _lib
+dev = torch.device("cuda:0")
+rng = np.random.default_rng(5)
+B, N, nc = 3, 4000, 20                       # N / nc = 200: a many-class configuration, the long-segment kernel comes last
+rows = np.zeros((B, N, 6), dtype=np.float32)
+rows[..., 0:2] = rng.uniform(30, 380, size=(B, N, 2))
+rows[..., 2:4] = rng.uniform(20, 120, size=(B, N, 2))
+rows[..., 4] = rng.uniform(0.0, 1.0, size=(B, N))
+rows[..., 5] = rng.integers(0, nc, size=(B, N))
+rows[:, :1800, 5] = 3                        # ~1350 candidates of one class per image: segments > 512
+pp = engine.PostProcessor(nc, synth.YOLOV3_ANCHORS, 416, 0.25)
+t = torch.from_numpy(rows).to(dev)
+outs = []
+for call in range(3):                        # fresh process: the first call launches the kernel narrow (if the hint is on)
+    r = pp.nms_rows(t, want_keep_idx=True)
+    torch.cuda.synchronize()
+    outs.append((r.keep_count.cpu().numpy().copy(), r.keep_idx.cpu().numpy().copy()))
+for kc, ki in outs[1:]:
+    assert np.array_equal(kc, outs[0][0])
+    for b in range(B):
+        assert np.array_equal(ki[b, : kc[b]], outs[0][1][b, : kc[b]])
+kc, ki = outs[0]
+for b in range(B):
+    keep, _ = O.nms_v3_indices(rows[b], 0.25, 0.45, offset_mode=_lib.OFFSET_AUTO_CUDA, union_mode=_lib.UNION_FMA)
+    k = np.asarray(keep, dtype=np.int64)
+    k = k[np.lexsort((k, -rows[b][k, 4].astype(np.float64)))]
+    assert kc[b] == len(k) and np.array_equal(ki[b, : kc[b]], k), b
+print("adaptive ok", int(kc.sum()))
+"""
+
+
+@pytest.mark.parametrize("hint", ["1", "0"])
+def test_launch_width_hint_does_not_change_results(cuda, hint):
+    """ypp_adaptive_launch (include/ypp.h): until a device has seen a long segment the long-segment kernel of a
+    many-class configuration is launched 8 CTAs wide.  Fresh process, long segments in the very first batch: the narrow
+    launch, the full-width launches after it and the library without the hint all give the oracle's keep sets."""
+    env = dict(os.environ)
+    env["YPP_ADAPTIVE"] = hint
+    out = subprocess.run([sys.executable, "-c", _ADAPTIVE % (ROOT, os.path.join(ROOT, "pytorch-object-detection_b200"))],
+                         env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-4000:]
+    assert "adaptive ok" in out.stdout
+
+
 if __name__ == "__main__":
     _compute(sys.argv[1])

@@ -1204,7 +1204,7 @@ int launch_nms_t(const YppNmsParams& p, cudaStream_t st)
         if (ctas > sms_d[dev]) ctas = sms_d[dev];
         YppNmsParams pb = p;
         pb.big_smem_bytes = smem;
-        pb.big_seen = big_seen_word(dev);
+        pb.big_seen = big_first ? nullptr : big_seen_word(dev);      // few-class batches say nothing about many-class ones
         // many classes and no long segment seen on this device so far: a narrow launch (see above)
         if (!big_first && pb.big_seen && !*(volatile int*)&g_big_seen[dev][0] && ctas > YPP_BIG_IDLE_CTAS) ctas = YPP_BIG_IDLE_CTAS;
         ypp_launch_chain(3, ypp_nms_big_kernel<kFast, kFma>, dim3(ctas), dim3(YPP_NMS_BIG_THREADS), smem, st, pb);

@@ -584,7 +584,7 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
         from ypp.compat.yolov3_utils import MeanAveragePrecision as MAPv3
         ann = [synth.make_annots(B, nc, g=900 + i).to(dev) for i in range(len(ring_all))]
         vl = {}
-        for depth in (1, 2, 3, 4):
+        for depth in (1, 2, 3, 4, None):
             mm = MAPv3(nc, anchors, w["input_size"], w["conf"], anchors_per_scale=A, pipeline_depth=depth)
             best = None
             for rep in range(4):                     # epochs of ONE metric object (module/yolov3_detector.py:43): from the
@@ -597,11 +597,13 @@ def run_extras(args, torch, dist, engine, synth, dev, rank, world, w, anchors, p
                 torch.cuda.synchronize()
                 dt = (time.perf_counter() - t0) * 1e3 / 96
                 best = dt if best is None else min(best, dt)
-            vl["depth_%d_ms_per_batch" % depth] = best
+            vl["depth_%d_ms_per_batch" % depth if depth else "auto_ms_per_batch"] = best
+            if depth is None:
+                vl["auto_depth_chosen"] = int(mm._pp._auto_depth)
             vl["rows"] = int(n_rows)
             del mm
-        vl["default_depth"] = 3
-        vl["images_per_s_default"] = B / (vl["depth_3_ms_per_batch"] * 1e-3)
+        vl["default_depth"] = "auto: 3; 2 once eight batches have reported fewer than 64 rows per image"
+        vl["images_per_s_default"] = B / (vl["auto_ms_per_batch"] * 1e-3)
         vl["what"] = "96 dense batches per epoch through ypp.compat.yolov3_utils.MeanAveragePrecision.update_state, wall clock incl. the final row count read; best of 4 epochs"
         out["val_loop_dense"] = vl
     # detection writers: integer box columns of one dense step's kept rows

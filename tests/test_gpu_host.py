@@ -220,3 +220,35 @@ def test_batches_in_flight_with_changing_batch_sizes(cuda):
         got = acc.view()
         assert got.shape == want.shape and want.shape[0] > 50
         assert torch.equal(got, want)
+
+
+def test_default_depth_settles_on_two_for_sparse_output(cuda):
+    """pipeline_depth not given: three batches in flight at first; once eight appends have reported fewer than 64 rows
+    per image through the probe word the processor goes down to two (the host is the limit there).  The switch happens
+    in the middle of the accumulation (old ring joined, new ring behind it): rows and order must not notice."""
+    from ypp import engine, synth
+    pp = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    seq = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25, pipeline_depth=1)
+    batches = [_heads(cuda, 4, 1100 + i, mu=-5.0) for i in range(20)]           # 4 x 10647 boxes: above the pipelining limit
+    want = torch.cat([seq(h, img_idx_base=4 * i).rows().clone() for i, h in enumerate(batches)])
+    assert 0 < want.shape[0] < 64 * 4 * len(batches)
+    acc = engine.RowAccumulator(cuda, 4)
+    for i, h in enumerate(batches):
+        if i == 12:
+            torch.cuda.synchronize()                                            # every probe so far has arrived
+        if i <= 8 or i > 12:                                                    # in between it depends on how far the GPU is
+            assert pp._depth(4, 10647, None) == (3 if i <= 8 else 2)
+        pp.accumulate(acc, [x.clone() for x in h], img_idx_base=4 * i)
+    assert pp._auto_fixed and pp._auto_depth == 2
+    got = acc.view()
+    assert got.shape == want.shape and torch.equal(got, want)
+    # dense output keeps three
+    pd = engine.PostProcessor(20, synth.YOLOV3_ANCHORS, 416, 0.25)
+    accd = engine.RowAccumulator(cuda, 4)
+    dense = [_heads(cuda, 4, 1200 + i, mu=0.0) for i in range(3)]
+    for i in range(12):
+        if i == 10:
+            torch.cuda.synchronize()
+        pd.accumulate(accd, dense[i % 3], img_idx_base=4 * i)
+    assert pd._auto_fixed and pd._auto_depth == 3
+    accd.view()
